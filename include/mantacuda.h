@@ -1,0 +1,153 @@
+/* mantacuda.h -- C-ABI of libmantacuda.so, the B200 (sm_100a) implementation of Mantaflow's
+ * per-step Eulerian grid hot path (advection -> wall BCs / forces -> pressure projection).
+ *
+ * Every entry point replaces the body of one reference function / PYTHON() plugin; the
+ * reference location is cited next to it (paths relative to the reference checkout).
+ * INTEGRATION.md shows the plugin-side stub a Mantaflow maintainer would add.
+ *
+ * Conventions
+ *  - plain C types only; grids and solvers are opaque handles owned by the library.
+ *  - host buffers passed to upload/download use the REFERENCE layout: x fastest,
+ *    idx = i + nx*(j + ny*k); Real = float, int = int32, Vec3 = 3 packed floats (AoS, 12 B)
+ *    (source/grid.h:77, source/util/vectorbase.h:202-213).
+ *  - every function returns 0 on success, non-zero on error (never throws across the ABI);
+ *    mf_last_error() returns the message of the last failure on the calling thread, in the
+ *    reference's errMsg style (source/general.h:75-77).
+ *  - work is enqueued on the solver's CUDA stream; calls that return values to the host
+ *    (download, reductions, solve statistics) synchronise that stream, nothing else does.
+ *  - there is NO CPU fallback: without a CUDA device mf_solver_create fails.
+ */
+#ifndef MANTACUDA_H
+#define MANTACUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mf_solver mf_solver;
+typedef struct mf_grid   mf_grid;
+
+/* GridBase::GridType bits, source/grid.h:29 */
+enum { MF_TYPE_REAL = 1, MF_TYPE_INT = 2, MF_TYPE_VEC3 = 4, MF_TYPE_MAC = 8, MF_TYPE_LEVELSET = 16, MF_TYPE_FLAGS = 32 };
+/* FlagGrid::CellType bits, source/grid.h:306-320 */
+enum { MF_FLUID = 1, MF_OBSTACLE = 2, MF_EMPTY = 4, MF_INFLOW = 8, MF_OUTFLOW = 16, MF_OPEN = 32, MF_STICK = 64 };
+/* enum Preconditioner, source/plugin/pressure.cpp:27 */
+enum { MF_PC_NONE = 0, MF_PC_MIC = 1, MF_PC_MG_DYNAMIC = 2, MF_PC_MG_STATIC = 3 };
+
+/* ---- library ---------------------------------------------------------------------- */
+int          mf_version(void);
+const char*  mf_last_error(void);
+int          mf_device_count(void);                      /* number of visible CUDA devices */
+const char*  mf_build_info(void);                        /* cf. buildInfoString(), source/general.cpp */
+
+/* ---- FluidSolver: grid size, dt, temp-grid pool (source/fluidsolver.h:27-119, .cpp:25-50,107) */
+mf_solver*   mf_solver_create(int nx, int ny, int nz, int dim, int device);
+void         mf_solver_destroy(mf_solver* s);
+int          mf_solver_set_dt(mf_solver* s, float dt);   /* FluidSolver::mDt ("timestep") */
+float        mf_solver_get_dt(const mf_solver* s);
+int          mf_solver_sync(mf_solver* s);                /* cudaStreamSynchronize on the solver stream */
+void*        mf_solver_stream(mf_solver* s);              /* cudaStream_t, for CUDA-event timing by the caller */
+long long    mf_solver_launch_count(const mf_solver* s);  /* kernels launched so far by this library for s */
+long long    mf_solver_pool_bytes(const mf_solver* s);    /* device bytes currently held by the temp-grid pool */
+
+/* ---- Grid<T> / MACGrid / FlagGrid (source/grid.h:99,255,298; grid.cpp:49,95,100,228) - */
+mf_grid*     mf_grid_create(mf_solver* s, int type);      /* type = OR of MF_TYPE_*; zero-filled */
+void         mf_grid_destroy(mf_grid* g);
+int          mf_grid_type(const mf_grid* g);
+int          mf_grid_clear(mf_grid* g);                                   /* Grid::clear  grid.cpp:95 */
+int          mf_grid_copy(mf_grid* dst, const mf_grid* src);             /* Grid::copyFrom grid.cpp:228 */
+int          mf_grid_swap(mf_grid* a, mf_grid* b);                       /* Grid::swap   grid.cpp:100 */
+int          mf_grid_upload(mf_grid* g, const void* host);               /* host -> device, reference layout */
+int          mf_grid_download(const mf_grid* g, void* host);             /* device -> host, reference layout */
+int          mf_grid_set_const_real(mf_grid* g, float v);                /* Grid::setConst grid.cpp:288 */
+int          mf_grid_set_const_int (mf_grid* g, int v);
+int          mf_grid_set_const_vec3(mf_grid* g, float x, float y, float z);
+int          mf_grid_add_scaled(mf_grid* g, const mf_grid* a, float fx, float fy, float fz); /* Grid::addScaled */
+int          mf_grid_mult_const(mf_grid* g, float fx, float fy, float fz);                   /* Grid::multConst */
+int          mf_grid_max_abs(const mf_grid* g, float* out);              /* Grid::getMaxAbs grid.cpp:356-368 */
+int          mf_grid_min_max(const mf_grid* g, float* out_min, float* out_max); /* getMin/getMax (Real, int) */
+int          mf_grid_sum_sqr(const mf_grid* g, double* out);             /* GridSumSqr commonkernels.h:32 */
+int          mf_grid_dot(const mf_grid* a, const mf_grid* b, double* out);/* GridDotProduct conjugategrad.cpp:175 */
+int          mf_grid_max_diff(const mf_grid* a, const mf_grid* b, double* out); /* gridMaxDiff* grid.cpp:437-467 */
+
+/* FlagGrid setup (source/grid.cpp:798-927, plugin/extforces.cpp:106-131) */
+int          mf_flags_init_domain(mf_grid* flags, int boundaryWidth, const char* wall, const char* open,
+                                  const char* inflow, const char* outflow, mf_grid* phiWalls /* or NULL */);
+int          mf_flags_fill_grid(mf_grid* flags, int type);
+int          mf_flags_count_cells(const mf_grid* flags, int flag, int bnd, int* out);
+int          mf_flags_set_open_bound(mf_grid* flags, int bWidth, const char* openBound, int type);
+/* Box obstacle / source helper: set value (or flag) in cells whose centre lies in [p0,p1]
+ * (Shape::applyToGrid with a Box, source/shapes.cpp:71,178) */
+int          mf_apply_box_to_real(mf_grid* g, float x0, float y0, float z0, float x1, float y1, float z1, float value);
+int          mf_apply_box_to_flags(mf_grid* g, float x0, float y0, float z0, float x1, float y1, float z1, int value);
+/* Cylinder::applyToGrid (source/shapes.cpp:71,367): centre c, axis vector z (half-length = |z|), radius r */
+int          mf_apply_cylinder_to_real(mf_grid* g, float cx, float cy, float cz, float r, float zx, float zy, float zz, float value);
+
+/* ---- advection (source/plugin/advection.cpp:443) ------------------------------------- */
+int          mf_advect_semi_lagrange(const mf_grid* flags, const mf_grid* vel, mf_grid* grid,
+                                     int order, float strength, int orderSpace, int clampMode, int orderTrace);
+
+/* ---- boundary conditions and forces (source/plugin/extforces.cpp) -------------------- */
+int          mf_set_wall_bcs(const mf_grid* flags, mf_grid* vel, const mf_grid* obvel, const mf_grid* fractions,
+                             const mf_grid* phiObs, int boundaryWidth);                     /* :327 */
+int          mf_add_buoyancy(const mf_grid* flags, const mf_grid* density, mf_grid* vel,
+                             float gx, float gy, float gz, float coefficient, int scale);   /* :84  */
+int          mf_add_gravity(const mf_grid* flags, mf_grid* vel, float gx, float gy, float gz,
+                            const mf_grid* exclude, int scale);                             /* :62  */
+int          mf_set_inflow_bcs(mf_grid* vel, const char* dir, float vx, float vy, float vz);/* :171 */
+int          mf_reset_outflow(mf_grid* flags, mf_grid* phi, mf_grid* real);                 /* :134 (grid part) */
+
+/* ---- pressure projection (source/plugin/pressure.cpp) -------------------------------- */
+typedef struct mf_pressure_params {          /* keyword arguments of solvePressure, pressure.cpp:482-497 */
+  float  cgAccuracy;            /* 1e-3 */
+  const mf_grid* phi;           /* 0 */
+  const mf_grid* perCellCorr;   /* 0 */
+  const mf_grid* fractions;     /* 0 */
+  const mf_grid* obvel;         /* 0 */
+  float  gfClamp;               /* 1e-4 */
+  float  cgMaxIterFac;          /* 1.5 */
+  int    precondition;          /* true (deprecated switch) */
+  int    preconditioner;        /* MF_PC_MIC */
+  int    enforceCompatibility;  /* false */
+  int    useL2Norm;             /* false */
+  int    zeroPressureFixing;    /* false */
+  const mf_grid* curv;          /* NULL */
+  float  surfTens;              /* 0 */
+  mf_grid* retRhs;              /* NULL (solvePressure only) */
+} mf_pressure_params;
+void         mf_pressure_params_default(mf_pressure_params* p);
+
+typedef struct mf_solve_info {               /* what the reference prints at debug level 2, pressure.cpp:442 */
+  int    iterations;
+  float  resNorm;
+  int    maxIter;
+  int    fixedCell;             /* linear index pinned by zeroPressureFixing, or -1 */
+  int    mgLevels;              /* 0 if no multigrid */
+  int    mgRebuilt;             /* 1 if the hierarchy was (re)built in this call */
+} mf_solve_info;
+
+int          mf_compute_pressure_rhs(mf_grid* rhs, const mf_grid* vel, const mf_grid* pressure, const mf_grid* flags,
+                                     const mf_pressure_params* p);                           /* :277 */
+int          mf_solve_pressure_system(mf_grid* rhs, mf_grid* vel, mf_grid* pressure, const mf_grid* flags,
+                                      const mf_pressure_params* p, mf_solve_info* info);     /* :312 */
+int          mf_correct_velocity(mf_grid* vel, mf_grid* pressure, const mf_grid* flags,
+                                 const mf_pressure_params* p);                               /* :457 */
+int          mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* flags,
+                               const mf_pressure_params* p, mf_solve_info* info);            /* :482 */
+int          mf_release_mg(mf_solver* s);                                                    /* :252 */
+
+/* pieces of the solver exposed for kernel-level parity tests */
+int          mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_grid* Aj, mf_grid* Ak,
+                                    const mf_grid* fractions);          /* conjugategrad.h:154 */
+int          mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* src,
+                             const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak); /* conjugategrad.h:118/136 */
+/* cgSolveDiffusion(flags, grid, alpha, cgMaxIterFac, cgAccuracy), conjugategrad.cpp:350 */
+int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float alpha, float cgMaxIterFac, float cgAccuracy);
+
+/* ---- multi-GPU z-slab decomposition (no reference equivalent: SURVEY 8e) ------------- */
+/* see mantacuda_dist.h */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

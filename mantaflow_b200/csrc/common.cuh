@@ -1,0 +1,140 @@
+// common.cuh -- internal data model of libmantacuda (not part of the ABI).
+//
+// Device data layout (DESIGN.md "Data layout in HBM"):
+//   Real / int grids : dense x-fastest array, idx = i + nx*(j + ny*k)  (== reference, grid.h:77)
+//   Vec3 / MAC grids : SoA, three component planes of Np floats each (Np = N rounded up to 32
+//                      elements so every plane is 128 B aligned).  The reference's 12-byte AoS
+//                      (vectorbase.h:202-213) only exists at the upload/download boundary.
+// All kernels are compiled with -fmad=false so float arithmetic rounds exactly like the
+// reference's x86-64 (non-FMA) build.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <map>
+#include <stdexcept>
+#include <sstream>
+#include "../../include/mantacuda.h"
+
+namespace mf {
+
+struct Error : public std::runtime_error { Error(const std::string& s) : std::runtime_error(s) {} };
+
+void set_last_error(const std::string& s);
+
+#define MF_STR2(x) #x
+#define MF_STR(x) MF_STR2(x)
+#define mfErr(msg) do { std::ostringstream _s; _s << msg << "\nError raised in " << __FILE__ << ":" << __LINE__; throw mf::Error(_s.str()); } while (0)
+#define mfAssert(cond, msg) do { if (!(cond)) mfErr(msg); } while (0)
+#define CUDA_CHECK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) mfErr("CUDA error: " << cudaGetErrorString(_e) << " in " #x); } while (0)
+
+// boundary wrapper: run body, translate exceptions into status codes
+#define MF_API_BEGIN try {
+#define MF_API_END   return 0; } catch (const std::exception& e) { mf::set_last_error(e.what()); return 1; } catch (...) { mf::set_last_error("unknown error"); return 2; }
+
+struct Solver;
+struct MgHierarchy;
+
+struct Grid {
+  Solver* s;
+  int type;          // MF_TYPE_* bits
+  float* d;          // device storage (int grids reinterpret)
+  bool pooled;       // storage came from the solver pool
+  mutable int outflowState;  // flag grids: -1 unknown, 0 no TypeOutflow cell, 1 some (cache for applyOutflowBC)
+  bool isVec() const { return (type & MF_TYPE_VEC3) != 0; }
+  bool isMAC() const { return (type & MF_TYPE_MAC) != 0; }
+  bool isReal() const { return (type & MF_TYPE_REAL) != 0; }
+  bool isInt() const { return (type & MF_TYPE_INT) != 0; }
+  int* di() const { return reinterpret_cast<int*>(d); }
+  inline float* comp(int c) const;
+};
+
+struct Solver {
+  int nx, ny, nz, dim;
+  bool is3D;
+  long long N;        // cells
+  long long Np;       // padded plane stride for SoA vec grids
+  long long strideZ;  // nx*ny in 3-D, 0 in 2-D  (grid.cpp:56)
+  float dt, dx;
+  int device;
+  cudaStream_t stream;
+  long long launches;
+  // temp-grid pool with the reference's stack discipline (fluidsolver.cpp:33-50)
+  std::vector<float*> poolReal, poolVec;
+  long long poolBytes;
+  // reduction scratch (device) + pinned host result
+  double* redScratch;   // per-block partials
+  unsigned int* redCounter;
+  double* redOut;       // device results (16 doubles)
+  double* redHost;      // pinned
+  int* devFlagsScratch; // small int scratch (8 ints)
+  int* hostInts;        // pinned
+  float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
+  MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
+  int numSMs;
+
+  float* getReal();           // un-cleared scratch of N floats
+  void   putReal(float* p);
+  float* getVec();            // un-cleared scratch of 3*Np floats
+  void   putVec(float* p);
+  void   use() const;         // cudaSetDevice
+};
+
+inline float* Grid::comp(int c) const { return d + (long long)c * s->Np; }
+
+// RAII temp grids
+struct TmpReal { Solver* s; float* p; TmpReal(Solver* s_) : s(s_), p(s_->getReal()) {} ~TmpReal() { s->putReal(p); } operator float*() const { return p; } };
+struct TmpVec  { Solver* s; float* p; TmpVec(Solver* s_) : s(s_), p(s_->getVec()) {} ~TmpVec() { s->putVec(p); }  float* comp(int c) const { return p + (long long)c * s->Np; } };
+
+// grid geometry passed by value to kernels
+struct Geo {
+  int nx, ny, nz;
+  int is3D;
+  long long Z;   // strideZ (0 in 2-D)
+  long long N;
+};
+inline Geo geo(const Solver* s) { Geo g; g.nx = s->nx; g.ny = s->ny; g.nz = s->nz; g.is3D = s->is3D; g.Z = s->strideZ; g.N = s->N; return g; }
+
+// three component pointers of a SoA vec grid
+struct V3 { float* x; float* y; float* z; };
+struct CV3 { const float* x; const float* y; const float* z; };
+inline V3 v3(const Grid* g) { V3 v; v.x = g->comp(0); v.y = g->comp(1); v.z = g->comp(2); return v; }
+inline CV3 cv3(const Grid* g) { CV3 v; v.x = g->comp(0); v.y = g->comp(1); v.z = g->comp(2); return v; }
+inline CV3 cv3(const TmpVec& t) { CV3 v; v.x = t.comp(0); v.y = t.comp(1); v.z = t.comp(2); return v; }
+inline V3 v3(const TmpVec& t) { V3 v; v.x = t.comp(0); v.y = t.comp(1); v.z = t.comp(2); return v; }
+
+inline const Grid* G(const mf_grid* g) { return reinterpret_cast<const Grid*>(g); }
+inline Grid* G(mf_grid* g) { return reinterpret_cast<Grid*>(g); }
+inline Solver* S(mf_solver* s) { return reinterpret_cast<Solver*>(s); }
+inline const Solver* S(const mf_solver* s) { return reinterpret_cast<const Solver*>(s); }
+
+void check_same_solver(const Grid* a, const Grid* b, const char* what);
+#define REQ_GRID(g, cond, name, fn) mfAssert((g) != nullptr && (cond), fn ": argument '" name "' has the wrong grid type or is missing")
+
+// launch helpers -----------------------------------------------------------------------
+inline unsigned int cdiv(long long a, long long b) { return (unsigned int)((a + b - 1) / b); }
+#define MF_LAUNCH(s, kern, grid, block, ...) do { kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
+#define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())
+
+// reductions (reduce.cu)
+// Deterministic two-stage reductions: per-block partial in fixed order, last block sums partials in block order.
+double reduce_dot(Solver* s, const float* a, const float* b, long long n);     // sum of float(a*b) in double (GridDotProduct)
+double reduce_sumsqr(Solver* s, const float* a, long long n);                  // sum of double(a)^2 (GridSumSqr)
+void   reduce_minmax(Solver* s, const float* a, long long n, float* mn, float* mx);
+void   reduce_minmax_int(Solver* s, const int* a, long long n, int* mn, int* mx);
+
+// device-side helpers ------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ bool fIsFluid(int f) { return (f & MF_FLUID) != 0; }
+__device__ __forceinline__ bool fIsObstacle(int f) { return (f & MF_OBSTACLE) != 0; }
+__device__ __forceinline__ bool fIsEmpty(int f) { return (f & MF_EMPTY) != 0; }
+__device__ __forceinline__ bool fIsOutflow(int f) { return (f & MF_OUTFLOW) != 0; }
+__device__ __forceinline__ bool fIsStick(int f) { return (f & MF_STICK) != 0; }
+
+__device__ __forceinline__ float warpSum(float v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+__device__ __forceinline__ double warpSumD(double v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+#endif
+
+} // namespace mf

@@ -1,0 +1,460 @@
+// forces.cu -- FlagGrid setup, wall boundary conditions and body forces.
+// Reference: source/grid.cpp (initDomain :798, initBoundaries :890, fillGrid :922),
+//            source/plugin/extforces.cpp (KnApplyForce :46, KnAddBuoyancy :73, setOpenBound :106,
+//            resetOutflow :134, KnSetInflow :164, KnSetWallBcs :187, KnSetWallBcsFrac :240),
+//            source/shapes.cpp (ApplyShapeToGrid :40, Box::isInside :151, Cylinder::isInside :324).
+#include "common.cuh"
+#include "sample.cuh"
+#include <cstring>
+#include <cmath>
+
+namespace mf {
+
+#define IJK_FROM_BLOCK \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x; \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y; \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z; \
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return; \
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+
+static inline dim3 ijkBlock(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
+static inline dim3 ijkGrid(const Solver* s, dim3 b) { return dim3(cdiv(s->nx, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z)); }
+
+__device__ __forceinline__ bool interior1(const Geo& g, int i, int j, int k) {
+  return i >= 1 && j >= 1 && i < g.nx - 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+}
+
+// ---- flags -------------------------------------------------------------------------------------
+struct Types6 { int t[6]; };
+
+// setConst(TypeEmpty) + initBoundaries (grid.cpp:886-908): later sides overwrite earlier ones
+__global__ void k_init_domain(Geo g, int* __restrict__ flags, int w, Types6 types) {
+  IJK_FROM_BLOCK
+  int f = MF_EMPTY;
+  if (i <= w) f = types.t[0];
+  if (i >= g.nx - 1 - w) f = types.t[1];
+  if (j <= w) f = types.t[2];
+  if (j >= g.ny - 1 - w) f = types.t[3];
+  if (g.is3D) {
+    if (k <= w) f = types.t[4];
+    if (k >= g.nz - 1 - w) f = types.t[5];
+  }
+  flags[idx] = f;
+}
+// phiWalls (grid.cpp:756-796): phi = min(dist to each wall - 0.5 - w ...), computed in double like the reference
+__global__ void k_init_phi_walls(Geo g, float* __restrict__ phi, int w, int wallMask) {
+  IJK_FROM_BLOCK
+  float p = 1000000000.0f;
+  if (wallMask & 1)  p = (float)fmin((double)i - 0.5 - (double)w, (double)p);
+  if (wallMask & 2)  p = (float)fmin((double)g.nx - (double)i - 1.5 - (double)w, (double)p);
+  if (wallMask & 4)  p = (float)fmin((double)j - 0.5 - (double)w, (double)p);
+  if (wallMask & 8)  p = (float)fmin((double)g.ny - (double)j - 1.5 - (double)w, (double)p);
+  if (wallMask & 16) p = (float)fmin((double)k - 0.5 - (double)w, (double)p);
+  if (wallMask & 32) p = (float)fmin((double)g.nz - (double)k - 1.5 - (double)w, (double)p);
+  phi[idx] = p;
+}
+__global__ void k_fill_grid(int* __restrict__ flags, int type, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) {
+    const int f = flags[i];
+    if ((f & MF_OBSTACLE) == 0 && (f & MF_INFLOW) == 0 && (f & MF_OUTFLOW) == 0 && (f & MF_OPEN) == 0)
+      flags[i] = (f & ~(MF_EMPTY | MF_FLUID)) | type;
+  }
+}
+__global__ void k_count_cells(Geo g, const int* __restrict__ flags, int flag, int bnd, int* out) {
+  IJK_FROM_BLOCK
+  const bool in = i >= bnd && j >= bnd && i < g.nx - bnd && j < g.ny - bnd && (!g.is3D || (k >= bnd && k < g.nz - bnd));
+  const bool hit = in && ((flags[idx] & flag) != 0);
+  const unsigned int m = __ballot_sync(__activemask(), hit);
+  if (hit && (threadIdx.x & 31) == (__ffs(m) - 1)) atomicAdd(out, __popc(m));
+}
+// setOpenBound (extforces.cpp:106-131)
+__global__ void k_set_open_bound(Geo g, int* __restrict__ flags, int bWidth, int lo, int up, int type) {
+  IJK_FROM_BLOCK
+  const bool loX = (lo & 1) && i <= bWidth, loY = (lo & 2) && j <= bWidth;
+  const bool upX = (up & 1) && i >= g.nx - bWidth - 1, upY = (up & 2) && j >= g.ny - bWidth - 1;
+  const bool innerI = i > bWidth && i < g.nx - bWidth - 1, innerJ = j > bWidth && j < g.ny - bWidth - 1;
+  const int f = flags[idx];
+  if (!g.is3D && (loX || upX || loY || upY)) {
+    if ((loX || upX || innerI) && (loY || upY || innerJ) && fIsObstacle(f)) flags[idx] = type;
+  } else {
+    const bool loZ = (lo & 4) && k <= bWidth, upZ = (up & 4) && k >= g.nz - bWidth - 1;
+    const bool innerK = k > bWidth && k < g.nz - bWidth - 1;
+    if (loX || upX || loY || upY || loZ || upZ) {
+      if ((loX || upX || innerI) && (loY || upY || innerJ) && (loZ || upZ || innerK) && fIsObstacle(f)) flags[idx] = type;
+    }
+  }
+}
+__global__ void k_reset_outflow(int* __restrict__ flags, float* phi, float* real, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) {
+    const int f = flags[i];
+    if (fIsOutflow(f)) {
+      flags[i] = (f | MF_EMPTY) & ~MF_FLUID;
+      if (phi) phi[i] = 0.5f;
+      if (real) real[i] = 0.0f;
+    }
+  }
+}
+
+// ---- shapes ---------------------------------------------------------------------------------------
+template <class T>
+__global__ void k_apply_box(Geo g, T* __restrict__ d, float x0, float y0, float z0, float x1, float y1, float z1, T value) {
+  IJK_FROM_BLOCK
+  const float px = i + 0.5f, py = j + 0.5f, pz = k + 0.5f;
+  if (px >= x0 && py >= y0 && pz >= z0 && px <= x1 && py <= y1 && pz <= z1) d[idx] = value;
+}
+__global__ void k_apply_cylinder(Geo g, float* __restrict__ d, float cx, float cy, float cz, float radius, float zx, float zy, float zz,
+                                 float zlen, float value) {
+  IJK_FROM_BLOCK
+  const float dx = (i + 0.5f) - cx, dy = (j + 0.5f) - cy, dz = (k + 0.5f) - cz;
+  const float z = dx * zx + dy * zy + dz * zz;
+  if (fabsf(z) > zlen) return;
+  const float r2 = (dx * dx + dy * dy + dz * dz) - z * z;
+  if (r2 < radius * radius) d[idx] = value;
+}
+
+// ---- forces ---------------------------------------------------------------------------------------
+// KnAddBuoyancy (extforces.cpp:73-81): (0.5*strength) is a double product, the update is done in double
+__global__ void __launch_bounds__(256) k_add_buoyancy(Geo g, const int* __restrict__ flags, const float* __restrict__ factor, V3 vel,
+                                                      float sx, float sy, float sz) {
+  IJK_FROM_BLOCK
+  if (!interior1(g, i, j, k)) return;
+  if (!fIsFluid(flags[idx])) return;
+  const float f0 = factor[idx];
+  if (fIsFluid(flags[idx - 1]))
+    vel.x[idx] = (float)((double)vel.x[idx] + (0.5 * (double)sx) * (double)(f0 + factor[idx - 1]));
+  if (fIsFluid(flags[idx - g.nx]))
+    vel.y[idx] = (float)((double)vel.y[idx] + (0.5 * (double)sy) * (double)(f0 + factor[idx - g.nx]));
+  if (g.is3D && fIsFluid(flags[idx - g.Z]))
+    vel.z[idx] = (float)((double)vel.z[idx] + (0.5 * (double)sz) * (double)(f0 + factor[idx - g.Z]));
+}
+// KnApplyForce (extforces.cpp:46-59), additive flag as in addGravity
+__global__ void __launch_bounds__(256) k_apply_force(Geo g, const int* __restrict__ flags, V3 vel, float fx, float fy, float fz,
+                                                     const float* __restrict__ exclude, int additive) {
+  IJK_FROM_BLOCK
+  if (!interior1(g, i, j, k)) return;
+  const int f = flags[idx];
+  const bool curFluid = fIsFluid(f), curEmpty = fIsEmpty(f);
+  if (!curFluid && !curEmpty) return;
+  if (exclude && exclude[idx] < 0.0f) return;
+  const int fxm = flags[idx - 1], fym = flags[idx - g.nx];
+  if (fIsFluid(fxm) || (curFluid && fIsEmpty(fxm))) vel.x[idx] = additive ? vel.x[idx] + fx : fx;
+  if (fIsFluid(fym) || (curFluid && fIsEmpty(fym))) vel.y[idx] = additive ? vel.y[idx] + fy : fy;
+  if (g.is3D) {
+    const int fzm = flags[idx - g.Z];
+    if (fIsFluid(fzm) || (curFluid && fIsEmpty(fzm))) vel.z[idx] = additive ? vel.z[idx] + fz : fz;
+  }
+}
+// KnSetInflow (extforces.cpp:164-168)
+__global__ void k_set_inflow(Geo g, V3 vel, int dim, int p0, float vx, float vy, float vz) {
+  IJK_FROM_BLOCK
+  const int p = dim == 0 ? i : (dim == 1 ? j : k);
+  if (p == p0 || p == p0 + 1) { vel.x[idx] = vx; vel.y[idx] = vy; vel.z[idx] = vz; }
+}
+
+// KnSetWallBcs (extforces.cpp:187-237): all cells, in place
+__global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel) {
+  IJK_FROM_BLOCK
+  const int f = flags[idx];
+  const bool curFluid = fIsFluid(f), curObs = fIsObstacle(f);
+  if (!curFluid && !curObs) return;
+  float bx = 0.f, by = 0.f, bz = 0.f;
+  if (haveObvel) { bx = obvel.x[idx]; by = obvel.y[idx]; if (g.is3D) bz = obvel.z[idx]; }
+  if (i > 0) { const int fm = flags[idx - 1];    if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.x[idx] = bx; }
+  if (j > 0) { const int fm = flags[idx - g.nx]; if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.y[idx] = by; }
+  if (!g.is3D) vel.z[idx] = 0.0f;
+  else if (k > 0) { const int fm = flags[idx - g.Z]; if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.z[idx] = bz; }
+  if (curFluid) {
+    if ((i > 0 && fIsStick(flags[idx - 1])) || (i < g.nx - 1 && fIsStick(flags[idx + 1]))) { vel.y[idx] = 0.f; vel.z[idx] = 0.f; }
+    if ((j > 0 && fIsStick(flags[idx - g.nx])) || (j < g.ny - 1 && fIsStick(flags[idx + g.nx]))) { vel.x[idx] = 0.f; vel.z[idx] = 0.f; }
+    if (g.is3D && ((k > 0 && fIsStick(flags[idx - g.Z])) || (k < g.nz - 1 && fIsStick(flags[idx + g.Z])))) { vel.x[idx] = 0.f; vel.y[idx] = 0.f; }
+  }
+}
+
+__device__ __forceinline__ void normalize3(float& x, float& y, float& z) {   // vectorbase.h:421-434
+  const float l = x * x + y * y + z * z;
+  if (fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) { /* unit length */ }
+  else if (l > 1e-6f * 1e-6f) { const float nrm = sqrtf(l); const float inv = (float)(1. / (double)nrm); x *= inv; y *= inv; z *= inv; }
+  else { x = y = z = 0.f; }
+}
+
+// KnSetWallBcsFrac (extforces.cpp:240-323): writes velTarget for every cell
+__global__ void __launch_bounds__(256) k_set_wall_bcs_frac(Geo g, const int* __restrict__ flags, CV3 vel, V3 tgt, const float* __restrict__ phiObs) {
+  IJK_FROM_BLOCK
+  const int f = flags[idx];
+  const bool curFluid = fIsFluid(f), curObs = fIsObstacle(f);
+  float tx = vel.x[idx], ty = vel.y[idx], tz = vel.z[idx];
+  if ((curFluid || curObs) && interior1(g, i, j, k)) {
+    const long long X = 1, Y = g.nx, Z = g.Z;
+    const float* p = phiObs + idx;
+    if (curObs | fIsObstacle(flags[idx - X])) {
+      float dx = 0.f, dy = 0.f, dz = 0.f;
+      const float tmp1 = (p[0] + p[-X]) * .5f;
+      float tmp2 = (p[Y] + p[-X + Y]) * .5f;
+      float phi1 = (tmp1 + tmp2) * .5f;
+      tmp2 = (p[-Y] + p[-X - Y]) * .5f;
+      float phi2 = (tmp1 + tmp2) * .5f;
+      dx = p[0] - p[-X];
+      dy = phi1 - phi2;
+      if (g.is3D) {
+        tmp2 = (p[Z] + p[-X + Z]) * .5f; phi1 = (tmp1 + tmp2) * .5f;
+        tmp2 = (p[-Z] + p[-X - Z]) * .5f; phi2 = (tmp1 + tmp2) * .5f;
+        dz = phi1 - phi2;
+      }
+      normalize3(dx, dy, dz);
+      float mx, my, mz; getAtMACX(vel, g, idx, mx, my, mz);
+      tx = mx - (dx * mx + dy * my + dz * mz) * dx;
+    }
+    if (curObs | fIsObstacle(flags[idx - Y])) {
+      float dx = 0.f, dy = 0.f, dz = 0.f;
+      const float tmp1 = (p[0] + p[-Y]) * .5f;
+      float tmp2 = (p[X] + p[X - Y]) * .5f;
+      float phi1 = (tmp1 + tmp2) * .5f;
+      tmp2 = (p[-X] + p[-X - Y]) * .5f;
+      float phi2 = (tmp1 + tmp2) * .5f;
+      dx = phi1 - phi2;
+      dy = p[0] - p[-Y];
+      if (g.is3D) {
+        tmp2 = (p[Z] + p[-Y + Z]) * .5f; phi1 = (tmp1 + tmp2) * .5f;
+        tmp2 = (p[-Z] + p[-Y - Z]) * .5f; phi2 = (tmp1 + tmp2) * .5f;
+        dz = phi1 - phi2;
+      }
+      normalize3(dx, dy, dz);
+      float mx, my, mz; getAtMACY(vel, g, idx, mx, my, mz);
+      ty = my - (dx * mx + dy * my + dz * mz) * dy;
+    }
+    if (g.is3D && (curObs | fIsObstacle(flags[idx - Z]))) {
+      float dx = 0.f, dy = 0.f, dz = 0.f;
+      const float tmp1 = (p[0] + p[-Z]) * .5f;
+      float tmp2 = (p[X] + p[X - Z]) * .5f;
+      float phi1 = (tmp1 + tmp2) * .5f;
+      tmp2 = (p[-X] + p[-X - Z]) * .5f;
+      float phi2 = (tmp1 + tmp2) * .5f;
+      dx = phi1 - phi2;
+      tmp2 = (p[Y] + p[Y - Z]) * .5f; phi1 = (tmp1 + tmp2) * .5f;
+      tmp2 = (p[-Y] + p[-Y - Z]) * .5f; phi2 = (tmp1 + tmp2) * .5f;
+      dy = phi1 - phi2;
+      dz = p[0] - p[-Z];
+      normalize3(dx, dy, dz);
+      float mx, my, mz; getAtMACZ(vel, g, idx, mx, my, mz);
+      tz = mz - (dx * mx + dy * my + dz * mz) * dz;
+    }
+  }
+  tgt.x[idx] = tx; tgt.y[idx] = ty; tgt.z[idx] = tz;
+}
+
+static void parseDesc(const char* desc, int& lo, int& up, const char* fn) {
+  lo = up = 0;
+  for (const char* c = desc; c && *c; c++) {
+    if (*c == 'x') lo |= 1; else if (*c == 'y') lo |= 2; else if (*c == 'z') lo |= 4;
+    else if (*c == 'X') up |= 1; else if (*c == 'Y') up |= 2; else if (*c == 'Z') up |= 4;
+    else mfErr("invalid character in boundary description string. Only [xyzXYZ] allowed.");
+  }
+  (void)fn;
+}
+
+} // namespace mf
+
+using namespace mf;
+
+extern "C" {
+
+int mf_flags_init_domain(mf_grid* fp, int boundaryWidth, const char* wallIn, const char* openIn,
+                         const char* inflowIn, const char* outflowIn, mf_grid* phiWalls) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::initDomain");
+  Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  flags->outflowState = -1;
+  std::string wall = wallIn ? wallIn : "xXyYzZ", open = openIn ? openIn : "", inflow = inflowIn ? inflowIn : "", outflow = outflowIn ? outflowIn : "";
+  wall.append("      "); open.append("      "); inflow.append("      "); outflow.append("      ");
+  Types6 types; bool set[6] = { false, false, false, false, false, false };
+  for (int i = 0; i < 6; i++) types.t[i] = 0;
+  int wallMask = 0;
+  const char lower[6] = { 'x', 'X', 'y', 'Y', 'z', 'Z' };
+  for (int i = 0; i < 6; ++i) {           // grid.cpp:813-882
+    for (int side = 0; side < (s->is3D ? 6 : 4); side++) {
+      if (set[side]) continue;
+      const char c = lower[side];
+      if (open[i] == c) { types.t[side] = MF_OPEN; set[side] = true; }
+      else if (inflow[i] == c) { types.t[side] = MF_INFLOW; set[side] = true; }
+      else if (outflow[i] == c) { types.t[side] = MF_OUTFLOW; set[side] = true; }
+      else if (wall[i] == c) { types.t[side] = MF_OBSTACLE; wallMask |= (1 << side); set[side] = true; }
+    }
+  }
+  const Geo g = geo(s);
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  if (phiWalls) {
+    REQ_GRID(phiWalls, G(phiWalls)->isReal(), "phiWalls", "FlagGrid::initDomain");
+    MF_LAUNCH(s, k_init_phi_walls, gr, b, g, G(phiWalls)->d, boundaryWidth, wallMask);
+  }
+  MF_LAUNCH(s, k_init_domain, gr, b, g, flags->di(), boundaryWidth, types);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_flags_fill_grid(mf_grid* fp, int type) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::fillGrid");
+  Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  flags->outflowState = -1;
+  MF_LAUNCH(s, k_fill_grid, s->numSMs * 8, 256, flags->di(), type, s->N);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_flags_count_cells(const mf_grid* fp, int flag, int bnd, int* out) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::countCells");
+  mfAssert(out, "FlagGrid::countCells: null output");
+  const Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  CUDA_CHECK(cudaMemsetAsync(s->devFlagsScratch + 1, 0, sizeof(int), s->stream));
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  MF_LAUNCH(s, k_count_cells, gr, b, geo(s), flags->di(), flag, bnd, s->devFlagsScratch + 1);
+  MF_LAUNCH_CHECK();
+  CUDA_CHECK(cudaMemcpyAsync(s->hostInts, s->devFlagsScratch + 1, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  *out = s->hostInts[0];
+  MF_API_END
+}
+
+int mf_flags_set_open_bound(mf_grid* fp, int bWidth, const char* openBound, int type) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "setOpenBound");
+  if (!openBound || !*openBound) return 0;
+  Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  flags->outflowState = -1;
+  int lo, up; parseDesc(openBound, lo, up, "setOpenBound");
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  MF_LAUNCH(s, k_set_open_bound, gr, b, geo(s), flags->di(), bWidth, lo, up, type);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_reset_outflow(mf_grid* fp, mf_grid* phi, mf_grid* real) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "resetOutflow");
+  Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  if (phi) REQ_GRID(phi, G(phi)->isReal(), "phi", "resetOutflow");
+  if (real) REQ_GRID(real, G(real)->isReal(), "real", "resetOutflow");
+  MF_LAUNCH(s, k_reset_outflow, s->numSMs * 8, 256, flags->di(), phi ? G(phi)->d : nullptr, real ? G(real)->d : nullptr, s->N);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_apply_box_to_real(mf_grid* gp, float x0, float y0, float z0, float x1, float y1, float z1, float value) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isReal(), "grid", "Shape::applyToGrid");
+  Grid* gr = G(gp); Solver* s = gr->s; s->use();
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  MF_LAUNCH(s, k_apply_box<float>, gd, b, geo(s), gr->d, x0, y0, z0, x1, y1, z1, value);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_apply_box_to_flags(mf_grid* gp, float x0, float y0, float z0, float x1, float y1, float z1, int value) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isInt(), "grid", "Shape::applyToGrid");
+  Grid* gr = G(gp); Solver* s = gr->s; s->use();
+  gr->outflowState = -1;
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  MF_LAUNCH(s, k_apply_box<int>, gd, b, geo(s), gr->di(), x0, y0, z0, x1, y1, z1, value);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_apply_cylinder_to_real(mf_grid* gp, float cx, float cy, float cz, float r, float zx, float zy, float zz, float value) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isReal(), "grid", "Shape::applyToGrid");
+  Grid* gr = G(gp); Solver* s = gr->s; s->use();
+  // Cylinder ctor: mZDir = z; mZ = normalize(mZDir)  (shapes.cpp:316-322, vectorbase.h:421-434)
+  float zlen;
+  {
+    const float l = zx * zx + zy * zy + zz * zz;
+    if (std::fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) zlen = 1.f;
+    else if (l > 1e-6f * 1e-6f) { zlen = std::sqrt(l); const float inv = (float)(1. / (double)zlen); zx *= inv; zy *= inv; zz *= inv; }
+    else { zx = zy = zz = 0.f; zlen = 0.f; }
+  }
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  MF_LAUNCH(s, k_apply_cylinder, gd, b, geo(s), gr->d, cx, cy, cz, r, zx, zy, zz, zlen, value);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_add_buoyancy(const mf_grid* fp, const mf_grid* dp, mf_grid* vp, float gx, float gy, float gz, float coefficient, int scale) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "addBuoyancy");
+  REQ_GRID(dp, G(dp)->isReal(), "density", "addBuoyancy");
+  REQ_GRID(vp, G(vp)->isMAC(), "vel", "addBuoyancy");
+  const Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  check_same_solver(flags, G(dp), "addBuoyancy"); check_same_solver(flags, G(vp), "addBuoyancy");
+  // Vec3 f = -gravity * dt / gridScale * coefficient  (extforces.cpp:85-86), all in float
+  const float gridScale = scale ? s->dx : 1.0f;
+  const float dt = s->dt;
+  const float fx = ((-gx * dt) / gridScale) * coefficient;
+  const float fy = ((-gy * dt) / gridScale) * coefficient;
+  const float fz = ((-gz * dt) / gridScale) * coefficient;
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  MF_LAUNCH(s, k_add_buoyancy, gd, b, geo(s), flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_add_gravity(const mf_grid* fp, mf_grid* vp, float gx, float gy, float gz, const mf_grid* exclude, int scale) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "addGravity");
+  REQ_GRID(vp, G(vp)->isMAC(), "vel", "addGravity");
+  if (exclude) REQ_GRID(exclude, G(exclude)->isReal(), "exclude", "addGravity");
+  const Grid* flags = G(fp); Solver* s = flags->s; s->use();
+  const float gridScale = scale ? s->dx : 1.0f;
+  const float dt = s->dt;
+  const float fx = (gx * dt) / gridScale, fy = (gy * dt) / gridScale, fz = (gz * dt) / gridScale;   // extforces.cpp:63-64
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  MF_LAUNCH(s, k_apply_force, gd, b, geo(s), flags->di(), v3(G(vp)), fx, fy, fz, exclude ? G(exclude)->d : nullptr, 1);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_set_inflow_bcs(mf_grid* vp, const char* dir, float vx, float vy, float vz) {
+  MF_API_BEGIN
+  REQ_GRID(vp, G(vp)->isMAC(), "vel", "setInflowBcs");
+  Grid* vel = G(vp); Solver* s = vel->s; s->use();
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  const int size[3] = { s->nx, s->ny, s->nz };
+  for (const char* c = dir; c && *c; c++) {
+    if (*c >= 'x' && *c <= 'z') { MF_LAUNCH(s, k_set_inflow, gd, b, geo(s), v3(vel), *c - 'x', 0, vx, vy, vz); }
+    else if (*c >= 'X' && *c <= 'Z') { const int d = *c - 'X'; MF_LAUNCH(s, k_set_inflow, gd, b, geo(s), v3(vel), d, size[d] - 1, vx, vy, vz); }
+    else mfErr("invalid character in direction string. Only [xyzXYZ] allowed.");
+  }
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_set_wall_bcs(const mf_grid* fp, mf_grid* vp, const mf_grid* obvel, const mf_grid* fractions, const mf_grid* phiObs, int boundaryWidth) {
+  MF_API_BEGIN
+  REQ_GRID(fp, G(fp)->isInt(), "flags", "setWallBcs");
+  REQ_GRID(vp, G(vp)->isMAC(), "vel", "setWallBcs");
+  const Grid* flags = G(fp); Grid* vel = G(vp); Solver* s = flags->s; s->use();
+  check_same_solver(flags, vel, "setWallBcs");
+  if (obvel) REQ_GRID(obvel, G(obvel)->isMAC(), "obvel", "setWallBcs");
+  if (fractions) REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "setWallBcs");
+  if (phiObs) REQ_GRID(phiObs, G(phiObs)->isReal(), "phiObs", "setWallBcs");
+  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
+  if (!phiObs || !fractions) {
+    CV3 ov; ov.x = ov.y = ov.z = nullptr;
+    if (obvel) ov = cv3(G(obvel));
+    MF_LAUNCH(s, k_set_wall_bcs, gd, b, geo(s), flags->di(), v3(vel), ov, obvel ? 1 : 0);
+  } else {
+    mfAssert(s->nx >= 3 && s->ny >= 3, "setWallBcs: grid too small");
+    float* tmp = s->getVec();
+    Grid tg = *vel; tg.d = tmp;
+    MF_LAUNCH(s, k_set_wall_bcs_frac, gd, b, geo(s), flags->di(), cv3(vel), v3(&tg), G(phiObs)->d);
+    float* old = vel->d; vel->d = tmp;     // vel.swap(tmpvel)
+    s->putVec(old);
+  }
+  (void)boundaryWidth;
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+} // extern "C"

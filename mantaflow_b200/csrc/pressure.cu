@@ -1,0 +1,349 @@
+// pressure.cu -- pressure projection orchestration (reference: source/plugin/pressure.cpp:277-523,
+// source/conjugategrad.cpp:201-335,350-423).
+#include "common.cuh"
+#include "reduce.cuh"
+#include "pressure_kernels.cuh"
+#include "cg.cuh"
+#include "multigrid.h"
+#include <cmath>
+#include <cstdlib>
+
+namespace mf {
+
+static inline dim3 ijkBlock(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
+static inline dim3 ijkGrid(const Solver* s, dim3 b) { return dim3(cdiv(s->nx, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z)); }
+static inline int ewBlocks(const Solver* s, long long n) {
+  long long b = (n + 255) / 256, cap = (long long)s->numSMs * 16;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+static void checkParams(const Solver* s, const mf_pressure_params* p, const char* fn) {
+  mfAssert(p, fn << ": null params");
+  auto chkReal = [&](const mf_grid* g, const char* name) { if (g) { mfAssert(G(g)->isReal(), fn << ": argument '" << name << "' must be a RealGrid"); mfAssert(G(g)->s == s, fn << ": grids belong to different solvers"); } };
+  auto chkMac = [&](const mf_grid* g, const char* name) { if (g) { mfAssert(G(g)->isMAC(), fn << ": argument '" << name << "' must be a MACGrid"); mfAssert(G(g)->s == s, fn << ": grids belong to different solvers"); } };
+  chkReal(p->phi, "phi"); chkReal(p->perCellCorr, "perCellCorr"); chkReal(p->curv, "curv"); chkReal(p->retRhs, "retRhs");
+  chkMac(p->fractions, "fractions"); chkMac(p->obvel, "obvel");
+}
+
+// computePressureRhs (pressure.cpp:277-299)
+static void computeRhs(Solver* s, float* rhs, const Grid* vel, const Grid* flags, const mf_pressure_params* p, bool freshTemp) {
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "computePressureRhs: grid too small");
+  RhsArgs a;
+  a.flags = flags->di(); a.rhs = rhs; a.vel = cv3(vel);
+  a.perCellCorr = p->perCellCorr ? G(p->perCellCorr)->d : nullptr;
+  a.haveFractions = p->fractions ? 1 : 0; if (p->fractions) a.fractions = cv3(G(p->fractions)); else a.fractions = cv3(vel);
+  a.haveObvel = p->obvel ? 1 : 0; if (p->obvel) a.obvel = cv3(G(p->obvel)); else a.obvel = cv3(vel);
+  a.phi = p->phi ? G(p->phi)->d : nullptr; a.curv = p->curv ? G(p->curv)->d : nullptr;
+  a.surfTens = p->surfTens; a.gfClamp = p->gfClamp;
+  a.writeBorder = freshTemp ? 1 : 0;
+  MF_LAUNCH(s, k_make_rhs, tileBlocks(s), 256, geo(s), a, s->redScratch, s->redCounter, s->redOut);
+  if (p->enforceCompatibility) {
+    fetchRed(s, 2);
+    const double sum = s->redHost[0]; const int cnt = (int)s->redHost[1];
+    const float corr = (float)(-sum / (float)cnt);            // rhs += (Real)(-sum / (Real)cnt)
+    MF_LAUNCH(s, k_add_scalar, ewBlocks(s, s->N), 256, rhs, corr, s->N);
+  }
+}
+
+struct SolveTemps {   // the 7 (+4) temp grids of solvePressureSystem (pressure.cpp:332-338,412-415)
+  Solver* s; float *residual, *search, *A0, *Ai, *Aj, *Ak, *tmp, *pc;
+  SolveTemps(Solver* s_) : s(s_) { residual = s->getReal(); search = s->getReal(); A0 = s->getReal(); Ai = s->getReal(); Aj = s->getReal(); Ak = s->getReal(); tmp = s->getReal(); pc = nullptr; }
+  ~SolveTemps() { if (pc) s->putReal(pc); s->putReal(tmp); s->putReal(Ak); s->putReal(Aj); s->putReal(Ai); s->putReal(A0); s->putReal(search); s->putReal(residual); }
+};
+
+struct CgDriver {
+  Solver* s; CgVecs v; CgState* st; int pcMethod;   // 0 none, 1 red-black MIC, 2 multigrid
+  float* P; MgHierarchy* mg;
+  CgState host;
+  void applyPrecond(bool init) {
+    const Geo g = geo(s);
+    if (pcMethod == 1) {
+      dim3 b = ijkBlock(s); dim3 gr(cdiv((s->nx + 1) / 2, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z));
+      MF_LAUNCH(s, k_rbic_black, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st);
+      MF_LAUNCH(s, k_rbic_red, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st);
+    } else if (pcMethod == 2) {
+      mg_apply(mg, v.tmp, v.residual);
+    }
+    (void)init;
+  }
+  void fetch() {
+    CUDA_CHECK(cudaMemcpyAsync(s->hostInts, st, sizeof(CgState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_CHECK(cudaStreamSynchronize(s->stream));
+    memcpy(&host, s->hostInts, sizeof(CgState));
+  }
+  // doInit (conjugategrad.cpp:210-235)
+  void init(float accuracy, bool useL2) {
+    const long long N = s->N;
+    CgState h; memset(&h, 0, sizeof(h));
+    h.accuracy = accuracy; h.useL2 = useL2 ? 1 : 0; h.resNorm = 1e20f;
+    memcpy(s->hostInts, &h, sizeof(h));
+    CUDA_CHECK(cudaMemcpyAsync(st, s->hostInts, sizeof(CgState), cudaMemcpyHostToDevice, s->stream));
+    CUDA_CHECK(cudaStreamSynchronize(s->stream));   // hostInts is reused below
+    CUDA_CHECK(cudaMemsetAsync(v.dst, 0, sizeof(float) * N, s->stream));
+    CUDA_CHECK(cudaMemcpyAsync(v.residual, v.rhs, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
+    const float* z = v.residual;
+    if (pcMethod != 0) { applyPrecond(true); z = v.tmp; }
+    CUDA_CHECK(cudaMemcpyAsync(v.search, z, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
+    MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, N), 256, N, z, v.residual, st, s->redScratch, s->redCounter);
+  }
+  void iterate() {
+    const Geo g = geo(s);
+    const long long N = s->N;
+    MF_LAUNCH(s, k_cg_spmv_dot, tileBlocks(s), 256, g, v, st, s->redScratch, s->redCounter);
+    if (pcMethod == 0) {
+      MF_LAUNCH(s, k_cg_update<true>, redBlocks(s, N), 256, g, v, st, s->redScratch, s->redCounter);
+      MF_LAUNCH(s, k_cg_search, ewBlocks(s, N), 256, N, v.search, v.residual, st);
+    } else {
+      MF_LAUNCH(s, k_cg_update<false>, redBlocks(s, N), 256, g, v, st, s->redScratch, s->redCounter);
+      applyPrecond(false);
+      MF_LAUNCH(s, k_cg_dot_beta, redBlocks(s, N), 256, N, v.tmp, v.residual, st, s->redScratch, s->redCounter);
+      MF_LAUNCH(s, k_cg_search, ewBlocks(s, N), 256, N, v.search, v.tmp, st);
+    }
+  }
+  // for (iter < maxIter) if (!iterate()) break;   host polls the device flag every `batch` iterations
+  void solve(int maxIter, int batch) {
+    int it = 0;
+    host.done = 0; host.diverged = 0; host.iterations = 0;
+    while (it < maxIter) {
+      int nb = batch < (maxIter - it) ? batch : (maxIter - it);
+      for (int b = 0; b < nb; b++) iterate();
+      it += nb;
+      MF_LAUNCH_CHECK();
+      fetch();
+      if (host.done) break;
+    }
+    if (maxIter <= 0) fetch();
+    if (host.diverged) mfErr("GridCg::iterate: The CG solver diverged, residual norm > 1e30, stopping.");
+  }
+};
+
+static CgState* cgStateBuf(Solver* s) {
+  // carve the device CgState out of the reduction output buffer (16 doubles): doubles 8..15
+  return reinterpret_cast<CgState*>(s->redOut + 8);
+}
+
+// solvePressureSystem (pressure.cpp:312-454)
+static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, const Grid* flags, const mf_pressure_params* p, mf_solve_info* info) {
+  int preconditioner = p->preconditioner;
+  if (!p->precondition) preconditioner = MF_PC_NONE;
+  mfAssert(preconditioner >= 0 && preconditioner <= 3, "solvePressureSystem: unknown preconditioner " << preconditioner);
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "solvePressureSystem: grid too small");
+  const Geo g = geo(s);
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  SolveTemps t(s);
+  CV3 fr = p->fractions ? cv3(G(p->fractions)) : cv3(vel);
+  MF_LAUNCH(s, k_make_laplace, gr, b, g, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0,
+            p->phi ? G(p->phi)->d : nullptr, p->gfClamp);
+  int* fixedDev = s->devFlagsScratch + 2;
+  bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
+  if (fixing) {
+    MF_LAUNCH(s, k_flag_stats, tileBlocks(s), 256, g, flags->di(), s->redScratch, s->redCounter, s->redOut);
+    MF_LAUNCH(s, k_fix_pressure, 1, 32, g, flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, fixedDev);
+  }
+  CgDriver cg;
+  cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr;
+  cg.v.flags = flags->di(); cg.v.dst = pressure->d; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
+  cg.v.rhs = rhs; cg.v.A0 = t.A0; cg.v.Ai = t.Ai; cg.v.Aj = t.Aj; cg.v.Ak = t.Ak;
+  int maxIter = 0, batch = 8;
+  int mgLevels = 0, mgRebuilt = 0;
+  int maxDim = s->nx > s->ny ? s->nx : s->ny; if (s->nz > maxDim) maxDim = s->nz;
+  if (preconditioner == MF_PC_NONE || preconditioner == MF_PC_MIC) {
+    maxIter = (int)(p->cgMaxIterFac * maxDim) * (s->is3D ? 1 : 4);
+    // 2-D: ICP/mICP silently disabled (conjugategrad.cpp:315-321)
+    if (preconditioner == MF_PC_MIC && s->is3D) {
+      cg.pcMethod = 1;
+      t.pc = s->getReal(); cg.P = t.pc;
+      MF_LAUNCH(s, k_rbic_init, gr, b, g, flags->di(), cg.P, t.A0, t.Ai, t.Aj, t.Ak);
+    } else cg.pcMethod = 0;
+  } else {
+    maxIter = 100; batch = 1;
+    cg.pcMethod = 2;
+    if (s->mg && preconditioner == MF_PC_MG_DYNAMIC) { mg_destroy(s->mg); s->mg = nullptr; }
+    if (!s->mg) s->mg = mg_create(s);
+    cg.mg = s->mg;
+    // InitPreconditionMultigrid (conjugategrad.cpp:100-106)
+    if (!mg_is_a_set(cg.mg)) { mg_set_a(cg.mg, t.A0, t.Ai, t.Aj, t.Ak); mgRebuilt = 1; }
+    mg_set_coarsest_accuracy(cg.mg, p->cgAccuracy * 1E-4f);
+    mg_set_smoothing(cg.mg, 1, 1);
+    mgLevels = mg_num_levels(cg.mg);
+  }
+  cg.init(p->cgAccuracy, p->useL2Norm != 0);
+  cg.solve(maxIter, batch);
+  if (info) {
+    info->iterations = cg.host.iterations; info->resNorm = cg.host.resNorm; info->maxIter = maxIter;
+    info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
+    if (fixing) {
+      CUDA_CHECK(cudaMemcpyAsync(s->hostInts, fixedDev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+      CUDA_CHECK(cudaStreamSynchronize(s->stream));
+      info->fixedCell = s->hostInts[0];
+    }
+  }
+  if (cg.mg && preconditioner == MF_PC_MG_DYNAMIC) { mg_destroy(s->mg); s->mg = nullptr; }
+}
+
+static void correctVel(Solver* s, Grid* vel, const Grid* pressure, const Grid* flags, const mf_pressure_params* p) {
+  const Geo g = geo(s);
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  MF_LAUNCH(s, k_correct_velocity, gr, b, g, flags->di(), v3(vel), pressure->d);
+  if (p->phi) {
+    MF_LAUNCH(s, k_correct_velocity_gf, gr, b, g, flags->di(), v3(vel), pressure->d, G(p->phi)->d, p->gfClamp,
+              p->curv ? G(p->curv)->d : nullptr, p->surfTens);
+    MF_LAUNCH(s, k_replace_clamped_gf, gr, b, g, flags->di(), v3(vel), G(p->phi)->d, p->gfClamp);
+  }
+}
+
+// matrix of cgSolveDiffusion (conjugategrad.cpp:359-375): MakeLaplaceMatrix on an all-fluid dummy flag grid, then
+// identity rows in obstacles and (1 + alpha*L) elsewhere
+__global__ void __launch_bounds__(256) k_diffusion_matrix(Geo g, const int* __restrict__ flags, float* A0, float* Ai, float* Aj, float* Ak, float alpha) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  float a0 = 0.f, ai = 0.f, aj = 0.f, ak = 0.f;
+  if (interiorCell(g, i, j, k)) { a0 = g.is3D ? 6.f : 4.f; ai = -1.f; aj = -1.f; ak = g.is3D ? -1.f : 0.f; }
+  if (fIsObstacle(flags[idx])) { ai = aj = ak = 0.f; a0 = 1.f; }
+  else { ai *= alpha; aj *= alpha; ak *= alpha; a0 *= alpha; a0 += 1.f; }
+  A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak;
+}
+
+} // namespace mf
+
+using namespace mf;
+
+void mf_release_mg_impl(mf::Solver* s) { if (s->mg) { mg_destroy(s->mg); s->mg = nullptr; } }
+
+extern "C" {
+
+void mf_pressure_params_default(mf_pressure_params* p) {
+  if (!p) return;
+  p->cgAccuracy = 1e-3f; p->phi = nullptr; p->perCellCorr = nullptr; p->fractions = nullptr; p->obvel = nullptr;
+  p->gfClamp = 1e-04f; p->cgMaxIterFac = 1.5f; p->precondition = 1; p->preconditioner = MF_PC_MIC;
+  p->enforceCompatibility = 0; p->useL2Norm = 0; p->zeroPressureFixing = 0; p->curv = nullptr; p->surfTens = 0.f; p->retRhs = nullptr;
+}
+
+int mf_compute_pressure_rhs(mf_grid* rhs, const mf_grid* vel, const mf_grid* pressure, const mf_grid* flags, const mf_pressure_params* p) {
+  MF_API_BEGIN
+  REQ_GRID(rhs, G(rhs)->isReal(), "rhs", "computePressureRhs");
+  REQ_GRID(vel, G(vel)->isMAC(), "vel", "computePressureRhs");
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "computePressureRhs");
+  Solver* s = G(flags)->s; s->use();
+  check_same_solver(G(flags), G(vel), "computePressureRhs"); check_same_solver(G(flags), G(rhs), "computePressureRhs");
+  checkParams(s, p, "computePressureRhs");
+  (void)pressure;
+  computeRhs(s, G(rhs)->d, G(vel), G(flags), p, false);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_solve_pressure_system(mf_grid* rhs, mf_grid* vel, mf_grid* pressure, const mf_grid* flags, const mf_pressure_params* p, mf_solve_info* info) {
+  MF_API_BEGIN
+  REQ_GRID(rhs, G(rhs)->isReal(), "rhs", "solvePressureSystem");
+  REQ_GRID(vel, G(vel)->isMAC(), "vel", "solvePressureSystem");
+  REQ_GRID(pressure, G(pressure)->isReal(), "pressure", "solvePressureSystem");
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "solvePressureSystem");
+  Solver* s = G(flags)->s; s->use();
+  check_same_solver(G(flags), G(vel), "solvePressureSystem"); check_same_solver(G(flags), G(rhs), "solvePressureSystem");
+  check_same_solver(G(flags), G(pressure), "solvePressureSystem");
+  checkParams(s, p, "solvePressureSystem");
+  solveSystem(s, G(rhs)->d, G(vel), G(pressure), G(flags), p, info);
+  MF_API_END
+}
+
+int mf_correct_velocity(mf_grid* vel, mf_grid* pressure, const mf_grid* flags, const mf_pressure_params* p) {
+  MF_API_BEGIN
+  REQ_GRID(vel, G(vel)->isMAC(), "vel", "correctVelocity");
+  REQ_GRID(pressure, G(pressure)->isReal(), "pressure", "correctVelocity");
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "correctVelocity");
+  Solver* s = G(flags)->s; s->use();
+  check_same_solver(G(flags), G(vel), "correctVelocity"); check_same_solver(G(flags), G(pressure), "correctVelocity");
+  checkParams(s, p, "correctVelocity");
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "correctVelocity: grid too small");
+  correctVel(s, G(vel), G(pressure), G(flags), p);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* flags, const mf_pressure_params* p, mf_solve_info* info) {
+  MF_API_BEGIN
+  REQ_GRID(vel, G(vel)->isMAC(), "vel", "solvePressure");
+  REQ_GRID(pressure, G(pressure)->isReal(), "pressure", "solvePressure");
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "solvePressure");
+  Solver* s = G(flags)->s; s->use();
+  check_same_solver(G(flags), G(vel), "solvePressure"); check_same_solver(G(flags), G(pressure), "solvePressure");
+  checkParams(s, p, "solvePressure");
+  TmpReal rhs(s);                                    // Grid<Real> rhs(vel.getParent())  (pressure.cpp:499)
+  computeRhs(s, rhs.p, G(vel), G(flags), p, true);
+  solveSystem(s, rhs.p, G(vel), G(pressure), G(flags), p, info);
+  correctVel(s, G(vel), G(pressure), G(flags), p);
+  if (p->retRhs) CUDA_CHECK(cudaMemcpyAsync(G(p->retRhs)->d, rhs.p, sizeof(float) * s->N, cudaMemcpyDeviceToDevice, s->stream));
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_release_mg(mf_solver* sp) {
+  MF_API_BEGIN
+  mfAssert(sp, "releaseMG: null solver");
+  S(sp)->use();
+  mf_release_mg_impl(S(sp));
+  MF_API_END
+}
+
+int mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_grid* Aj, mf_grid* Ak, const mf_grid* fractions) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "MakeLaplaceMatrix");
+  REQ_GRID(A0, G(A0)->isReal(), "A0", "MakeLaplaceMatrix"); REQ_GRID(Ai, G(Ai)->isReal(), "Ai", "MakeLaplaceMatrix");
+  REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "MakeLaplaceMatrix"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "MakeLaplaceMatrix");
+  if (fractions) REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "MakeLaplaceMatrix");
+  Solver* s = G(flags)->s; s->use();
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "MakeLaplaceMatrix: grid too small");
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
+  MF_LAUNCH(s, k_make_laplace, gr, b, geo(s), G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* src, const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "ApplyMatrix");
+  REQ_GRID(dst, G(dst)->isReal(), "dst", "ApplyMatrix"); REQ_GRID(src, G(src)->isReal(), "src", "ApplyMatrix");
+  REQ_GRID(A0, G(A0)->isReal(), "A0", "ApplyMatrix"); REQ_GRID(Ai, G(Ai)->isReal(), "Ai", "ApplyMatrix");
+  REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "ApplyMatrix"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "ApplyMatrix");
+  mfAssert(G(dst)->d != G(src)->d, "ApplyMatrix: dst and src must differ");
+  Solver* s = G(flags)->s; s->use();
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  MF_LAUNCH(s, k_apply_matrix, gr, b, geo(s), G(flags)->di(), G(dst)->d, G(src)->d, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_cg_solve_diffusion(const mf_grid* flagsp, mf_grid* gridp, float alpha, float cgMaxIterFac, float cgAccuracy) {
+  MF_API_BEGIN
+  REQ_GRID(flagsp, G(flagsp)->isInt(), "flags", "cgSolveDiffusion");
+  mfAssert(gridp, "cgSolveDiffusion: argument 'grid' is missing");
+  const Grid* flags = G(flagsp); Grid* grid = G(gridp); Solver* s = flags->s; s->use();
+  check_same_solver(flags, grid, "cgSolveDiffusion");
+  mfAssert(grid->isReal() || grid->isVec(), "cgSolveDiffusion: Grid Type is not supported (only Real, Vec3, MAC, or Levelset)");
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "cgSolveDiffusion: grid too small");
+  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
+  SolveTemps t(s);
+  TmpReal rhs(s);
+  MF_LAUNCH(s, k_diffusion_matrix, gr, b, geo(s), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, alpha);
+  int maxDim = s->nx > s->ny ? s->nx : s->ny; if (s->nz > maxDim) maxDim = s->nz;
+  const int maxIter = (int)(cgMaxIterFac * maxDim) * (s->is3D ? 1 : 4);
+  const int ncomp = grid->isVec() ? (s->is3D ? 3 : 2) : 1;
+  for (int c = 0; c < ncomp; c++) {
+    float* u = grid->isVec() ? grid->comp(c) : grid->d;
+    CUDA_CHECK(cudaMemcpyAsync(rhs.p, u, sizeof(float) * s->N, cudaMemcpyDeviceToDevice, s->stream));
+    CgDriver cg;
+    cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr; cg.pcMethod = 0;
+    cg.v.flags = flags->di(); cg.v.dst = u; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
+    cg.v.rhs = rhs.p; cg.v.A0 = t.A0; cg.v.Ai = t.Ai; cg.v.Aj = t.Aj; cg.v.Ak = t.Ak;
+    cg.init(cgAccuracy, true);      // GridCgInterface() defaults to the L2 norm (conjugategrad.h:31)
+    cg.solve(maxIter, 8);
+  }
+  MF_API_END
+}
+
+} // extern "C"

@@ -1,0 +1,297 @@
+// pressure_kernels.cuh -- streaming kernels of the pressure projection.
+// Reference: source/plugin/pressure.cpp (MakeRhs :32, knCorrectVelocity :87, thetaHelper :115,
+// ghostFluidHelper :123, surfTensHelper :130, ApplyGhostFluidDiagonal :136, knCorrectVelocityGhostFluid :154,
+// knReplaceClampedGhostFluidVels :198, CountEmptyCells :217, fixPressure :226),
+// source/conjugategrad.h (ApplyMatrix :118, ApplyMatrix2D :136, MakeLaplaceMatrix :154).
+#pragma once
+#include "common.cuh"
+#include "reduce.cuh"
+
+namespace mf {
+
+__device__ __forceinline__ bool interiorCell(const Geo& g, int i, int j, int k) {
+  return i >= 1 && j >= 1 && i < g.nx - 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+}
+
+// ---- ghost fluid helpers (pressure.cpp:115-133) ------------------------------------------------------
+__device__ __forceinline__ float thetaHelper(float inside, float outside) {
+  const float denom = inside - outside;
+  if ((double)denom > -1e-04) return 0.5f;
+  return fmaxf(0.0f, fminf(1.0f, inside / denom));
+}
+__device__ __forceinline__ float ghostFluidHelper(const float* __restrict__ phi, long long idx, long long offset, float gfClamp) {
+  const float alpha = thetaHelper(phi[idx], phi[idx + offset]);
+  if (alpha < gfClamp) return gfClamp;
+  return (float)(1. - (1. / (double)alpha));
+}
+__device__ __forceinline__ bool ghostFluidWasClamped(const float* __restrict__ phi, long long idx, long long offset, float gfClamp) {
+  return thetaHelper(phi[idx], phi[idx + offset]) < gfClamp;
+}
+__device__ __forceinline__ float surfTensHelper(const float* __restrict__ phi, const float* __restrict__ curv, long long idx, long long offset,
+                                                float surfTens, float gfClamp) {
+  return surfTens * (curv[idx + offset] - ghostFluidHelper(phi, idx, offset, gfClamp) * curv[idx]);
+}
+
+struct RhsArgs {
+  const int* flags; float* rhs; CV3 vel;
+  const float* perCellCorr; CV3 fractions; int haveFractions; CV3 obvel; int haveObvel;
+  const float* phi; const float* curv; float surfTens; float gfClamp;
+  int writeBorder;     // 1: rhs is a fresh temp -> also write the zeros the reference's cleared grid holds on the border
+};
+
+// MakeRhs: bnd=1, reduce+ (double sum, int cnt)
+__global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double sum = 0.0, cnt = 0.0;
+  MF_TILE_LOOP_BEGIN(g)
+    if (!interiorCell(g, i, j, k)) { if (a.writeBorder) a.rhs[idx] = 0.0f; continue; }
+    if (!fIsFluid(a.flags[idx])) { a.rhs[idx] = 0.0f; continue; }
+    const long long X = 1, Y = g.nx, Z = g.Z;
+    float set;
+    if (!a.haveFractions) {
+      set = a.vel.x[idx] - a.vel.x[idx + X] + a.vel.y[idx] - a.vel.y[idx + Y];
+      if (g.is3D) set += a.vel.z[idx] - a.vel.z[idx + Z];
+    } else {
+      set = a.fractions.x[idx] * a.vel.x[idx] - a.fractions.x[idx + X] * a.vel.x[idx + X]
+          + a.fractions.y[idx] * a.vel.y[idx] - a.fractions.y[idx + Y] * a.vel.y[idx + Y];
+      if (g.is3D) set += a.fractions.z[idx] * a.vel.z[idx] - a.fractions.z[idx + Z] * a.vel.z[idx + Z];
+      if (a.haveObvel) {
+        set += (1 - a.fractions.x[idx]) * a.obvel.x[idx] - (1 - a.fractions.x[idx + X]) * a.obvel.x[idx + X]
+             + (1 - a.fractions.y[idx]) * a.obvel.y[idx] - (1 - a.fractions.y[idx + Y]) * a.obvel.y[idx + Y];
+        if (g.is3D) set += (1 - a.fractions.z[idx]) * a.obvel.z[idx] - (1 - a.fractions.z[idx + Z]) * a.obvel.z[idx + Z];
+      }
+    }
+    if (a.phi && a.curv) {
+      if (fIsEmpty(a.flags[idx - X])) set += surfTensHelper(a.phi, a.curv, idx, -X, a.surfTens, a.gfClamp);
+      if (fIsEmpty(a.flags[idx + X])) set += surfTensHelper(a.phi, a.curv, idx, +X, a.surfTens, a.gfClamp);
+      if (fIsEmpty(a.flags[idx - Y])) set += surfTensHelper(a.phi, a.curv, idx, -Y, a.surfTens, a.gfClamp);
+      if (fIsEmpty(a.flags[idx + Y])) set += surfTensHelper(a.phi, a.curv, idx, +Y, a.surfTens, a.gfClamp);
+      if (g.is3D) {
+        if (fIsEmpty(a.flags[idx - Z])) set += surfTensHelper(a.phi, a.curv, idx, -Z, a.surfTens, a.gfClamp);
+        if (fIsEmpty(a.flags[idx + Z])) set += surfTensHelper(a.phi, a.curv, idx, +Z, a.surfTens, a.gfClamp);
+      }
+    }
+    if (a.perCellCorr) set += a.perCellCorr[idx];
+    sum += (double)set;
+    cnt += 1.0;
+    a.rhs[idx] = set;
+  MF_TILE_LOOP_END
+  sum = blockReduce<OpSum>(sum, sh);
+  cnt = blockReduce<OpSum>(cnt, sh);
+  gridFinish<OpSum, OpSum, 2>(sum, cnt, partials, counter, out, sh);
+}
+
+__global__ void k_add_scalar(float* d, float v, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) d[i] += v;
+}
+
+// MakeLaplaceMatrix (+ ApplyGhostFluidDiagonal) -- writes all four coefficient grids for every cell
+// (the reference accumulates into cleared temp grids, conjugategrad.h:154-187, pressure.cpp:136-151)
+__global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restrict__ flags, float* __restrict__ A0, float* __restrict__ Ai,
+                                                      float* __restrict__ Aj, float* __restrict__ Ak, CV3 fr, int haveFractions,
+                                                      const float* __restrict__ phi, float gfClamp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  float a0 = 0.f, ai = 0.f, aj = 0.f, ak = 0.f;
+  if (interiorCell(g, i, j, k) && fIsFluid(flags[idx])) {
+    const long long X = 1, Y = g.nx, Z = g.Z;
+    const int fxm = flags[idx - X], fxp = flags[idx + X], fym = flags[idx - Y], fyp = flags[idx + Y];
+    const int fzm = g.is3D ? flags[idx - Z] : 0, fzp = g.is3D ? flags[idx + Z] : 0;
+    if (!haveFractions) {
+      if (!fIsObstacle(fxm)) a0 += 1.f;
+      if (!fIsObstacle(fxp)) a0 += 1.f;
+      if (!fIsObstacle(fym)) a0 += 1.f;
+      if (!fIsObstacle(fyp)) a0 += 1.f;
+      if (g.is3D && !fIsObstacle(fzm)) a0 += 1.f;
+      if (g.is3D && !fIsObstacle(fzp)) a0 += 1.f;
+      if (fIsFluid(fxp)) ai = -1.f;
+      if (fIsFluid(fyp)) aj = -1.f;
+      if (g.is3D && fIsFluid(fzp)) ak = -1.f;
+    } else {
+      a0 += fr.x[idx]; a0 += fr.x[idx + X];
+      a0 += fr.y[idx]; a0 += fr.y[idx + Y];
+      if (g.is3D) { a0 += fr.z[idx]; a0 += fr.z[idx + Z]; }
+      if (fIsFluid(fxp)) ai = -fr.x[idx + X];
+      if (fIsFluid(fyp)) aj = -fr.y[idx + Y];
+      if (g.is3D && fIsFluid(fzp)) ak = -fr.z[idx + Z];
+    }
+    if (phi) {
+      if (fIsEmpty(fxm)) a0 -= ghostFluidHelper(phi, idx, -X, gfClamp);
+      if (fIsEmpty(fxp)) a0 -= ghostFluidHelper(phi, idx, +X, gfClamp);
+      if (fIsEmpty(fym)) a0 -= ghostFluidHelper(phi, idx, -Y, gfClamp);
+      if (fIsEmpty(fyp)) a0 -= ghostFluidHelper(phi, idx, +Y, gfClamp);
+      if (g.is3D) {
+        if (fIsEmpty(fzm)) a0 -= ghostFluidHelper(phi, idx, -Z, gfClamp);
+        if (fIsEmpty(fzp)) a0 -= ghostFluidHelper(phi, idx, +Z, gfClamp);
+      }
+    }
+  }
+  A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak;
+}
+
+// CountEmptyCells (pressure.cpp:217) + "first interior fluid cell in FOR_IJK_BND order" (:371-381)
+// out[0] = numEmpty, out[1] = min interior fluid index (or INT_MAX-ish)
+__global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict__ flags, double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double numEmpty = 0.0, minFluid = 1e300;
+  MF_TILE_LOOP_BEGIN(g)
+    const int f = flags[idx];
+    if (fIsEmpty(f)) numEmpty += 1.0;
+    if (fIsFluid(f) && interiorCell(g, i, j, k)) { const double v = (double)idx; if (v < minFluid) minFluid = v; }
+  MF_TILE_LOOP_END
+  numEmpty = blockReduce<OpSum>(numEmpty, sh);
+  minFluid = blockReduce<OpMin>(minFluid, sh);
+  gridFinish<OpSum, OpMin, 2>(numEmpty, minFluid, partials, counter, out, sh);
+}
+
+// zeroPressureFixing: pick the cell (pressure.cpp:352-383) and apply fixPressure(idx, 0, ...) (:226-245); one thread
+__global__ void k_fix_pressure(Geo g, const int* __restrict__ flags, const double* __restrict__ stats, float* rhs, float* A0, float* Ai,
+                               float* Aj, float* Ak, int* fixedOut) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  long long fix = -1;
+  if (stats[0] == 0.0) {
+    const int tx = g.nx / 2, ty = g.ny - 1, tz = g.is3D ? g.nz / 2 : 0;
+    for (int q = 0; q < 3 && fix < 0; q++) {
+      const int y = ty - q;
+      if (y < 0) continue;
+      const long long p = (long long)tx + (long long)g.nx * y + g.Z * tz;
+      if (fIsFluid(flags[p])) fix = p;
+    }
+    if (fix < 0 && stats[1] < 1e299) fix = (long long)stats[1];
+  }
+  *fixedOut = (int)fix;
+  if (fix < 0) return;
+  const float value = 0.0f;
+  const long long X = 1, Y = g.nx, Z = g.Z;
+  rhs[fix + X] -= Ai[fix] * value;
+  rhs[fix + Y] -= Aj[fix] * value;
+  rhs[fix - X] -= Ai[fix - X] * value;
+  rhs[fix - Y] -= Aj[fix - Y] * value;
+  if (g.is3D) { rhs[fix + Z] -= Ak[fix] * value; rhs[fix - Z] -= Ak[fix - Z] * value; }
+  rhs[fix] = value;
+  A0[fix] = 1.0f;
+  Ai[fix] = Aj[fix] = Ak[fix] = 0.0f;
+  Ai[fix - X] = 0.0f;
+  Aj[fix - Y] = 0.0f;
+  if (g.is3D) Ak[fix - Z] = 0.0f;
+}
+
+// ApplyMatrix / ApplyMatrix2D for one cell; neighbours outside the array contribute nothing
+// (the reference reads out of bounds there, which only happens for fluid cells on the domain border)
+__device__ __forceinline__ float applyRow(const Geo& g, long long idx, const float* __restrict__ src, const float* __restrict__ A0,
+                                          const float* __restrict__ Ai, const float* __restrict__ Aj, const float* __restrict__ Ak) {
+  const long long X = 1, Y = g.nx, Z = g.Z, N = g.N;
+  float r = src[idx] * A0[idx];
+  r += (idx - X >= 0) ? src[idx - X] * Ai[idx - X] : 0.0f;
+  r += (idx + X < N) ? src[idx + X] * Ai[idx] : 0.0f;
+  r += (idx - Y >= 0) ? src[idx - Y] * Aj[idx - Y] : 0.0f;
+  r += (idx + Y < N) ? src[idx + Y] * Aj[idx] : 0.0f;
+  if (g.is3D) {
+    r += (idx - Z >= 0) ? src[idx - Z] * Ak[idx - Z] : 0.0f;
+    r += (idx + Z < N) ? src[idx + Z] * Ak[idx] : 0.0f;
+  }
+  return r;
+}
+
+__global__ void __launch_bounds__(256) k_apply_matrix(Geo g, const int* __restrict__ flags, float* __restrict__ dst, const float* __restrict__ src,
+                                                      const float* __restrict__ A0, const float* __restrict__ Ai, const float* __restrict__ Aj,
+                                                      const float* __restrict__ Ak) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  dst[idx] = fIsFluid(flags[idx]) ? applyRow(g, idx, src, A0, Ai, Aj, Ak) : src[idx];
+}
+
+// knCorrectVelocity (pressure.cpp:87-109), in place
+__global__ void __launch_bounds__(256) k_correct_velocity(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ p) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  if (!interiorCell(g, i, j, k)) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  const long long X = 1, Y = g.nx, Z = g.Z;
+  const int f = flags[idx];
+  const int fx = flags[idx - X], fy = flags[idx - Y], fz = g.is3D ? flags[idx - Z] : 0;
+  if (fIsFluid(f)) {
+    const float pc = p[idx];
+    float vx = vel.x[idx], vy = vel.y[idx];
+    if (fIsFluid(fx)) vx -= (pc - p[idx - X]);
+    if (fIsFluid(fy)) vy -= (pc - p[idx - Y]);
+    if (fIsEmpty(fx)) vx -= pc;
+    if (fIsEmpty(fy)) vy -= pc;
+    vel.x[idx] = vx; vel.y[idx] = vy;
+    if (g.is3D) {
+      float vz = vel.z[idx];
+      if (fIsFluid(fz)) vz -= (pc - p[idx - Z]);
+      if (fIsEmpty(fz)) vz -= pc;
+      vel.z[idx] = vz;
+    }
+  } else if (fIsEmpty(f) && !fIsOutflow(f)) {
+    if (fIsFluid(fx)) vel.x[idx] += p[idx - X]; else vel.x[idx] = 0.f;
+    if (fIsFluid(fy)) vel.y[idx] += p[idx - Y]; else vel.y[idx] = 0.f;
+    if (g.is3D) { if (fIsFluid(fz)) vel.z[idx] += p[idx - Z]; else vel.z[idx] = 0.f; }
+  }
+}
+
+// knCorrectVelocityGhostFluid (pressure.cpp:154-187)
+__global__ void __launch_bounds__(256) k_correct_velocity_gf(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ p,
+                                                             const float* __restrict__ phi, float gfClamp, const float* __restrict__ curv, float surfTens) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  if (!interiorCell(g, i, j, k)) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  const long long X = 1, Y = g.nx, Z = g.Z;
+  const int f = flags[idx];
+  const int fx = flags[idx - X], fy = flags[idx - Y], fz = g.is3D ? flags[idx - Z] : 0;
+  const bool fluid = fIsFluid(f), emptyNoOut = fIsEmpty(f) && !fIsOutflow(f);
+  if (fluid) {
+    if (fIsEmpty(fx)) vel.x[idx] += p[idx] * ghostFluidHelper(phi, idx, -X, gfClamp);
+    if (fIsEmpty(fy)) vel.y[idx] += p[idx] * ghostFluidHelper(phi, idx, -Y, gfClamp);
+    if (g.is3D && fIsEmpty(fz)) vel.z[idx] += p[idx] * ghostFluidHelper(phi, idx, -Z, gfClamp);
+  } else if (emptyNoOut) {
+    if (fIsFluid(fx)) vel.x[idx] -= p[idx - X] * ghostFluidHelper(phi, idx - X, +X, gfClamp); else vel.x[idx] = 0.f;
+    if (fIsFluid(fy)) vel.y[idx] -= p[idx - Y] * ghostFluidHelper(phi, idx - Y, +Y, gfClamp); else vel.y[idx] = 0.f;
+    if (g.is3D) { if (fIsFluid(fz)) vel.z[idx] -= p[idx - Z] * ghostFluidHelper(phi, idx - Z, +Z, gfClamp); else vel.z[idx] = 0.f; }
+  }
+  if (curv) {
+    if (fluid) {
+      if (fIsEmpty(fx)) vel.x[idx] += surfTensHelper(phi, curv, idx, -X, surfTens, gfClamp);
+      if (fIsEmpty(fy)) vel.y[idx] += surfTensHelper(phi, curv, idx, -Y, surfTens, gfClamp);
+      if (g.is3D && fIsEmpty(fz)) vel.z[idx] += surfTensHelper(phi, curv, idx, -Z, surfTens, gfClamp);
+    } else if (emptyNoOut) {
+      vel.x[idx] -= fIsFluid(fx) ? surfTensHelper(phi, curv, idx - X, +X, surfTens, gfClamp) : 0.f;
+      vel.y[idx] -= fIsFluid(fy) ? surfTensHelper(phi, curv, idx - Y, +Y, surfTens, gfClamp) : 0.f;
+      if (g.is3D) vel.z[idx] -= fIsFluid(fz) ? surfTensHelper(phi, curv, idx - Z, +Z, surfTens, gfClamp) : 0.f;
+    }
+  }
+}
+
+// knReplaceClampedGhostFluidVels (pressure.cpp:198-214): empty cells copy face velocities from fluid neighbours
+__global__ void __launch_bounds__(256) k_replace_clamped_gf(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ phi, float gfClamp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  if (!interiorCell(g, i, j, k)) return;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  const long long X = 1, Y = g.nx, Z = g.Z;
+  if (!fIsEmpty(flags[idx])) return;
+  if (fIsFluid(flags[idx - X]) && ghostFluidWasClamped(phi, idx - X, +X, gfClamp)) vel.x[idx] = vel.x[idx - X];
+  if (fIsFluid(flags[idx - Y]) && ghostFluidWasClamped(phi, idx - Y, +Y, gfClamp)) vel.y[idx] = vel.y[idx - Y];
+  if (g.is3D && fIsFluid(flags[idx - Z]) && ghostFluidWasClamped(phi, idx - Z, +Z, gfClamp)) vel.z[idx] = vel.z[idx - Z];
+  if (fIsFluid(flags[idx + X]) && ghostFluidWasClamped(phi, idx + X, -X, gfClamp)) vel.x[idx] = vel.x[idx + X];
+  if (fIsFluid(flags[idx + Y]) && ghostFluidWasClamped(phi, idx + Y, -Y, gfClamp)) vel.y[idx] = vel.y[idx + Y];
+  if (g.is3D && fIsFluid(flags[idx + Z]) && ghostFluidWasClamped(phi, idx + Z, -Z, gfClamp)) vel.z[idx] = vel.z[idx + Z];
+}
+
+} // namespace mf

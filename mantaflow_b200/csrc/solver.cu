@@ -1,0 +1,438 @@
+// solver.cu -- FluidSolver / Grid<T> data model on the device, elementwise ops and reductions.
+// Reference: source/fluidsolver.{h,cpp} (temp-grid pool :25-50, ctor :107), source/grid.{h,cpp}.
+#include "common.cuh"
+#include "reduce.cuh"
+#include <cstring>
+#include <cmath>
+
+namespace mf { struct Grid; struct Solver; }
+void launch_norm_square(mf::Solver* s, const mf::Grid* g, float* o);
+
+namespace mf {
+
+static thread_local std::string g_lastError;
+void set_last_error(const std::string& s) { g_lastError = s; }
+
+void check_same_solver(const Grid* a, const Grid* b, const char* what) {
+  if (a && b && a->s != b->s) mfErr(what << ": grids belong to different solvers");
+}
+
+void Solver::use() const { cudaSetDevice(device); }
+
+float* Solver::getReal() {
+  if (!poolReal.empty()) { float* p = poolReal.back(); poolReal.pop_back(); return p; }
+  float* p = nullptr;
+  CUDA_CHECK(cudaMalloc(&p, sizeof(float) * (size_t)(N + 64)));
+  poolBytes += sizeof(float) * (N + 64);
+  return p;
+}
+void Solver::putReal(float* p) { poolReal.push_back(p); }
+float* Solver::getVec() {
+  if (!poolVec.empty()) { float* p = poolVec.back(); poolVec.pop_back(); return p; }
+  float* p = nullptr;
+  CUDA_CHECK(cudaMalloc(&p, sizeof(float) * (size_t)(3 * Np + 64)));
+  poolBytes += sizeof(float) * (3 * Np + 64);
+  return p;
+}
+void Solver::putVec(float* p) { poolVec.push_back(p); }
+
+void fetchRed(Solver* s, int count) {
+  CUDA_CHECK(cudaMemcpyAsync(s->redHost, s->redOut, sizeof(double) * count, cudaMemcpyDeviceToHost, s->stream));
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+}
+
+// ---- elementwise kernels ---------------------------------------------------------------
+__global__ void k_fill_f(float* d, float v, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) d[i] = v;
+}
+__global__ void k_fill_i(int* d, int v, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) d[i] = v;
+}
+// me += f * other   (gridScaledAdd, grid.h:514)
+__global__ void k_scaled_add(float* me, const float* other, float f, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) me[i] += f * other[i];
+}
+__global__ void k_mult_const(float* me, float f, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) me[i] *= f;
+}
+__global__ void k_aos_to_soa(const float* __restrict__ aos, float* x, float* y, float* z, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { x[i] = aos[3 * i]; y[i] = aos[3 * i + 1]; z[i] = aos[3 * i + 2]; }
+}
+__global__ void k_soa_to_aos(float* __restrict__ aos, const float* x, const float* y, const float* z, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { aos[3 * i] = x[i]; aos[3 * i + 1] = y[i]; aos[3 * i + 2] = z[i]; }
+}
+
+static inline int ewBlocks(const Solver* s, long long n) {
+  long long b = (n + 255) / 256;
+  long long cap = (long long)s->numSMs * 16;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+// ---- reductions --------------------------------------------------------------------------
+__global__ void k_dot(const float* __restrict__ a, const float* __restrict__ b, long long n,
+                      double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) acc += (double)(a[i] * b[i]);   // float product, double accumulate (conjugategrad.cpp:177)
+  acc = blockReduce<OpSum>(acc, sh);
+  gridFinish<OpSum, OpSum, 1>(acc, 0.0, partials, counter, out, sh);
+}
+__global__ void k_sumsqr(const float* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { double v = (double)a[i]; acc += v * v; }
+  acc = blockReduce<OpSum>(acc, sh);
+  gridFinish<OpSum, OpSum, 1>(acc, 0.0, partials, counter, out, sh);
+}
+__global__ void k_minmax(const float* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double mn = 1e300, mx = -1e300;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { double v = (double)a[i]; if (v < mn) mn = v; if (v > mx) mx = v; }
+  mn = blockReduce<OpMin>(mn, sh);
+  mx = blockReduce<OpMax>(mx, sh);
+  gridFinish<OpMin, OpMax, 2>(mn, mx, partials, counter, out, sh);
+}
+__global__ void k_minmax_i(const int* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double mn = 1e300, mx = -1e300;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { double v = (double)a[i]; if (v < mn) mn = v; if (v > mx) mx = v; }
+  mn = blockReduce<OpMin>(mn, sh);
+  mx = blockReduce<OpMax>(mx, sh);
+  gridFinish<OpMin, OpMax, 2>(mn, mx, partials, counter, out, sh);
+}
+// max over cells of |a-b| (Real, gridMaxDiff grid.cpp:437) or sum of component |diffs| (Vec3, :457)
+__global__ void k_maxdiff(const float* __restrict__ a, const float* __restrict__ b, long long n, long long np, int ncomp,
+                          double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double mx = 0.0;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) {
+    double d = 0.0;
+    for (int c = 0; c < ncomp; c++) d += fabs((double)a[i + c * np] - (double)b[i + c * np]);
+    if (d > mx) mx = d;
+  }
+  mx = blockReduce<OpMax>(mx, sh);
+  gridFinish<OpMax, OpMax, 1>(mx, 0.0, partials, counter, out, sh);
+}
+__global__ void k_maxdiff_i(const int* __restrict__ a, const int* __restrict__ b, long long n,
+                            double* partials, unsigned int* counter, double* out) {
+  __shared__ double sh[32];
+  double mx = 0.0;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) { double d = fabs((double)a[i] - (double)b[i]); if (d > mx) mx = d; }
+  mx = blockReduce<OpMax>(mx, sh);
+  gridFinish<OpMax, OpMax, 1>(mx, 0.0, partials, counter, out, sh);
+}
+
+double reduce_dot(Solver* s, const float* a, const float* b, long long n) {
+  MF_LAUNCH(s, k_dot, redBlocks(s, n), RED_THREADS, a, b, n, s->redScratch, s->redCounter, s->redOut);
+  fetchRed(s, 1);
+  return s->redHost[0];
+}
+double reduce_sumsqr(Solver* s, const float* a, long long n) {
+  MF_LAUNCH(s, k_sumsqr, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
+  fetchRed(s, 1);
+  return s->redHost[0];
+}
+void reduce_minmax(Solver* s, const float* a, long long n, float* mn, float* mx) {
+  MF_LAUNCH(s, k_minmax, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
+  fetchRed(s, 2);
+  *mn = (float)s->redHost[0]; *mx = (float)s->redHost[1];
+}
+void reduce_minmax_int(Solver* s, const int* a, long long n, int* mn, int* mx) {
+  MF_LAUNCH(s, k_minmax_i, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
+  fetchRed(s, 2);
+  *mn = (int)s->redHost[0]; *mx = (int)s->redHost[1];
+}
+
+} // namespace mf
+
+using namespace mf;
+
+extern "C" {
+
+int mf_version(void) { return 100; }
+const char* mf_last_error(void) { return g_lastError.c_str(); }
+int mf_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+const char* mf_build_info(void) { return "mantaflow-b200 0.1 linux 64bit fp1 cuda sm_100a"; }
+
+mf_solver* mf_solver_create(int nx, int ny, int nz, int dim, int device) {
+  try {
+    mfAssert(dim == 2 || dim == 3, "FluidSolver: dim must be 2 or 3");
+    mfAssert(nx > 0 && ny > 0 && nz > 0, "FluidSolver: invalid grid size");
+    if (dim == 2) nz = 1;   // fluidsolver.cpp:107-112 forces z=1 in 2-D
+    int ndev = mf_device_count();
+    mfAssert(ndev > 0, "mantacuda: no CUDA device available (there is no CPU fallback)");
+    mfAssert(device >= 0 && device < ndev, "mantacuda: invalid device index " << device);
+    CUDA_CHECK(cudaSetDevice(device));
+    Solver* s = new Solver();
+    s->nx = nx; s->ny = ny; s->nz = nz; s->dim = dim; s->is3D = (dim == 3);
+    s->N = (long long)nx * ny * nz;
+    s->Np = (s->N + 31) / 32 * 32;
+    s->strideZ = s->is3D ? (long long)nx * ny : 0;
+    s->dt = 1.0f;
+    int mx = nx > ny ? nx : ny; if (nz > mx) mx = nz;
+    s->dx = (float)(1.0 / mx);       // grid.cpp:57
+    s->device = device;
+    s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    s->numSMs = prop.multiProcessorCount;
+    CUDA_CHECK(cudaMalloc(&s->redScratch, sizeof(double) * 8 * RED_MAX_BLOCKS));
+    CUDA_CHECK(cudaMalloc(&s->redCounter, sizeof(unsigned int) * 4));
+    CUDA_CHECK(cudaMemset(s->redCounter, 0, sizeof(unsigned int) * 4));
+    CUDA_CHECK(cudaMalloc(&s->redOut, sizeof(double) * 16));
+    CUDA_CHECK(cudaMemset(s->redOut, 0, sizeof(double) * 16));
+    CUDA_CHECK(cudaMallocHost(&s->redHost, sizeof(double) * 16));
+    CUDA_CHECK(cudaMalloc(&s->devFlagsScratch, sizeof(int) * 16));
+    CUDA_CHECK(cudaMemset(s->devFlagsScratch, 0, sizeof(int) * 16));
+    CUDA_CHECK(cudaMallocHost(&s->hostInts, sizeof(int) * 16));
+    return reinterpret_cast<mf_solver*>(s);
+  } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+}
+
+void mf_release_mg_impl(Solver* s);
+
+void mf_solver_destroy(mf_solver* sp) {
+  if (!sp) return;
+  Solver* s = S(sp);
+  s->use();
+  cudaStreamSynchronize(s->stream);
+  mf_release_mg_impl(s);
+  for (float* p : s->poolReal) cudaFree(p);
+  for (float* p : s->poolVec) cudaFree(p);
+  cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);
+  cudaFree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
+  if (s->aosStage) cudaFree(s->aosStage);
+  cudaStreamDestroy(s->stream);
+  delete s;
+}
+
+int mf_solver_set_dt(mf_solver* s, float dt) { MF_API_BEGIN mfAssert(s, "null solver"); S(s)->dt = dt; MF_API_END }
+float mf_solver_get_dt(const mf_solver* s) { return s ? S(s)->dt : 0.f; }
+int mf_solver_sync(mf_solver* s) { MF_API_BEGIN mfAssert(s, "null solver"); S(s)->use(); CUDA_CHECK(cudaStreamSynchronize(S(s)->stream)); CUDA_CHECK(cudaGetLastError()); MF_API_END }
+void* mf_solver_stream(mf_solver* s) { return s ? (void*)S(s)->stream : nullptr; }
+long long mf_solver_launch_count(const mf_solver* s) { return s ? S(s)->launches : 0; }
+long long mf_solver_pool_bytes(const mf_solver* s) { return s ? S(s)->poolBytes : 0; }
+
+mf_grid* mf_grid_create(mf_solver* sp, int type) {
+  try {
+    mfAssert(sp, "Grid: null solver");
+    Solver* s = S(sp); s->use();
+    Grid* g = new Grid();
+    g->s = s; g->type = type; g->pooled = false; g->d = nullptr; g->outflowState = -1;
+    size_t bytes = (type & MF_TYPE_VEC3) ? sizeof(float) * (size_t)(3 * s->Np + 64) : sizeof(float) * (size_t)(s->N + 64);
+    CUDA_CHECK(cudaMalloc(&g->d, bytes));
+    CUDA_CHECK(cudaMemsetAsync(g->d, 0, bytes, s->stream));   // Grid ctor clears (grid.cpp:58)
+    return reinterpret_cast<mf_grid*>(g);
+  } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+}
+void mf_grid_destroy(mf_grid* gp) {
+  if (!gp) return;
+  Grid* g = G(gp);
+  g->s->use();
+  cudaStreamSynchronize(g->s->stream);
+  cudaFree(g->d);
+  delete g;
+}
+int mf_grid_type(const mf_grid* g) { return g ? G(g)->type : 0; }
+
+int mf_grid_clear(mf_grid* gp) {
+  MF_API_BEGIN
+  mfAssert(gp, "Grid::clear: null grid");
+  Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
+  size_t bytes = g->isVec() ? sizeof(float) * (size_t)(3 * s->Np) : sizeof(float) * (size_t)s->N;
+  CUDA_CHECK(cudaMemsetAsync(g->d, 0, bytes, s->stream));
+  MF_API_END
+}
+int mf_grid_copy(mf_grid* dp, const mf_grid* sp) {
+  MF_API_BEGIN
+  mfAssert(dp && sp, "Grid::copyFrom: null grid");
+  Grid* d = G(dp); const Grid* a = G(sp); Solver* s = d->s; s->use();
+  check_same_solver(d, a, "Grid::copyFrom");
+  mfAssert(d->isVec() == a->isVec() && d->isInt() == a->isInt(), "Grid::copyFrom: grid types do not match");
+  size_t bytes = d->isVec() ? sizeof(float) * (size_t)(3 * s->Np) : sizeof(float) * (size_t)s->N;
+  CUDA_CHECK(cudaMemcpyAsync(d->d, a->d, bytes, cudaMemcpyDeviceToDevice, s->stream));
+  d->outflowState = a->outflowState;
+  MF_API_END
+}
+int mf_grid_swap(mf_grid* ap, mf_grid* bp) {
+  MF_API_BEGIN
+  mfAssert(ap && bp, "Grid::swap: null grid");
+  Grid* a = G(ap); Grid* b = G(bp);
+  check_same_solver(a, b, "Grid::swap");
+  mfAssert(a->isVec() == b->isVec() && a->isInt() == b->isInt(), "Grid::swap(): Grid types mismatch.");
+  float* t = a->d; a->d = b->d; b->d = t;
+  int o = a->outflowState; a->outflowState = b->outflowState; b->outflowState = o;
+  MF_API_END
+}
+int mf_grid_upload(mf_grid* gp, const void* host) {
+  MF_API_BEGIN
+  mfAssert(gp && host, "Grid upload: null argument");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  g->outflowState = -1;
+  if (!g->isVec()) {
+    CUDA_CHECK(cudaMemcpyAsync(g->d, host, sizeof(float) * (size_t)s->N, cudaMemcpyHostToDevice, s->stream));
+  } else {
+    if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * s->N)));
+    CUDA_CHECK(cudaMemcpyAsync(s->aosStage, host, sizeof(float) * (size_t)(3 * s->N), cudaMemcpyHostToDevice, s->stream));
+    MF_LAUNCH(s, k_aos_to_soa, ewBlocks(s, s->N), 256, s->aosStage, g->comp(0), g->comp(1), g->comp(2), s->N);
+    MF_LAUNCH_CHECK();
+  }
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));  // host buffer may be reused by the caller
+  MF_API_END
+}
+int mf_grid_download(const mf_grid* gp, void* host) {
+  MF_API_BEGIN
+  mfAssert(gp && host, "Grid download: null argument");
+  const Grid* g = G(gp); Solver* s = g->s; s->use();
+  if (!g->isVec()) {
+    CUDA_CHECK(cudaMemcpyAsync(host, g->d, sizeof(float) * (size_t)s->N, cudaMemcpyDeviceToHost, s->stream));
+  } else {
+    if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * s->N)));
+    MF_LAUNCH(s, k_soa_to_aos, ewBlocks(s, s->N), 256, s->aosStage, g->comp(0), g->comp(1), g->comp(2), s->N);
+    MF_LAUNCH_CHECK();
+    CUDA_CHECK(cudaMemcpyAsync(host, s->aosStage, sizeof(float) * (size_t)(3 * s->N), cudaMemcpyDeviceToHost, s->stream));
+  }
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  CUDA_CHECK(cudaGetLastError());
+  MF_API_END
+}
+int mf_grid_set_const_real(mf_grid* gp, float v) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isReal(), "grid", "Grid<Real>::setConst");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->d, v, s->N); MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_set_const_int(mf_grid* gp, int v) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isInt(), "grid", "Grid<int>::setConst");
+  Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
+  MF_LAUNCH(s, k_fill_i, ewBlocks(s, s->N), 256, g->di(), v, s->N); MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_set_const_vec3(mf_grid* gp, float x, float y, float z) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isVec(), "grid", "Grid<Vec3>::setConst");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(0), x, s->N);
+  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(1), y, s->N);
+  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(2), z, s->N); MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_add_scaled(mf_grid* gp, const mf_grid* ap, float fx, float fy, float fz) {
+  MF_API_BEGIN
+  mfAssert(gp && ap, "Grid::addScaled: null grid");
+  Grid* g = G(gp); const Grid* a = G(ap); Solver* s = g->s; s->use();
+  check_same_solver(g, a, "Grid::addScaled");
+  mfAssert(!g->isInt() && g->isVec() == a->isVec(), "Grid::addScaled: grid types do not match");
+  if (!g->isVec()) { MF_LAUNCH(s, k_scaled_add, ewBlocks(s, s->N), 256, g->d, a->d, fx, s->N); }
+  else {
+    const float f[3] = { fx, fy, fz };
+    for (int c = 0; c < 3; c++) MF_LAUNCH(s, k_scaled_add, ewBlocks(s, s->N), 256, g->comp(c), a->comp(c), f[c], s->N);
+  }
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_mult_const(mf_grid* gp, float fx, float fy, float fz) {
+  MF_API_BEGIN
+  mfAssert(gp, "Grid::multConst: null grid");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  mfAssert(!g->isInt(), "Grid::multConst: int grids not supported");
+  if (!g->isVec()) { MF_LAUNCH(s, k_mult_const, ewBlocks(s, s->N), 256, g->d, fx, s->N); }
+  else {
+    const float f[3] = { fx, fy, fz };
+    for (int c = 0; c < 3; c++) MF_LAUNCH(s, k_mult_const, ewBlocks(s, s->N), 256, g->comp(c), f[c], s->N);
+  }
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_max_abs(const mf_grid* gp, float* out) {
+  MF_API_BEGIN
+  mfAssert(gp && out, "Grid::getMaxAbs: null argument");
+  const Grid* g = G(gp); Solver* s = g->s; s->use();
+  if (g->isInt()) { int mn, mx; reduce_minmax_int(s, g->di(), s->N, &mn, &mx); *out = (float)(abs(mn) > abs(mx) ? abs(mn) : abs(mx)); }
+  else if (!g->isVec()) { float mn, mx; reduce_minmax(s, g->d, s->N, &mn, &mx); *out = fmaxf(fabsf(mn), fabsf(mx)); }
+  else {
+    // Grid<Vec3>::getMaxAbs = sqrt(max normSquare) (grid.cpp:366-368 via CompMaxVec)
+    TmpReal t(s);
+    launch_norm_square(s, g, t.p);
+    float mn, mx; reduce_minmax(s, t.p, s->N, &mn, &mx); *out = sqrtf(mx);
+  }
+  MF_API_END
+}
+int mf_grid_min_max(const mf_grid* gp, float* omin, float* omax) {
+  MF_API_BEGIN
+  mfAssert(gp && omin && omax, "Grid::getMin/getMax: null argument");
+  const Grid* g = G(gp); Solver* s = g->s; s->use();
+  mfAssert(!g->isVec(), "Grid::getMin/getMax: Vec3 grids not supported here");
+  if (g->isInt()) { int mn, mx; reduce_minmax_int(s, g->di(), s->N, &mn, &mx); *omin = (float)mn; *omax = (float)mx; }
+  else reduce_minmax(s, g->d, s->N, omin, omax);
+  MF_API_END
+}
+int mf_grid_sum_sqr(const mf_grid* gp, double* out) {
+  MF_API_BEGIN
+  REQ_GRID(gp, G(gp)->isReal(), "grid", "GridSumSqr");
+  mfAssert(out, "GridSumSqr: null output");
+  *out = reduce_sumsqr(G(gp)->s, G(gp)->d, G(gp)->s->N);
+  MF_API_END
+}
+int mf_grid_dot(const mf_grid* ap, const mf_grid* bp, double* out) {
+  MF_API_BEGIN
+  REQ_GRID(ap, G(ap)->isReal(), "a", "GridDotProduct");
+  REQ_GRID(bp, G(bp)->isReal(), "b", "GridDotProduct");
+  mfAssert(out, "GridDotProduct: null output");
+  check_same_solver(G(ap), G(bp), "GridDotProduct");
+  G(ap)->s->use();
+  *out = reduce_dot(G(ap)->s, G(ap)->d, G(bp)->d, G(ap)->s->N);
+  MF_API_END
+}
+int mf_grid_max_diff(const mf_grid* ap, const mf_grid* bp, double* out) {
+  MF_API_BEGIN
+  mfAssert(ap && bp && out, "gridMaxDiff: null argument");
+  const Grid* a = G(ap); const Grid* b = G(bp); Solver* s = a->s; s->use();
+  check_same_solver(a, b, "gridMaxDiff");
+  mfAssert(a->isVec() == b->isVec() && a->isInt() == b->isInt(), "gridMaxDiff: grid types do not match");
+  if (a->isInt()) { MF_LAUNCH(s, k_maxdiff_i, redBlocks(s, s->N), RED_THREADS, a->di(), b->di(), s->N, s->redScratch, s->redCounter, s->redOut); }
+  else { MF_LAUNCH(s, k_maxdiff, redBlocks(s, s->N), RED_THREADS, a->d, b->d, s->N, s->Np, a->isVec() ? 3 : 1, s->redScratch, s->redCounter, s->redOut); }
+  MF_LAUNCH_CHECK();
+  fetchRed(s, 1);
+  *out = s->redHost[0];
+  MF_API_END
+}
+
+} // extern "C"
+
+namespace mf {
+__global__ void k_norm_square(const float* x, const float* y, const float* z, float* o, long long n) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) o[i] = x[i] * x[i] + y[i] * y[i] + z[i] * z[i];
+}
+}
+void launch_norm_square(mf::Solver* s, const mf::Grid* g, float* o) {
+  MF_LAUNCH(s, mf::k_norm_square, mf::ewBlocks(s, s->N), 256, g->comp(0), g->comp(1), g->comp(2), o, s->N);
+}
