@@ -144,8 +144,17 @@ int          mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* 
 /* cgSolveDiffusion(flags, grid, alpha, cgMaxIterFac, cgAccuracy), conjugategrad.cpp:350 */
 int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float alpha, float cgMaxIterFac, float cgAccuracy);
 
-/* ---- multi-GPU z-slab decomposition (no reference equivalent: SURVEY 8e) ------------- */
-/* see mantacuda_dist.h */
+/* ---- GridMg inspection hooks for parity tests (source/multigrid.h:31-137 keeps these private) ---- */
+/* levels / host-fallback count of the solver's cached hierarchy (the gMapMG entry, pressure.cpp:250) */
+int          mf_mg_info(mf_solver* s, int* levels, int* usedHostFallback);
+/* size3[0..2] = vertex counts of level l; returns non-zero if there is no such level */
+int          mf_mg_level_size(mf_solver* s, int l, int* size3);
+/* type: n bytes of GridMg::VertexType; A: n*stencil floats in the reference's interleaved order mA[l][v*stencil+e] */
+int          mf_mg_download_level(mf_solver* s, int l, void* type, void* A);
+/* GridMg(size); setA(A0..Ak); setCoarsestLevelAccuracy(acc); setSmoothing(1,1); setRhs(rhs); doVCycle(dst)
+ * -- the hierarchy stays cached on the solver like PcMGStatic's */
+int          mf_mg_vcycle(mf_solver* s, const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak,
+                          const mf_grid* rhs, mf_grid* dst, float coarsestAccuracy);
 
 #ifdef __cplusplus
 }

@@ -111,6 +111,7 @@ inline Solver* S(mf_solver* s) { return reinterpret_cast<Solver*>(s); }
 inline const Solver* S(const mf_solver* s) { return reinterpret_cast<const Solver*>(s); }
 
 void check_same_solver(const Grid* a, const Grid* b, const char* what);
+void release_mg(Solver* s);   // drop the cached multigrid hierarchy (pressure.cu)
 #define REQ_GRID(g, cond, name, fn) mfAssert((g) != nullptr && (cond), fn ": argument '" name "' has the wrong grid type or is missing")
 
 // launch helpers -----------------------------------------------------------------------

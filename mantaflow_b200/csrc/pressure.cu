@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(256) k_diffusion_matrix(Geo g, const int* __re
 
 using namespace mf;
 
-void mf_release_mg_impl(mf::Solver* s) { if (s->mg) { mg_destroy(s->mg); s->mg = nullptr; } }
+namespace mf { void release_mg(Solver* s) { if (s->mg) { mg_destroy(s->mg); s->mg = nullptr; } } }
 
 extern "C" {
 
@@ -285,7 +285,7 @@ int mf_release_mg(mf_solver* sp) {
   MF_API_BEGIN
   mfAssert(sp, "releaseMG: null solver");
   S(sp)->use();
-  mf_release_mg_impl(S(sp));
+  release_mg(S(sp));
   MF_API_END
 }
 
@@ -343,6 +343,48 @@ int mf_cg_solve_diffusion(const mf_grid* flagsp, mf_grid* gridp, float alpha, fl
     cg.init(cgAccuracy, true);      // GridCgInterface() defaults to the L2 norm (conjugategrad.h:31)
     cg.solve(maxIter, 8);
   }
+  MF_API_END
+}
+
+int mf_mg_info(mf_solver* sp, int* levels, int* usedHostFallback) {
+  MF_API_BEGIN
+  mfAssert(sp, "mf_mg_info: null solver");
+  Solver* s = S(sp);
+  if (levels) *levels = s->mg ? mg_num_levels(s->mg) : 0;
+  if (usedHostFallback) *usedHostFallback = s->mg ? mg_used_host_fallback(s->mg) : 0;
+  MF_API_END
+}
+int mf_mg_level_size(mf_solver* sp, int l, int* size3) {
+  MF_API_BEGIN
+  mfAssert(sp && size3, "mf_mg_level_size: null argument");
+  Solver* s = S(sp);
+  mfAssert(s->mg, "mf_mg_level_size: no multigrid hierarchy cached on this solver");
+  mfAssert(mg_level_size(s->mg, l, &size3[0], &size3[1], &size3[2]) > 0, "mf_mg_level_size: no such level");
+  MF_API_END
+}
+int mf_mg_download_level(mf_solver* sp, int l, void* type, void* A) {
+  MF_API_BEGIN
+  mfAssert(sp, "mf_mg_download_level: null solver");
+  Solver* s = S(sp); s->use();
+  mfAssert(s->mg && l >= 0 && l < mg_num_levels(s->mg), "mf_mg_download_level: no such level");
+  mg_download_level(s->mg, l, (unsigned char*)type, (float*)A);
+  MF_API_END
+}
+int mf_mg_vcycle(mf_solver* sp, const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak,
+                 const mf_grid* rhs, mf_grid* dst, float coarsestAccuracy) {
+  MF_API_BEGIN
+  mfAssert(sp, "mf_mg_vcycle: null solver");
+  Solver* s = S(sp); s->use();
+  REQ_GRID(A0, G(A0)->isReal(), "A0", "mf_mg_vcycle"); REQ_GRID(Ai, G(Ai)->isReal(), "Ai", "mf_mg_vcycle");
+  REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "mf_mg_vcycle"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "mf_mg_vcycle");
+  REQ_GRID(rhs, G(rhs)->isReal(), "rhs", "mf_mg_vcycle"); REQ_GRID(dst, G(dst)->isReal(), "dst", "mf_mg_vcycle");
+  release_mg(s);
+  s->mg = mg_create(s);
+  mg_set_a(s->mg, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+  mg_set_coarsest_accuracy(s->mg, coarsestAccuracy);
+  mg_set_smoothing(s->mg, 1, 1);
+  mg_apply(s->mg, G(dst)->d, G(rhs)->d);
+  MF_LAUNCH_CHECK();
   MF_API_END
 }
 

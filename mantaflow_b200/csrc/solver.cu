@@ -213,14 +213,13 @@ mf_solver* mf_solver_create(int nx, int ny, int nz, int dim, int device) {
   } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
 }
 
-void mf_release_mg_impl(Solver* s);
 
 void mf_solver_destroy(mf_solver* sp) {
   if (!sp) return;
   Solver* s = S(sp);
   s->use();
   cudaStreamSynchronize(s->stream);
-  mf_release_mg_impl(s);
+  release_mg(s);
   for (float* p : s->poolReal) cudaFree(p);
   for (float* p : s->poolVec) cudaFree(p);
   cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);

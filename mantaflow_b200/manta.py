@@ -1,0 +1,490 @@
+"""Host-side mirror of the reference's Python scene API for the Eulerian grid hot path.
+
+`from mantaflow_b200.manta import *` gives the names a Mantaflow scene uses for the path
+(`Solver`/`FluidSolver`, `FlagGrid`, `MACGrid`, `RealGrid`, `vec3`, `advectSemiLagrange`, `setWallBcs`,
+`addBuoyancy`, `solvePressure`, constants of source/python/defines.py ...) with the reference's keyword
+names, defaults and error behaviour (unknown keyword -> RuntimeError "Argument 'x' unknown",
+source/pwrapper/pconvert.cpp:460-474).  Every call goes through the C-ABI of libmantacuda.so; grids live
+in device memory and only cross to the host in `to_numpy`/`save`/reductions.
+"""
+import ctypes as C
+import gzip
+import struct
+import time as _time
+
+import numpy as np
+
+from ._lib import lib, check, MantaError, PressureParams, SolveInfo
+
+# ---- module constants (source/python/defines.py:24-50, pwrapper/registry.cpp:398-420) ---------------
+FlagFluid, FlagObstacle, FlagEmpty, FlagInflow, FlagOutflow, FlagOpen, FlagStick, FlagReserved = 1, 2, 4, 8, 16, 32, 64, 256
+TypeFluid, TypeObstacle, TypeEmpty, TypeInflow, TypeOutflow, TypeStick, TypeReserved = 1, 2, 4, 8, 16, 64, 256
+IntEuler, IntRK2, IntRK4 = 0, 1, 2
+PcNone, PcMIC, PcMGDynamic, PcMGStatic = 0, 1, 2, 3
+GUI = False
+DEBUG = False
+MT = True
+DOUBLEPRECISION = False
+CUDA = True
+
+_TYPE_REAL, _TYPE_INT, _TYPE_VEC3, _TYPE_MAC, _TYPE_LEVELSET, _TYPE_FLAGS = 1, 2, 4, 8, 16, 32
+
+_debugLevel = 1
+# the reference's solvePressure(preconditioner=PcNone) throws in setICPreconditioner (conjugategrad.cpp:312);
+# set allowPcNone = True to run plain CG instead
+allowPcNone = False
+lastSolveInfo = None
+
+
+def setDebugLevel(level=1):
+    global _debugLevel
+    _debugLevel = int(level)
+
+
+def mantaMsg(out, level=1):
+    if level <= _debugLevel:
+        print(out)
+
+
+def printBuildInfo():
+    s = lib().mf_build_info().decode()
+    mantaMsg("Build info: %s " % s, 1)
+    return s
+
+
+def _f32(v):
+    return np.float32(v)
+
+
+class vec3(object):
+    """Python `vec3` (source/pwrapper/pvec3.cpp): three Reals (float32), component-wise arithmetic."""
+    __slots__ = ("x", "y", "z")
+
+    def __init__(self, x=0.0, y=None, z=None):
+        if isinstance(x, vec3):
+            x, y, z = x.x, x.y, x.z
+        elif isinstance(x, (tuple, list, np.ndarray)):
+            x, y, z = x[0], x[1], x[2]
+        elif y is None:
+            y = z = x
+        elif z is None:
+            z = 0.0
+        self.x, self.y, self.z = _f32(x), _f32(y), _f32(z)
+
+    def _bin(self, o, op):
+        o = o if isinstance(o, vec3) else vec3(o)
+        return vec3(op(self.x, o.x), op(self.y, o.y), op(self.z, o.z))
+
+    def __add__(self, o): return self._bin(o, lambda a, b: a + b)
+    def __radd__(self, o): return self._bin(o, lambda a, b: b + a)
+    def __sub__(self, o): return self._bin(o, lambda a, b: a - b)
+    def __rsub__(self, o): return self._bin(o, lambda a, b: b - a)
+    def __mul__(self, o): return self._bin(o, lambda a, b: a * b)
+    def __rmul__(self, o): return self._bin(o, lambda a, b: b * a)
+    def __truediv__(self, o): return self._bin(o, lambda a, b: a / b)
+    def __neg__(self): return vec3(-self.x, -self.y, -self.z)
+    def __getitem__(self, i): return (self.x, self.y, self.z)[i]
+    def __iter__(self): return iter((self.x, self.y, self.z))
+    def __eq__(self, o): return isinstance(o, vec3) and (self.x, self.y, self.z) == (o.x, o.y, o.z)
+    def __repr__(self): return "[%g,%g,%g]" % (self.x, self.y, self.z)
+    def max(self): return max(self.x, self.y, self.z)
+    def min(self): return min(self.x, self.y, self.z)
+
+
+Vec3 = vec3
+
+
+def _v3(v):
+    return v if isinstance(v, vec3) else vec3(v)
+
+
+def _checkArgs(fn, kwargs, allowed):
+    """PbArgs::check (pconvert.cpp:460-474): unknown keyword arguments are an error; `notiming` is implicit."""
+    for k in kwargs:
+        if k not in allowed and k != "notiming":
+            raise MantaError("Argument '%s' unknown" % k)
+
+
+class _Timing(object):
+    """TimingData (source/timing.cpp:23-112): wall-clock per plugin, the stream is synchronised before stop()."""
+    def __init__(self):
+        self.data = {}
+        self.enabled = False
+
+    def add(self, name, ms):
+        self.data.setdefault(name, []).append(ms)
+
+
+_timing = _Timing()
+
+
+class Timings(object):
+    def __init__(self):
+        _timing.enabled = True
+
+    def display(self):
+        total = 0.0
+        for name, v in _timing.data.items():
+            ms = sum(v)
+            total += ms
+            print("[%8.2f ms] %s (%d calls)" % (ms, name, len(v)))
+        print("Total : %.2f ms" % total)
+        _timing.data.clear()
+
+    def step(self):
+        pass
+
+
+def _plugin(fn):
+    def wrapper(*args, **kwargs):
+        if _timing.enabled and not kwargs.get("notiming", False):
+            solver = None
+            for a in list(args) + list(kwargs.values()):
+                if isinstance(a, GridBase):
+                    solver = a.parent
+                    break
+            t0 = _time.perf_counter()
+            kwargs.pop("notiming", None)
+            r = fn(*args, **kwargs)
+            if solver is not None:
+                solver.sync()
+            _timing.add(fn.__name__, (_time.perf_counter() - t0) * 1e3)
+            return r
+        kwargs.pop("notiming", None)
+        return fn(*args, **kwargs)
+    wrapper.__name__ = fn.__name__
+    wrapper.__doc__ = fn.__doc__
+    return wrapper
+
+
+# ---- FluidSolver -----------------------------------------------------------------------------------------
+class FluidSolver(object):
+    """FluidSolver / Solver (source/fluidsolver.h:26-119, fluidsolver.cpp:107-166)."""
+
+    def __init__(self, name="solver", gridSize=None, dim=3, device=0, **kwargs):
+        _checkArgs("Solver", kwargs, ())
+        if gridSize is None:
+            raise MantaError("Argument 'gridSize' is not defined.")
+        gs = _v3(gridSize)
+        self.name = name
+        nx, ny, nz = int(gs.x), int(gs.y), int(gs.z)
+        if dim not in (2, 3):
+            raise MantaError("Only 2D and 3D solvers allowed.")
+        if dim == 2 and nz != 1:
+            raise MantaError("Trying to create 2D solver with size.z != 1")
+        self._size = (nx, ny, nz)
+        self._dim = dim
+        self._h = lib().mf_solver_create(nx, ny, nz, dim, device)
+        if not self._h:
+            raise MantaError(lib().mf_last_error().decode())
+        self._dt = np.float32(1.0)
+        self.timeTotal = np.float32(0.0)
+        self.frame = 0
+        self._count = 0
+        self.cfl = np.float32(1000)
+        self.timestepMin = np.float32(1.0)
+        self.timestepMax = np.float32(1.0)
+        self.frameLength = np.float32(1.0)
+        self.timePerFrame = np.float32(0.0)
+        self._lockDt = False
+
+    @property
+    def timestep(self):
+        return self._dt
+
+    @timestep.setter
+    def timestep(self, v):
+        self._dt = np.float32(v)
+        check(lib().mf_solver_set_dt(self._h, float(self._dt)))
+
+    def getGridSize(self): return vec3(*self._size)
+    def is2D(self): return self._dim == 2
+    def is3D(self): return self._dim == 3
+    def getDx(self): return np.float32(1.0 / max(self._size))
+
+    def create(self, type=None, name="", **kwargs):
+        if type is None:
+            raise MantaError("Need to specify object type. Use e.g. Solver.create(FlagGrid, ...) or Solver.create(type=FlagGrid, ...)")
+        return type(self, name=name, **kwargs)
+
+    def step(self, frame=-1):
+        """fluidsolver.cpp:143-166"""
+        eps = np.float32(1e-6)
+        self.timePerFrame = np.float32(self.timePerFrame + self._dt)
+        self.timeTotal = np.float32(self.timeTotal + self._dt)
+        self._count += 1
+        if (self.timePerFrame + eps) > self.frameLength:
+            self.frame += 1
+            self.timeTotal = np.float32(float(self.frame) * float(self.frameLength))
+            self.timePerFrame = np.float32(0.0)
+            self._lockDt = False
+        if frame >= 0:
+            self.frame = frame
+
+    def adaptTimestep(self, maxVel):
+        """fluidsolver.cpp:184-205"""
+        f = np.float32
+        mvt = f(maxVel) * self._dt
+        if not self._lockDt:
+            dt = max(min(self._dt * f(float(self.cfl) / (float(mvt) + 1e-05)), self.timestepMax), self.timestepMin)
+            if (float(self.timePerFrame) + float(dt) * 1.05) > float(self.frameLength):
+                dt = f(float(self.frameLength - self.timePerFrame) + 1e-04)
+            elif (self.timePerFrame + dt + self.timestepMin) > self.frameLength or (float(self.timePerFrame) + float(dt) * 1.25) > float(self.frameLength):
+                dt = f((float(self.frameLength - self.timePerFrame) + 1e-04) * 0.5)
+                self._lockDt = True
+            self.timestep = dt
+        if not (self._dt > self.timestepMin / 2.0):
+            raise MantaError("Invalid dt encountered! Shouldnt happen...")
+
+    def sync(self):
+        check(lib().mf_solver_sync(self._h))
+
+    def launchCount(self):
+        return int(lib().mf_solver_launch_count(self._h))
+
+    def printMemInfo(self):
+        print("Device temp-grid pool: %d bytes" % lib().mf_solver_pool_bytes(self._h))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                lib().mf_solver_destroy(h)
+            except Exception:
+                pass
+
+
+Solver = FluidSolver
+
+
+# ---- grids -----------------------------------------------------------------------------------------------
+class GridBase(object):
+    _type = 0
+    _dtype = np.float32
+    _ncomp = 1
+
+    def __init__(self, parent, show=True, name="", **kwargs):
+        _checkArgs("Grid", kwargs, ())
+        if not isinstance(parent, FluidSolver):
+            raise MantaError("Grid: need a Solver as parent")
+        self.parent = parent
+        self._name = name
+        self._h = lib().mf_grid_create(parent._h, self._type)
+        if not self._h:
+            raise MantaError(lib().mf_last_error().decode())
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and getattr(self.parent, "_h", None):
+            try:
+                lib().mf_grid_destroy(h)
+            except Exception:
+                pass
+
+    # --- reference Python methods (source/grid.h:27-247) ---
+    def get_name(self): return self._name
+    def set_name(self, s): self._name = s
+    def getSizeX(self): return self.parent._size[0]
+    def getSizeY(self): return self.parent._size[1]
+    def getSizeZ(self): return self.parent._size[2]
+    def getSize(self): return vec3(*self.parent._size)
+    def is3D(self): return self.parent.is3D()
+    def is4D(self): return False
+    def getGridType(self): return self._type
+    def getParent(self): return self.parent
+
+    def clear(self): check(lib().mf_grid_clear(self._h))
+
+    def copyFrom(self, a, copyType=True):
+        check(lib().mf_grid_copy(self._h, a._h))
+        return self
+
+    def swap(self, other): check(lib().mf_grid_swap(self._h, other._h))
+
+    def getMaxAbs(self):
+        out = C.c_float()
+        check(lib().mf_grid_max_abs(self._h, C.byref(out)))
+        return out.value
+
+    def getMax(self):
+        mn, mx = C.c_float(), C.c_float()
+        check(lib().mf_grid_min_max(self._h, C.byref(mn), C.byref(mx)))
+        return mx.value
+
+    def getMin(self):
+        mn, mx = C.c_float(), C.c_float()
+        check(lib().mf_grid_min_max(self._h, C.byref(mn), C.byref(mx)))
+        return mn.value
+
+    # --- host <-> device (reference layout: x fastest; Vec3 = 3 packed floats) ---
+    def _shape(self):
+        nx, ny, nz = self.parent._size
+        return (nz, ny, nx) if self._ncomp == 1 else (nz, ny, nx, 3)
+
+    def to_numpy(self):
+        a = np.empty(self._shape(), dtype=self._dtype)
+        check(lib().mf_grid_download(self._h, a.ctypes.data_as(C.c_void_p)))
+        return a
+
+    def from_numpy(self, a):
+        a = np.ascontiguousarray(a, dtype=self._dtype)
+        if a.shape != self._shape():
+            a = a.reshape(self._shape())
+        check(lib().mf_grid_upload(self._h, a.ctypes.data_as(C.c_void_p)))
+        return self
+
+    def get(self, i, j, k):
+        v = self.to_numpy()[k, j, i]
+        return vec3(v) if self._ncomp == 3 else v.item()
+
+    # --- file I/O on the host mirror (source/grid.cpp:136-179, fileio/iogrids.cpp:255-300,386-513) ---
+    def save(self, name):
+        a = self.to_numpy()
+        if name.endswith(".raw"):
+            with gzip.open(name, "wb", compresslevel=1) as f:
+                f.write(a.tobytes())
+        elif name.endswith(".uni"):
+            nx, ny, nz = self.parent._size
+            et = 0 if self._dtype == np.int32 else (2 if self._ncomp == 3 else 1)
+            info = lib().mf_build_info()[:251]
+            head = struct.pack("<iiiiii252sQ", nx, ny, nz, self._type, et, a.itemsize * self._ncomp,
+                               info, int(_time.time()))
+            with gzip.open(name, "wb", compresslevel=1) as f:
+                f.write(b"MNT3")
+                f.write(head)
+                f.write(a.tobytes())
+        elif name.endswith(".npy"):
+            np.save(name, a)
+        else:
+            raise MantaError("file '%s' filetype not supported" % name)
+        return 1
+
+    def load(self, name):
+        if name.endswith(".raw"):
+            with gzip.open(name, "rb") as f:
+                a = np.frombuffer(f.read(), dtype=self._dtype)
+        elif name.endswith(".uni"):
+            with gzip.open(name, "rb") as f:
+                ident = f.read(4)
+                if ident != b"MNT3":
+                    raise MantaError("readGridUni: Unknown header '%s' " % ident.decode("ascii", "replace"))
+                nx, ny, nz, gt, et, bpe = struct.unpack("<iiiiii", f.read(24))
+                f.read(252 + 8)
+                if (nx, ny, nz) != self.parent._size:
+                    raise MantaError("grid dim doesn't match, [%d,%d,%d] vs %s" % (nx, ny, nz, self.getSize()))
+                a = np.frombuffer(f.read(), dtype=self._dtype)
+        elif name.endswith(".npy"):
+            a = np.load(name)
+        else:
+            raise MantaError("file '%s' filetype not supported" % name)
+        self.from_numpy(a.reshape(self._shape()))
+        return 1
+
+
+class RealGrid(GridBase):
+    _type = _TYPE_REAL
+
+    def setConst(self, s): check(lib().mf_grid_set_const_real(self._h, float(s)))
+    def addScaled(self, a, factor): check(lib().mf_grid_add_scaled(self._h, a._h, float(factor), 0.0, 0.0))
+    def add(self, a): check(lib().mf_grid_add_scaled(self._h, a._h, 1.0, 0.0, 0.0))
+    def sub(self, a): check(lib().mf_grid_add_scaled(self._h, a._h, -1.0, 0.0, 0.0))
+    def multConst(self, s): check(lib().mf_grid_mult_const(self._h, float(s), 0.0, 0.0))
+
+
+class LevelsetGrid(RealGrid):
+    _type = _TYPE_REAL | _TYPE_LEVELSET
+
+
+class IntGrid(GridBase):
+    _type = _TYPE_INT
+    _dtype = np.int32
+
+    def setConst(self, s): check(lib().mf_grid_set_const_int(self._h, int(s)))
+
+
+class VecGrid(GridBase):
+    _type = _TYPE_VEC3
+    _ncomp = 3
+
+    def setConst(self, s):
+        s = _v3(s)
+        check(lib().mf_grid_set_const_vec3(self._h, float(s.x), float(s.y), float(s.z)))
+
+    def addScaled(self, a, factor):
+        f = _v3(factor)
+        check(lib().mf_grid_add_scaled(self._h, a._h, float(f.x), float(f.y), float(f.z)))
+
+    def multConst(self, s):
+        f = _v3(s)
+        check(lib().mf_grid_mult_const(self._h, float(f.x), float(f.y), float(f.z)))
+
+
+Vec3Grid = VecGrid
+
+
+class MACGrid(VecGrid):
+    _type = _TYPE_MAC | _TYPE_VEC3
+
+
+class FlagGrid(IntGrid):
+    _type = _TYPE_FLAGS | _TYPE_INT
+
+    def __init__(self, parent, dim=3, show=True, name="", **kwargs):
+        IntGrid.__init__(self, parent, show=show, name=name, **kwargs)
+
+    def initDomain(self, boundaryWidth=0, wall="xXyYzZ", open="      ", inflow="      ", outflow="      ", phiWalls=None):
+        """FlagGrid::initDomain (source/grid.cpp:798-888)"""
+        check(lib().mf_flags_init_domain(self._h, int(boundaryWidth), wall.encode(), open.encode(), inflow.encode(),
+                                         outflow.encode(), phiWalls._h if phiWalls is not None else None))
+
+    def fillGrid(self, type=TypeFluid):
+        check(lib().mf_flags_fill_grid(self._h, int(type)))
+
+    def countCells(self, flag, bnd=0, mask=None):
+        out = C.c_int()
+        check(lib().mf_flags_count_cells(self._h, int(flag), int(bnd), C.byref(out)))
+        return out.value
+
+
+# ---- shapes used by the config scenes (source/shapes.cpp) -------------------------------------------------
+class Shape(object):
+    def __init__(self, parent):
+        self.parent = parent
+
+
+class Box(Shape):
+    def __init__(self, parent, center=None, p0=None, p1=None, size=None, **kwargs):
+        _checkArgs("Box", kwargs, ())
+        Shape.__init__(self, parent)
+        if center is not None and size is not None:
+            self.p0, self.p1 = _v3(center) - _v3(size), _v3(center) + _v3(size)
+        elif p0 is not None and p1 is not None:
+            self.p0, self.p1 = _v3(p0), _v3(p1)
+        else:
+            raise MantaError("Box: specify either p0,p1 or size,center")
+
+    def applyToGrid(self, grid, value=0, respectFlags=None):
+        a, b = self.p0, self.p1
+        if isinstance(grid, IntGrid):
+            check(lib().mf_apply_box_to_flags(grid._h, float(a.x), float(a.y), float(a.z), float(b.x), float(b.y), float(b.z), int(value)))
+        elif isinstance(grid, RealGrid):
+            check(lib().mf_apply_box_to_real(grid._h, float(a.x), float(a.y), float(a.z), float(b.x), float(b.y), float(b.z), float(value)))
+        else:
+            raise MantaError("Shape::applyToGrid(): unknown grid type")
+
+
+class Cylinder(Shape):
+    def __init__(self, parent, center=None, radius=None, z=None, **kwargs):
+        _checkArgs("Cylinder", kwargs, ())
+        Shape.__init__(self, parent)
+        self.center, self.radius, self.z = _v3(center), np.float32(radius), _v3(z)
+
+    def applyToGrid(self, grid, value=0, respectFlags=None):
+        if not isinstance(grid, RealGrid):
+            raise MantaError("Shape::applyToGrid(): unknown grid type")
+        c, z = self.center, self.z
+        check(lib().mf_apply_cylinder_to_real(grid._h, float(c.x), float(c.y), float(c.z), float(self.radius),
+                                              float(z.x), float(z.y), float(z.z), float(value)))
+
+
+from .plugins import *  # noqa: E402,F401,F403  (plugin functions of the hot path)

@@ -1,0 +1,207 @@
+"""PYTHON() plugin functions of the hot path, with the reference's keyword names and defaults.
+
+advectSemiLagrange  source/plugin/advection.cpp:443
+setWallBcs / addBuoyancy / addGravity / setInflowBcs / setOpenBound / resetOutflow  source/plugin/extforces.cpp
+computePressureRhs / solvePressureSystem / correctVelocity / solvePressure / releaseMG  source/plugin/pressure.cpp
+cgSolveDiffusion  source/conjugategrad.cpp:350
+gridMaxDiff / gridMaxDiffInt / gridMaxDiffVec3  source/grid.cpp:437-467
+"""
+import ctypes as C
+
+from . import manta as M
+from ._lib import lib, check, MantaError, PressureParams, SolveInfo
+
+__all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "addGravityNoScale", "setInflowBcs",
+           "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
+           "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
+           "getSolveInfo"]
+
+
+def _h(g):
+    return g._h if g is not None else None
+
+
+def _req(g, cls, name, fn):
+    if g is None:
+        raise MantaError("Argument '%s' is not defined." % name)
+    if not isinstance(g, cls):
+        raise MantaError("%s: can't convert argument '%s' to type '%s'" % (fn, name, cls.__name__))
+    return g
+
+
+@M._plugin
+def advectSemiLagrange(flags=None, vel=None, grid=None, order=1, strength=1.0, orderSpace=1, openBounds=False,
+                       boundaryWidth=-1, clampMode=2, orderTrace=1, **kwargs):
+    M._checkArgs("advectSemiLagrange", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "advectSemiLagrange")
+    _req(vel, M.MACGrid, "vel", "advectSemiLagrange")
+    _req(grid, M.GridBase, "grid", "advectSemiLagrange")
+    if boundaryWidth != -1 or openBounds:
+        M.mantaMsg("Warning: boundaryWidth and openBounds parameters in AdvectSemiLagrange plugin are deprecated "
+                   "(and have no more effect), please remove.", 0)
+    if isinstance(grid, M.MACGrid) and orderSpace != 1:
+        M.mantaMsg("Warning higher order for MAC grids not yet implemented...", 1)
+    check(lib().mf_advect_semi_lagrange(flags._h, vel._h, grid._h, int(order), float(strength), int(orderSpace),
+                                        int(clampMode), int(orderTrace)))
+
+
+@M._plugin
+def setWallBcs(flags=None, vel=None, obvel=None, fractions=None, phiObs=None, boundaryWidth=0, **kwargs):
+    M._checkArgs("setWallBcs", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "setWallBcs")
+    _req(vel, M.MACGrid, "vel", "setWallBcs")
+    check(lib().mf_set_wall_bcs(flags._h, vel._h, _h(obvel), _h(fractions), _h(phiObs), int(boundaryWidth)))
+
+
+@M._plugin
+def addBuoyancy(flags=None, density=None, vel=None, gravity=None, coefficient=1.0, scale=True, **kwargs):
+    M._checkArgs("addBuoyancy", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "addBuoyancy")
+    _req(density, M.RealGrid, "density", "addBuoyancy")
+    _req(vel, M.MACGrid, "vel", "addBuoyancy")
+    if gravity is None:
+        raise MantaError("Argument 'gravity' is not defined.")
+    g = M._v3(gravity)
+    check(lib().mf_add_buoyancy(flags._h, density._h, vel._h, float(g.x), float(g.y), float(g.z), float(coefficient), int(bool(scale))))
+
+
+@M._plugin
+def addGravity(flags=None, vel=None, gravity=None, exclude=None, scale=True, **kwargs):
+    M._checkArgs("addGravity", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "addGravity")
+    _req(vel, M.MACGrid, "vel", "addGravity")
+    if gravity is None:
+        raise MantaError("Argument 'gravity' is not defined.")
+    g = M._v3(gravity)
+    check(lib().mf_add_gravity(flags._h, vel._h, float(g.x), float(g.y), float(g.z), _h(exclude), int(bool(scale))))
+
+
+def addGravityNoScale(flags=None, vel=None, gravity=None, exclude=None, **kwargs):
+    addGravity(flags=flags, vel=vel, gravity=gravity, exclude=exclude, scale=False, **kwargs)
+
+
+@M._plugin
+def setInflowBcs(vel=None, dir="", value=None, **kwargs):
+    M._checkArgs("setInflowBcs", kwargs, ())
+    _req(vel, M.MACGrid, "vel", "setInflowBcs")
+    v = M._v3(value)
+    check(lib().mf_set_inflow_bcs(vel._h, dir.encode(), float(v.x), float(v.y), float(v.z)))
+
+
+@M._plugin
+def setOpenBound(flags=None, bWidth=None, openBound="", type=M.FlagOutflow | M.FlagEmpty, **kwargs):
+    M._checkArgs("setOpenBound", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "setOpenBound")
+    check(lib().mf_flags_set_open_bound(flags._h, int(bWidth), openBound.encode(), int(type)))
+
+
+@M._plugin
+def resetOutflow(flags=None, phi=None, parts=None, real=None, index=None, indexSys=None, **kwargs):
+    M._checkArgs("resetOutflow", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "resetOutflow")
+    if parts is not None:
+        raise MantaError("resetOutflow: particle systems are not part of the device grid path")
+    check(lib().mf_reset_outflow(flags._h, _h(phi), _h(real)))
+
+
+_PRESSURE_KW = ("cgAccuracy", "phi", "perCellCorr", "fractions", "obvel", "gfClamp", "cgMaxIterFac", "precondition",
+                "preconditioner", "enforceCompatibility", "useL2Norm", "zeroPressureFixing", "curv", "surfTens", "retRhs")
+
+
+def _params(fn, kw, allowObvel=True, allowRetRhs=False):
+    p = PressureParams()
+    lib().mf_pressure_params_default(C.byref(p))
+    keep = []
+    for k, v in kw.items():
+        if k not in _PRESSURE_KW or (k == "obvel" and not allowObvel) or (k == "retRhs" and not allowRetRhs):
+            raise MantaError("Argument '%s' unknown" % k)
+        if k in ("phi", "perCellCorr", "curv", "retRhs"):
+            if v is not None:
+                _req(v, M.RealGrid, k, fn); keep.append(v)
+            setattr(p, k, _h(v))
+        elif k in ("fractions", "obvel"):
+            if v is not None:
+                _req(v, M.MACGrid, k, fn); keep.append(v)
+            setattr(p, k, _h(v))
+        elif k in ("precondition", "enforceCompatibility", "useL2Norm", "zeroPressureFixing"):
+            setattr(p, k, int(bool(v)))
+        elif k == "preconditioner":
+            p.preconditioner = int(v)
+        else:
+            setattr(p, k, float(v))
+    pc = p.preconditioner if p.precondition else M.PcNone
+    if pc == M.PcNone and not M.allowPcNone and fn in ("solvePressure", "solvePressureSystem"):
+        # setICPreconditioner(PC_None, ...) asserts in the reference (conjugategrad.cpp:312, reached from pressure.cpp:417)
+        raise MantaError("GridCg<APPLYMAT>::setICPreconditioner: Invalid method specified.")
+    return p, keep
+
+
+def _publish(info):
+    M.lastSolveInfo = dict(iterations=info.iterations, resNorm=info.resNorm, maxIter=info.maxIter,
+                           fixedCell=info.fixedCell, mgLevels=info.mgLevels, mgRebuilt=info.mgRebuilt)
+    M.mantaMsg("FluidSolver::solvePressure done. Iterations:%d, residual:%g" % (info.iterations, info.resNorm), 2)
+
+
+def getSolveInfo():
+    """Iterations / residual of the last pressure solve (the reference prints them at debug level 2, pressure.cpp:442)."""
+    return M.lastSolveInfo
+
+
+@M._plugin
+def computePressureRhs(rhs=None, vel=None, pressure=None, flags=None, **kwargs):
+    _req(rhs, M.RealGrid, "rhs", "computePressureRhs"); _req(vel, M.MACGrid, "vel", "computePressureRhs")
+    _req(pressure, M.RealGrid, "pressure", "computePressureRhs"); _req(flags, M.FlagGrid, "flags", "computePressureRhs")
+    p, keep = _params("computePressureRhs", kwargs)
+    check(lib().mf_compute_pressure_rhs(rhs._h, vel._h, pressure._h, flags._h, C.byref(p)))
+
+
+@M._plugin
+def solvePressureSystem(rhs=None, vel=None, pressure=None, flags=None, **kwargs):
+    _req(rhs, M.RealGrid, "rhs", "solvePressureSystem"); _req(vel, M.MACGrid, "vel", "solvePressureSystem")
+    _req(pressure, M.RealGrid, "pressure", "solvePressureSystem"); _req(flags, M.FlagGrid, "flags", "solvePressureSystem")
+    p, keep = _params("solvePressureSystem", kwargs, allowObvel=False)
+    info = SolveInfo()
+    check(lib().mf_solve_pressure_system(rhs._h, vel._h, pressure._h, flags._h, C.byref(p), C.byref(info)))
+    _publish(info)
+
+
+@M._plugin
+def correctVelocity(vel=None, pressure=None, flags=None, **kwargs):
+    _req(vel, M.MACGrid, "vel", "correctVelocity"); _req(pressure, M.RealGrid, "pressure", "correctVelocity")
+    _req(flags, M.FlagGrid, "flags", "correctVelocity")
+    p, keep = _params("correctVelocity", kwargs, allowObvel=False)
+    check(lib().mf_correct_velocity(vel._h, pressure._h, flags._h, C.byref(p)))
+
+
+@M._plugin
+def solvePressure(vel=None, pressure=None, flags=None, **kwargs):
+    _req(vel, M.MACGrid, "vel", "solvePressure"); _req(pressure, M.RealGrid, "pressure", "solvePressure")
+    _req(flags, M.FlagGrid, "flags", "solvePressure")
+    p, keep = _params("solvePressure", kwargs, allowRetRhs=True)
+    info = SolveInfo()
+    check(lib().mf_solve_pressure(vel._h, pressure._h, flags._h, C.byref(p), C.byref(info)))
+    _publish(info)
+
+
+def releaseMG(solver=None, **kwargs):
+    M._checkArgs("releaseMG", kwargs, ())
+    if solver is not None:
+        check(lib().mf_release_mg(solver._h))
+
+
+@M._plugin
+def cgSolveDiffusion(flags=None, grid=None, alpha=0.25, cgMaxIterFac=1.0, cgAccuracy=1e-4, **kwargs):
+    M._checkArgs("cgSolveDiffusion", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "cgSolveDiffusion"); _req(grid, M.GridBase, "grid", "cgSolveDiffusion")
+    check(lib().mf_cg_solve_diffusion(flags._h, grid._h, float(alpha), float(cgMaxIterFac), float(cgAccuracy)))
+
+
+def _maxDiff(g1, g2):
+    out = C.c_double()
+    check(lib().mf_grid_max_diff(g1._h, g2._h, C.byref(out)))
+    return out.value
+
+
+def gridMaxDiff(g1, g2): return _maxDiff(g1, g2)
+def gridMaxDiffInt(g1, g2): return _maxDiff(g1, g2)
+def gridMaxDiffVec3(g1, g2): return _maxDiff(g1, g2)

@@ -1,0 +1,94 @@
+"""Runs one test 'case' (a small scene described as data) against a manta-style API.
+
+The SAME case description is executed
+  * by the unmodified reference (`oracle/_ref/manta tests/golden/ref_driver.py`, in generate mode), and
+  * by mantaflow_b200.manta on the GPU (tests/test_*_gpu.py),
+so the parity tests are literally the same scene calls on identical inputs.
+
+case = {
+  "size": [nx, ny, nz], "dim": 3, "dt": 1.0,
+  "grids": {"flags": "FlagGrid", "vel": "MACGrid", ...},
+  "load":  ["vel", "density"],          # grids whose initial content comes from inputs (in_<name>)
+  "ops":   [["call", "advectSemiLagrange", {"flags": "@flags", "vel": "@vel", "grid": "@density", "order": 2}],
+            ["method", "flags", "initDomain", {"boundaryWidth": 0}],
+            ["repeat", 5, [ ...ops... ]]],
+  "save":  ["density", "vel"],
+}
+Values: "@name" -> grid object, ["vec3", x, y, z] -> vec3, everything else literal.
+"""
+import gzip
+import os
+
+# numpy is imported lazily: the reference's embedded interpreter may not have it
+DTYPES = {"FlagGrid": "int32", "IntGrid": "int32"}
+NCOMP = {"MACGrid": 3, "VecGrid": 3, "Vec3Grid": 3}
+
+
+def grid_shape(case, gtype):
+    nx, ny, nz = case["size"]
+    return (nz, ny, nx, 3) if NCOMP.get(gtype, 1) == 3 else (nz, ny, nx)
+
+
+def write_raw(path, arr):
+    import numpy as np
+    with gzip.open(path, "wb", compresslevel=1) as f:
+        f.write(np.ascontiguousarray(arr).tobytes())
+
+
+def read_raw(path, dtype, shape):
+    import numpy as np
+    with gzip.open(path, "rb") as f:
+        return np.frombuffer(f.read(), dtype=dtype).reshape(shape).copy()
+
+
+def _resolve(v, grids, api):
+    if isinstance(v, str) and v.startswith("@"):
+        return grids[v[1:]]
+    if isinstance(v, list) and len(v) == 4 and v[0] == "vec3":
+        return api["vec3"](v[1], v[2], v[3])
+    if isinstance(v, str) and v.startswith("$"):
+        return api[v[1:]]          # module constant, e.g. "$PcMGStatic"
+    return v
+
+
+def _run_ops(ops, grids, api, solver, log):
+    for op in ops:
+        kind = op[0]
+        if kind == "call":
+            kw = {k: _resolve(v, grids, api) for k, v in op[2].items()}
+            api[op[1]](**kw)
+        elif kind == "method":
+            obj = solver if op[1] == "solver" else grids[op[1]]
+            kw = {k: _resolve(v, grids, api) for k, v in op[3].items()}
+            r = getattr(obj, op[2])(**kw)
+            if r is not None:
+                log.append([op[1], op[2], float(r) if not isinstance(r, (str, bytes)) else r])
+        elif kind == "shape":   # ["shape", "Box", {ctor kwargs}, "applyToGrid", {"grid": "@flags", "value": 2}]
+            ckw = {k: _resolve(v, grids, api) for k, v in op[2].items()}
+            shp = api[op[1]](parent=solver, **ckw)
+            kw = {k: _resolve(v, grids, api) for k, v in op[4].items()}
+            getattr(shp, op[3])(**kw)
+        elif kind == "repeat":
+            for _ in range(op[1]):
+                _run_ops(op[2], grids, api, solver, log)
+                solver.step()
+        else:
+            raise ValueError("unknown op kind %r" % (kind,))
+
+
+def run_case(case, api, loader, saver):
+    """loader(name, grid, gtype) fills a grid from the case inputs; saver(name, grid, gtype) collects an output."""
+    nx, ny, nz = case["size"]
+    s = api["Solver"](name="main", gridSize=api["vec3"](nx, ny, nz), dim=case.get("dim", 3))
+    s.timestep = case.get("dt", 1.0)
+    grids = {}
+    for name, gtype in case["grids"].items():
+        grids[name] = s.create(api[gtype])
+    for name in case.get("load", []):
+        loader(name, grids[name], case["grids"][name])
+    log = []
+    _run_ops(case["ops"], grids, api, s, log)
+    out = {}
+    for name in case.get("save", []):
+        out[name] = saver(name, grids[name], case["grids"][name])
+    return out, log
