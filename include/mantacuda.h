@@ -49,6 +49,17 @@ int          mf_solver_sync(mf_solver* s);                /* cudaStreamSynchroni
 void*        mf_solver_stream(mf_solver* s);              /* cudaStream_t, for CUDA-event timing by the caller */
 long long    mf_solver_launch_count(const mf_solver* s);  /* kernels launched so far by this library for s */
 long long    mf_solver_pool_bytes(const mf_solver* s);    /* device bytes currently held by the temp-grid pool */
+/* Per-kernel device timing, the role of the reference's TimingData / MG_TIMINGS (source/timing.cpp:23-112,
+ * multigrid.cpp:39-40): between _begin and _end every kernel launch is bracketed by a CUDA-event pair on the solver
+ * stream; _end synchronises and writes "kernel launches total_ms\n" lines (sorted by time) into buf. */
+int          mf_solver_profile_begin(mf_solver* s);
+int          mf_solver_profile_end(mf_solver* s, char* buf, int buflen);
+/* CUDA-event stopwatch on the solver stream, slots 0..15 (cf. MuTime, source/general.cpp:51-66) */
+int          mf_solver_event_record(mf_solver* s, int slot);
+int          mf_solver_event_elapsed_ms(mf_solver* s, int from_slot, int to_slot, float* ms);
+/* page-locked host buffers for upload/download (cudaMallocHost); plain malloc'ed memory works too, only slower */
+void*        mf_host_alloc(long long bytes);
+void         mf_host_free(void* p);
 
 /* ---- Grid<T> / MACGrid / FlagGrid (source/grid.h:99,255,298; grid.cpp:49,95,100,228) - */
 mf_grid*     mf_grid_create(mf_solver* s, int type);      /* type = OR of MF_TYPE_*; zero-filled */

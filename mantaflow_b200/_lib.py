@@ -46,6 +46,12 @@ SIGNATURES = {
     "mf_solver_stream": (_P, [_P]),
     "mf_solver_launch_count": (C.c_longlong, [_P]),
     "mf_solver_pool_bytes": (C.c_longlong, [_P]),
+    "mf_solver_profile_begin": (_i, [_P]),
+    "mf_solver_profile_end": (_i, [_P, C.c_char_p, _i]),
+    "mf_solver_event_record": (_i, [_P, _i]),
+    "mf_solver_event_elapsed_ms": (_i, [_P, _i, _i, C.POINTER(_f)]),
+    "mf_host_alloc": (_P, [C.c_longlong]),
+    "mf_host_free": (None, [_P]),
     "mf_grid_create": (_P, [_P, _i]),
     "mf_grid_destroy": (None, [_P]),
     "mf_grid_type": (_i, [_P]),

@@ -74,6 +74,13 @@ struct Solver {
   float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
   int numSMs;
+  // per-kernel CUDA-event timing (mf_solver_profile_*): one event pair per launch while enabled
+  bool profiling;
+  struct ProfRec { const char* name; cudaEvent_t a, b; };
+  std::vector<ProfRec> profRecs;
+  std::vector<cudaEvent_t> evPool;
+  cudaEvent_t profEvent();
+  cudaEvent_t userEvents[16];
 
   float* getReal();           // un-cleared scratch of N floats
   void   putReal(float* p);
@@ -116,7 +123,16 @@ void release_mg(Solver* s);   // drop the cached multigrid hierarchy (pressure.c
 
 // launch helpers -----------------------------------------------------------------------
 inline unsigned int cdiv(long long a, long long b) { return (unsigned int)((a + b - 1) / b); }
-#define MF_LAUNCH(s, kern, grid, block, ...) do { kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
+struct ProfScope {   // brackets one launch with events on the solver stream when profiling is on
+  Solver* s; cudaEvent_t b;
+  ProfScope(Solver* s_, const char* name) : s(s_), b(nullptr) {
+    if (!s->profiling) return;
+    Solver::ProfRec r; r.name = name; r.a = s->profEvent(); r.b = s->profEvent(); b = r.b;
+    cudaEventRecord(r.a, s->stream); s->profRecs.push_back(r);
+  }
+  ~ProfScope() { if (b) cudaEventRecord(b, s->stream); }
+};
+#define MF_LAUNCH(s, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
 #define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())
 
 // reductions (reduce.cu)

@@ -4,6 +4,7 @@
 #include "reduce.cuh"
 #include <cstring>
 #include <cmath>
+#include <algorithm>
 
 namespace mf { struct Grid; struct Solver; }
 void launch_norm_square(mf::Solver* s, const mf::Grid* g, float* o);
@@ -35,6 +36,10 @@ float* Solver::getVec() {
   return p;
 }
 void Solver::putVec(float* p) { poolVec.push_back(p); }
+cudaEvent_t Solver::profEvent() {
+  if (!evPool.empty()) { cudaEvent_t e = evPool.back(); evPool.pop_back(); return e; }
+  cudaEvent_t e; CUDA_CHECK(cudaEventCreate(&e)); return e;
+}
 
 void fetchRed(Solver* s, int count) {
   CUDA_CHECK(cudaMemcpyAsync(s->redHost, s->redOut, sizeof(double) * count, cudaMemcpyDeviceToHost, s->stream));
@@ -196,7 +201,8 @@ mf_solver* mf_solver_create(int nx, int ny, int nz, int dim, int device) {
     int mx = nx > ny ? nx : ny; if (nz > mx) mx = nz;
     s->dx = (float)(1.0 / mx);       // grid.cpp:57
     s->device = device;
-    s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr;
+    s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->profiling = false;
+    for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
     CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
     s->numSMs = prop.multiProcessorCount;
@@ -225,6 +231,9 @@ void mf_solver_destroy(mf_solver* sp) {
   cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);
   cudaFree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
   if (s->aosStage) cudaFree(s->aosStage);
+  for (auto& r : s->profRecs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (cudaEvent_t e : s->evPool) cudaEventDestroy(e);
+  for (int q = 0; q < 16; q++) if (s->userEvents[q]) cudaEventDestroy(s->userEvents[q]);
   cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -235,6 +244,71 @@ int mf_solver_sync(mf_solver* s) { MF_API_BEGIN mfAssert(s, "null solver"); S(s)
 void* mf_solver_stream(mf_solver* s) { return s ? (void*)S(s)->stream : nullptr; }
 long long mf_solver_launch_count(const mf_solver* s) { return s ? S(s)->launches : 0; }
 long long mf_solver_pool_bytes(const mf_solver* s) { return s ? S(s)->poolBytes : 0; }
+
+int mf_solver_profile_begin(mf_solver* sp) {
+  MF_API_BEGIN
+  mfAssert(sp, "null solver");
+  Solver* s = S(sp); s->use();
+  for (auto& r : s->profRecs) { s->evPool.push_back(r.a); s->evPool.push_back(r.b); }
+  s->profRecs.clear();
+  s->profiling = true;
+  MF_API_END
+}
+// stops recording and writes one line per kernel, "name launches total_ms\n", sorted by total time
+int mf_solver_profile_end(mf_solver* sp, char* buf, int buflen) {
+  MF_API_BEGIN
+  mfAssert(sp && buf && buflen > 0, "mf_solver_profile_end: null argument");
+  Solver* s = S(sp); s->use();
+  s->profiling = false;
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto& r : s->profRecs) {
+    float ms = 0.f; CUDA_CHECK(cudaEventElapsedTime(&ms, r.a, r.b));
+    std::string n(r.name);
+    // "(k_sl<NC, OS, OT>)" -> "k_sl"
+    size_t b0 = n.find_first_not_of("( "); if (b0 == std::string::npos) b0 = 0;
+    size_t e0 = n.find_first_of("<)", b0); n = n.substr(b0, e0 == std::string::npos ? std::string::npos : e0 - b0);
+    if (n.compare(0, 4, "mf::") == 0) n = n.substr(4);
+    auto& a = agg[n]; a.first++; a.second += ms;
+    s->evPool.push_back(r.a); s->evPool.push_back(r.b);
+  }
+  s->profRecs.clear();
+  std::vector<std::pair<double, std::string>> order;
+  for (auto& kv : agg) order.push_back({ -kv.second.second, kv.first });
+  std::sort(order.begin(), order.end());
+  std::ostringstream o;
+  for (auto& e : order) { auto& a = agg[e.second]; o << e.second << " " << a.first << " " << a.second << "\n"; }
+  std::string out = o.str();
+  if ((int)out.size() >= buflen) out.resize(buflen - 1);
+  memcpy(buf, out.c_str(), out.size() + 1);
+  MF_API_END
+}
+
+// CUDA-event stopwatch on the solver stream (slots 0..15): callers time whole steps without touching the CUDA runtime
+int mf_solver_event_record(mf_solver* sp, int slot) {
+  MF_API_BEGIN
+  mfAssert(sp && slot >= 0 && slot < 16, "mf_solver_event_record: bad argument");
+  Solver* s = S(sp); s->use();
+  if (!s->userEvents[slot]) CUDA_CHECK(cudaEventCreate(&s->userEvents[slot]));
+  CUDA_CHECK(cudaEventRecord(s->userEvents[slot], s->stream));
+  MF_API_END
+}
+int mf_solver_event_elapsed_ms(mf_solver* sp, int from, int to, float* ms) {
+  MF_API_BEGIN
+  mfAssert(sp && ms && from >= 0 && from < 16 && to >= 0 && to < 16, "mf_solver_event_elapsed_ms: bad argument");
+  Solver* s = S(sp); s->use();
+  mfAssert(s->userEvents[from] && s->userEvents[to], "mf_solver_event_elapsed_ms: event not recorded");
+  CUDA_CHECK(cudaEventSynchronize(s->userEvents[to]));
+  CUDA_CHECK(cudaEventElapsedTime(ms, s->userEvents[from], s->userEvents[to]));
+  MF_API_END
+}
+
+void* mf_host_alloc(long long bytes) {
+  void* p = nullptr;
+  if (bytes <= 0 || cudaMallocHost(&p, (size_t)bytes) != cudaSuccess) { cudaGetLastError(); set_last_error("mf_host_alloc: cudaMallocHost failed"); return nullptr; }
+  return p;
+}
+void mf_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 mf_grid* mf_grid_create(mf_solver* sp, int type) {
   try {
