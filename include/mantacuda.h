@@ -26,6 +26,7 @@ extern "C" {
 
 typedef struct mf_solver mf_solver;
 typedef struct mf_grid   mf_grid;
+typedef struct mf_comm   mf_comm;
 
 /* GridBase::GridType bits, source/grid.h:29 */
 enum { MF_TYPE_REAL = 1, MF_TYPE_INT = 2, MF_TYPE_VEC3 = 4, MF_TYPE_MAC = 8, MF_TYPE_LEVELSET = 16, MF_TYPE_FLAGS = 32 };
@@ -60,6 +61,19 @@ int          mf_solver_event_elapsed_ms(mf_solver* s, int from_slot, int to_slot
 /* page-locked host buffers for upload/download (cudaMallocHost); plain malloc'ed memory works too, only slower */
 void*        mf_host_alloc(long long bytes);
 void         mf_host_free(void* p);
+
+/* ---- multi-GPU: one process per GPU, z-slab partition, one global address space over NVLink ---------------
+ * The reference is a shared-memory program whose KERNELs split the z range over TBB/OpenMP threads
+ * (source/preprocessor/codegen_kernel.cpp:187-190; source/kernel.h:65).  mf_comm is the B200 counterpart of that thread
+ * team: every rank maps every grid into one contiguous virtual range (CUDA VMM + POSIX-fd exchange), hosts one z-slab of
+ * it and launches each kernel on its own z range; neighbour planes are peer loads over NVLink, dependent launches are
+ * separated by a device-side flag barrier, reductions combine per-rank partials in rank order on every rank.
+ * All calls on a distributed solver are COLLECTIVE: every rank makes the same calls in the same order. */
+mf_comm*     mf_comm_create(int rank, int nranks, int device, const char* session);  /* session: any name unique to the job */
+void         mf_comm_destroy(mf_comm* c);
+/* out[0] mismatches seen through peer mappings, out[1] device-barrier latency (us), out[2]/out[3] peer read/write GB/s,
+ * out[4] allocation granularity (bytes), out[5] local copy GB/s */
+int          mf_comm_selftest(mf_comm* c, long long bytesPerRank, int iters, double* out);
 
 /* ---- Grid<T> / MACGrid / FlagGrid (source/grid.h:99,255,298; grid.cpp:49,95,100,228) - */
 mf_grid*     mf_grid_create(mf_solver* s, int type);      /* type = OR of MF_TYPE_*; zero-filled */

@@ -50,6 +50,9 @@ SIGNATURES = {
     "mf_solver_profile_end": (_i, [_P, C.c_char_p, _i]),
     "mf_solver_event_record": (_i, [_P, _i]),
     "mf_solver_event_elapsed_ms": (_i, [_P, _i, _i, C.POINTER(_f)]),
+    "mf_comm_create": (_P, [_i, _i, _i, _s]),
+    "mf_comm_destroy": (None, [_P]),
+    "mf_comm_selftest": (_i, [_P, C.c_longlong, _i, C.POINTER(C.c_double)]),
     "mf_host_alloc": (_P, [C.c_longlong]),
     "mf_host_free": (None, [_P]),
     "mf_grid_create": (_P, [_P, _i]),
