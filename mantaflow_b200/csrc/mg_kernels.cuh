@@ -1,7 +1,20 @@
 // mg_kernels.cuh -- device kernels of the multigrid preconditioner (reference: source/multigrid.cpp).
-// Layout: level 0 keeps the 7-point matrix as four planes A[d*n + v] (d = 0: diagonal, 1..3: +x,+y,+z coupling,
-// i.e. the reference's mA[0][v*4+d], multigrid.cpp:351-358); levels > 0 keep the symmetric 27-point operator as
-// 14 (5 in 2-D) planes A[e*n + v] (reference: mA[l][v*14+e], :208-218).  type[] holds GridMg::VertexType.
+//
+// Layout (DESIGN.md "Multigrid layout"):
+//  level 0  : natural x-fastest vertex order (x and b alias the CG vectors).  Operator either as four float planes
+//             A[d*n + v] (d = 0 diagonal, 1..3 = +x,+y,+z coupling; the reference's mA[0][v*4+d], multigrid.cpp:351-358)
+//             or, when every entry is representable, as one 16-bit code per cell (L0Code below): 2 B instead of 16 B.
+//  levels>0 : COLOUR-BLOCKED, z-pair major, zero-padded.  The reference's 27-point Gauss-Seidel sweeps 8 colours = parity
+//             of (x,y,z) (multigrid.cpp:713-737).  Vertex (x,y,z) of colour c = (x&1)|(y&1)<<1|(z&1)<<2 is stored at
+//                 p = (((z>>1)+1)*8 + c)*PY*PX + ((y>>1)+1)*PX + (x>>1)+1,      PX = (sx+1)/2 + 2, ...
+//             (2-D: 4 colours, no z padding).  All vertices of one colour in one pair of z planes are contiguous, and a
+//             stencil neighbour (dx,dy,dz) of every vertex of a colour sits in ONE other colour block at a constant index
+//             shift, so a colour sweep reads its 27 coefficients and 26 neighbour values fully coalesced (the natural order
+//             gives stride-2 access).  z-pair major keeps a z-slab of the level contiguous (multi-GPU hosting).  Padding
+//             entries and inactive vertices hold A = x = b = r = 0 and type = inactive, so the stencil loops need neither
+//             bounds nor type tests on the neighbours: a zero coefficient leaves the running sum bit-unchanged.
+//             The symmetric operator keeps 14 (5 in 2-D) planes A[e*na + p] (reference: mA[l][v*14+e], multigrid.cpp:208-218).
+// Arithmetic (summation order, float products) is the reference's; only the storage order differs.
 #pragma once
 #include "common.cuh"
 #include "reduce.cuh"
@@ -12,29 +25,61 @@ enum : unsigned char { vtInactive = 0, vtActive = 1, vtActiveTrivial = 2, vtRemo
 
 struct LvlD {
   int sx, sy, sz;
-  int n;
+  int n;               // sx*sy*sz vertices
+  int perm;            // 0 natural (level 0), 1 colour-blocked
+  int PX, PY, PZ;      // blocked: padded half sizes
+  int NC, zoff;        // blocked: colours (8 / 4) and z padding offset (1 / 0)
+  int na;              // entries per plane: n (natural) or PZ*NC*PY*PX
   float* A; float* x; float* b; float* r;
   unsigned char* type;
+  const unsigned short* code;   // level 0 only: compact operator (or nullptr)
 };
 
 struct MgDims { int is3D; int dim; int SS; int SS0; int zmin; int zmax; };   // mStencilSize, mStencilSize0, mStencilMin/Max.z
 
-#define MG_V_FROM_THREAD(L) \
-  const int v = blockIdx.x * blockDim.x + threadIdx.x; \
-  if (v >= (L).n) return; \
-  const int vx = v % (L).sx, vy = (v % ((L).sx * (L).sy)) / (L).sx, vz = v / ((L).sx * (L).sy);
-
-__device__ __forceinline__ bool mgInGrid(const LvlD& L, int x, int y, int z) {
+__device__ __host__ __forceinline__ bool mgInGrid(const LvlD& L, int x, int y, int z) {
   return x >= 0 && y >= 0 && z >= 0 && x < L.sx && y < L.sy && z < L.sz;
 }
-__device__ __forceinline__ int mgLin(const LvlD& L, int x, int y, int z) { return x + y * L.sx + z * L.sx * L.sy; }
+// storage index of vertex (x,y,z); for blocked levels any x in [-2, 2*(PX-2)+1] etc. is addressable (padding)
+__device__ __host__ __forceinline__ int mgIdx(const LvlD& L, int x, int y, int z) {
+  if (L.perm) {
+    const int c = (x & 1) | ((y & 1) << 1) | ((z & 1) << 2);
+    return ((((z >> 1) + L.zoff) * L.NC + c) * L.PY + (y >> 1) + 1) * L.PX + (x >> 1) + 1;
+  }
+  return x + L.sx * (y + L.sy * z);
+}
+// storage index p -> vertex coordinates; false for padding entries
+__device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, int& y, int& z) {
+  if (p >= L.na) return false;
+  if (!L.perm) { x = p % L.sx; const int q = p / L.sx; y = q % L.sy; z = q / L.sy; return true; }
+  const int lx = p % L.PX - 1; int q = p / L.PX;
+  const int ly = q % L.PY - 1; q /= L.PY;
+  const int c = q % L.NC; const int lz = q / L.NC - L.zoff;
+  x = 2 * lx + (c & 1); y = 2 * ly + ((c >> 1) & 1); z = 2 * lz + ((c >> 2) & 1);
+  return lx >= 0 && ly >= 0 && lz >= 0 && x < L.sx && y < L.sy && z < L.sz;
+}
+#define MG_P_FROM_THREAD(L) \
+  const int p = blockIdx.x * blockDim.x + threadIdx.x; \
+  int vx, vy, vz; \
+  if (!mgDecode((L), p, vx, vy, vz)) return;
 
-// knCopyA + knActivateVertices + analyzeStencil (multigrid.cpp:321-384)
+// ---- level-0 operator -------------------------------------------------------------------------------------
+// 16-bit code: bit0/1/2 coupling to +x/+y/+z (coefficient -1), bit3/4/5 coupling to -x/-y/-z, bits 6-8 the diagonal
+// (0..7), bit 9 set when the whole row is the identity (ActiveTrivial, multigrid.cpp:345-347).
+// Representable whenever the matrix comes from flags alone (no fractions, no ghost fluid): MakeLaplaceMatrix
+// (conjugategrad.h:154-171) only produces A0 in {0..6} and Ai,Aj,Ak in {0,-1}; fixPressure (pressure.cpp:226-245) keeps that.
+enum { MGC_XP = 1, MGC_YP = 2, MGC_ZP = 4, MGC_XM = 8, MGC_YM = 16, MGC_ZM = 32, MGC_DIAG_SHIFT = 6, MGC_TRIVIAL = 512 };
+__device__ __host__ __forceinline__ int codeDiag(int c) { return (c >> MGC_DIAG_SHIFT) & 7; }
+
+// knCopyA + knActivateVertices + analyzeStencil (multigrid.cpp:321-384).  CODE: write the 16-bit code (found[2] is set when a
+// row is not representable); otherwise the float planes.
+template <bool CODE>
 __global__ void __launch_bounds__(256) k_mg_copy_activate(LvlD L, MgDims D, const float* __restrict__ A0, const float* __restrict__ Ai,
                                                           const float* __restrict__ Aj, const float* __restrict__ Ak, float trivialScale,
-                                                          int* __restrict__ found /* [0]=nonZeroStencilSum, [1]=trivial */) {
-  MG_V_FROM_THREAD(L)
-  const int n = L.n;
+                                                          unsigned short* __restrict__ code,
+                                                          int* __restrict__ found /* [0]=nonZeroStencilSum, [1]=trivial, [2]=not codable */) {
+  MG_P_FROM_THREAD(L)
+  const int v = p, n = L.n;
   float a[7];
   a[0] = A0[v]; a[1] = Ai[v]; a[2] = Aj[v]; a[3] = D.is3D ? Ak[v] : 0.f;
   a[4] = vx != 0 ? Ai[v - 1] : 0.f;
@@ -42,94 +87,317 @@ __global__ void __launch_bounds__(256) k_mg_copy_activate(LvlD L, MgDims D, cons
   a[6] = (vz != 0 && D.is3D) ? Ak[v - L.sx * L.sy] : 0.f;
   unsigned char t = vtInactive;
   float diag = a[0];
+  bool trivial = false;
   if (a[0] != 0.f) {
     t = vtActive;
     float stencilMax = 0.f, stencilSum = 0.f;
     for (int q = 0; q < 7; q++) { stencilSum += a[q]; stencilMax = fmaxf(stencilMax, fabsf(a[q])); }
     if (fabsf(stencilSum / stencilMax) > 1E-6f) found[0] = 1;
-    const bool trivial = a[0] == 1.f && a[1] == 0.f && a[2] == 0.f && a[3] == 0.f && a[4] == 0.f && a[5] == 0.f && a[6] == 0.f;
+    trivial = a[0] == 1.f && a[1] == 0.f && a[2] == 0.f && a[3] == 0.f && a[4] == 0.f && a[5] == 0.f && a[6] == 0.f;
     if (trivial) { t = vtActiveTrivial; diag = a[0] * trivialScale; found[1] = 1; }
   }
   L.type[v] = t;
-  L.A[v] = diag; L.A[n + v] = a[1]; L.A[2 * n + v] = a[2];
-  if (D.is3D) L.A[3 * n + v] = a[3];
+  if (CODE) {
+    bool ok = a[0] >= 0.f && a[0] <= 7.f && a[0] == (float)(int)a[0];
+    int c = ok ? ((int)a[0] << MGC_DIAG_SHIFT) : 0;
+    // neighbours at the grid boundary: the matching coefficient of an in-range row must be 0 (never read by the stencils)
+#pragma unroll
+    for (int q = 1; q < 7; q++) {
+      if (a[q] == -1.f) c |= (1 << (q - 1));
+      else if (a[q] != 0.f) ok = false;
+    }
+    if ((vx == L.sx - 1 && a[1] != 0.f) || (vy == L.sy - 1 && a[2] != 0.f) || (D.is3D && vz == L.sz - 1 && a[3] != 0.f)) ok = false;
+    if (trivial) c |= MGC_TRIVIAL;
+    if (!ok) found[2] = 1;
+    code[v] = (unsigned short)c;
+  } else {
+    L.A[v] = diag; L.A[n + v] = a[1]; L.A[2 * (long long)n + v] = a[2];
+    if (D.is3D) L.A[3 * (long long)n + v] = a[3];
+  }
 }
 
-// knSetRhs (multigrid.cpp:417-424), only launched when trivial equations exist
-__global__ void __launch_bounds__(256) k_mg_set_rhs(LvlD L, const float* __restrict__ rhs, float* __restrict__ b, float trivialScale) {
-  MG_V_FROM_THREAD(L)
-  float r = rhs[v];
-  if (L.type[v] == vtActiveTrivial) r *= trivialScale;
-  b[v] = r;
-}
-
-__global__ void k_mg_fill_type(unsigned char* t, unsigned char val, int n) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v < n) t[v] = val;
+__global__ void k_mg_fill_type(LvlD L, unsigned char val) {
+  MG_P_FROM_THREAD(L)
+  L.type[p] = val;
 }
 
 // one sweep of the order-independent part of genCoarseGrid (multigrid.cpp:520-578): a fine vertex that is still in the
 // heap with exactly one free interpolation vertex selects it ('zero').  flags[0] = changed, flags[1] = some vertex still
 // has >= 2 free interpolation vertices (the serial algorithm would have to pop it: order-dependent -> host fallback).
 __global__ void __launch_bounds__(256) k_mg_coarsen_sweep(LvlD F, LvlD C, int* __restrict__ flags) {
-  MG_V_FROM_THREAD(F)
-  if (F.type[v] == vtInactive) return;
+  MG_P_FROM_THREAD(F)
+  if (F.type[p] == vtInactive) return;
   int cnt = 0, last = -1;
   for (int z = vz / 2; z <= (vz + 1) / 2; z++)
     for (int y = vy / 2; y <= (vy + 1) / 2; y++)
       for (int x = vx / 2; x <= (vx + 1) / 2; x++) {
-        const int i = mgLin(C, x, y, z);
+        const int i = mgIdx(C, x, y, z);
         if (((volatile unsigned char*)C.type)[i] == vtFree) { cnt++; last = i; }
       }
   if (cnt == 1) { C.type[last] = vtZero; flags[0] = 1; }
   else if (cnt >= 2) flags[1] = 1;
 }
 // knActivateCoarseVertices (multigrid.cpp:507-516)
-__global__ void k_mg_coarsen_finalize(unsigned char* t, int n) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= n) return;
-  unsigned char c = t[v];
+__global__ void k_mg_coarsen_finalize(LvlD L) {
+  MG_P_FROM_THREAD(L)
+  unsigned char c = L.type[p];
   if (c == vtFree) c = vtRemoved;
   if (c == vtZero) c = vtActive;
   if (c == vtRemoved) c = vtInactive;
-  t[v] = c;
+  L.type[p] = c;
 }
 
+// ---- level-0 operator policies: float planes or compact code ------------------------------------------------
+struct L0Float {
+  const float* A; const unsigned char* type; int n; float trivialScale;
+  __device__ __forceinline__ L0Float(const LvlD& L, float ts) : A(L.A), type(L.type), n(L.n), trivialScale(ts) {}
+  struct Row { unsigned char t; };
+  __device__ __forceinline__ Row row(int v) const { Row r; r.t = type[v]; return r; }
+  __device__ __forceinline__ bool inactive(const Row& r) const { return r.t == vtInactive; }
+  __device__ __forceinline__ float rhs(const Row& r, float b) const { return r.t == vtActiveTrivial ? b * trivialScale : b; }   // knSetRhs :417-424
+  __device__ __forceinline__ float diag(const Row&, int v) const { return A[v]; }
+  // coefficient of the edge leaving v in direction DIR (0:-x 1:+x 2:-y 3:+y 4:-z 5:+z); nb = neighbour index
+  template <int DIR> __device__ __forceinline__ float coef(const Row&, int v, int nb) const {
+    return A[(long long)(1 + DIR / 2) * n + ((DIR & 1) ? v : nb)];
+  }
+  template <int DIR> __device__ __forceinline__ float sub(const Row& r, int v, int nb, float sum, float xn) const { return sum - coef<DIR>(r, v, nb) * xn; }
+};
+struct L0Code {
+  const unsigned short* code; float trivialScale;
+  __device__ __forceinline__ L0Code(const LvlD& L, float ts) : code(L.code), trivialScale(ts) {}
+  struct Row { int c; };
+  __device__ __forceinline__ Row row(int v) const { Row r; r.c = code[v]; return r; }
+  __device__ __forceinline__ bool inactive(const Row& r) const { return codeDiag(r.c) == 0; }
+  __device__ __forceinline__ float rhs(const Row& r, float b) const { return (r.c & MGC_TRIVIAL) ? b * trivialScale : b; }
+  __device__ __forceinline__ float diag(const Row& r, int) const { const float d = (float)codeDiag(r.c); return (r.c & MGC_TRIVIAL) ? d * trivialScale : d; }
+  template <int DIR> __device__ __forceinline__ float coef(const Row& r, int, int) const {
+    constexpr int bit = (DIR == 0) ? MGC_XM : (DIR == 1) ? MGC_XP : (DIR == 2) ? MGC_YM : (DIR == 3) ? MGC_YP : (DIR == 4) ? MGC_ZM : MGC_ZP;
+    return (r.c & bit) ? -1.0f : 0.0f;
+  }
+  template <int DIR> __device__ __forceinline__ float sub(const Row& r, int v, int nb, float sum, float xn) const {
+    return sum - coef<DIR>(r, v, nb) * xn;      // 0 * xn = +-0 leaves sum bit-unchanged
+  }
+};
+
+// b - sum_offdiag(A x) in the reference's order (-x,+x,-y,+y,-z,+z; multigrid.cpp:686-689, :750-753)
+template <class OP>
+__device__ __forceinline__ float mgOffdiag0(const OP& op, const typename OP::Row& row, const LvlD& L, const MgDims& D, const float* __restrict__ x,
+                                            int v, int vx, int vy, int vz, float sum) {
+  const int Y = L.sx, Z = L.sx * L.sy;
+  if (vx > 0)        sum = op.template sub<0>(row, v, v - 1, sum, x[v - 1]);
+  if (vx < L.sx - 1) sum = op.template sub<1>(row, v, v + 1, sum, x[v + 1]);
+  if (vy > 0)        sum = op.template sub<2>(row, v, v - Y, sum, x[v - Y]);
+  if (vy < L.sy - 1) sum = op.template sub<3>(row, v, v + Y, sum, x[v + Y]);
+  if (D.is3D) {
+    if (vz > 0)        sum = op.template sub<4>(row, v, v - Z, sum, x[v - Z]);
+    if (vz < L.sz - 1) sum = op.template sub<5>(row, v, v + Z, sum, x[v + Z]);
+  }
+  return sum;
+}
+// knSmoothColor, l == 0: all vertices with (x+y+z)&1 == color (the reference's two colour groups, :721,:724).
+// One warp handles one (y,z) row of the z range [z0,z1).  XZERO: x is known to be all zero (first colour of a V-cycle that
+// starts from x = 0, doVCycle with src == nullptr): no neighbour loads, and the other colour / inactive cells are written 0
+// so that no separate clear of x is needed.
+template <class OP, bool XZERO>
+__global__ void __launch_bounds__(256) k_mg_smooth0(LvlD L, MgDims D, float trivialScale, int color, int z0, int z1) {
+  const OP op(L, trivialScale);
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5) + z0 * L.sy;
+  if (row >= L.sy * z1) return;
+  const int vy = row % L.sy, vz = row / L.sy;
+  const int par = (vy + vz + color) & 1;
+  const int base = row * L.sx;
+  if (XZERO) {
+    for (int vx = threadIdx.x & 31; vx < L.sx; vx += 32) {
+      const int v = base + vx;
+      float out = 0.f;
+      if (((vx ^ par) & 1) == 0) {
+        const typename OP::Row r = op.row(v);
+        if (!op.inactive(r)) out = op.rhs(r, L.b[v]) / op.diag(r, v);
+      }
+      L.x[v] = out;
+    }
+  } else {
+    for (int vx = 2 * (threadIdx.x & 31) + par; vx < L.sx; vx += 64) {
+      const int v = base + vx;
+      const typename OP::Row r = op.row(v);
+      if (op.inactive(r)) continue;
+      const float sum = mgOffdiag0(op, r, L, D, L.x, v, vx, vy, vz, op.rhs(r, L.b[v]));
+      L.x[v] = sum / op.diag(r, v);
+    }
+  }
+}
+// knCalcResidual, l == 0
+template <class OP>
+__global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D, float trivialScale, int z0, int z1) {
+  const OP op(L, trivialScale);
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5) + z0 * L.sy;
+  if (row >= L.sy * z1) return;
+  const int vy = row % L.sy, vz = row / L.sy;
+  const int base = row * L.sx;
+  for (int vx = threadIdx.x & 31; vx < L.sx; vx += 32) {
+    const int v = base + vx;
+    const typename OP::Row r = op.row(v);
+    if (op.inactive(r)) continue;        // r stays 0 at inactive vertices (cleared at creation, never written)
+    float sum = mgOffdiag0(op, r, L, D, L.x, v, vx, vy, vz, op.rhs(r, L.b[v]));
+    sum -= op.diag(r, v) * L.x[v];
+    L.r[v] = sum;
+  }
+}
+
+// ---- levels > 0 (27-point, 14 stored), colour-blocked -----------------------------------------------------
+// storage position of the thread's vertex of colour c in the lz range [lz0, lz1); returns false outside
+struct BlkPos { int p; int lx, ly, lz; };
+__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int lz1, BlkPos& q) {
+  const int BX = L.PX - 2, BY = L.PY - 2;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  q.lx = t % BX; const int u = t / BX; q.ly = u % BY; q.lz = lz0 + u / BY;
+  if (q.lz >= lz1) return false;
+  q.p = (((q.lz + L.zoff) * L.NC + c) * L.PY + q.ly + 1) * L.PX + q.lx + 1;
+  return true;
+}
+// b - sum A x over the stencil in the reference's order (dz, dy, dx ascending; multigrid.cpp:691-706, :755-770)
+template <bool IS3D, bool WITH_CENTER>
+__device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float sum) {
+  constexpr int SS = IS3D ? 14 : 5;
+  const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
+  const int PXY = L.PX * L.PY;
+  const float* __restrict__ A = L.A; const float* __restrict__ x = L.x;
+  int s = 0;
+#pragma unroll
+  for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+      for (int dx = -1; dx <= 1; dx++, s++) {
+        if (s == SS - 1) { if (WITH_CENTER) sum -= A[p] * x[p]; continue; }
+        const int ncx = (cx + dx) & 1, ncy = (cy + dy) & 1, ncz = (cz + dz) & 1;
+        const int nc = ncx | (ncy << 1) | (ncz << 2);
+        const int pn = p + ((cz + dz) >> 1) * L.NC * PXY + (nc - c) * PXY + ((cy + dy) >> 1) * L.PX + ((cx + dx) >> 1);
+        const float a = (s < SS) ? A[(long long)(SS - 1 - s) * L.na + pn] : A[(long long)(s - SS + 1) * L.na + p];
+        sum -= a * x[pn];
+      }
+  return sum;
+}
+// knSmoothColor, l > 0: one of the 8 (4) colours (multigrid.cpp:668-711)
+template <bool IS3D>
+__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int lz1) {
+  BlkPos q;
+  if (!mgBlockThread(L, c, lz0, lz1, q)) return;
+  if (L.type[q.p] == vtInactive) return;
+  const float sum = mgStencilSub<IS3D, false>(L, c, q.p, L.b[q.p]);
+  L.x[q.p] = sum / L.A[q.p];
+}
+// knCalcResidual, l > 0: blockIdx.y = colour
+template <bool IS3D>
+__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {
+  BlkPos q;
+  const int c = blockIdx.y;
+  if (!mgBlockThread(L, c, lz0, lz1, q)) return;
+  if (L.type[q.p] == vtInactive) return;
+  L.r[q.p] = mgStencilSub<IS3D, true>(L, c, q.p, L.b[q.p]);
+}
+
+// knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472).  Threads run over the natural
+// coordinates of the coarse level, z range [z0,z1) of the coarse level.  r_fine is 0 at inactive / padding / (level 0:
+// guarded) out-of-grid vertices.
+template <bool IS3D>
+__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int vx = t % C.sx; const int u = t / C.sx; const int vy = u % C.sy, vz = z0 + u / C.sy;
+  if (vz >= z1) return;
+  const int v = mgIdx(C, vx, vy, vz);
+  C.x[v] = 0.f;
+  if (C.type[v] == vtInactive) return;
+  float sum = 0.f;
+  const float* __restrict__ fr = F.r;
+  if (F.perm) {
+#pragma unroll
+    for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
+#pragma unroll
+      for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+        for (int dx = -1; dx <= 1; dx++) {
+          const int x = vx * 2 + dx, y = vy * 2 + dy, z = vz * 2 + dz;
+          // the reference clamps the loops to the grid: skipped terms, not zero terms -- identical sums because the
+          // first in-range term is added to +0 either way
+          const float rw = 1.0f / (float)(1 << ((dx & 1) + (dy & 1) + (dz & 1)));
+          sum += rw * fr[mgIdx(F, x, y, z)];
+        }
+  } else {
+    for (int z = max(0, vz * 2 - 1); z <= min(F.sz - 1, vz * 2 + 1); z++)
+      for (int y = max(0, vy * 2 - 1); y <= min(F.sy - 1, vy * 2 + 1); y++)
+        for (int x = max(0, vx * 2 - 1); x <= min(F.sx - 1, vx * 2 + 1); x++) {
+          const float rw = 1.0f / (float)(1 << ((x % 2) + (y % 2) + (z % 2)));
+          sum += rw * fr[mgIdx(F, x, y, z)];
+        }
+  }
+  C.b[v] = sum;
+}
+// knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse.  Threads run over the natural
+// coordinates of the fine level, z range [z0,z1) of the fine level; x_coarse is 0 at inactive / padding vertices.
+__global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, int z1) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int vx = t % F.sx; const int u = t / F.sx; const int vy = u % F.sy, vz = z0 + u / F.sy;
+  if (vz >= z1) return;
+  const int v = mgIdx(F, vx, vy, vz);
+  if (F.type[v] == vtInactive) return;
+  float sum = 0.f;
+  const float* __restrict__ cx = C.x;
+  for (int z = vz / 2; z <= (vz + 1) / 2; z++)
+    for (int y = vy / 2; y <= (vy + 1) / 2; y++)
+      for (int x = vx / 2; x <= (vx + 1) / 2; x++) sum += cx[mgIdx(C, x, y, z)];
+  const float iw = 1.0f / (float)(1 << ((vx % 2) + (vy % 2) + (vz % 2)));
+  F.x[v] += iw * sum;
+}
+
+// ---- Galerkin coarse operators (setup) ---------------------------------------------------------------------
 // precomputed coarsening paths for level 1 (multigrid.cpp:286-318)
 struct MgPath { signed char Nx, Ny, Nz, Ux, Uy, Uz, Wx, Wy, Wz; signed char sc, sf, inU; float rw, iw; };
 
+// level-0 coefficient by stencil slot sf (0 diagonal, 1..3 = +x,+y,+z) at storage vertex v
+template <class OP> __device__ __forceinline__ float mgCoef0(const OP& op, int sf, int v) {
+  const typename OP::Row r = op.row(v);
+  if (sf == 0) return op.diag(r, v);
+  if (sf == 1) return op.template coef<1>(r, v, v);
+  if (sf == 2) return op.template coef<3>(r, v, v);
+  return op.template coef<5>(r, v, v);
+}
 // knGenCoarseGridOperator, l == 1 (multigrid.cpp:594-614)
-__global__ void __launch_bounds__(128) k_mg_galerkin1(LvlD F, LvlD C, MgDims D, const MgPath* __restrict__ paths, int npaths) {
-  MG_V_FROM_THREAD(C)
-  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.n + v] = 0.f; return; }
+template <class OP>
+__global__ void __launch_bounds__(128) k_mg_galerkin1(LvlD F, LvlD C, MgDims D, const MgPath* __restrict__ paths, int npaths, float trivialScale) {
+  MG_P_FROM_THREAD(C)
+  const int v = p;
+  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = 0.f; return; }
+  const OP op(F, trivialScale);
   float acc[14];
 #pragma unroll
   for (int e = 0; e < 14; e++) acc[e] = 0.f;
   for (int q = 0; q < npaths; q++) {
-    const MgPath p = paths[q];
-    const int Nx = vx + p.Nx, Ny = vy + p.Ny, Nz = vz + p.Nz;
-    if (!mgInGrid(C, Nx, Ny, Nz) || C.type[mgLin(C, Nx, Ny, Nz)] == vtInactive) continue;
-    const int Ux = vx * 2 + p.Ux, Uy = vy * 2 + p.Uy, Uz = vz * 2 + p.Uz;
+    const MgPath pt = paths[q];
+    const int Nx = vx + pt.Nx, Ny = vy + pt.Ny, Nz = vz + pt.Nz;
+    if (!mgInGrid(C, Nx, Ny, Nz) || C.type[mgIdx(C, Nx, Ny, Nz)] == vtInactive) continue;
+    const int Ux = vx * 2 + pt.Ux, Uy = vy * 2 + pt.Uy, Uz = vz * 2 + pt.Uz;
     if (!mgInGrid(F, Ux, Uy, Uz)) continue;
-    const int u = mgLin(F, Ux, Uy, Uz);
+    const int u = mgIdx(F, Ux, Uy, Uz);
     if (F.type[u] == vtInactive) continue;
-    const int Wx = vx * 2 + p.Wx, Wy = vy * 2 + p.Wy, Wz = vz * 2 + p.Wz;
+    const int Wx = vx * 2 + pt.Wx, Wy = vy * 2 + pt.Wy, Wz = vz * 2 + pt.Wz;
     if (!mgInGrid(F, Wx, Wy, Wz)) continue;
-    const int w = mgLin(F, Wx, Wy, Wz);
+    const int w = mgIdx(F, Wx, Wy, Wz);
     if (F.type[w] == vtInactive) continue;
-    const float a = F.A[(long long)p.sf * F.n + (p.inU ? u : w)];
-    const float add = p.rw * a * p.iw;
+    const float a = mgCoef0(op, pt.sf, pt.inU ? u : w);
+    const float add = pt.rw * a * pt.iw;
     // static indexing keeps acc[] in registers
 #pragma unroll
-    for (int e = 0; e < 14; e++) if (e == p.sc) acc[e] += add;
+    for (int e = 0; e < 14; e++) if (e == pt.sc) acc[e] += add;
   }
-  for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.n + v] = acc[e];
+  for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = acc[e];
 }
 
 // knGenCoarseGridOperator, l > 1 (multigrid.cpp:615-656); F has the 27-point layout
 __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D) {
-  MG_V_FROM_THREAD(C)
-  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.n + v] = 0.f; return; }
+  MG_P_FROM_THREAD(C)
+  const int v = p;
+  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = 0.f; return; }
   float acc[14];
 #pragma unroll
   for (int e = 0; e < 14; e++) acc[e] = 0.f;
@@ -138,14 +406,14 @@ __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D) {
   for (int Uz = max(0, vz * 2 - 1); Uz <= min(F.sz - 1, vz * 2 + 1); Uz++)
   for (int Uy = max(0, vy * 2 - 1); Uy <= min(F.sy - 1, vy * 2 + 1); Uy++)
   for (int Ux = max(0, vx * 2 - 1); Ux <= min(F.sx - 1, vx * 2 + 1); Ux++) {
-    const int u = mgLin(F, Ux, Uy, Uz);
+    const int u = mgIdx(F, Ux, Uy, Uz);
     if (F.type[u] == vtInactive) continue;
     const float rw = 1.0f / (float)(1 << ((Ux % 2) + (Uy % 2) + (Uz % 2)));
     // (U-1)/2 uses C++ truncating division, as in the reference
     for (int Nz = (Uz - 1) / 2; Nz <= min(C.sz - 1, (Uz + 2) / 2); Nz++)
     for (int Ny = (Uy - 1) / 2; Ny <= min(C.sy - 1, (Uy + 2) / 2); Ny++)
     for (int Nx = (Ux - 1) / 2; Nx <= min(C.sx - 1, (Ux + 2) / 2); Nx++) {
-      const int nn = mgLin(C, Nx, Ny, Nz);
+      const int nn = mgIdx(C, Nx, Ny, Nz);
       if (C.type[nn] == vtInactive) continue;
       const int sc = (Nx - vx + 1) + 3 * (Ny - vy + 1) + 9 * (Nz - vz + smz);
       if (sc < SS - 1) continue;
@@ -153,123 +421,20 @@ __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D) {
       for (int Wz = max(0, max(Uz - 1, Nz * 2 - 1)); Wz <= min(F.sz - 1, min(Uz + 1, Nz * 2 + 1)); Wz++)
       for (int Wy = max(0, max(Uy - 1, Ny * 2 - 1)); Wy <= min(F.sy - 1, min(Uy + 1, Ny * 2 + 1)); Wy++)
       for (int Wx = max(0, max(Ux - 1, Nx * 2 - 1)); Wx <= min(F.sx - 1, min(Ux + 1, Nx * 2 + 1)); Wx++) {
-        const int w = mgLin(F, Wx, Wy, Wz);
+        const int w = mgIdx(F, Wx, Wy, Wz);
         if (F.type[w] == vtInactive) continue;
         const int sf = (Wx - Ux + 1) + 3 * (Wy - Uy + 1) + 9 * (Wz - Uz + smz);
         const float iw = 1.0f / (float)(1 << ((Wx % 2) + (Wy % 2) + (Wz % 2)));
         float a;
-        if (sf < SS) a = F.A[(long long)(SS - 1 - sf) * F.n + w];
-        else         a = F.A[(long long)(sf - SS + 1) * F.n + u];
+        if (sf < SS) a = F.A[(long long)(SS - 1 - sf) * F.na + w];
+        else         a = F.A[(long long)(sf - SS + 1) * F.na + u];
         const float add = rw * a * iw;
 #pragma unroll
         for (int q = 0; q < 14; q++) if (q == e) acc[q] += add;
       }
     }
   }
-  for (int e = 0; e < SS; e++) C.A[(long long)e * C.n + v] = acc[e];
-}
-
-// ---- level 0 (7-point) -----------------------------------------------------------------------------
-// b - sum_offdiag(A x) in the reference's order (-x,+x,-y,+y,-z,+z; multigrid.cpp:686-689, :750-753)
-__device__ __forceinline__ float mgOffdiag0(const LvlD& L, const MgDims& D, int v, int vx, int vy, int vz, float sum) {
-  const int n = L.n, Y = L.sx, Z = L.sx * L.sy;
-  if (vx > 0)        sum -= L.A[n + v - 1] * L.x[v - 1];
-  if (vx < L.sx - 1) sum -= L.A[n + v] * L.x[v + 1];
-  if (vy > 0)        sum -= L.A[2 * n + v - Y] * L.x[v - Y];
-  if (vy < L.sy - 1) sum -= L.A[2 * n + v] * L.x[v + Y];
-  if (D.is3D) {
-    if (vz > 0)        sum -= L.A[3 * (long long)n + v - Z] * L.x[v - Z];
-    if (vz < L.sz - 1) sum -= L.A[3 * (long long)n + v] * L.x[v + Z];
-  }
-  return sum;
-}
-// knSmoothColor, l == 0: all vertices with (x+y+z)&1 == color (the reference's two colour groups, :721,:724)
-__global__ void __launch_bounds__(256) k_mg_smooth0(LvlD L, MgDims D, int color) {
-  const int hx = (L.sx + 1) / 2;
-  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (t >= (long long)hx * L.sy * L.sz) return;
-  const int ii = (int)(t % hx), vy = (int)((t / hx) % L.sy), vz = (int)(t / ((long long)hx * L.sy));
-  const int vx = 2 * ii + ((vy + vz + color) & 1);
-  if (vx >= L.sx) return;
-  const int v = mgLin(L, vx, vy, vz);
-  if (L.type[v] == vtInactive) return;
-  const float sum = mgOffdiag0(L, D, v, vx, vy, vz, L.b[v]);
-  L.x[v] = sum / L.A[v];
-}
-// knCalcResidual, l == 0
-__global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D) {
-  MG_V_FROM_THREAD(L)
-  if (L.type[v] == vtInactive) return;
-  float sum = mgOffdiag0(L, D, v, vx, vy, vz, L.b[v]);
-  sum -= L.A[v] * L.x[v];
-  L.r[v] = sum;
-}
-
-// ---- levels > 0 (27-point, 14 stored) -----------------------------------------------------------------
-template <bool WITH_CENTER>
-__device__ __forceinline__ float mgStencilSub(const LvlD& L, const MgDims& D, int v, int vx, int vy, int vz, float sum) {
-  const int SS = D.SS;
-  int s = 0;
-  for (int dz = D.zmin; dz <= D.zmax; dz++)
-    for (int dy = -1; dy <= 1; dy++)
-      for (int dx = -1; dx <= 1; dx++, s++) {
-        if (!WITH_CENTER && s == SS - 1) continue;
-        const int Nx = vx + dx, Ny = vy + dy, Nz = vz + dz;
-        if (!mgInGrid(L, Nx, Ny, Nz)) continue;
-        const int nn = mgLin(L, Nx, Ny, Nz);
-        if (L.type[nn] == vtInactive) continue;
-        if (s < SS) sum -= L.A[(long long)(SS - 1 - s) * L.n + nn] * L.x[nn];
-        else        sum -= L.A[(long long)(s - SS + 1) * L.n + v] * L.x[nn];
-      }
-  return sum;
-}
-// knSmoothColor, l > 0: one of the 8 (4) colours = corner offset of the 2x2(x2) blocks (multigrid.cpp:668-711)
-__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, MgDims D, int ox, int oy, int oz) {
-  const int bx = (L.sx + 1) / 2, by = (L.sy + 1) / 2, bz = (L.sz + 1) / 2;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= bx * by * bz) return;
-  const int vx = (t % bx) * 2 + ox, vy = ((t % (bx * by)) / bx) * 2 + oy, vz = (t / (bx * by)) * 2 + oz;
-  if (!mgInGrid(L, vx, vy, vz)) return;
-  const int v = mgLin(L, vx, vy, vz);
-  if (L.type[v] == vtInactive) return;
-  const float sum = mgStencilSub<false>(L, D, v, vx, vy, vz, L.b[v]);
-  L.x[v] = sum / L.A[v];
-}
-__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, MgDims D) {
-  MG_V_FROM_THREAD(L)
-  if (L.type[v] == vtInactive) return;
-  L.r[v] = mgStencilSub<true>(L, D, v, vx, vy, vz, L.b[v]);
-}
-
-// knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472)
-__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C) {
-  MG_V_FROM_THREAD(C)
-  C.x[v] = 0.f;
-  if (C.type[v] == vtInactive) return;
-  float sum = 0.f;
-  for (int z = max(0, vz * 2 - 1); z <= min(F.sz - 1, vz * 2 + 1); z++)
-    for (int y = max(0, vy * 2 - 1); y <= min(F.sy - 1, vy * 2 + 1); y++)
-      for (int x = max(0, vx * 2 - 1); x <= min(F.sx - 1, vx * 2 + 1); x++) {
-        const int r = mgLin(F, x, y, z);
-        if (F.type[r] == vtInactive) continue;
-        const float rw = 1.0f / (float)(1 << ((x % 2) + (y % 2) + (z % 2)));
-        sum += rw * F.r[r];
-      }
-  C.b[v] = sum;
-}
-// knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse
-__global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C) {
-  MG_V_FROM_THREAD(F)
-  if (F.type[v] == vtInactive) return;
-  float sum = 0.f;
-  for (int z = vz / 2; z <= (vz + 1) / 2; z++)
-    for (int y = vy / 2; y <= (vy + 1) / 2; y++)
-      for (int x = vx / 2; x <= (vx + 1) / 2; x++) {
-        const int i = mgLin(C, x, y, z);
-        if (C.type[i] != vtInactive) sum += C.x[i];
-      }
-  const float iw = 1.0f / (float)(1 << ((vx % 2) + (vy % 2) + (vz % 2)));
-  F.x[v] += iw * sum;
+  for (int e = 0; e < SS; e++) C.A[(long long)e * C.na + v] = acc[e];
 }
 
 } // namespace mf

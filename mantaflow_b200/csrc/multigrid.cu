@@ -13,7 +13,8 @@ struct MgHierarchy {
   Solver* s;
   MgDims D;
   std::vector<LvlD> lv;
-  float* b0;                // scaled copy of the rhs, only used when trivial equations exist
+  unsigned short* code0;    // level 0: compact operator (allocated on first use)
+  bool useCode;             // level-0 kernels read code0 instead of float planes
   bool aSet;
   bool hasTrivial, nonZeroStencilSum;
   float coarsestAcc, trivialScale;
@@ -24,82 +25,113 @@ struct MgHierarchy {
 };
 
 // ---- coarsest level: Jacobi-preconditioned CG in double, one CTA (solveCG, multigrid.cpp:796-902) ---------
-__device__ __forceinline__ double cgBlockSum(double v, double* sh) {
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+// One thread per vertex (n <= 1024).  The 27 (7) coefficients of the thread's row are loaded once into registers, the
+// search vector lives in shared memory; 3 block barriers per iteration.
+__device__ __forceinline__ void cgBlockSum2(double& a, double& b, double (*sh)[2][32], int& buf) {
+  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { sh[buf][0][w] = a; sh[buf][1][w] = b; }
   __syncthreads();
-  if (l == 0) sh[w] = v;
-  __syncthreads();
-  double t = (l < (int)(blockDim.x >> 5)) ? sh[l] : 0.0;
-  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-  return t;   // every thread holds the block total
+  const int nw = (blockDim.x + 31) >> 5;
+  a = (l < nw) ? sh[buf][0][l] : 0.0;
+  b = (l < nw) ? sh[buf][1][l] : 0.0;
+  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+  buf ^= 1;     // the next reduction writes the other buffer: no barrier needed before it
 }
 
-__device__ __forceinline__ double cgApplyA(const LvlD& L, const MgDims& D, int level0, int v, int vx, int vy, int vz, const double* vec) {
-  double sum = 0;
-  if (level0) {
-    const int n = L.n, Y = L.sx, Z = L.sx * L.sy;
-    if (vx > 0)        sum += (double)L.A[n + v - 1] * vec[v - 1];
-    if (vx < L.sx - 1) sum += (double)L.A[n + v] * vec[v + 1];
-    if (vy > 0)        sum += (double)L.A[2 * n + v - Y] * vec[v - Y];
-    if (vy < L.sy - 1) sum += (double)L.A[2 * n + v] * vec[v + Y];
-    if (D.is3D) {
-      if (vz > 0)        sum += (double)L.A[3 * n + v - Z] * vec[v - Z];
-      if (vz < L.sz - 1) sum += (double)L.A[3 * n + v] * vec[v + Z];
-    }
-    sum += (double)L.A[v] * vec[v];
-  } else {
-    const int SS = D.SS;
-    int s = 0;
-    for (int dz = D.zmin; dz <= D.zmax; dz++)
-      for (int dy = -1; dy <= 1; dy++)
-        for (int dx = -1; dx <= 1; dx++, s++) {
-          const int Nx = vx + dx, Ny = vy + dy, Nz = vz + dz;
-          if (!mgInGrid(L, Nx, Ny, Nz)) continue;
-          const int nn = mgLin(L, Nx, Ny, Nz);
-          if (L.type[nn] == vtInactive) continue;
-          if (s < SS) sum += (double)L.A[(SS - 1 - s) * L.n + nn] * vec[nn];
-          else        sum += (double)L.A[(s - SS + 1) * L.n + v] * vec[nn];
-        }
-  }
-  return sum;
-}
-
-__global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, int level0, float accuracy) {
-  __shared__ double sh[32];
+template <bool LEVEL0>
+__global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
+  __shared__ double sh[2][2][32];
   __shared__ double vec[1024];
+  constexpr int NS = LEVEL0 ? 7 : 27;
   const int v = threadIdx.x;
   const bool in = v < L.n;
   const int vx = in ? v % L.sx : 0, vy = in ? (v % (L.sx * L.sy)) / L.sx : 0, vz = in ? v / (L.sx * L.sy) : 0;
-  const bool active = in && L.type[v] != vtInactive;
-  const double diag = active ? (double)L.A[v] : 1.0;
-  double x = in ? (double)L.x[v] : 0.0, r = 0.0, z = 0.0, p = 0.0;
+  const int p = in ? mgIdx(L, vx, vy, vz) : 0;
+  const bool active = in && L.type[p] != vtInactive;
+  // row of A in the order the reference applies it; nbr[] = natural index of the neighbour, mask bit = term present
+  float coef[NS]; unsigned mask = 0;
+#pragma unroll
+  for (int s = 0; s < NS; s++) coef[s] = 0.f;
+  const int Y = L.sx, Z = L.sx * L.sy;
+  if (active) {
+    if (LEVEL0) {
+      // order -x,+x,-y,+y,-z,+z, centre (multigrid.cpp:840-850 for l == 0)
+      const int n = L.n;
+      if (vx > 0)        { coef[0] = L.A[n + v - 1]; mask |= 1u; }
+      if (vx < L.sx - 1) { coef[1] = L.A[n + v]; mask |= 2u; }
+      if (vy > 0)        { coef[2] = L.A[2 * n + v - Y]; mask |= 4u; }
+      if (vy < L.sy - 1) { coef[3] = L.A[2 * n + v]; mask |= 8u; }
+      if (D.is3D) {
+        if (vz > 0)        { coef[4] = L.A[3 * n + v - Z]; mask |= 16u; }
+        if (vz < L.sz - 1) { coef[5] = L.A[3 * n + v]; mask |= 32u; }
+      }
+      coef[6] = L.A[v]; mask |= 64u;
+    } else {
+      const int SS = D.SS;
+      int s = 0;
+#pragma unroll
+      for (int dz = -1; dz <= 1; dz++)
+#pragma unroll
+        for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+          for (int dx = -1; dx <= 1; dx++) {
+            if (dz < D.zmin || dz > D.zmax) continue;
+            const int Nx = vx + dx, Ny = vy + dy, Nz = vz + dz;
+            const int slot = (dx + 1) + 3 * (dy + 1) + 9 * (dz + 1);     // register slot (compile time)
+            if (mgInGrid(L, Nx, Ny, Nz)) {
+              const int pn = mgIdx(L, Nx, Ny, Nz);
+              if (L.type[pn] != vtInactive) {
+                coef[slot] = (s < SS) ? L.A[(long long)(SS - 1 - s) * L.na + pn] : L.A[(long long)(s - SS + 1) * L.na + p];
+                mask |= 1u << slot;
+              }
+            }
+            s++;
+          }
+    }
+  }
+  auto applyA = [&]() {
+    double sum = 0;
+#pragma unroll
+    for (int s = 0; s < NS; s++) {
+      int off;
+      if (LEVEL0) off = (s == 0) ? -1 : (s == 1) ? 1 : (s == 2) ? -Y : (s == 3) ? Y : (s == 4) ? -Z : (s == 5) ? Z : 0;
+      else off = (s % 3 - 1) + Y * ((s / 3) % 3 - 1) + Z * (s / 9 - 1);
+      if (mask & (1u << s)) sum += (double)coef[s] * vec[v + off];
+    }
+    return sum;
+  };
+  const double diag = active ? (double)L.A[p] : 1.0;
+  double x = in ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
+  int buf = 0;
   vec[v] = x;
   __syncthreads();
   if (active) {
-    r = (double)L.b[v] - cgApplyA(L, D, level0, v, vx, vy, vz, vec);
+    r = (double)L.b[p] - applyA();
     z = r / diag;
-    p = z;
+    pp = z;
   }
-  double initialResidual = sqrt(cgBlockSum(active ? r * r : 0.0, sh));
-  double alphaTop = cgBlockSum(active ? r * z : 0.0, sh);
+  double rr = active ? r * r : 0.0, rz = active ? r * z : 0.0;
+  cgBlockSum2(rr, rz, sh, buf);
+  const double initialResidual = sqrt(rr);
+  double alphaTop = rz;
   const double acc = (double)accuracy;
   for (int iter = 0; iter < 10000 && initialResidual > 1E-12; iter++) {
+    vec[v] = pp;              // all reads of the previous vec happened before the last reduction barrier
     __syncthreads();
-    vec[v] = p;
-    __syncthreads();
-    if (active) z = cgApplyA(L, D, level0, v, vx, vy, vz, vec);
-    const double alphaBot = cgBlockSum(active ? p * z : 0.0, sh);
-    const double alpha = alphaTop / alphaBot;
-    if (active) { x += alpha * p; r -= alpha * z; z = r / diag; }
-    const double residual = sqrt(cgBlockSum(active ? r * r : 0.0, sh));
-    const double alphaTopNew = cgBlockSum(active ? r * z : 0.0, sh);
-    if (residual / initialResidual < acc) break;
-    const double beta = alphaTopNew / alphaTop;
-    alphaTop = alphaTopNew;
-    p = z + beta * p;
+    if (active) z = applyA();
+    double pz = active ? pp * z : 0.0, dummy = 0.0;
+    cgBlockSum2(pz, dummy, sh, buf);
+    const double alpha = alphaTop / pz;
+    if (active) { x += alpha * pp; r -= alpha * z; z = r / diag; }
+    rr = active ? r * r : 0.0; rz = active ? r * z : 0.0;
+    cgBlockSum2(rr, rz, sh, buf);
+    if (sqrt(rr) / initialResidual < acc) break;
+    const double beta = rz / alphaTop;
+    alphaTop = rz;
+    pp = z + beta * pp;
   }
-  if (in) L.x[v] = (float)x;
+  if (in) L.x[p] = (float)x;
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------
@@ -150,10 +182,21 @@ static void buildPaths(MgHierarchy* mg) {
   CUDA_CHECK(cudaMemcpy(mg->dPaths, hp.data(), sizeof(MgPath) * hp.size(), cudaMemcpyHostToDevice));
 }
 
+static void setLayout(LvlD& L, int sx, int sy, int sz, bool is3D, bool blocked) {
+  L.sx = sx; L.sy = sy; L.sz = sz; L.n = sx * sy * sz;
+  L.perm = blocked ? 1 : 0;
+  L.NC = is3D ? 8 : 4; L.zoff = is3D ? 1 : 0;
+  L.PX = (sx + 1) / 2 + 2; L.PY = (sy + 1) / 2 + 2; L.PZ = is3D ? (sz + 1) / 2 + 2 : 1;
+  const long long na = blocked ? (long long)L.PZ * L.NC * L.PY * L.PX : (long long)L.n;
+  mfAssert(na * 14 < (1LL << 40) && na < (1LL << 31), "GridMg: level too large for 32-bit vertex indices");
+  L.na = (int)na;
+  L.A = L.x = L.b = L.r = nullptr; L.type = nullptr; L.code = nullptr;
+}
+
 MgHierarchy* mg_create(Solver* s) {
   mfAssert(s->N < (1LL << 31), "GridMg: grid too large for 32-bit vertex indices");
   MgHierarchy* mg = new MgHierarchy();
-  mg->s = s; mg->b0 = nullptr; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
+  mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
@@ -161,19 +204,20 @@ MgHierarchy* mg_create(Solver* s) {
   int sx = s->nx, sy = s->ny, sz = s->nz;
   long long n = (long long)sx * sy * sz;
   auto addLevel = [&](int l) {
-    LvlD L; L.sx = sx; L.sy = sy; L.sz = sz; L.n = (int)n; L.A = L.x = L.b = L.r = nullptr; L.type = nullptr;
-    const int ss = (l == 0) ? mg->D.SS0 : mg->D.SS;
-    CUDA_CHECK(cudaMalloc(&L.A, sizeof(float) * (size_t)n * ss));
-    CUDA_CHECK(cudaMemset(L.A, 0, sizeof(float) * (size_t)n * ss));
-    CUDA_CHECK(cudaMalloc(&L.r, sizeof(float) * (size_t)n));
-    CUDA_CHECK(cudaMemset(L.r, 0, sizeof(float) * (size_t)n));
-    CUDA_CHECK(cudaMalloc(&L.type, (size_t)n));
+    LvlD L; setLayout(L, sx, sy, sz, is3D, l > 0);
+    const size_t na = (size_t)L.na;
+    CUDA_CHECK(cudaMalloc(&L.r, sizeof(float) * na));
+    CUDA_CHECK(cudaMemset(L.r, 0, sizeof(float) * na));
+    CUDA_CHECK(cudaMalloc(&L.type, na));
+    CUDA_CHECK(cudaMemset(L.type, 0, na));
     if (l > 0) {
-      CUDA_CHECK(cudaMalloc(&L.x, sizeof(float) * (size_t)n));
-      CUDA_CHECK(cudaMalloc(&L.b, sizeof(float) * (size_t)n));
-      CUDA_CHECK(cudaMemset(L.x, 0, sizeof(float) * (size_t)n));
-      CUDA_CHECK(cudaMemset(L.b, 0, sizeof(float) * (size_t)n));
-    }
+      CUDA_CHECK(cudaMalloc(&L.A, sizeof(float) * na * mg->D.SS));
+      CUDA_CHECK(cudaMemset(L.A, 0, sizeof(float) * na * mg->D.SS));
+      CUDA_CHECK(cudaMalloc(&L.x, sizeof(float) * na));
+      CUDA_CHECK(cudaMalloc(&L.b, sizeof(float) * na));
+      CUDA_CHECK(cudaMemset(L.x, 0, sizeof(float) * na));
+      CUDA_CHECK(cudaMemset(L.b, 0, sizeof(float) * na));
+    }                                                      // level 0: A (float planes) or code0 are allocated by mg_set_a
     mg->lv.push_back(L);
   };
   addLevel(0);
@@ -184,6 +228,7 @@ MgHierarchy* mg_create(Solver* s) {
     n = (long long)sx * sy * sz;
     addLevel(l);
   }
+  mfAssert(mg->lv.back().n <= 1024, "GridMg: coarsest level has more than 1024 vertices");
   CUDA_CHECK(cudaMalloc(&mg->dFlags, sizeof(int) * 8));
   buildPaths(mg);
   return mg;
@@ -194,10 +239,11 @@ void mg_destroy(MgHierarchy* mg) {
   cudaStreamSynchronize(mg->s->stream);
   for (size_t l = 0; l < mg->lv.size(); l++) {
     LvlD& L = mg->lv[l];
-    cudaFree(L.A); cudaFree(L.r); cudaFree(L.type);
+    if (L.A) cudaFree(L.A);
+    cudaFree(L.r); cudaFree(L.type);
     if (l > 0) { cudaFree(L.x); cudaFree(L.b); }
   }
-  if (mg->b0) cudaFree(mg->b0);
+  if (mg->code0) cudaFree(mg->code0);
   cudaFree(mg->dFlags); cudaFree(mg->dPaths);
   delete mg;
 }
@@ -260,11 +306,12 @@ struct BucketHeap {
 static void coarsenOnHost(MgHierarchy* mg, int l) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[l - 1]; LvlD& C = mg->lv[l];
-  std::vector<unsigned char> ft(F.n), ct(C.n, vtFree);
-  CUDA_CHECK(cudaMemcpyAsync(ft.data(), F.type, F.n, cudaMemcpyDeviceToHost, s->stream));
+  std::vector<unsigned char> fts(F.na), ft(F.n), ct(C.n, vtFree), cts(C.na, vtInactive);
+  CUDA_CHECK(cudaMemcpyAsync(fts.data(), F.type, F.na, cudaMemcpyDeviceToHost, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
-  BucketHeap heap(F.n, mg->D.is3D ? 9 : 5);
   const int fxy = F.sx * F.sy, cxy = C.sx * C.sy;
+  for (int v = 0; v < F.n; v++) ft[v] = fts[mgIdx(F, v % F.sx, (v % fxy) / F.sx, v / fxy)];   // natural order, as the reference walks it
+  BucketHeap heap(F.n, mg->D.is3D ? 9 : 5);
   for (int v = 0; v < F.n; v++) {
     if (ft[v] != vtInactive) {
       const int x = v % F.sx, y = (v % fxy) / F.sx, z = v / fxy;
@@ -297,9 +344,9 @@ static void coarsenOnHost(MgHierarchy* mg, int l) {
     if (c == vtFree) c = vtRemoved;
     if (c == vtZero) c = vtActive;
     if (c == vtRemoved) c = vtInactive;
-    ct[i] = c;
+    cts[mgIdx(C, i % C.sx, (i % cxy) / C.sx, i / cxy)] = c;
   }
-  CUDA_CHECK(cudaMemcpyAsync(C.type, ct.data(), C.n, cudaMemcpyHostToDevice, s->stream));
+  CUDA_CHECK(cudaMemcpyAsync(C.type, cts.data(), C.na, cudaMemcpyHostToDevice, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   mg->usedFallback++;
 }
@@ -307,55 +354,86 @@ static void coarsenOnHost(MgHierarchy* mg, int l) {
 static void genCoarseGrid(MgHierarchy* mg, int l) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[l - 1]; LvlD& C = mg->lv[l];
-  MF_LAUNCH(s, k_mg_fill_type, cdiv(C.n, 256), 256, C.type, (unsigned char)vtFree, C.n);
-  int* flags = mg->dFlags + 2;
+  MF_LAUNCH(s, k_mg_fill_type, cdiv(C.na, 256), 256, C, (unsigned char)vtFree);
+  int* flags = mg->dFlags + 4;
   bool pending = false;
   for (int sweep = 0; sweep < 10000; sweep++) {
     CUDA_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * 2, s->stream));
-    MF_LAUNCH(s, k_mg_coarsen_sweep, cdiv(F.n, 256), 256, F, C, flags);
+    MF_LAUNCH(s, k_mg_coarsen_sweep, cdiv(F.na, 256), 256, F, C, flags);
     CUDA_CHECK(cudaMemcpyAsync(s->hostInts, flags, sizeof(int) * 2, cudaMemcpyDeviceToHost, s->stream));
     CUDA_CHECK(cudaStreamSynchronize(s->stream));
     pending = s->hostInts[1] != 0;
     if (!s->hostInts[0]) break;
   }
   if (pending) { coarsenOnHost(mg, l); return; }
-  MF_LAUNCH(s, k_mg_coarsen_finalize, cdiv(C.n, 256), 256, C.type, C.n);
+  MF_LAUNCH(s, k_mg_coarsen_finalize, cdiv(C.na, 256), 256, C);
 }
 
 void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj, const float* Ak) {
   Solver* s = mg->s;
   LvlD& L0 = mg->lv[0];
-  CUDA_CHECK(cudaMemsetAsync(mg->dFlags, 0, sizeof(int) * 2, s->stream));
-  MF_LAUNCH(s, k_mg_copy_activate, cdiv(L0.n, 256), 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, mg->dFlags);
-  CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 2, cudaMemcpyDeviceToHost, s->stream));
-  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  const int maxLevel = (int)mg->lv.size() - 1;
+  // try the compact level-0 operator first (any matrix built from flags alone); a single-level hierarchy keeps float
+  // planes because the coarsest-level CG reads them
+  bool coded = false;
+  if (maxLevel > 0) {
+    if (!mg->code0) CUDA_CHECK(cudaMalloc(&mg->code0, sizeof(unsigned short) * (size_t)L0.n));
+    CUDA_CHECK(cudaMemsetAsync(mg->dFlags, 0, sizeof(int) * 4, s->stream));
+    MF_LAUNCH(s, k_mg_copy_activate<true>, cdiv(L0.n, 256), 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, mg->code0, mg->dFlags);
+    CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 4, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_CHECK(cudaStreamSynchronize(s->stream));
+    coded = s->hostInts[2] == 0;
+  }
+  if (!coded) {
+    if (!L0.A) CUDA_CHECK(cudaMalloc(&L0.A, sizeof(float) * (size_t)L0.n * mg->D.SS0));
+    CUDA_CHECK(cudaMemsetAsync(mg->dFlags, 0, sizeof(int) * 4, s->stream));
+    MF_LAUNCH(s, k_mg_copy_activate<false>, cdiv(L0.n, 256), 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, (unsigned short*)nullptr, mg->dFlags);
+    CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 4, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  }
+  mg->useCode = coded;
+  L0.code = coded ? mg->code0 : nullptr;
   mg->nonZeroStencilSum = s->hostInts[0] != 0;
   mg->hasTrivial = s->hostInts[1] != 0;
   for (size_t l = 1; l < mg->lv.size(); l++) {
     genCoarseGrid(mg, (int)l);
-    if (l == 1) { MF_LAUNCH(s, k_mg_galerkin1, cdiv(mg->lv[1].n, 128), 128, mg->lv[0], mg->lv[1], mg->D, mg->dPaths, mg->npaths); }
-    else { MF_LAUNCH(s, k_mg_galerkin, cdiv(mg->lv[l].n, 128), 128, mg->lv[l - 1], mg->lv[l], mg->D); }
+    if (l == 1) {
+      if (coded) { MF_LAUNCH(s, k_mg_galerkin1<L0Code>, cdiv(mg->lv[1].na, 128), 128, mg->lv[0], mg->lv[1], mg->D, mg->dPaths, mg->npaths, mg->trivialScale); }
+      else       { MF_LAUNCH(s, k_mg_galerkin1<L0Float>, cdiv(mg->lv[1].na, 128), 128, mg->lv[0], mg->lv[1], mg->D, mg->dPaths, mg->npaths, mg->trivialScale); }
+    } else { MF_LAUNCH(s, k_mg_galerkin, cdiv(mg->lv[l].na, 128), 128, mg->lv[l - 1], mg->lv[l], mg->D); }
   }
   MF_LAUNCH_CHECK();
   mg->aSet = true;
 }
 
-static void smoothGS(MgHierarchy* mg, int l, bool reversed) {
+// launch helpers: z range of level l handled by this process (the whole level on a single GPU)
+static inline int rowsBlocks(const LvlD& L, int z0, int z1) { return (int)cdiv((long long)L.sy * (z1 - z0), 8); }   // 8 warps per CTA, one row each
+
+template <class OP>
+static void smooth0(MgHierarchy* mg, bool reversed, bool xzero) {
+  Solver* s = mg->s;
+  LvlD& L = mg->lv[0];
+  const int z0 = 0, z1 = L.sz;
+  for (int c = 0; c < 2; c++) {
+    const int color = reversed ? 1 - c : c;
+    if (xzero && c == 0) { MF_LAUNCH(s, (k_mg_smooth0<OP, true>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+    else                 { MF_LAUNCH(s, (k_mg_smooth0<OP, false>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+  }
+}
+
+static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
   Solver* s = mg->s;
   LvlD& L = mg->lv[l];
   if (l == 0) {
-    const long long half = (long long)((L.sx + 1) / 2) * L.sy * L.sz;
-    for (int c = 0; c < 2; c++) {
-      const int color = reversed ? 1 - c : c;
-      MF_LAUNCH(s, k_mg_smooth0, cdiv(half, 256), 256, L, mg->D, color);
-    }
-  } else {
-    const int nc = mg->D.is3D ? 8 : 4;
-    const int nb = ((L.sx + 1) / 2) * ((L.sy + 1) / 2) * ((L.sz + 1) / 2);
-    for (int c = 0; c < nc; c++) {
-      const int color = reversed ? nc - 1 - c : c;
-      MF_LAUNCH(s, k_mg_smooth, cdiv(nb, 128), 128, L, mg->D, color & 1, (color >> 1) & 1, (color >> 2) & 1);
-    }
+    if (mg->useCode) smooth0<L0Code>(mg, reversed, xzero); else smooth0<L0Float>(mg, reversed, xzero);
+    return;
+  }
+  const int lz0 = 0, lz1 = mg->D.is3D ? L.PZ - 2 : 1;
+  const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0);
+  for (int c = 0; c < L.NC; c++) {
+    const int color = reversed ? L.NC - 1 - c : c;
+    if (mg->D.is3D) { MF_LAUNCH(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+    else            { MF_LAUNCH(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
   }
 }
 
@@ -364,25 +442,32 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
   mfAssert(mg->aSet, "GridMg::setRhs Error: A has not been set.");
   const int maxLevel = (int)mg->lv.size() - 1;
+  const bool is3D = mg->D.is3D != 0;
   LvlD& L0 = mg->lv[0];
-  if (mg->hasTrivial) {
-    if (!mg->b0) CUDA_CHECK(cudaMalloc(&mg->b0, sizeof(float) * (size_t)L0.n));
-    MF_LAUNCH(s, k_mg_set_rhs, cdiv(L0.n, 256), 256, L0, rhs, mg->b0, mg->trivialScale);
-    L0.b = mg->b0;
-  } else L0.b = const_cast<float*>(rhs);
+  L0.b = const_cast<float*>(rhs);      // knSetRhs' trivial-row scaling is applied on the fly (OP::rhs)
   L0.x = dst;
-  CUDA_CHECK(cudaMemsetAsync(dst, 0, sizeof(float) * (size_t)L0.n, s->stream));
+  if (maxLevel == 0 || mg->pre == 0) CUDA_CHECK(cudaMemsetAsync(dst, 0, sizeof(float) * (size_t)L0.n, s->stream));
   for (int l = 0; l < maxLevel; l++) {
-    for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false);
-    LvlD& L = mg->lv[l];
-    if (l == 0) { MF_LAUNCH(s, k_mg_residual0, cdiv(L.n, 256), 256, L, mg->D); }
-    else { MF_LAUNCH(s, k_mg_residual, cdiv(L.n, 128), 128, L, mg->D); }
-    MF_LAUNCH(s, k_mg_restrict, cdiv(mg->lv[l + 1].n, 128), 128, L, mg->lv[l + 1]);
+    for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0);
+    LvlD& L = mg->lv[l]; LvlD& C = mg->lv[l + 1];
+    if (l == 0) {
+      if (mg->useCode) { MF_LAUNCH(s, k_mg_residual0<L0Code>, rowsBlocks(L, 0, L.sz), 256, L, mg->D, mg->trivialScale, 0, L.sz); }
+      else             { MF_LAUNCH(s, k_mg_residual0<L0Float>, rowsBlocks(L, 0, L.sz), 256, L, mg->D, mg->trivialScale, 0, L.sz); }
+    } else {
+      const int lz1 = is3D ? L.PZ - 2 : 1;
+      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2) * lz1, 128), L.NC);
+      if (is3D) { MF_LAUNCH(s, k_mg_residual<true>, gr, 128, L, 0, lz1); }
+      else      { MF_LAUNCH(s, k_mg_residual<false>, gr, 128, L, 0, lz1); }
+    }
+    if (is3D) { MF_LAUNCH(s, k_mg_restrict<true>, cdiv(C.n, 128), 128, L, C, 0, C.sz); }
+    else      { MF_LAUNCH(s, k_mg_restrict<false>, cdiv(C.n, 128), 128, L, C, 0, C.sz); }
   }
-  MF_LAUNCH(s, k_mg_coarse_cg, 1, 1024, mg->lv[maxLevel], mg->D, maxLevel == 0 ? 1 : 0, mg->coarsestAcc);
+  if (maxLevel == 0) { MF_LAUNCH(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
+  else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
   for (int l = maxLevel - 1; l >= 0; l--) {
-    MF_LAUNCH(s, k_mg_interp_add, cdiv(mg->lv[l].n, 256), 256, mg->lv[l], mg->lv[l + 1]);
-    for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true);
+    LvlD& L = mg->lv[l];
+    MF_LAUNCH(s, k_mg_interp_add, cdiv(L.n, 256), 256, L, mg->lv[l + 1], 0, L.sz);
+    for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }
   // the trailing calcResidual(0)/calcResidualNorm(0) of doVCycle only feed its return value, which the CG driver
   // ignores (conjugategrad.cpp:162-167) -- skipped.
@@ -392,12 +477,31 @@ void mg_download_level(MgHierarchy* mg, int l, unsigned char* type, float* A) {
   Solver* s = mg->s;
   LvlD& L = mg->lv[l];
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
-  if (type) CUDA_CHECK(cudaMemcpy(type, L.type, L.n, cudaMemcpyDeviceToHost));
+  const int xy = L.sx * L.sy;
+  std::vector<unsigned char> ts((size_t)L.na);
+  CUDA_CHECK(cudaMemcpy(ts.data(), L.type, (size_t)L.na, cudaMemcpyDeviceToHost));
+  if (type) for (int v = 0; v < L.n; v++) type[v] = ts[mgIdx(L, v % L.sx, (v % xy) / L.sx, v / xy)];
   if (A) {
     const int ss = (l == 0) ? mg->D.SS0 : mg->D.SS;
-    std::vector<float> planes((size_t)L.n * ss);
-    CUDA_CHECK(cudaMemcpy(planes.data(), L.A, sizeof(float) * planes.size(), cudaMemcpyDeviceToHost));
-    for (int v = 0; v < L.n; v++) for (int e = 0; e < ss; e++) A[(size_t)v * ss + e] = planes[(size_t)e * L.n + v];
+    if (l == 0 && mg->useCode) {
+      std::vector<unsigned short> code((size_t)L.n);
+      CUDA_CHECK(cudaMemcpy(code.data(), mg->code0, sizeof(unsigned short) * code.size(), cudaMemcpyDeviceToHost));
+      for (int v = 0; v < L.n; v++) {
+        const int c = code[v];
+        float d = (float)codeDiag(c); if (c & MGC_TRIVIAL) d = d * mg->trivialScale;
+        A[(size_t)v * ss] = d;
+        A[(size_t)v * ss + 1] = (c & MGC_XP) ? -1.f : 0.f;
+        A[(size_t)v * ss + 2] = (c & MGC_YP) ? -1.f : 0.f;
+        if (ss > 3) A[(size_t)v * ss + 3] = (c & MGC_ZP) ? -1.f : 0.f;
+      }
+    } else {
+      std::vector<float> planes((size_t)L.na * ss);
+      CUDA_CHECK(cudaMemcpy(planes.data(), L.A, sizeof(float) * planes.size(), cudaMemcpyDeviceToHost));
+      for (int v = 0; v < L.n; v++) {
+        const int p = mgIdx(L, v % L.sx, (v % xy) / L.sx, v / xy);
+        for (int e = 0; e < ss; e++) A[(size_t)v * ss + e] = planes[(size_t)e * L.na + p];
+      }
+    }
   }
 }
 
