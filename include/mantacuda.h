@@ -70,7 +70,19 @@ void         mf_host_free(void* p);
  * separated by a device-side flag barrier, reductions combine per-rank partials in rank order on every rank.
  * All calls on a distributed solver are COLLECTIVE: every rank makes the same calls in the same order. */
 mf_comm*     mf_comm_create(int rank, int nranks, int device, const char* session);  /* session: any name unique to the job */
+/* all nranks ranks inside THIS process on one device: every launch group runs rank after rank on one stream, barriers are
+ * stream order.  Exercises the partitioned code path (z ranges, cross-rank reductions, solo levels) on a single GPU. */
+mf_comm*     mf_comm_create_emulated(int nranks, int device);
 void         mf_comm_destroy(mf_comm* c);
+/* FluidSolver whose grids are z-slab partitioned over the ranks of c (3-D, nz >= 2*nranks) */
+mf_solver*   mf_solver_create_dist(mf_comm* c, int nx, int ny, int nz, int dim);
+int          mf_solver_ranks(const mf_solver* s);                              /* 1 for a single-GPU solver */
+int          mf_solver_slab(const mf_solver* s, int rank, int* k0, int* k1);   /* planes [k0,k1) of rank (-1: this process) */
+long long    mf_solver_barrier_count(const mf_solver* s);                      /* device barriers enqueued so far */
+/* host buffers that hold only this rank's slab (planes k0..k1-1, reference layout); mf_grid_upload/_download take the FULL
+ * grid on every rank (upload: each rank copies its own slab from it; download: every rank receives the whole grid) */
+int          mf_grid_upload_slab(mf_grid* g, const void* host_slab);
+int          mf_grid_download_slab(const mf_grid* g, void* host_slab);
 /* out[0] mismatches seen through peer mappings, out[1] device-barrier latency (us), out[2]/out[3] peer read/write GB/s,
  * out[4] allocation granularity (bytes), out[5] local copy GB/s */
 int          mf_comm_selftest(mf_comm* c, long long bytesPerRank, int iters, double* out);

@@ -51,7 +51,14 @@ SIGNATURES = {
     "mf_solver_event_record": (_i, [_P, _i]),
     "mf_solver_event_elapsed_ms": (_i, [_P, _i, _i, C.POINTER(_f)]),
     "mf_comm_create": (_P, [_i, _i, _i, _s]),
+    "mf_comm_create_emulated": (_P, [_i, _i]),
     "mf_comm_destroy": (None, [_P]),
+    "mf_solver_create_dist": (_P, [_P, _i, _i, _i, _i]),
+    "mf_solver_ranks": (_i, [_P]),
+    "mf_solver_slab": (_i, [_P, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "mf_solver_barrier_count": (C.c_longlong, [_P]),
+    "mf_grid_upload_slab": (_i, [_P, _P]),
+    "mf_grid_download_slab": (_i, [_P, _P]),
     "mf_comm_selftest": (_i, [_P, C.c_longlong, _i, C.POINTER(C.c_double)]),
     "mf_host_alloc": (_P, [C.c_longlong]),
     "mf_host_free": (None, [_P]),

@@ -28,8 +28,8 @@ __device__ __forceinline__ bool isBorder(const Geo& g, int i, int j, int k) {
 #define IJK_FROM_BLOCK \
   const int i = blockIdx.x * blockDim.x + threadIdx.x; \
   const int j = blockIdx.y * blockDim.y + threadIdx.y; \
-  const int k = blockIdx.z * blockDim.z + threadIdx.z; \
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return; \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0; \
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return; \
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
 
 // back-traced position for centred grids (advection.cpp:28-38)
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(256) k_mc_mac(Geo g, const int* __restrict__ f
   dst.z[idx] = mcMacComp<2, OS, OT>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, clampMode, sz, border);
 }
 
-__global__ void k_scan_outflow(const int* __restrict__ flags, long long n, int* anyOutflow) {
+__global__ void k_scan_outflow(const int* __restrict__ flags, long long n, int* anyOutflow) {   // flags: the rank's slab
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long st = (long long)gridDim.x * blockDim.x;
   bool any = false;
@@ -348,14 +348,12 @@ __global__ void k_outflow_copy(Geo g, const int* __restrict__ flags, CV3 velDst,
 
 
 // ---- host side ------------------------------------------------------------------------------------
-static inline dim3 ijkBlock(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
-static inline dim3 ijkGrid(const Solver* s, dim3 b) { return dim3(cdiv(s->nx, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z)); }
-
 bool flagsHaveOutflow(const Grid* flags) {
   if (flags->outflowState >= 0) return flags->outflowState != 0;
   Solver* s = flags->s;
-  CUDA_CHECK(cudaMemsetAsync(s->devFlagsScratch, 0, sizeof(int), s->stream));
-  MF_LAUNCH(s, k_scan_outflow, s->numSMs * 8, 256, flags->di(), s->N, s->devFlagsScratch);
+  s->clearShared(s->devFlagsScratch, sizeof(int));
+  MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_scan_outflow, s->numSMs * 8, 256, flags->di() + sp.off, sp.n, s->devFlagsScratch); }
+  s->rankSync();
   CUDA_CHECK(cudaMemcpyAsync(s->hostInts, s->devFlagsScratch, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   flags->outflowState = s->hostInts[0] ? 1 : 0;
@@ -366,27 +364,23 @@ bool flagsHaveOutflow(const Grid* flags) {
 static void applyOutflowBC(Solver* s, const Grid* flags, V3 vel, CV3 velPrev, float dt) {
   if (!flagsHaveOutflow(flags)) return;
   TmpVec velDst(s);
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   const float timeStep = (float)fmax(1.0, (double)dt * 4);   // max(1.0, timeStep*4) evaluated in double, passed as Real
   CV3 cvel; cvel.x = vel.x; cvel.y = vel.y; cvel.z = vel.z;
-  MF_LAUNCH(s, k_outflow_extrapolate, gr, b, g, flags->di(), cvel, v3(velDst), velPrev, timeStep);
-  MF_LAUNCH(s, k_outflow_copy, gr, b, g, flags->di(), cv3(velDst), vel);
+  MF_LAUNCH_IJK(s, k_outflow_extrapolate, flags->di(), cvel, v3(velDst), velPrev, timeStep);
+  MF_LAUNCH_IJK(s, k_outflow_copy, flags->di(), cv3(velDst), vel);
 }
 
 template <int NC, int OS, int OT>
 static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* grid, int order, float strength, int clampMode) {
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   const long long np = s->Np;
   const float dt = s->dt;
   float* fwd = (NC == 1) ? s->getReal() : s->getVec();
-  MF_LAUNCH(s, (k_sl<NC, OS, OT>), gr, b, g, cv3(vel), grid->d, fwd, dt, np);
+  MF_LAUNCH_IJK(s, (k_sl<NC, OS, OT>), cv3(vel), grid->d, fwd, dt, np);
   if (order == 1) {
     float* old = grid->d; grid->d = fwd; fwd = old;       // orig.swap(fwd)
   } else {
     float* nw = (NC == 1) ? s->getReal() : s->getVec();
-    MF_LAUNCH(s, (k_mc_centered<NC, OS, OT>), gr, b, g, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
+    MF_LAUNCH_IJK(s, (k_mc_centered<NC, OS, OT>), flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
     float* old = grid->d; grid->d = nw;                   // orig.swap(newGrid)
     if (NC == 1) s->putReal(old); else s->putVec(old);
   }
@@ -395,20 +389,18 @@ static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* 
 
 template <int OS, int OT>
 static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid, int order, float strength, int clampMode) {
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   const float dt = s->dt;
   const bool self = (vel == grid) || (vel->d == grid->d);
   float* fwd = s->getVec();
   Grid fw = *grid; fw.d = fwd;
-  MF_LAUNCH(s, (k_sl_mac<OS, OT>), gr, b, g, cv3(vel), cv3(grid), v3(&fw), dt);
+  MF_LAUNCH_IJK(s, (k_sl_mac<OS, OT>), cv3(vel), cv3(grid), v3(&fw), dt);
   if (order == 1) {
     applyOutflowBC(s, flags, v3(&fw), cv3(grid), dt);
     float* old = grid->d; grid->d = fwd; fwd = old;
   } else {
     float* nw = s->getVec();
     Grid ng = *grid; ng.d = nw;
-    MF_LAUNCH(s, (k_mc_mac<OS, OT>), gr, b, g, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
+    MF_LAUNCH_IJK(s, (k_mc_mac<OS, OT>), flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
     applyOutflowBC(s, flags, v3(&ng), cv3(grid), dt);
     float* old = grid->d; grid->d = nw;
     s->putVec(old);

@@ -33,8 +33,49 @@ struct CgVecs {
   const float *A0, *Ai, *Aj, *Ak;
 };
 
+// finishing functors of the CG reductions: run once per process with the grid-wide (and rank-wide) results
+struct FinAlpha {   // dp = tmp . search ; alpha = sigma / dp (conjugategrad.cpp:250-252)
+  CgState* st;
+  __device__ void operator()(double* r) const {
+    if (st->done) return;
+    const float dp = (float)r[0];
+    float alpha = 0.f;
+    if (fabsf(dp) > 0.f) alpha = st->sigma / dp;
+    st->alpha = alpha;
+    st->iterations += 1;
+  }
+};
+template <bool PCNONE> struct FinUpdate {   // residual norm and stop test (conjugategrad.cpp:262-277) [+ sigma, beta when unpreconditioned]
+  CgState* st;
+  __device__ void operator()(double* r) const {
+    if (st->done) return;
+    float resNorm;
+    if (st->useL2) resNorm = (float)r[0];
+    else resNorm = fmaxf(fabsf((float)r[1]), fabsf((float)r[2]));
+    st->resNorm = resNorm;
+    if (resNorm < st->accuracy) { st->sigma = resNorm; st->done = 1; return; }
+    if (PCNONE) {
+      const float sigmaNew = (float)r[3];
+      st->beta = sigmaNew / st->sigma;
+      st->sigma = sigmaNew;
+      if (!(resNorm < 1e35f)) { st->diverged = 1; st->done = 1; }
+    }
+  }
+};
+struct FinBeta {    // sigmaNew, beta = sigmaNew / sigma (conjugategrad.cpp:279-295)
+  CgState* st;
+  __device__ void operator()(double* r) const {
+    if (st->done) return;
+    const float sigmaNew = (float)r[0];
+    st->beta = sigmaNew / st->sigma;
+    st->sigma = sigmaNew;
+    if (!(st->resNorm < 1e35f)) { st->diverged = 1; st->done = 1; }
+  }
+};
+struct FinSigma { CgState* st; __device__ void operator()(double* r) const { st->sigma = (float)r[0]; } };
+
 // tmp = A * search ; dp = tmp . search ; alpha = sigma / dp        (conjugategrad.cpp:247-252)
-__global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* st, double* partials, unsigned int* counter) {
+__global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* st, RedCtx ctx) {
   __shared__ double sh[32];
   if (st->done) return;
   double acc[1] = { 0.0 };
@@ -45,27 +86,21 @@ __global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* s
     acc[0] += (double)(t * s);
   MF_TILE_LOOP_END
   const int ops[1] = { 0 };
-  gridReduceK<1>(acc, ops, partials, counter, sh, [=](double* r) {
-    const float dp = (float)r[0];
-    float alpha = 0.f;
-    if (fabsf(dp) > 0.f) alpha = st->sigma / dp;
-    st->alpha = alpha;
-    st->iterations += 1;
-  });
+  gridReduceK<1>(acc, ops, ctx, sh, FinAlpha{ st });
 }
 
 // dst += alpha*search ; residual += -alpha*tmp ; norm(residual)     (conjugategrad.cpp:254-277)
 // PCNONE: also tmp := residual (implicitly) and sigmaNew = residual . residual, beta        (:279-286)
 template <bool PCNONE>
-__global__ void __launch_bounds__(256) k_cg_update(Geo g, CgVecs v, CgState* st, double* partials, unsigned int* counter) {
+__global__ void __launch_bounds__(256) k_cg_update(Span sp, CgVecs v, CgState* st, RedCtx ctx) {
   __shared__ double sh[32];
   if (st->done) return;
   const float alpha = st->alpha, nalpha = -alpha;
   const int useL2 = st->useL2;
   double acc[4] = { 0.0, 1e300, -1e300, 0.0 };   // sumsqr, min, max, r.r (float products)
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long i0 = sp.off + blockIdx.x * (long long)blockDim.x + threadIdx.x, iend = sp.off + sp.n;
   const long long st_ = (long long)gridDim.x * blockDim.x;
-  for (long long idx = i0; idx < g.N; idx += st_) {
+  for (long long idx = i0; idx < iend; idx += st_) {
     v.dst[idx] += alpha * v.search[idx];
     const float r = v.residual[idx] + nalpha * v.tmp[idx];
     v.residual[idx] = r;
@@ -74,24 +109,12 @@ __global__ void __launch_bounds__(256) k_cg_update(Geo g, CgVecs v, CgState* st,
     if (PCNONE) acc[3] += (double)(r * r);
   }
   const int ops[4] = { 0, 1, 2, 0 };
-  gridReduceK<4>(acc, ops, partials, counter, sh, [=](double* r) {
-    float resNorm;
-    if (useL2) resNorm = (float)r[0];
-    else resNorm = fmaxf(fabsf((float)r[1]), fabsf((float)r[2]));
-    st->resNorm = resNorm;
-    if (resNorm < st->accuracy) { st->sigma = resNorm; st->done = 1; return; }
-    if (PCNONE) {
-      const float sigmaNew = (float)r[3];
-      st->beta = sigmaNew / st->sigma;
-      st->sigma = sigmaNew;
-      if (!(resNorm < 1e35f)) { st->diverged = 1; st->done = 1; }
-    }
-  });
+  gridReduceK<4>(acc, ops, ctx, sh, FinUpdate<PCNONE>{ st });
 }
 
 // sigmaNew = tmp . residual ; beta = sigmaNew / sigma                 (conjugategrad.cpp:279-295), preconditioned path
 __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* __restrict__ tmp, const float* __restrict__ residual,
-                                                     CgState* st, double* partials, unsigned int* counter) {
+                                                     CgState* st, RedCtx ctx) {
   __shared__ double sh[32];
   if (st->done) return;
   double acc[1] = { 0.0 };
@@ -99,24 +122,19 @@ __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* _
   const long long stp = (long long)gridDim.x * blockDim.x;
   for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]);
   const int ops[1] = { 0 };
-  gridReduceK<1>(acc, ops, partials, counter, sh, [=](double* r) {
-    const float sigmaNew = (float)r[0];
-    st->beta = sigmaNew / st->sigma;
-    st->sigma = sigmaNew;
-    if (!(st->resNorm < 1e35f)) { st->diverged = 1; st->done = 1; }
-  });
+  gridReduceK<1>(acc, ops, ctx, sh, FinBeta{ st });
 }
 
 // init: sigma = tmp . residual                                           (conjugategrad.cpp:234)
 __global__ void __launch_bounds__(256) k_cg_dot_sigma(long long n, const float* __restrict__ tmp, const float* __restrict__ residual,
-                                                      CgState* st, double* partials, unsigned int* counter) {
+                                                      CgState* st, RedCtx ctx) {
   __shared__ double sh[32];
   double acc[1] = { 0.0 };
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long stp = (long long)gridDim.x * blockDim.x;
   for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]);
   const int ops[1] = { 0 };
-  gridReduceK<1>(acc, ops, partials, counter, sh, [=](double* r) { st->sigma = (float)r[0]; });
+  gridReduceK<1>(acc, ops, ctx, sh, FinSigma{ st });
 }
 
 // search = tmp + beta * search                                            (UpdateSearchVec, conjugategrad.cpp:193)
@@ -152,8 +170,8 @@ __global__ void __launch_bounds__(256) k_rbic_init(Geo g, const int* __restrict_
                                                    const float* __restrict__ Ai, const float* __restrict__ Aj, const float* __restrict__ Ak) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   float p = 0.f;
   if (interiorCell(g, i, j, k) && fIsFluid(flags[idx]) && A0[idx] > 0.f) {
@@ -185,9 +203,9 @@ __global__ void __launch_bounds__(256) k_rbic_black(Geo g, const float* __restri
   if (st->done) return;
   const int ii = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
   const int i = 2 * ii + ((j + k + 1) & 1);       // black cells of this row
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   const float p = P[idx];
   if (p == 0.f) { z[idx] = 0.f; return; }
@@ -205,9 +223,9 @@ __global__ void __launch_bounds__(256) k_rbic_red(Geo g, const float* __restrict
   if (st->done) return;
   const int ii = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
   const int i = 2 * ii + ((j + k) & 1);           // red cells of this row
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   const float p = P[idx];
   if (p == 0.f) { z[idx] = 0.f; return; }

@@ -75,6 +75,7 @@ struct Comm {
 
 int comm_rank(const Comm* c) { return c->rank; }
 int comm_nranks(const Comm* c) { return c->nranks; }
+int comm_device(const Comm* c) { return c->device; }
 bool comm_emulated(const Comm* c) { return c->emulated; }
 size_t comm_granularity(const Comm* c) { return c->gran; }
 long long comm_barriers_issued(const Comm* c) { return c->barriers; }
@@ -347,6 +348,12 @@ extern "C" {
 
 mf_comm* mf_comm_create(int rank, int nranks, int device, const char* session) {
   try { return reinterpret_cast<mf_comm*>(comm_create(rank, nranks, device, session)); }
+  catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+}
+// all ranks of the job inside this process on one device: launches run rank after rank on one stream (single-GPU testing of
+// the partitioned code path)
+mf_comm* mf_comm_create_emulated(int nranks, int device) {
+  try { return reinterpret_cast<mf_comm*>(comm_create_emulated(nranks, device)); }
   catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
 }
 void mf_comm_destroy(mf_comm* c) { comm_destroy(reinterpret_cast<Comm*>(c)); }

@@ -33,6 +33,7 @@ Comm* comm_create_emulated(int nranks, int device);
 void  comm_destroy(Comm* c);
 
 int   comm_rank(const Comm* c);
+int   comm_device(const Comm* c);
 int   comm_nranks(const Comm* c);
 bool  comm_emulated(const Comm* c);
 size_t comm_granularity(const Comm* c);

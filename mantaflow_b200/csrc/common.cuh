@@ -36,6 +36,8 @@ void set_last_error(const std::string& s);
 
 struct Solver;
 struct MgHierarchy;
+struct Comm;
+struct CommShared;
 
 struct Grid {
   Solver* s;
@@ -69,11 +71,23 @@ struct Solver {
   unsigned int* redCounter;
   double* redOut;       // device results (16 doubles)
   double* redHost;      // pinned
-  int* devFlagsScratch; // small int scratch (8 ints)
+  int* devFlagsScratch; // small int scratch (16 ints), job-wide when partitioned over GPUs: any rank's kernels raise flags here
+  int* localInts;       // small int scratch (16 ints), private to this process
   int* hostInts;        // pinned
   float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
   int numSMs;
+  // ---- z-slab partition over GPUs (comm.h).  Single GPU: nranks = 1, comm = nullptr.
+  Comm* comm;           // not owned
+  int nranks;           // ranks of the job
+  int rankBegin, rankEnd;   // ranks this process executes: [rank, rank+1) per process; [0, nranks) when emulated on one GPU
+  int zsplit[17];       // rank r owns planes [zsplit[r], zsplit[r+1])
+  int redParity;        // alternates the cross-rank reduction slot set
+  bool multi() const { return nranks > 1; }
+  void* galloc(size_t bytesPerComp, int ncomp = 1, size_t compStride = 0);   // global (all ranks map it) when multi, else cudaMalloc; zero-filled
+  void  gfree(void* p);
+  void  rankSync();      // device barrier across ranks on the solver stream (no-op on a single GPU / emulated)
+  void  clearShared(void* p, size_t bytes);   // zero a small job-wide scratch array (one rank clears, then barrier)
   // per-kernel CUDA-event timing (mf_solver_profile_*): one event pair per launch while enabled
   bool profiling;
   struct ProfRec { const char* name; cudaEvent_t a, b; };
@@ -101,8 +115,13 @@ struct Geo {
   int is3D;
   long long Z;   // strideZ (0 in 2-D)
   long long N;
+  int k0, k1;    // z range the launch works on ([0,nz) on a single GPU): kernels index memory globally, iterate locally
 };
-inline Geo geo(const Solver* s) { Geo g; g.nx = s->nx; g.ny = s->ny; g.nz = s->nz; g.is3D = s->is3D; g.Z = s->strideZ; g.N = s->N; return g; }
+inline Geo geo(const Solver* s) { Geo g; g.nx = s->nx; g.ny = s->ny; g.nz = s->nz; g.is3D = s->is3D; g.Z = s->strideZ; g.N = s->N; g.k0 = 0; g.k1 = s->nz; return g; }
+inline Geo geo(const Solver* s, int rank) { Geo g = geo(s); g.k0 = s->zsplit[rank]; g.k1 = s->zsplit[rank + 1]; return g; }
+// cell range [off, off+n) of rank r's slab
+struct Span { long long off, n; };
+inline Span span(const Solver* s, int rank) { Span sp; const long long xy = (long long)s->nx * s->ny; sp.off = xy * s->zsplit[rank]; sp.n = xy * (s->zsplit[rank + 1] - s->zsplit[rank]); return sp; }
 
 // three component pointers of a SoA vec grid
 struct V3 { float* x; float* y; float* z; };
@@ -134,6 +153,14 @@ struct ProfScope {   // brackets one launch with events on the solver stream whe
 };
 #define MF_LAUNCH(s, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
 #define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())
+// SPMD launch helpers: MF_RANKS iterates over the ranks this process executes; every group of per-rank launches is followed
+// by rankSync (dependent launches on other GPUs read/write the same global arrays).
+#define MF_RANKS(s, r) for (int r = (s)->rankBegin; r < (s)->rankEnd; ++r)
+inline dim3 ijkBlockOf(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
+inline dim3 ijkGridOf(dim3 b, const Geo& g) { return dim3(cdiv(g.nx, b.x), cdiv(g.ny, b.y), cdiv(g.k1 - g.k0, b.z)); }
+// ijk kernel (first parameter Geo) over every local rank's z range, then the cross-rank barrier
+#define MF_LAUNCH_IJK(s, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { const mf::Geo _g = mf::geo((s), _r); \
+  if (_g.k1 > _g.k0) { MF_LAUNCH(s, kern, mf::ijkGridOf(_b, _g), _b, _g, __VA_ARGS__); } } (s)->rankSync(); } while (0)
 
 // reductions (reduce.cu)
 // Deterministic two-stage reductions: per-block partial in fixed order, last block sums partials in block order.

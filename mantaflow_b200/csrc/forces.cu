@@ -13,12 +13,10 @@ namespace mf {
 #define IJK_FROM_BLOCK \
   const int i = blockIdx.x * blockDim.x + threadIdx.x; \
   const int j = blockIdx.y * blockDim.y + threadIdx.y; \
-  const int k = blockIdx.z * blockDim.z + threadIdx.z; \
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return; \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0; \
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return; \
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
 
-static inline dim3 ijkBlock(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
-static inline dim3 ijkGrid(const Solver* s, dim3 b) { return dim3(cdiv(s->nx, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z)); }
 
 __device__ __forceinline__ bool interior1(const Geo& g, int i, int j, int k) {
   return i >= 1 && j >= 1 && i < g.nx - 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
@@ -284,13 +282,11 @@ int mf_flags_init_domain(mf_grid* fp, int boundaryWidth, const char* wallIn, con
       else if (wall[i] == c) { types.t[side] = MF_OBSTACLE; wallMask |= (1 << side); set[side] = true; }
     }
   }
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   if (phiWalls) {
     REQ_GRID(phiWalls, G(phiWalls)->isReal(), "phiWalls", "FlagGrid::initDomain");
-    MF_LAUNCH(s, k_init_phi_walls, gr, b, g, G(phiWalls)->d, boundaryWidth, wallMask);
+    MF_LAUNCH_IJK(s, k_init_phi_walls, G(phiWalls)->d, boundaryWidth, wallMask);
   }
-  MF_LAUNCH(s, k_init_domain, gr, b, g, flags->di(), boundaryWidth, types);
+  MF_LAUNCH_IJK(s, k_init_domain, flags->di(), boundaryWidth, types);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -300,7 +296,8 @@ int mf_flags_fill_grid(mf_grid* fp, int type) {
   REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::fillGrid");
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
   flags->outflowState = -1;
-  MF_LAUNCH(s, k_fill_grid, s->numSMs * 8, 256, flags->di(), type, s->N);
+  MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_fill_grid, s->numSMs * 8, 256, flags->di() + sp.off, type, sp.n); }
+  s->rankSync();
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -310,9 +307,8 @@ int mf_flags_count_cells(const mf_grid* fp, int flag, int bnd, int* out) {
   REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::countCells");
   mfAssert(out, "FlagGrid::countCells: null output");
   const Grid* flags = G(fp); Solver* s = flags->s; s->use();
-  CUDA_CHECK(cudaMemsetAsync(s->devFlagsScratch + 1, 0, sizeof(int), s->stream));
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
-  MF_LAUNCH(s, k_count_cells, gr, b, geo(s), flags->di(), flag, bnd, s->devFlagsScratch + 1);
+  s->clearShared(s->devFlagsScratch + 1, sizeof(int));
+  MF_LAUNCH_IJK(s, k_count_cells, flags->di(), flag, bnd, s->devFlagsScratch + 1);
   MF_LAUNCH_CHECK();
   CUDA_CHECK(cudaMemcpyAsync(s->hostInts, s->devFlagsScratch + 1, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
@@ -327,8 +323,7 @@ int mf_flags_set_open_bound(mf_grid* fp, int bWidth, const char* openBound, int 
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
   flags->outflowState = -1;
   int lo, up; parseDesc(openBound, lo, up, "setOpenBound");
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
-  MF_LAUNCH(s, k_set_open_bound, gr, b, geo(s), flags->di(), bWidth, lo, up, type);
+  MF_LAUNCH_IJK(s, k_set_open_bound, flags->di(), bWidth, lo, up, type);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -339,7 +334,9 @@ int mf_reset_outflow(mf_grid* fp, mf_grid* phi, mf_grid* real) {
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
   if (phi) REQ_GRID(phi, G(phi)->isReal(), "phi", "resetOutflow");
   if (real) REQ_GRID(real, G(real)->isReal(), "real", "resetOutflow");
-  MF_LAUNCH(s, k_reset_outflow, s->numSMs * 8, 256, flags->di(), phi ? G(phi)->d : nullptr, real ? G(real)->d : nullptr, s->N);
+  MF_RANKS(s, r) { const Span sp = span(s, r);
+    MF_LAUNCH(s, k_reset_outflow, s->numSMs * 8, 256, flags->di() + sp.off, phi ? G(phi)->d + sp.off : nullptr, real ? G(real)->d + sp.off : nullptr, sp.n); }
+  s->rankSync();
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -348,8 +345,7 @@ int mf_apply_box_to_real(mf_grid* gp, float x0, float y0, float z0, float x1, fl
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isReal(), "grid", "Shape::applyToGrid");
   Grid* gr = G(gp); Solver* s = gr->s; s->use();
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
-  MF_LAUNCH(s, k_apply_box<float>, gd, b, geo(s), gr->d, x0, y0, z0, x1, y1, z1, value);
+  MF_LAUNCH_IJK(s, k_apply_box<float>, gr->d, x0, y0, z0, x1, y1, z1, value);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -358,8 +354,7 @@ int mf_apply_box_to_flags(mf_grid* gp, float x0, float y0, float z0, float x1, f
   REQ_GRID(gp, G(gp)->isInt(), "grid", "Shape::applyToGrid");
   Grid* gr = G(gp); Solver* s = gr->s; s->use();
   gr->outflowState = -1;
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
-  MF_LAUNCH(s, k_apply_box<int>, gd, b, geo(s), gr->di(), x0, y0, z0, x1, y1, z1, value);
+  MF_LAUNCH_IJK(s, k_apply_box<int>, gr->di(), x0, y0, z0, x1, y1, z1, value);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -375,8 +370,7 @@ int mf_apply_cylinder_to_real(mf_grid* gp, float cx, float cy, float cz, float r
     else if (l > 1e-6f * 1e-6f) { zlen = std::sqrt(l); const float inv = (float)(1. / (double)zlen); zx *= inv; zy *= inv; zz *= inv; }
     else { zx = zy = zz = 0.f; zlen = 0.f; }
   }
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
-  MF_LAUNCH(s, k_apply_cylinder, gd, b, geo(s), gr->d, cx, cy, cz, r, zx, zy, zz, zlen, value);
+  MF_LAUNCH_IJK(s, k_apply_cylinder, gr->d, cx, cy, cz, r, zx, zy, zz, zlen, value);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -394,8 +388,7 @@ int mf_add_buoyancy(const mf_grid* fp, const mf_grid* dp, mf_grid* vp, float gx,
   const float fx = ((-gx * dt) / gridScale) * coefficient;
   const float fy = ((-gy * dt) / gridScale) * coefficient;
   const float fz = ((-gz * dt) / gridScale) * coefficient;
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
-  MF_LAUNCH(s, k_add_buoyancy, gd, b, geo(s), flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
+  MF_LAUNCH_IJK(s, k_add_buoyancy, flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -409,8 +402,7 @@ int mf_add_gravity(const mf_grid* fp, mf_grid* vp, float gx, float gy, float gz,
   const float gridScale = scale ? s->dx : 1.0f;
   const float dt = s->dt;
   const float fx = (gx * dt) / gridScale, fy = (gy * dt) / gridScale, fz = (gz * dt) / gridScale;   // extforces.cpp:63-64
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
-  MF_LAUNCH(s, k_apply_force, gd, b, geo(s), flags->di(), v3(G(vp)), fx, fy, fz, exclude ? G(exclude)->d : nullptr, 1);
+  MF_LAUNCH_IJK(s, k_apply_force, flags->di(), v3(G(vp)), fx, fy, fz, exclude ? G(exclude)->d : nullptr, 1);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -419,11 +411,10 @@ int mf_set_inflow_bcs(mf_grid* vp, const char* dir, float vx, float vy, float vz
   MF_API_BEGIN
   REQ_GRID(vp, G(vp)->isMAC(), "vel", "setInflowBcs");
   Grid* vel = G(vp); Solver* s = vel->s; s->use();
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
   const int size[3] = { s->nx, s->ny, s->nz };
   for (const char* c = dir; c && *c; c++) {
-    if (*c >= 'x' && *c <= 'z') { MF_LAUNCH(s, k_set_inflow, gd, b, geo(s), v3(vel), *c - 'x', 0, vx, vy, vz); }
-    else if (*c >= 'X' && *c <= 'Z') { const int d = *c - 'X'; MF_LAUNCH(s, k_set_inflow, gd, b, geo(s), v3(vel), d, size[d] - 1, vx, vy, vz); }
+    if (*c >= 'x' && *c <= 'z') { MF_LAUNCH_IJK(s, k_set_inflow, v3(vel), *c - 'x', 0, vx, vy, vz); }
+    else if (*c >= 'X' && *c <= 'Z') { const int d = *c - 'X'; MF_LAUNCH_IJK(s, k_set_inflow, v3(vel), d, size[d] - 1, vx, vy, vz); }
     else mfErr("invalid character in direction string. Only [xyzXYZ] allowed.");
   }
   MF_LAUNCH_CHECK();
@@ -439,16 +430,15 @@ int mf_set_wall_bcs(const mf_grid* fp, mf_grid* vp, const mf_grid* obvel, const 
   if (obvel) REQ_GRID(obvel, G(obvel)->isMAC(), "obvel", "setWallBcs");
   if (fractions) REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "setWallBcs");
   if (phiObs) REQ_GRID(phiObs, G(phiObs)->isReal(), "phiObs", "setWallBcs");
-  const dim3 b = ijkBlock(s), gd = ijkGrid(s, b);
   if (!phiObs || !fractions) {
     CV3 ov; ov.x = ov.y = ov.z = nullptr;
     if (obvel) ov = cv3(G(obvel));
-    MF_LAUNCH(s, k_set_wall_bcs, gd, b, geo(s), flags->di(), v3(vel), ov, obvel ? 1 : 0);
+    MF_LAUNCH_IJK(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0);
   } else {
     mfAssert(s->nx >= 3 && s->ny >= 3, "setWallBcs: grid too small");
     float* tmp = s->getVec();
     Grid tg = *vel; tg.d = tmp;
-    MF_LAUNCH(s, k_set_wall_bcs_frac, gd, b, geo(s), flags->di(), cv3(vel), v3(&tg), G(phiObs)->d);
+    MF_LAUNCH_IJK(s, k_set_wall_bcs_frac, flags->di(), cv3(vel), v3(&tg), G(phiObs)->d);
     float* old = vel->d; vel->d = tmp;     // vel.swap(tmpvel)
     s->putVec(old);
   }

@@ -29,7 +29,8 @@ struct LvlD {
   int perm;            // 0 natural (level 0), 1 colour-blocked
   int PX, PY, PZ;      // blocked: padded half sizes
   int NC, zoff;        // blocked: colours (8 / 4) and z padding offset (1 / 0)
-  int na;              // entries per plane: n (natural) or PZ*NC*PY*PX
+  int na;              // entries per vector: n (natural) or PZ*NC*PY*PX
+  long long as;        // stride between operator planes A[e*as + p] (>= na; a whole number of allocation granules when distributed)
   float* A; float* x; float* b; float* r;
   unsigned char* type;
   const unsigned short* code;   // level 0 only: compact operator (or nullptr)
@@ -58,10 +59,11 @@ __device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, 
   x = 2 * lx + (c & 1); y = 2 * ly + ((c >> 1) & 1); z = 2 * lz + ((c >> 2) & 1);
   return lx >= 0 && ly >= 0 && lz >= 0 && x < L.sx && y < L.sy && z < L.sz;
 }
+// setup kernels walk the storage range [p0, p1) (a rank's share of the level)
 #define MG_P_FROM_THREAD(L) \
-  const int p = blockIdx.x * blockDim.x + threadIdx.x; \
+  const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x; \
   int vx, vy, vz; \
-  if (!mgDecode((L), p, vx, vy, vz)) return;
+  if (p >= p1 || !mgDecode((L), p, vx, vy, vz)) return;
 
 // ---- level-0 operator -------------------------------------------------------------------------------------
 // 16-bit code: bit0/1/2 coupling to +x/+y/+z (coefficient -1), bit3/4/5 coupling to -x/-y/-z, bits 6-8 the diagonal
@@ -77,7 +79,8 @@ template <bool CODE>
 __global__ void __launch_bounds__(256) k_mg_copy_activate(LvlD L, MgDims D, const float* __restrict__ A0, const float* __restrict__ Ai,
                                                           const float* __restrict__ Aj, const float* __restrict__ Ak, float trivialScale,
                                                           unsigned short* __restrict__ code,
-                                                          int* __restrict__ found /* [0]=nonZeroStencilSum, [1]=trivial, [2]=not codable */) {
+                                                          int* __restrict__ found /* [0]=nonZeroStencilSum, [1]=trivial, [2]=not codable */,
+                                                          int p0, int p1) {
   MG_P_FROM_THREAD(L)
   const int v = p, n = L.n;
   float a[7];
@@ -111,12 +114,12 @@ __global__ void __launch_bounds__(256) k_mg_copy_activate(LvlD L, MgDims D, cons
     if (!ok) found[2] = 1;
     code[v] = (unsigned short)c;
   } else {
-    L.A[v] = diag; L.A[n + v] = a[1]; L.A[2 * (long long)n + v] = a[2];
-    if (D.is3D) L.A[3 * (long long)n + v] = a[3];
+    L.A[v] = diag; L.A[L.as + v] = a[1]; L.A[2 * L.as + v] = a[2];
+    if (D.is3D) L.A[3 * L.as + v] = a[3];
   }
 }
 
-__global__ void k_mg_fill_type(LvlD L, unsigned char val) {
+__global__ void k_mg_fill_type(LvlD L, unsigned char val, int p0, int p1) {
   MG_P_FROM_THREAD(L)
   L.type[p] = val;
 }
@@ -124,7 +127,7 @@ __global__ void k_mg_fill_type(LvlD L, unsigned char val) {
 // one sweep of the order-independent part of genCoarseGrid (multigrid.cpp:520-578): a fine vertex that is still in the
 // heap with exactly one free interpolation vertex selects it ('zero').  flags[0] = changed, flags[1] = some vertex still
 // has >= 2 free interpolation vertices (the serial algorithm would have to pop it: order-dependent -> host fallback).
-__global__ void __launch_bounds__(256) k_mg_coarsen_sweep(LvlD F, LvlD C, int* __restrict__ flags) {
+__global__ void __launch_bounds__(256) k_mg_coarsen_sweep(LvlD F, LvlD C, int* __restrict__ flags, int p0, int p1) {
   MG_P_FROM_THREAD(F)
   if (F.type[p] == vtInactive) return;
   int cnt = 0, last = -1;
@@ -138,7 +141,7 @@ __global__ void __launch_bounds__(256) k_mg_coarsen_sweep(LvlD F, LvlD C, int* _
   else if (cnt >= 2) flags[1] = 1;
 }
 // knActivateCoarseVertices (multigrid.cpp:507-516)
-__global__ void k_mg_coarsen_finalize(LvlD L) {
+__global__ void k_mg_coarsen_finalize(LvlD L, int p0, int p1) {
   MG_P_FROM_THREAD(L)
   unsigned char c = L.type[p];
   if (c == vtFree) c = vtRemoved;
@@ -149,8 +152,8 @@ __global__ void k_mg_coarsen_finalize(LvlD L) {
 
 // ---- level-0 operator policies: float planes or compact code ------------------------------------------------
 struct L0Float {
-  const float* A; const unsigned char* type; int n; float trivialScale;
-  __device__ __forceinline__ L0Float(const LvlD& L, float ts) : A(L.A), type(L.type), n(L.n), trivialScale(ts) {}
+  const float* A; const unsigned char* type; long long n; float trivialScale;
+  __device__ __forceinline__ L0Float(const LvlD& L, float ts) : A(L.A), type(L.type), n(L.as), trivialScale(ts) {}
   struct Row { unsigned char t; };
   __device__ __forceinline__ Row row(int v) const { Row r; r.t = type[v]; return r; }
   __device__ __forceinline__ bool inactive(const Row& r) const { return r.t == vtInactive; }
@@ -158,7 +161,7 @@ struct L0Float {
   __device__ __forceinline__ float diag(const Row&, int v) const { return A[v]; }
   // coefficient of the edge leaving v in direction DIR (0:-x 1:+x 2:-y 3:+y 4:-z 5:+z); nb = neighbour index
   template <int DIR> __device__ __forceinline__ float coef(const Row&, int v, int nb) const {
-    return A[(long long)(1 + DIR / 2) * n + ((DIR & 1) ? v : nb)];
+    return A[(1 + DIR / 2) * n + ((DIR & 1) ? v : nb)];
   }
   template <int DIR> __device__ __forceinline__ float sub(const Row& r, int v, int nb, float sum, float xn) const { return sum - coef<DIR>(r, v, nb) * xn; }
 };
@@ -273,7 +276,7 @@ __device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float
         const int ncx = (cx + dx) & 1, ncy = (cy + dy) & 1, ncz = (cz + dz) & 1;
         const int nc = ncx | (ncy << 1) | (ncz << 2);
         const int pn = p + ((cz + dz) >> 1) * L.NC * PXY + (nc - c) * PXY + ((cy + dy) >> 1) * L.PX + ((cx + dx) >> 1);
-        const float a = (s < SS) ? A[(long long)(SS - 1 - s) * L.na + pn] : A[(long long)(s - SS + 1) * L.na + p];
+        const float a = (s < SS) ? A[(SS - 1 - s) * L.as + pn] : A[(s - SS + 1) * L.as + p];
         sum -= a * x[pn];
       }
   return sum;
@@ -364,10 +367,11 @@ template <class OP> __device__ __forceinline__ float mgCoef0(const OP& op, int s
 }
 // knGenCoarseGridOperator, l == 1 (multigrid.cpp:594-614)
 template <class OP>
-__global__ void __launch_bounds__(128) k_mg_galerkin1(LvlD F, LvlD C, MgDims D, const MgPath* __restrict__ paths, int npaths, float trivialScale) {
+__global__ void __launch_bounds__(128) k_mg_galerkin1(LvlD F, LvlD C, MgDims D, const MgPath* __restrict__ paths, int npaths, float trivialScale,
+                                                      int p0, int p1) {
   MG_P_FROM_THREAD(C)
   const int v = p;
-  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = 0.f; return; }
+  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[e * C.as + v] = 0.f; return; }
   const OP op(F, trivialScale);
   float acc[14];
 #pragma unroll
@@ -390,14 +394,14 @@ __global__ void __launch_bounds__(128) k_mg_galerkin1(LvlD F, LvlD C, MgDims D, 
 #pragma unroll
     for (int e = 0; e < 14; e++) if (e == pt.sc) acc[e] += add;
   }
-  for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = acc[e];
+  for (int e = 0; e < D.SS; e++) C.A[e * C.as + v] = acc[e];
 }
 
 // knGenCoarseGridOperator, l > 1 (multigrid.cpp:615-656); F has the 27-point layout
-__global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D) {
+__global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D, int p0, int p1) {
   MG_P_FROM_THREAD(C)
   const int v = p;
-  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[(long long)e * C.na + v] = 0.f; return; }
+  if (C.type[v] == vtInactive) { for (int e = 0; e < D.SS; e++) C.A[e * C.as + v] = 0.f; return; }
   float acc[14];
 #pragma unroll
   for (int e = 0; e < 14; e++) acc[e] = 0.f;
@@ -426,15 +430,15 @@ __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D) {
         const int sf = (Wx - Ux + 1) + 3 * (Wy - Uy + 1) + 9 * (Wz - Uz + smz);
         const float iw = 1.0f / (float)(1 << ((Wx % 2) + (Wy % 2) + (Wz % 2)));
         float a;
-        if (sf < SS) a = F.A[(long long)(SS - 1 - sf) * F.na + w];
-        else         a = F.A[(long long)(sf - SS + 1) * F.na + u];
+        if (sf < SS) a = F.A[(SS - 1 - sf) * F.as + w];
+        else         a = F.A[(sf - SS + 1) * F.as + u];
         const float add = rw * a * iw;
 #pragma unroll
         for (int q = 0; q < 14; q++) if (q == e) acc[q] += add;
       }
     }
   }
-  for (int e = 0; e < SS; e++) C.A[(long long)e * C.na + v] = acc[e];
+  for (int e = 0; e < SS; e++) C.A[e * C.as + v] = acc[e];
 }
 
 } // namespace mf

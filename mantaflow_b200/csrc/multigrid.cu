@@ -3,6 +3,7 @@
 // knGenCoarseGridOperator :580-657, smoothGS :713-737, solveCG :796-902).
 #include "multigrid.h"
 #include "mg_kernels.cuh"
+#include "comm.h"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -20,9 +21,45 @@ struct MgHierarchy {
   float coarsestAcc, trivialScale;
   int pre, post;
   MgPath* dPaths; int npaths;
-  int* dFlags;              // device scratch: [0..1] activate flags, [2..3] coarsening flags
+  int* dFlags;              // job-wide device scratch: [0..3] activate flags, [4..5] coarsening flags
   int usedFallback;
+  bool pendingSolo;         // a group of rank-0-only launches has not been followed by a cross-rank barrier yet
 };
+
+// ---- partition of a level over the ranks ----------------------------------------------------------------------
+// Levels are split by z (level 0: the solver's slabs; blocked levels: pairs of z planes).  Levels too small to be worth
+// splitting are handled by rank 0 alone ("solo"), and consecutive solo launch groups need no cross-rank barrier in between.
+static bool lvlSolo(const MgHierarchy* mg, int l) {
+  const Solver* s = mg->s;
+  if (!s->multi() || l == 0) return false;
+  const LvlD& L = mg->lv[l];
+  return L.n < 32768 || (L.PZ - 2) < 2 * s->nranks;
+}
+// blocked level: range of z pairs of rank r
+static void lvlPairs(const MgHierarchy* mg, int l, int r, int& lz0, int& lz1) {
+  const Solver* s = mg->s; const LvlD& L = mg->lv[l];
+  const int BZ = mg->D.is3D ? L.PZ - 2 : 1;
+  if (!s->multi()) { lz0 = 0; lz1 = BZ; return; }
+  if (lvlSolo(mg, l)) { lz0 = 0; lz1 = (r == 0) ? BZ : 0; return; }
+  lz0 = (int)((long long)BZ * r / s->nranks); lz1 = (int)((long long)BZ * (r + 1) / s->nranks);
+}
+// natural z range of rank r on level l
+static void lvlPlanes(const MgHierarchy* mg, int l, int r, int& z0, int& z1) {
+  const Solver* s = mg->s; const LvlD& L = mg->lv[l];
+  if (l == 0) { z0 = s->multi() ? s->zsplit[r] : 0; z1 = s->multi() ? s->zsplit[r + 1] : L.sz; return; }
+  int a, b; lvlPairs(mg, l, r, a, b);
+  z0 = 2 * a < L.sz ? 2 * a : L.sz; z1 = 2 * b < L.sz ? 2 * b : L.sz;
+}
+// storage range of rank r on level l (setup kernels)
+static void lvlStore(const MgHierarchy* mg, int l, int r, int& p0, int& p1) {
+  const Solver* s = mg->s; const LvlD& L = mg->lv[l];
+  if (!s->multi()) { p0 = 0; p1 = L.na; return; }
+  if (lvlSolo(mg, l)) { p0 = 0; p1 = (r == 0) ? L.na : 0; return; }
+  p0 = (int)((long long)L.na * r / s->nranks); p1 = (int)((long long)L.na * (r + 1) / s->nranks);
+}
+static void beginGroup(MgHierarchy* mg, bool solo) { if (!solo && mg->pendingSolo) { mg->s->rankSync(); mg->pendingSolo = false; } }
+static void endGroup(MgHierarchy* mg, bool solo) { if (!solo) mg->s->rankSync(); else if (mg->s->multi()) mg->pendingSolo = true; }
+static void flushGroups(MgHierarchy* mg) { if (mg->pendingSolo) { mg->s->rankSync(); mg->pendingSolo = false; } }
 
 // ---- coarsest level: Jacobi-preconditioned CG in double, one CTA (solveCG, multigrid.cpp:796-902) ---------
 // One thread per vertex (n <= 1024).  The 27 (7) coefficients of the thread's row are loaded once into registers, the
@@ -57,7 +94,7 @@ __global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float a
   if (active) {
     if (LEVEL0) {
       // order -x,+x,-y,+y,-z,+z, centre (multigrid.cpp:840-850 for l == 0)
-      const int n = L.n;
+      const long long n = L.as;
       if (vx > 0)        { coef[0] = L.A[n + v - 1]; mask |= 1u; }
       if (vx < L.sx - 1) { coef[1] = L.A[n + v]; mask |= 2u; }
       if (vy > 0)        { coef[2] = L.A[2 * n + v - Y]; mask |= 4u; }
@@ -82,7 +119,7 @@ __global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float a
             if (mgInGrid(L, Nx, Ny, Nz)) {
               const int pn = mgIdx(L, Nx, Ny, Nz);
               if (L.type[pn] != vtInactive) {
-                coef[slot] = (s < SS) ? L.A[(long long)(SS - 1 - s) * L.na + pn] : L.A[(long long)(s - SS + 1) * L.na + p];
+                coef[slot] = (s < SS) ? L.A[(SS - 1 - s) * L.as + pn] : L.A[(s - SS + 1) * L.as + p];
                 mask |= 1u << slot;
               }
             }
@@ -182,6 +219,14 @@ static void buildPaths(MgHierarchy* mg) {
   CUDA_CHECK(cudaMemcpy(mg->dPaths, hp.data(), sizeof(MgPath) * hp.size(), cudaMemcpyHostToDevice));
 }
 
+// stride (in floats) between operator planes: every plane is split over the GPUs by z like the vectors, so on a distributed
+// solver a plane covers a whole number of allocation granules
+static long long planeStride(const Solver* s, long long n) {
+  if (!(s->comm && !comm_emulated(s->comm))) return n;
+  const long long unit = (long long)(comm_granularity(s->comm) / sizeof(float));
+  return (n + unit - 1) / unit * unit;
+}
+
 static void setLayout(LvlD& L, int sx, int sy, int sz, bool is3D, bool blocked) {
   L.sx = sx; L.sy = sy; L.sz = sz; L.n = sx * sy * sz;
   L.perm = blocked ? 1 : 0;
@@ -189,14 +234,14 @@ static void setLayout(LvlD& L, int sx, int sy, int sz, bool is3D, bool blocked) 
   L.PX = (sx + 1) / 2 + 2; L.PY = (sy + 1) / 2 + 2; L.PZ = is3D ? (sz + 1) / 2 + 2 : 1;
   const long long na = blocked ? (long long)L.PZ * L.NC * L.PY * L.PX : (long long)L.n;
   mfAssert(na * 14 < (1LL << 40) && na < (1LL << 31), "GridMg: level too large for 32-bit vertex indices");
-  L.na = (int)na;
+  L.na = (int)na; L.as = na;
   L.A = L.x = L.b = L.r = nullptr; L.type = nullptr; L.code = nullptr;
 }
 
 MgHierarchy* mg_create(Solver* s) {
   mfAssert(s->N < (1LL << 31), "GridMg: grid too large for 32-bit vertex indices");
   MgHierarchy* mg = new MgHierarchy();
-  mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
+  mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
@@ -205,18 +250,15 @@ MgHierarchy* mg_create(Solver* s) {
   long long n = (long long)sx * sy * sz;
   auto addLevel = [&](int l) {
     LvlD L; setLayout(L, sx, sy, sz, is3D, l > 0);
-    const size_t na = (size_t)L.na;
-    CUDA_CHECK(cudaMalloc(&L.r, sizeof(float) * na));
-    CUDA_CHECK(cudaMemset(L.r, 0, sizeof(float) * na));
-    CUDA_CHECK(cudaMalloc(&L.type, na));
-    CUDA_CHECK(cudaMemset(L.type, 0, na));
+    // every array is zero-filled by galloc.  Operator planes are separate components, so that each plane is split over the
+    // GPUs by z like the vectors; the plane stride is padded to the allocation granularity when the level is distributed.
+    L.r = (float*)s->galloc(sizeof(float) * (size_t)L.na);
+    L.type = (unsigned char*)s->galloc((size_t)L.na);
     if (l > 0) {
-      CUDA_CHECK(cudaMalloc(&L.A, sizeof(float) * na * mg->D.SS));
-      CUDA_CHECK(cudaMemset(L.A, 0, sizeof(float) * na * mg->D.SS));
-      CUDA_CHECK(cudaMalloc(&L.x, sizeof(float) * na));
-      CUDA_CHECK(cudaMalloc(&L.b, sizeof(float) * na));
-      CUDA_CHECK(cudaMemset(L.x, 0, sizeof(float) * na));
-      CUDA_CHECK(cudaMemset(L.b, 0, sizeof(float) * na));
+      L.as = planeStride(s, L.na);
+      L.A = (float*)s->galloc(sizeof(float) * (size_t)L.na, mg->D.SS, sizeof(float) * (size_t)L.as);
+      L.x = (float*)s->galloc(sizeof(float) * (size_t)L.na);
+      L.b = (float*)s->galloc(sizeof(float) * (size_t)L.na);
     }                                                      // level 0: A (float planes) or code0 are allocated by mg_set_a
     mg->lv.push_back(L);
   };
@@ -229,7 +271,7 @@ MgHierarchy* mg_create(Solver* s) {
     addLevel(l);
   }
   mfAssert(mg->lv.back().n <= 1024, "GridMg: coarsest level has more than 1024 vertices");
-  CUDA_CHECK(cudaMalloc(&mg->dFlags, sizeof(int) * 8));
+  mg->dFlags = (int*)s->galloc(sizeof(int) * 8);
   buildPaths(mg);
   return mg;
 }
@@ -239,12 +281,13 @@ void mg_destroy(MgHierarchy* mg) {
   cudaStreamSynchronize(mg->s->stream);
   for (size_t l = 0; l < mg->lv.size(); l++) {
     LvlD& L = mg->lv[l];
-    if (L.A) cudaFree(L.A);
-    cudaFree(L.r); cudaFree(L.type);
-    if (l > 0) { cudaFree(L.x); cudaFree(L.b); }
+    Solver* s = mg->s;
+    if (L.A) s->gfree(L.A);
+    s->gfree(L.r); s->gfree(L.type);
+    if (l > 0) { s->gfree(L.x); s->gfree(L.b); }
   }
-  if (mg->code0) cudaFree(mg->code0);
-  cudaFree(mg->dFlags); cudaFree(mg->dPaths);
+  if (mg->code0) mg->s->gfree(mg->code0);
+  mg->s->gfree(mg->dFlags); cudaFree(mg->dPaths);
   delete mg;
 }
 
@@ -346,27 +389,37 @@ static void coarsenOnHost(MgHierarchy* mg, int l) {
     if (c == vtRemoved) c = vtInactive;
     cts[mgIdx(C, i % C.sx, (i % cxy) / C.sx, i / cxy)] = c;
   }
-  CUDA_CHECK(cudaMemcpyAsync(C.type, cts.data(), C.na, cudaMemcpyHostToDevice, s->stream));
+  // every process computes the same classification; one writes it
+  if (s->rankBegin == 0) CUDA_CHECK(cudaMemcpyAsync(C.type, cts.data(), C.na, cudaMemcpyHostToDevice, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  s->rankSync();
   mg->usedFallback++;
 }
+
+// per-rank launch of a setup kernel over its storage share of level l; args follow the kernel's leading parameters
+#define MG_SETUP(mg, l, kern, threads, ...) do { const bool _solo = lvlSolo(mg, l); beginGroup(mg, _solo); \
+  MF_RANKS((mg)->s, _r) { int p0, p1; lvlStore(mg, l, _r, p0, p1); if (p1 > p0) { MF_LAUNCH((mg)->s, kern, cdiv(p1 - p0, threads), threads, __VA_ARGS__, p0, p1); } } \
+  endGroup(mg, _solo); } while (0)
 
 static void genCoarseGrid(MgHierarchy* mg, int l) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[l - 1]; LvlD& C = mg->lv[l];
-  MF_LAUNCH(s, k_mg_fill_type, cdiv(C.na, 256), 256, C, (unsigned char)vtFree);
+  MG_SETUP(mg, l, k_mg_fill_type, 256, C, (unsigned char)vtFree);
+  flushGroups(mg);
   int* flags = mg->dFlags + 4;
   bool pending = false;
   for (int sweep = 0; sweep < 10000; sweep++) {
-    CUDA_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * 2, s->stream));
-    MF_LAUNCH(s, k_mg_coarsen_sweep, cdiv(F.na, 256), 256, F, C, flags);
+    s->clearShared(flags, sizeof(int) * 2);
+    MG_SETUP(mg, l - 1, k_mg_coarsen_sweep, 256, F, C, flags);
+    flushGroups(mg);
     CUDA_CHECK(cudaMemcpyAsync(s->hostInts, flags, sizeof(int) * 2, cudaMemcpyDeviceToHost, s->stream));
     CUDA_CHECK(cudaStreamSynchronize(s->stream));
     pending = s->hostInts[1] != 0;
     if (!s->hostInts[0]) break;
   }
   if (pending) { coarsenOnHost(mg, l); return; }
-  MF_LAUNCH(s, k_mg_coarsen_finalize, cdiv(C.na, 256), 256, C);
+  MG_SETUP(mg, l, k_mg_coarsen_finalize, 256, C);
+  flushGroups(mg);
 }
 
 void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj, const float* Ak) {
@@ -377,17 +430,17 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
   // planes because the coarsest-level CG reads them
   bool coded = false;
   if (maxLevel > 0) {
-    if (!mg->code0) CUDA_CHECK(cudaMalloc(&mg->code0, sizeof(unsigned short) * (size_t)L0.n));
-    CUDA_CHECK(cudaMemsetAsync(mg->dFlags, 0, sizeof(int) * 4, s->stream));
-    MF_LAUNCH(s, k_mg_copy_activate<true>, cdiv(L0.n, 256), 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, mg->code0, mg->dFlags);
+    if (!mg->code0) mg->code0 = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)L0.n);
+    s->clearShared(mg->dFlags, sizeof(int) * 4);
+    MG_SETUP(mg, 0, k_mg_copy_activate<true>, 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, mg->code0, mg->dFlags);
     CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 4, cudaMemcpyDeviceToHost, s->stream));
     CUDA_CHECK(cudaStreamSynchronize(s->stream));
     coded = s->hostInts[2] == 0;
   }
   if (!coded) {
-    if (!L0.A) CUDA_CHECK(cudaMalloc(&L0.A, sizeof(float) * (size_t)L0.n * mg->D.SS0));
-    CUDA_CHECK(cudaMemsetAsync(mg->dFlags, 0, sizeof(int) * 4, s->stream));
-    MF_LAUNCH(s, k_mg_copy_activate<false>, cdiv(L0.n, 256), 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, (unsigned short*)nullptr, mg->dFlags);
+    if (!L0.A) { L0.as = planeStride(s, L0.n); L0.A = (float*)s->galloc(sizeof(float) * (size_t)L0.n, mg->D.SS0, sizeof(float) * (size_t)L0.as); }
+    s->clearShared(mg->dFlags, sizeof(int) * 4);
+    MG_SETUP(mg, 0, k_mg_copy_activate<false>, 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, (unsigned short*)nullptr, mg->dFlags);
     CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 4, cudaMemcpyDeviceToHost, s->stream));
     CUDA_CHECK(cudaStreamSynchronize(s->stream));
   }
@@ -395,29 +448,36 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
   L0.code = coded ? mg->code0 : nullptr;
   mg->nonZeroStencilSum = s->hostInts[0] != 0;
   mg->hasTrivial = s->hostInts[1] != 0;
-  for (size_t l = 1; l < mg->lv.size(); l++) {
-    genCoarseGrid(mg, (int)l);
+  for (int l = 1; l <= maxLevel; l++) {
+    genCoarseGrid(mg, l);
+    LvlD& F = mg->lv[l - 1]; LvlD& C = mg->lv[l];
     if (l == 1) {
-      if (coded) { MF_LAUNCH(s, k_mg_galerkin1<L0Code>, cdiv(mg->lv[1].na, 128), 128, mg->lv[0], mg->lv[1], mg->D, mg->dPaths, mg->npaths, mg->trivialScale); }
-      else       { MF_LAUNCH(s, k_mg_galerkin1<L0Float>, cdiv(mg->lv[1].na, 128), 128, mg->lv[0], mg->lv[1], mg->D, mg->dPaths, mg->npaths, mg->trivialScale); }
-    } else { MF_LAUNCH(s, k_mg_galerkin, cdiv(mg->lv[l].na, 128), 128, mg->lv[l - 1], mg->lv[l], mg->D); }
+      if (coded) MG_SETUP(mg, l, k_mg_galerkin1<L0Code>, 128, F, C, mg->D, mg->dPaths, mg->npaths, mg->trivialScale);
+      else       MG_SETUP(mg, l, k_mg_galerkin1<L0Float>, 128, F, C, mg->D, mg->dPaths, mg->npaths, mg->trivialScale);
+    } else MG_SETUP(mg, l, k_mg_galerkin, 128, F, C, mg->D);
+    flushGroups(mg);
   }
   MF_LAUNCH_CHECK();
   mg->aSet = true;
 }
 
-// launch helpers: z range of level l handled by this process (the whole level on a single GPU)
+// ---- V-cycle launches: every group = the same kernel on every local rank's z range of the level, then the barrier ----
 static inline int rowsBlocks(const LvlD& L, int z0, int z1) { return (int)cdiv((long long)L.sy * (z1 - z0), 8); }   // 8 warps per CTA, one row each
 
 template <class OP>
 static void smooth0(MgHierarchy* mg, bool reversed, bool xzero) {
   Solver* s = mg->s;
   LvlD& L = mg->lv[0];
-  const int z0 = 0, z1 = L.sz;
   for (int c = 0; c < 2; c++) {
     const int color = reversed ? 1 - c : c;
-    if (xzero && c == 0) { MF_LAUNCH(s, (k_mg_smooth0<OP, true>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
-    else                 { MF_LAUNCH(s, (k_mg_smooth0<OP, false>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+    beginGroup(mg, false);
+    MF_RANKS(s, r) {
+      int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+      if (z1 <= z0) continue;
+      if (xzero && c == 0) { MF_LAUNCH(s, (k_mg_smooth0<OP, true>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+      else                 { MF_LAUNCH(s, (k_mg_smooth0<OP, false>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+    }
+    endGroup(mg, false);
   }
 }
 
@@ -428,13 +488,70 @@ static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
     if (mg->useCode) smooth0<L0Code>(mg, reversed, xzero); else smooth0<L0Float>(mg, reversed, xzero);
     return;
   }
-  const int lz0 = 0, lz1 = mg->D.is3D ? L.PZ - 2 : 1;
-  const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0);
+  const bool solo = lvlSolo(mg, l);
   for (int c = 0; c < L.NC; c++) {
     const int color = reversed ? L.NC - 1 - c : c;
-    if (mg->D.is3D) { MF_LAUNCH(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
-    else            { MF_LAUNCH(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+    beginGroup(mg, solo);
+    MF_RANKS(s, r) {
+      int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
+      if (lz1 <= lz0) continue;
+      const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0);
+      if (mg->D.is3D) { MF_LAUNCH(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+      else            { MF_LAUNCH(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+    }
+    endGroup(mg, solo);
   }
+}
+
+static void residual(MgHierarchy* mg, int l) {
+  Solver* s = mg->s;
+  LvlD& L = mg->lv[l];
+  const bool solo = lvlSolo(mg, l);
+  beginGroup(mg, solo);
+  MF_RANKS(s, r) {
+    if (l == 0) {
+      int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+      if (z1 <= z0) continue;
+      if (mg->useCode) { MF_LAUNCH(s, k_mg_residual0<L0Code>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
+      else             { MF_LAUNCH(s, k_mg_residual0<L0Float>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
+    } else {
+      int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
+      if (lz1 <= lz0) continue;
+      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0), 128), L.NC);
+      if (mg->D.is3D) { MF_LAUNCH(s, k_mg_residual<true>, gr, 128, L, lz0, lz1); }
+      else            { MF_LAUNCH(s, k_mg_residual<false>, gr, 128, L, lz0, lz1); }
+    }
+  }
+  endGroup(mg, solo);
+}
+// coarse level l+1 <- fine level l; the coarse level's partition drives the launch
+static void restrictTo(MgHierarchy* mg, int l) {
+  Solver* s = mg->s;
+  LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
+  const bool solo = lvlSolo(mg, l + 1);
+  beginGroup(mg, solo && lvlSolo(mg, l));     // reads the fine residual: the fine level's writers must have arrived
+  MF_RANKS(s, r) {
+    int z0, z1; lvlPlanes(mg, l + 1, r, z0, z1);
+    if (z1 <= z0) continue;
+    const long long nt = (long long)C.sx * C.sy * (z1 - z0);
+    if (mg->D.is3D) { MF_LAUNCH(s, k_mg_restrict<true>, cdiv(nt, 128), 128, F, C, z0, z1); }
+    else            { MF_LAUNCH(s, k_mg_restrict<false>, cdiv(nt, 128), 128, F, C, z0, z1); }
+  }
+  endGroup(mg, solo);
+}
+// fine level l += P * coarse level l+1; the fine level's partition drives the launch
+static void interpAdd(MgHierarchy* mg, int l) {
+  Solver* s = mg->s;
+  LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
+  const bool solo = lvlSolo(mg, l);
+  beginGroup(mg, solo);
+  MF_RANKS(s, r) {
+    int z0, z1; lvlPlanes(mg, l, r, z0, z1);
+    if (z1 <= z0) continue;
+    const long long nt = (long long)F.sx * F.sy * (z1 - z0);
+    MF_LAUNCH(s, k_mg_interp_add, cdiv(nt, 256), 256, F, C, z0, z1);
+  }
+  endGroup(mg, solo);
 }
 
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
@@ -442,33 +559,32 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
   mfAssert(mg->aSet, "GridMg::setRhs Error: A has not been set.");
   const int maxLevel = (int)mg->lv.size() - 1;
-  const bool is3D = mg->D.is3D != 0;
   LvlD& L0 = mg->lv[0];
   L0.b = const_cast<float*>(rhs);      // knSetRhs' trivial-row scaling is applied on the fly (OP::rhs)
   L0.x = dst;
-  if (maxLevel == 0 || mg->pre == 0) CUDA_CHECK(cudaMemsetAsync(dst, 0, sizeof(float) * (size_t)L0.n, s->stream));
+  if (maxLevel == 0 || mg->pre == 0) {
+    MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) CUDA_CHECK(cudaMemsetAsync(dst + sp.off, 0, sizeof(float) * (size_t)sp.n, s->stream)); }
+    s->rankSync();
+  }
   for (int l = 0; l < maxLevel; l++) {
     for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0);
-    LvlD& L = mg->lv[l]; LvlD& C = mg->lv[l + 1];
-    if (l == 0) {
-      if (mg->useCode) { MF_LAUNCH(s, k_mg_residual0<L0Code>, rowsBlocks(L, 0, L.sz), 256, L, mg->D, mg->trivialScale, 0, L.sz); }
-      else             { MF_LAUNCH(s, k_mg_residual0<L0Float>, rowsBlocks(L, 0, L.sz), 256, L, mg->D, mg->trivialScale, 0, L.sz); }
-    } else {
-      const int lz1 = is3D ? L.PZ - 2 : 1;
-      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2) * lz1, 128), L.NC);
-      if (is3D) { MF_LAUNCH(s, k_mg_residual<true>, gr, 128, L, 0, lz1); }
-      else      { MF_LAUNCH(s, k_mg_residual<false>, gr, 128, L, 0, lz1); }
-    }
-    if (is3D) { MF_LAUNCH(s, k_mg_restrict<true>, cdiv(C.n, 128), 128, L, C, 0, C.sz); }
-    else      { MF_LAUNCH(s, k_mg_restrict<false>, cdiv(C.n, 128), 128, L, C, 0, C.sz); }
+    residual(mg, l);
+    restrictTo(mg, l);
   }
-  if (maxLevel == 0) { MF_LAUNCH(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
-  else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
+  {
+    const bool solo = s->multi();        // the coarsest level is always handled by rank 0
+    beginGroup(mg, solo);
+    if (s->rankBegin == 0) {
+      if (maxLevel == 0) { MF_LAUNCH(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
+      else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
+    }
+    endGroup(mg, solo);
+  }
   for (int l = maxLevel - 1; l >= 0; l--) {
-    LvlD& L = mg->lv[l];
-    MF_LAUNCH(s, k_mg_interp_add, cdiv(L.n, 256), 256, L, mg->lv[l + 1], 0, L.sz);
+    interpAdd(mg, l);
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }
+  flushGroups(mg);
   // the trailing calcResidual(0)/calcResidualNorm(0) of doVCycle only feed its return value, which the CG driver
   // ignores (conjugategrad.cpp:162-167) -- skipped.
 }
@@ -495,11 +611,11 @@ void mg_download_level(MgHierarchy* mg, int l, unsigned char* type, float* A) {
         if (ss > 3) A[(size_t)v * ss + 3] = (c & MGC_ZP) ? -1.f : 0.f;
       }
     } else {
-      std::vector<float> planes((size_t)L.na * ss);
+      std::vector<float> planes((size_t)L.as * ss);
       CUDA_CHECK(cudaMemcpy(planes.data(), L.A, sizeof(float) * planes.size(), cudaMemcpyDeviceToHost));
       for (int v = 0; v < L.n; v++) {
         const int p = mgIdx(L, v % L.sx, (v % xy) / L.sx, v / xy);
-        for (int e = 0; e < ss; e++) A[(size_t)v * ss + e] = planes[(size_t)e * L.na + p];
+        for (int e = 0; e < ss; e++) A[(size_t)v * ss + e] = planes[(size_t)e * L.as + p];
       }
     }
   }

@@ -10,8 +10,15 @@
 
 namespace mf {
 
-static inline dim3 ijkBlock(const Solver* s) { return s->is3D ? dim3(32, 4, 2) : dim3(32, 8, 1); }
-static inline dim3 ijkGrid(const Solver* s, dim3 b) { return dim3(cdiv(s->nx, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z)); }
+// slab-wise whole-array operations (each rank touches its own z-slab of the global array)
+static void slabZero(Solver* s, float* p) {
+  MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) CUDA_CHECK(cudaMemsetAsync(p + sp.off, 0, sizeof(float) * sp.n, s->stream)); }
+  s->rankSync();
+}
+static void slabCopy(Solver* s, float* dst, const float* src) {
+  MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) CUDA_CHECK(cudaMemcpyAsync(dst + sp.off, src + sp.off, sizeof(float) * sp.n, cudaMemcpyDeviceToDevice, s->stream)); }
+  s->rankSync();
+}
 static inline int ewBlocks(const Solver* s, long long n) {
   long long b = (n + 255) / 256, cap = (long long)s->numSMs * 16;
   return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
@@ -36,12 +43,14 @@ static void computeRhs(Solver* s, float* rhs, const Grid* vel, const Grid* flags
   a.phi = p->phi ? G(p->phi)->d : nullptr; a.curv = p->curv ? G(p->curv)->d : nullptr;
   a.surfTens = p->surfTens; a.gfClamp = p->gfClamp;
   a.writeBorder = freshTemp ? 1 : 0;
-  MF_LAUNCH(s, k_make_rhs, tileBlocks(s), 256, geo(s), a, s->redScratch, s->redCounter, s->redOut);
+  MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs, tileBlocks(s, g), 256, g, a, redCtx(s, r), s->redOut); }
+  redFinish<2>(s, RedOps<2>{ { 0, 0 } }, FinStore<2>{ s->redOut });
   if (p->enforceCompatibility) {
     fetchRed(s, 2);
     const double sum = s->redHost[0]; const int cnt = (int)s->redHost[1];
     const float corr = (float)(-sum / (float)cnt);            // rhs += (Real)(-sum / (Real)cnt)
-    MF_LAUNCH(s, k_add_scalar, ewBlocks(s, s->N), 256, rhs, corr, s->N);
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_add_scalar, ewBlocks(s, sp.n), 256, rhs + sp.off, corr, sp.n); }
+    s->rankSync();
   }
 }
 
@@ -56,11 +65,14 @@ struct CgDriver {
   float* P; MgHierarchy* mg;
   CgState host;
   void applyPrecond(bool init) {
-    const Geo g = geo(s);
     if (pcMethod == 1) {
-      dim3 b = ijkBlock(s); dim3 gr(cdiv((s->nx + 1) / 2, b.x), cdiv(s->ny, b.y), cdiv(s->nz, b.z));
-      MF_LAUNCH(s, k_rbic_black, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st);
-      MF_LAUNCH(s, k_rbic_red, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st);
+      const dim3 b = ijkBlockOf(s);
+      MF_RANKS(s, r) { const Geo g = geo(s, r); dim3 gr(cdiv((s->nx + 1) / 2, b.x), cdiv(s->ny, b.y), cdiv(g.k1 - g.k0, b.z));
+                       MF_LAUNCH(s, k_rbic_black, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st); }
+      s->rankSync();
+      MF_RANKS(s, r) { const Geo g = geo(s, r); dim3 gr(cdiv((s->nx + 1) / 2, b.x), cdiv(s->ny, b.y), cdiv(g.k1 - g.k0, b.z));
+                       MF_LAUNCH(s, k_rbic_red, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st); }
+      s->rankSync();
     } else if (pcMethod == 2) {
       mg_apply(mg, v.tmp, v.residual);
     }
@@ -79,25 +91,31 @@ struct CgDriver {
     memcpy(s->hostInts, &h, sizeof(h));
     CUDA_CHECK(cudaMemcpyAsync(st, s->hostInts, sizeof(CgState), cudaMemcpyHostToDevice, s->stream));
     CUDA_CHECK(cudaStreamSynchronize(s->stream));   // hostInts is reused below
-    CUDA_CHECK(cudaMemsetAsync(v.dst, 0, sizeof(float) * N, s->stream));
-    CUDA_CHECK(cudaMemcpyAsync(v.residual, v.rhs, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
+    (void)N;
+    slabZero(s, v.dst);
+    slabCopy(s, v.residual, v.rhs);
     const float* z = v.residual;
     if (pcMethod != 0) { applyPrecond(true); z = v.tmp; }
-    CUDA_CHECK(cudaMemcpyAsync(v.search, z, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
-    MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, N), 256, N, z, v.residual, st, s->redScratch, s->redCounter);
+    slabCopy(s, v.search, z);
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, sp.n), 256, sp.n, z + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+    redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
   }
   void iterate() {
-    const Geo g = geo(s);
-    const long long N = s->N;
-    MF_LAUNCH(s, k_cg_spmv_dot, tileBlocks(s), 256, g, v, st, s->redScratch, s->redCounter);
+    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); }
+    redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
     if (pcMethod == 0) {
-      MF_LAUNCH(s, k_cg_update<true>, redBlocks(s, N), 256, g, v, st, s->redScratch, s->redCounter);
-      MF_LAUNCH(s, k_cg_search, ewBlocks(s, N), 256, N, v.search, v.residual, st);
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_update<true>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<true>{ st });
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
+      s->rankSync();
     } else {
-      MF_LAUNCH(s, k_cg_update<false>, redBlocks(s, N), 256, g, v, st, s->redScratch, s->redCounter);
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_update<false>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<false>{ st });
       applyPrecond(false);
-      MF_LAUNCH(s, k_cg_dot_beta, redBlocks(s, N), 256, N, v.tmp, v.residual, st, s->redScratch, s->redCounter);
-      MF_LAUNCH(s, k_cg_search, ewBlocks(s, N), 256, N, v.search, v.tmp, st);
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_beta, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+      redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
+      s->rankSync();
     }
   }
   // for (iter < maxIter) if (!iterate()) break;   host polls the device flag every `batch` iterations
@@ -128,17 +146,18 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   if (!p->precondition) preconditioner = MF_PC_NONE;
   mfAssert(preconditioner >= 0 && preconditioner <= 3, "solvePressureSystem: unknown preconditioner " << preconditioner);
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "solvePressureSystem: grid too small");
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   SolveTemps t(s);
   CV3 fr = p->fractions ? cv3(G(p->fractions)) : cv3(vel);
-  MF_LAUNCH(s, k_make_laplace, gr, b, g, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0,
-            p->phi ? G(p->phi)->d : nullptr, p->gfClamp);
-  int* fixedDev = s->devFlagsScratch + 2;
+  MF_LAUNCH_IJK(s, k_make_laplace, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0,
+                p->phi ? G(p->phi)->d : nullptr, p->gfClamp);
+  int* fixedDev = s->localInts + 2;
   bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
   if (fixing) {
-    MF_LAUNCH(s, k_flag_stats, tileBlocks(s), 256, g, flags->di(), s->redScratch, s->redCounter, s->redOut);
-    MF_LAUNCH(s, k_fix_pressure, 1, 32, g, flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, fixedDev);
+    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats, tileBlocks(s, g), 256, g, flags->di(), redCtx(s, r), s->redOut); }
+    redFinish<2>(s, RedOps<2>{ { 0, 1 } }, FinStore<2>{ s->redOut });
+    // every process applies the same single-cell fix (identical inputs, value 0: redundant peer writes are benign)
+    MF_LAUNCH(s, k_fix_pressure, 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, fixedDev);
+    s->rankSync();
   }
   CgDriver cg;
   cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr;
@@ -153,7 +172,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     if (preconditioner == MF_PC_MIC && s->is3D) {
       cg.pcMethod = 1;
       t.pc = s->getReal(); cg.P = t.pc;
-      MF_LAUNCH(s, k_rbic_init, gr, b, g, flags->di(), cg.P, t.A0, t.Ai, t.Aj, t.Ak);
+      MF_LAUNCH_IJK(s, k_rbic_init, flags->di(), cg.P, t.A0, t.Ai, t.Aj, t.Ak);
     } else cg.pcMethod = 0;
   } else {
     maxIter = 100; batch = 1;
@@ -182,13 +201,11 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
 }
 
 static void correctVel(Solver* s, Grid* vel, const Grid* pressure, const Grid* flags, const mf_pressure_params* p) {
-  const Geo g = geo(s);
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
-  MF_LAUNCH(s, k_correct_velocity, gr, b, g, flags->di(), v3(vel), pressure->d);
+  MF_LAUNCH_IJK(s, k_correct_velocity, flags->di(), v3(vel), pressure->d);
   if (p->phi) {
-    MF_LAUNCH(s, k_correct_velocity_gf, gr, b, g, flags->di(), v3(vel), pressure->d, G(p->phi)->d, p->gfClamp,
-              p->curv ? G(p->curv)->d : nullptr, p->surfTens);
-    MF_LAUNCH(s, k_replace_clamped_gf, gr, b, g, flags->di(), v3(vel), G(p->phi)->d, p->gfClamp);
+    MF_LAUNCH_IJK(s, k_correct_velocity_gf, flags->di(), v3(vel), pressure->d, G(p->phi)->d, p->gfClamp,
+                  p->curv ? G(p->curv)->d : nullptr, p->surfTens);
+    MF_LAUNCH_IJK(s, k_replace_clamped_gf, flags->di(), v3(vel), G(p->phi)->d, p->gfClamp);
   }
 }
 
@@ -197,8 +214,8 @@ static void correctVel(Solver* s, Grid* vel, const Grid* pressure, const Grid* f
 __global__ void __launch_bounds__(256) k_diffusion_matrix(Geo g, const int* __restrict__ flags, float* A0, float* Ai, float* Aj, float* Ak, float alpha) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   float a0 = 0.f, ai = 0.f, aj = 0.f, ak = 0.f;
   if (interiorCell(g, i, j, k)) { a0 = g.is3D ? 6.f : 4.f; ai = -1.f; aj = -1.f; ak = g.is3D ? -1.f : 0.f; }
@@ -276,7 +293,7 @@ int mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* flags, con
   computeRhs(s, rhs.p, G(vel), G(flags), p, true);
   solveSystem(s, rhs.p, G(vel), G(pressure), G(flags), p, info);
   correctVel(s, G(vel), G(pressure), G(flags), p);
-  if (p->retRhs) CUDA_CHECK(cudaMemcpyAsync(G(p->retRhs)->d, rhs.p, sizeof(float) * s->N, cudaMemcpyDeviceToDevice, s->stream));
+  if (p->retRhs) slabCopy(s, G(p->retRhs)->d, rhs.p);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -297,9 +314,8 @@ int mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_gr
   if (fractions) REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "MakeLaplaceMatrix");
   Solver* s = G(flags)->s; s->use();
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "MakeLaplaceMatrix: grid too small");
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
-  MF_LAUNCH(s, k_make_laplace, gr, b, geo(s), G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f);
+  MF_LAUNCH_IJK(s, k_make_laplace, G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -312,8 +328,7 @@ int mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* src, cons
   REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "ApplyMatrix"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "ApplyMatrix");
   mfAssert(G(dst)->d != G(src)->d, "ApplyMatrix: dst and src must differ");
   Solver* s = G(flags)->s; s->use();
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
-  MF_LAUNCH(s, k_apply_matrix, gr, b, geo(s), G(flags)->di(), G(dst)->d, G(src)->d, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+  MF_LAUNCH_IJK(s, k_apply_matrix, G(flags)->di(), G(dst)->d, G(src)->d, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -326,16 +341,15 @@ int mf_cg_solve_diffusion(const mf_grid* flagsp, mf_grid* gridp, float alpha, fl
   check_same_solver(flags, grid, "cgSolveDiffusion");
   mfAssert(grid->isReal() || grid->isVec(), "cgSolveDiffusion: Grid Type is not supported (only Real, Vec3, MAC, or Levelset)");
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "cgSolveDiffusion: grid too small");
-  const dim3 b = ijkBlock(s), gr = ijkGrid(s, b);
   SolveTemps t(s);
   TmpReal rhs(s);
-  MF_LAUNCH(s, k_diffusion_matrix, gr, b, geo(s), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, alpha);
+  MF_LAUNCH_IJK(s, k_diffusion_matrix, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, alpha);
   int maxDim = s->nx > s->ny ? s->nx : s->ny; if (s->nz > maxDim) maxDim = s->nz;
   const int maxIter = (int)(cgMaxIterFac * maxDim) * (s->is3D ? 1 : 4);
   const int ncomp = grid->isVec() ? (s->is3D ? 3 : 2) : 1;
   for (int c = 0; c < ncomp; c++) {
     float* u = grid->isVec() ? grid->comp(c) : grid->d;
-    CUDA_CHECK(cudaMemcpyAsync(rhs.p, u, sizeof(float) * s->N, cudaMemcpyDeviceToDevice, s->stream));
+    slabCopy(s, rhs.p, u);
     CgDriver cg;
     cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr; cg.pcMethod = 0;
     cg.v.flags = flags->di(); cg.v.dst = u; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;

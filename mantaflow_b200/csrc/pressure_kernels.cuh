@@ -40,7 +40,7 @@ struct RhsArgs {
 };
 
 // MakeRhs: bnd=1, reduce+ (double sum, int cnt)
-__global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, double* partials, unsigned int* counter, double* out) {
+__global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, RedCtx ctx, double* out) {
   __shared__ double sh[32];
   double sum = 0.0, cnt = 0.0;
   MF_TILE_LOOP_BEGIN(g)
@@ -76,9 +76,9 @@ __global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, double* part
     cnt += 1.0;
     a.rhs[idx] = set;
   MF_TILE_LOOP_END
-  sum = blockReduce<OpSum>(sum, sh);
-  cnt = blockReduce<OpSum>(cnt, sh);
-  gridFinish<OpSum, OpSum, 2>(sum, cnt, partials, counter, out, sh);
+  double acc[2] = { sum, cnt };
+  const int ops[2] = { 0, 0 };
+  gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
 }
 
 __global__ void k_add_scalar(float* d, float v, long long n) {
@@ -94,8 +94,8 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
                                                       const float* __restrict__ phi, float gfClamp) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   float a0 = 0.f, ai = 0.f, aj = 0.f, ak = 0.f;
   if (interiorCell(g, i, j, k) && fIsFluid(flags[idx])) {
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
 
 // CountEmptyCells (pressure.cpp:217) + "first interior fluid cell in FOR_IJK_BND order" (:371-381)
 // out[0] = numEmpty, out[1] = min interior fluid index (or INT_MAX-ish)
-__global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict__ flags, double* partials, unsigned int* counter, double* out) {
+__global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict__ flags, RedCtx ctx, double* out) {
   __shared__ double sh[32];
   double numEmpty = 0.0, minFluid = 1e300;
   MF_TILE_LOOP_BEGIN(g)
@@ -144,9 +144,9 @@ __global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict
     if (fIsEmpty(f)) numEmpty += 1.0;
     if (fIsFluid(f) && interiorCell(g, i, j, k)) { const double v = (double)idx; if (v < minFluid) minFluid = v; }
   MF_TILE_LOOP_END
-  numEmpty = blockReduce<OpSum>(numEmpty, sh);
-  minFluid = blockReduce<OpMin>(minFluid, sh);
-  gridFinish<OpSum, OpMin, 2>(numEmpty, minFluid, partials, counter, out, sh);
+  double acc[2] = { numEmpty, minFluid };
+  const int ops[2] = { 0, 1 };
+  gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
 }
 
 // zeroPressureFixing: pick the cell (pressure.cpp:352-383) and apply fixPressure(idx, 0, ...) (:226-245); one thread
@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(256) k_apply_matrix(Geo g, const int* __restri
                                                       const float* __restrict__ Ak) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   dst[idx] = fIsFluid(flags[idx]) ? applyRow(g, idx, src, A0, Ai, Aj, Ak) : src[idx];
 }
@@ -213,8 +213,8 @@ __global__ void __launch_bounds__(256) k_apply_matrix(Geo g, const int* __restri
 __global__ void __launch_bounds__(256) k_correct_velocity(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ p) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   if (!interiorCell(g, i, j, k)) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   const long long X = 1, Y = g.nx, Z = g.Z;
@@ -246,8 +246,8 @@ __global__ void __launch_bounds__(256) k_correct_velocity_gf(Geo g, const int* _
                                                              const float* __restrict__ phi, float gfClamp, const float* __restrict__ curv, float surfTens) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   if (!interiorCell(g, i, j, k)) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   const long long X = 1, Y = g.nx, Z = g.Z;
@@ -280,8 +280,8 @@ __global__ void __launch_bounds__(256) k_correct_velocity_gf(Geo g, const int* _
 __global__ void __launch_bounds__(256) k_replace_clamped_gf(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ phi, float gfClamp) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z;
-  if (i >= g.nx || j >= g.ny || k >= g.nz) return;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
   if (!interiorCell(g, i, j, k)) return;
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
   const long long X = 1, Y = g.nx, Z = g.Z;

@@ -2,6 +2,7 @@
 // Reference: source/fluidsolver.{h,cpp} (temp-grid pool :25-50, ctor :107), source/grid.{h,cpp}.
 #include "common.cuh"
 #include "reduce.cuh"
+#include "comm.h"
 #include <cstring>
 #include <cmath>
 #include <algorithm>
@@ -20,19 +21,49 @@ void check_same_solver(const Grid* a, const Grid* b, const char* what) {
 
 void Solver::use() const { cudaSetDevice(device); }
 
+// ---- multi-GPU plumbing (comm.h) -------------------------------------------------------------------------
+void* Solver::galloc(size_t bytesPerComp, int ncomp, size_t compStride) {
+  if (comm && !comm_emulated(comm)) return comm_alloc(comm, bytesPerComp, ncomp, compStride);
+  const size_t total = ncomp > 1 ? compStride * (size_t)(ncomp - 1) + bytesPerComp : bytesPerComp;
+  void* p = nullptr;
+  CUDA_CHECK(cudaMalloc(&p, total));
+  CUDA_CHECK(cudaMemsetAsync(p, 0, total, stream));
+  return p;
+}
+void Solver::gfree(void* p) {
+  if (!p) return;
+  if (comm && !comm_emulated(comm)) comm_free(comm, p); else cudaFree(p);
+}
+void Solver::rankSync() { if (comm && nranks > 1) comm_barrier(comm, stream); }
+void Solver::clearShared(void* p, size_t bytes) {
+  if (!multi() || comm_emulated(comm)) { CUDA_CHECK(cudaMemsetAsync(p, 0, bytes, stream)); return; }
+  rankSync();                                   // nobody still reads the previous contents
+  if (rankBegin == 0) CUDA_CHECK(cudaMemsetAsync(p, 0, bytes, stream));
+  rankSync();
+}
+RedCtx redCtx(Solver* s, int rank) {
+  RedCtx c; c.partials = s->redScratch; c.counter = s->redCounter; c.nranks = s->nranks; c.rank = rank;
+  c.shared = nullptr; c.stride = 0; c.parity = s->redParity; c.self = s->rankBegin;
+  if (s->multi()) {
+    c.shared = reinterpret_cast<char*>(comm_shared(s->comm, 0));
+    c.stride = (size_t)(reinterpret_cast<char*>(comm_shared(s->comm, 1)) - c.shared);
+  }
+  return c;
+}
+static_assert(COMM_MAX_RANKS == 16 && COMM_RED_K == 8 && offsetof(CommShared, red) == 16 * sizeof(unsigned long long),
+              "reduce.cuh redSlot() hard-codes the CommShared layout");
+
 float* Solver::getReal() {
   if (!poolReal.empty()) { float* p = poolReal.back(); poolReal.pop_back(); return p; }
-  float* p = nullptr;
-  CUDA_CHECK(cudaMalloc(&p, sizeof(float) * (size_t)(N + 64)));
+  float* p = (float*)galloc(sizeof(float) * (size_t)(N + 64));
   poolBytes += sizeof(float) * (N + 64);
   return p;
 }
 void Solver::putReal(float* p) { poolReal.push_back(p); }
 float* Solver::getVec() {
   if (!poolVec.empty()) { float* p = poolVec.back(); poolVec.pop_back(); return p; }
-  float* p = nullptr;
-  CUDA_CHECK(cudaMalloc(&p, sizeof(float) * (size_t)(3 * Np + 64)));
-  poolBytes += sizeof(float) * (3 * Np + 64);
+  float* p = (float*)galloc(sizeof(float) * (size_t)Np, 3, sizeof(float) * (size_t)Np);
+  poolBytes += sizeof(float) * (3 * Np);
   return p;
 }
 void Solver::putVec(float* p) { poolVec.push_back(p); }
@@ -86,48 +117,24 @@ static inline int ewBlocks(const Solver* s, long long n) {
 }
 
 // ---- reductions --------------------------------------------------------------------------
-__global__ void k_dot(const float* __restrict__ a, const float* __restrict__ b, long long n,
-                      double* partials, unsigned int* counter, double* out) {
+// what: 0 dot (float product, double accumulate; conjugategrad.cpp:177), 1 sum of squares in double, 2 min/max
+template <int WHAT, class T>
+__global__ void k_reduce(const T* __restrict__ a, const T* __restrict__ b, long long n, RedCtx ctx, double* out) {
   __shared__ double sh[32];
-  double acc = 0.0;
+  double acc[2] = { WHAT == 2 ? 1e300 : 0.0, -1e300 };
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long st = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += st) acc += (double)(a[i] * b[i]);   // float product, double accumulate (conjugategrad.cpp:177)
-  acc = blockReduce<OpSum>(acc, sh);
-  gridFinish<OpSum, OpSum, 1>(acc, 0.0, partials, counter, out, sh);
-}
-__global__ void k_sumsqr(const float* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
-  __shared__ double sh[32];
-  double acc = 0.0;
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const long long st = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += st) { double v = (double)a[i]; acc += v * v; }
-  acc = blockReduce<OpSum>(acc, sh);
-  gridFinish<OpSum, OpSum, 1>(acc, 0.0, partials, counter, out, sh);
-}
-__global__ void k_minmax(const float* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
-  __shared__ double sh[32];
-  double mn = 1e300, mx = -1e300;
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const long long st = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += st) { double v = (double)a[i]; if (v < mn) mn = v; if (v > mx) mx = v; }
-  mn = blockReduce<OpMin>(mn, sh);
-  mx = blockReduce<OpMax>(mx, sh);
-  gridFinish<OpMin, OpMax, 2>(mn, mx, partials, counter, out, sh);
-}
-__global__ void k_minmax_i(const int* __restrict__ a, long long n, double* partials, unsigned int* counter, double* out) {
-  __shared__ double sh[32];
-  double mn = 1e300, mx = -1e300;
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const long long st = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += st) { double v = (double)a[i]; if (v < mn) mn = v; if (v > mx) mx = v; }
-  mn = blockReduce<OpMin>(mn, sh);
-  mx = blockReduce<OpMax>(mx, sh);
-  gridFinish<OpMin, OpMax, 2>(mn, mx, partials, counter, out, sh);
+  for (; i < n; i += st) {
+    if (WHAT == 0) acc[0] += (double)((float)a[i] * (float)b[i]);
+    else if (WHAT == 1) { const double v = (double)a[i]; acc[0] += v * v; }
+    else { const double v = (double)a[i]; if (v < acc[0]) acc[0] = v; if (v > acc[1]) acc[1] = v; }
+  }
+  const int ops[2] = { WHAT == 2 ? 1 : 0, 2 };
+  gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
 }
 // max over cells of |a-b| (Real, gridMaxDiff grid.cpp:437) or sum of component |diffs| (Vec3, :457)
-__global__ void k_maxdiff(const float* __restrict__ a, const float* __restrict__ b, long long n, long long np, int ncomp,
-                          double* partials, unsigned int* counter, double* out) {
+template <class T>
+__global__ void k_maxdiff(const T* __restrict__ a, const T* __restrict__ b, long long n, long long np, int ncomp, RedCtx ctx, double* out) {
   __shared__ double sh[32];
   double mx = 0.0;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -137,39 +144,30 @@ __global__ void k_maxdiff(const float* __restrict__ a, const float* __restrict__
     for (int c = 0; c < ncomp; c++) d += fabs((double)a[i + c * np] - (double)b[i + c * np]);
     if (d > mx) mx = d;
   }
-  mx = blockReduce<OpMax>(mx, sh);
-  gridFinish<OpMax, OpMax, 1>(mx, 0.0, partials, counter, out, sh);
-}
-__global__ void k_maxdiff_i(const int* __restrict__ a, const int* __restrict__ b, long long n,
-                            double* partials, unsigned int* counter, double* out) {
-  __shared__ double sh[32];
-  double mx = 0.0;
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const long long st = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += st) { double d = fabs((double)a[i] - (double)b[i]); if (d > mx) mx = d; }
-  mx = blockReduce<OpMax>(mx, sh);
-  gridFinish<OpMax, OpMax, 1>(mx, 0.0, partials, counter, out, sh);
+  double acc[1] = { mx };
+  const int ops[1] = { 2 };
+  gridReduceK<1>(acc, ops, ctx, sh, FinStore<1>{ out });
 }
 
-double reduce_dot(Solver* s, const float* a, const float* b, long long n) {
-  MF_LAUNCH(s, k_dot, redBlocks(s, n), RED_THREADS, a, b, n, s->redScratch, s->redCounter, s->redOut);
-  fetchRed(s, 1);
-  return s->redHost[0];
+template <int WHAT, class T>
+static void reduce2(Solver* s, const T* a, const T* b, int nfetch) {
+  MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, (k_reduce<WHAT, T>), redBlocks(s, sp.n), RED_THREADS, a + sp.off, b ? b + sp.off : nullptr, sp.n, redCtx(s, r), s->redOut); }
+  redFinish<2>(s, RedOps<2>{ { WHAT == 2 ? 1 : 0, 2 } }, FinStore<2>{ s->redOut });
+  fetchRed(s, nfetch);
 }
-double reduce_sumsqr(Solver* s, const float* a, long long n) {
-  MF_LAUNCH(s, k_sumsqr, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
-  fetchRed(s, 1);
-  return s->redHost[0];
-}
-void reduce_minmax(Solver* s, const float* a, long long n, float* mn, float* mx) {
-  MF_LAUNCH(s, k_minmax, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
-  fetchRed(s, 2);
-  *mn = (float)s->redHost[0]; *mx = (float)s->redHost[1];
-}
-void reduce_minmax_int(Solver* s, const int* a, long long n, int* mn, int* mx) {
-  MF_LAUNCH(s, k_minmax_i, redBlocks(s, n), RED_THREADS, a, n, s->redScratch, s->redCounter, s->redOut);
-  fetchRed(s, 2);
-  *mn = (int)s->redHost[0]; *mx = (int)s->redHost[1];
+double reduce_dot(Solver* s, const float* a, const float* b, long long) { reduce2<0, float>(s, a, b, 1); return s->redHost[0]; }
+double reduce_sumsqr(Solver* s, const float* a, long long) { reduce2<1, float>(s, a, nullptr, 1); return s->redHost[0]; }
+void reduce_minmax(Solver* s, const float* a, long long, float* mn, float* mx) { reduce2<2, float>(s, a, nullptr, 2); *mn = (float)s->redHost[0]; *mx = (float)s->redHost[1]; }
+void reduce_minmax_int(Solver* s, const int* a, long long, int* mn, int* mx) { reduce2<2, int>(s, a, nullptr, 2); *mn = (int)s->redHost[0]; *mx = (int)s->redHost[1]; }
+
+// elementwise kernel over every local rank's slab of one array (or of each listed array pair)
+#define MF_EW(s, kern, ...) do { MF_RANKS(s, _r) { const Span sp = span(s, _r); if (sp.n) { MF_LAUNCH(s, kern, ewBlocks(s, sp.n), 256, __VA_ARGS__); } } } while (0)
+
+// per-rank slab of every component: f(component base pointer offset to the slab, cells in the slab)
+template <class F> static void forSlabs(Solver* s, const Grid* g, F f) {
+  const int nc = g->isVec() ? 3 : 1;
+  MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) for (int c = 0; c < nc; c++) f((g->isVec() ? g->comp(c) : g->d) + sp.off, sp.n, c, sp); }
+  s->rankSync();
 }
 
 } // namespace mf
@@ -183,42 +181,74 @@ const char* mf_last_error(void) { return g_lastError.c_str(); }
 int mf_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
 const char* mf_build_info(void) { return "mantaflow-b200 0.1 linux 64bit fp1 cuda sm_100a"; }
 
-mf_solver* mf_solver_create(int nx, int ny, int nz, int dim, int device) {
-  try {
-    mfAssert(dim == 2 || dim == 3, "FluidSolver: dim must be 2 or 3");
-    mfAssert(nx > 0 && ny > 0 && nz > 0, "FluidSolver: invalid grid size");
-    if (dim == 2) nz = 1;   // fluidsolver.cpp:107-112 forces z=1 in 2-D
-    int ndev = mf_device_count();
-    mfAssert(ndev > 0, "mantacuda: no CUDA device available (there is no CPU fallback)");
-    mfAssert(device >= 0 && device < ndev, "mantacuda: invalid device index " << device);
-    CUDA_CHECK(cudaSetDevice(device));
-    Solver* s = new Solver();
-    s->nx = nx; s->ny = ny; s->nz = nz; s->dim = dim; s->is3D = (dim == 3);
-    s->N = (long long)nx * ny * nz;
-    s->Np = (s->N + 31) / 32 * 32;
-    s->strideZ = s->is3D ? (long long)nx * ny : 0;
-    s->dt = 1.0f;
-    int mx = nx > ny ? nx : ny; if (nz > mx) mx = nz;
-    s->dx = (float)(1.0 / mx);       // grid.cpp:57
-    s->device = device;
-    s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->profiling = false;
-    for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
-    CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
-    s->numSMs = prop.multiProcessorCount;
-    CUDA_CHECK(cudaMalloc(&s->redScratch, sizeof(double) * 8 * RED_MAX_BLOCKS));
-    CUDA_CHECK(cudaMalloc(&s->redCounter, sizeof(unsigned int) * 4));
-    CUDA_CHECK(cudaMemset(s->redCounter, 0, sizeof(unsigned int) * 4));
-    CUDA_CHECK(cudaMalloc(&s->redOut, sizeof(double) * 16));
-    CUDA_CHECK(cudaMemset(s->redOut, 0, sizeof(double) * 16));
-    CUDA_CHECK(cudaMallocHost(&s->redHost, sizeof(double) * 16));
-    CUDA_CHECK(cudaMalloc(&s->devFlagsScratch, sizeof(int) * 16));
-    CUDA_CHECK(cudaMemset(s->devFlagsScratch, 0, sizeof(int) * 16));
-    CUDA_CHECK(cudaMallocHost(&s->hostInts, sizeof(int) * 16));
-    return reinterpret_cast<mf_solver*>(s);
-  } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* comm) {
+  mfAssert(dim == 2 || dim == 3, "FluidSolver: dim must be 2 or 3");
+  mfAssert(nx > 0 && ny > 0 && nz > 0, "FluidSolver: invalid grid size");
+  if (dim == 2) nz = 1;   // fluidsolver.cpp:107-112 forces z=1 in 2-D
+  int ndev = mf_device_count();
+  mfAssert(ndev > 0, "mantacuda: no CUDA device available (there is no CPU fallback)");
+  mfAssert(device >= 0 && device < ndev, "mantacuda: invalid device index " << device);
+  CUDA_CHECK(cudaSetDevice(device));
+  Solver* s = new Solver();
+  s->nx = nx; s->ny = ny; s->nz = nz; s->dim = dim; s->is3D = (dim == 3);
+  s->N = (long long)nx * ny * nz;
+  s->comm = comm; s->nranks = comm ? comm_nranks(comm) : 1; s->redParity = 0;
+  if (comm && comm_emulated(comm)) { s->rankBegin = 0; s->rankEnd = s->nranks; }
+  else { s->rankBegin = comm ? comm_rank(comm) : 0; s->rankEnd = s->rankBegin + 1; }
+  mfAssert(s->nranks == 1 || (s->is3D && nz >= 2 * s->nranks), "FluidSolver: a grid partitioned over " << s->nranks << " GPUs needs dim == 3 and at least 2 z planes per GPU");
+  for (int r = 0; r <= s->nranks; r++) s->zsplit[r] = (int)((long long)nz * r / s->nranks);
+  // SoA component stride: 64 floats of slack behind every component; a whole number of allocation granules when the
+  // components are mapped piecewise over several GPUs
+  const long long unit = (comm && !comm_emulated(comm)) ? (long long)(comm_granularity(comm) / sizeof(float)) : 32;
+  s->Np = (s->N + 64 + unit - 1) / unit * unit;
+  s->strideZ = s->is3D ? (long long)nx * ny : 0;
+  s->dt = 1.0f;
+  int mx = nx > ny ? nx : ny; if (nz > mx) mx = nz;
+  s->dx = (float)(1.0 / mx);       // grid.cpp:57
+  s->device = device;
+  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->profiling = false;
+  for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
+  CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+  s->numSMs = prop.multiProcessorCount;
+  CUDA_CHECK(cudaMalloc(&s->redScratch, sizeof(double) * 8 * RED_MAX_BLOCKS));
+  CUDA_CHECK(cudaMalloc(&s->redCounter, sizeof(unsigned int) * 4));
+  CUDA_CHECK(cudaMemset(s->redCounter, 0, sizeof(unsigned int) * 4));
+  CUDA_CHECK(cudaMalloc(&s->redOut, sizeof(double) * 16));
+  CUDA_CHECK(cudaMemset(s->redOut, 0, sizeof(double) * 16));
+  CUDA_CHECK(cudaMallocHost(&s->redHost, sizeof(double) * 16));
+  CUDA_CHECK(cudaMalloc(&s->localInts, sizeof(int) * 16));
+  CUDA_CHECK(cudaMemset(s->localInts, 0, sizeof(int) * 16));
+  s->devFlagsScratch = (int*)s->galloc(sizeof(int) * 16);      // job-wide: kernels on any rank raise flags here
+  CUDA_CHECK(cudaMallocHost(&s->hostInts, sizeof(int) * 16));
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  return s;
 }
 
+mf_solver* mf_solver_create(int nx, int ny, int nz, int dim, int device) {
+  try { return reinterpret_cast<mf_solver*>(createSolver(nx, ny, nz, dim, device, nullptr)); }
+  catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+}
+// z-slab partitioned solver: every rank of the communicator makes the same call (and every later call on the solver
+// and its grids, in the same order)
+mf_solver* mf_solver_create_dist(mf_comm* comm, int nx, int ny, int nz, int dim) {
+  try {
+    mfAssert(comm, "mf_solver_create_dist: null communicator");
+    Comm* c = reinterpret_cast<Comm*>(comm);
+    return reinterpret_cast<mf_solver*>(createSolver(nx, ny, nz, dim, comm_device(c), c));
+  } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
+}
+int mf_solver_slab(const mf_solver* sp, int rank, int* k0, int* k1) {
+  MF_API_BEGIN
+  mfAssert(sp && k0 && k1, "mf_solver_slab: null argument");
+  const Solver* s = S(sp);
+  if (rank < 0) rank = s->rankBegin;
+  mfAssert(rank < s->nranks, "mf_solver_slab: no such rank");
+  *k0 = s->zsplit[rank]; *k1 = s->zsplit[rank + 1];
+  MF_API_END
+}
+int mf_solver_ranks(const mf_solver* sp) { return sp ? S(sp)->nranks : 0; }
+long long mf_solver_barrier_count(const mf_solver* sp) { return (sp && S(sp)->comm) ? comm_barriers_issued(S(sp)->comm) : 0; }
 
 void mf_solver_destroy(mf_solver* sp) {
   if (!sp) return;
@@ -226,10 +256,10 @@ void mf_solver_destroy(mf_solver* sp) {
   s->use();
   cudaStreamSynchronize(s->stream);
   release_mg(s);
-  for (float* p : s->poolReal) cudaFree(p);
-  for (float* p : s->poolVec) cudaFree(p);
+  for (float* p : s->poolReal) s->gfree(p);
+  for (float* p : s->poolVec) s->gfree(p);
   cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);
-  cudaFree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
+  cudaFree(s->localInts); s->gfree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
   if (s->aosStage) cudaFree(s->aosStage);
   for (auto& r : s->profRecs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (cudaEvent_t e : s->evPool) cudaEventDestroy(e);
@@ -240,7 +270,13 @@ void mf_solver_destroy(mf_solver* sp) {
 
 int mf_solver_set_dt(mf_solver* s, float dt) { MF_API_BEGIN mfAssert(s, "null solver"); S(s)->dt = dt; MF_API_END }
 float mf_solver_get_dt(const mf_solver* s) { return s ? S(s)->dt : 0.f; }
-int mf_solver_sync(mf_solver* s) { MF_API_BEGIN mfAssert(s, "null solver"); S(s)->use(); CUDA_CHECK(cudaStreamSynchronize(S(s)->stream)); CUDA_CHECK(cudaGetLastError()); MF_API_END }
+int mf_solver_sync(mf_solver* s) {
+  MF_API_BEGIN
+  mfAssert(s, "null solver"); S(s)->use();
+  CUDA_CHECK(cudaStreamSynchronize(S(s)->stream)); CUDA_CHECK(cudaGetLastError());
+  mfAssert(!(S(s)->comm && comm_error(S(s)->comm)), "mantacuda: a cross-GPU barrier timed out (a peer rank died or made a different sequence of calls)");
+  MF_API_END
+}
 void* mf_solver_stream(mf_solver* s) { return s ? (void*)S(s)->stream : nullptr; }
 long long mf_solver_launch_count(const mf_solver* s) { return s ? S(s)->launches : 0; }
 long long mf_solver_pool_bytes(const mf_solver* s) { return s ? S(s)->poolBytes : 0; }
@@ -316,9 +352,9 @@ mf_grid* mf_grid_create(mf_solver* sp, int type) {
     Solver* s = S(sp); s->use();
     Grid* g = new Grid();
     g->s = s; g->type = type; g->pooled = false; g->d = nullptr; g->outflowState = -1;
-    size_t bytes = (type & MF_TYPE_VEC3) ? sizeof(float) * (size_t)(3 * s->Np + 64) : sizeof(float) * (size_t)(s->N + 64);
-    CUDA_CHECK(cudaMalloc(&g->d, bytes));
-    CUDA_CHECK(cudaMemsetAsync(g->d, 0, bytes, s->stream));   // Grid ctor clears (grid.cpp:58)
+    // Grid ctor clears (grid.cpp:58): galloc zero-fills
+    if (type & MF_TYPE_VEC3) g->d = (float*)s->galloc(sizeof(float) * (size_t)s->Np, 3, sizeof(float) * (size_t)s->Np);
+    else g->d = (float*)s->galloc(sizeof(float) * (size_t)(s->N + 64));
     return reinterpret_cast<mf_grid*>(g);
   } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
 }
@@ -327,7 +363,7 @@ void mf_grid_destroy(mf_grid* gp) {
   Grid* g = G(gp);
   g->s->use();
   cudaStreamSynchronize(g->s->stream);
-  cudaFree(g->d);
+  g->s->gfree(g->d);
   delete g;
 }
 int mf_grid_type(const mf_grid* g) { return g ? G(g)->type : 0; }
@@ -336,18 +372,18 @@ int mf_grid_clear(mf_grid* gp) {
   MF_API_BEGIN
   mfAssert(gp, "Grid::clear: null grid");
   Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
-  size_t bytes = g->isVec() ? sizeof(float) * (size_t)(3 * s->Np) : sizeof(float) * (size_t)s->N;
-  CUDA_CHECK(cudaMemsetAsync(g->d, 0, bytes, s->stream));
+  forSlabs(s, g, [&](float* p, long long n, int, const Span&) { CUDA_CHECK(cudaMemsetAsync(p, 0, sizeof(float) * n, s->stream)); });
   MF_API_END
 }
-int mf_grid_copy(mf_grid* dp, const mf_grid* sp) {
+int mf_grid_copy(mf_grid* dp, const mf_grid* sp_) {
   MF_API_BEGIN
-  mfAssert(dp && sp, "Grid::copyFrom: null grid");
-  Grid* d = G(dp); const Grid* a = G(sp); Solver* s = d->s; s->use();
+  mfAssert(dp && sp_, "Grid::copyFrom: null grid");
+  Grid* d = G(dp); const Grid* a = G(sp_); Solver* s = d->s; s->use();
   check_same_solver(d, a, "Grid::copyFrom");
   mfAssert(d->isVec() == a->isVec() && d->isInt() == a->isInt(), "Grid::copyFrom: grid types do not match");
-  size_t bytes = d->isVec() ? sizeof(float) * (size_t)(3 * s->Np) : sizeof(float) * (size_t)s->N;
-  CUDA_CHECK(cudaMemcpyAsync(d->d, a->d, bytes, cudaMemcpyDeviceToDevice, s->stream));
+  forSlabs(s, d, [&](float* p, long long n, int c, const Span& sp) {
+    const float* src = (a->isVec() ? a->comp(c) : a->d) + sp.off;
+    CUDA_CHECK(cudaMemcpyAsync(p, src, sizeof(float) * n, cudaMemcpyDeviceToDevice, s->stream)); });
   d->outflowState = a->outflowState;
   MF_API_END
 }
@@ -361,59 +397,74 @@ int mf_grid_swap(mf_grid* ap, mf_grid* bp) {
   int o = a->outflowState; a->outflowState = b->outflowState; b->outflowState = o;
   MF_API_END
 }
-int mf_grid_upload(mf_grid* gp, const void* host) {
-  MF_API_BEGIN
-  mfAssert(gp && host, "Grid upload: null argument");
-  Grid* g = G(gp); Solver* s = g->s; s->use();
+// host <-> device.  `host` is the FULL grid in the reference layout on every rank (slabOnly == 0: each rank uploads its own
+// slab from it; a download returns the whole grid to every rank, peers' slabs travelling over NVLink), or only the rank's own
+// z-slab [k0,k1) (slabOnly == 1; mf_solver_slab).
+static void gridUpload(Grid* g, const void* host, bool slabOnly) {
+  Solver* s = g->s; s->use();
   g->outflowState = -1;
-  if (!g->isVec()) {
-    CUDA_CHECK(cudaMemcpyAsync(g->d, host, sizeof(float) * (size_t)s->N, cudaMemcpyHostToDevice, s->stream));
-  } else {
-    if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * s->N)));
-    CUDA_CHECK(cudaMemcpyAsync(s->aosStage, host, sizeof(float) * (size_t)(3 * s->N), cudaMemcpyHostToDevice, s->stream));
-    MF_LAUNCH(s, k_aos_to_soa, ewBlocks(s, s->N), 256, s->aosStage, g->comp(0), g->comp(1), g->comp(2), s->N);
-    MF_LAUNCH_CHECK();
+  MF_RANKS(s, r) {
+    const Span sp = span(s, r);
+    if (!sp.n) continue;
+    const long long hoff = slabOnly ? 0 : sp.off;
+    if (!g->isVec()) {
+      CUDA_CHECK(cudaMemcpyAsync(g->d + sp.off, (const float*)host + hoff, sizeof(float) * (size_t)sp.n, cudaMemcpyHostToDevice, s->stream));
+    } else {
+      if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * span(s, s->rankBegin).n + 3 * (long long)s->nx * s->ny)));
+      CUDA_CHECK(cudaMemcpyAsync(s->aosStage, (const float*)host + 3 * hoff, sizeof(float) * (size_t)(3 * sp.n), cudaMemcpyHostToDevice, s->stream));
+      MF_LAUNCH(s, k_aos_to_soa, ewBlocks(s, sp.n), 256, s->aosStage, g->comp(0) + sp.off, g->comp(1) + sp.off, g->comp(2) + sp.off, sp.n);
+      MF_LAUNCH_CHECK();
+    }
   }
+  s->rankSync();
   CUDA_CHECK(cudaStreamSynchronize(s->stream));  // host buffer may be reused by the caller
-  MF_API_END
 }
-int mf_grid_download(const mf_grid* gp, void* host) {
-  MF_API_BEGIN
-  mfAssert(gp && host, "Grid download: null argument");
-  const Grid* g = G(gp); Solver* s = g->s; s->use();
-  if (!g->isVec()) {
-    CUDA_CHECK(cudaMemcpyAsync(host, g->d, sizeof(float) * (size_t)s->N, cudaMemcpyDeviceToHost, s->stream));
-  } else {
-    if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * s->N)));
-    MF_LAUNCH(s, k_soa_to_aos, ewBlocks(s, s->N), 256, s->aosStage, g->comp(0), g->comp(1), g->comp(2), s->N);
-    MF_LAUNCH_CHECK();
-    CUDA_CHECK(cudaMemcpyAsync(host, s->aosStage, sizeof(float) * (size_t)(3 * s->N), cudaMemcpyDeviceToHost, s->stream));
+static void gridDownload(const Grid* g, void* host, bool slabOnly) {
+  Solver* s = g->s; s->use();
+  // all ranks have passed the barrier behind the last launch group, so every slab is complete
+  const bool whole = !slabOnly && s->multi() && !comm_emulated(s->comm);
+  for (int r = whole ? 0 : s->rankBegin; r < (whole ? s->nranks : s->rankEnd); r++) {
+    const Span sp = span(s, r);
+    if (!sp.n) continue;
+    const long long hoff = slabOnly ? 0 : sp.off;
+    if (!g->isVec()) {
+      CUDA_CHECK(cudaMemcpyAsync((float*)host + hoff, g->d + sp.off, sizeof(float) * (size_t)sp.n, cudaMemcpyDeviceToHost, s->stream));
+    } else {
+      if (!s->aosStage) CUDA_CHECK(cudaMalloc(&s->aosStage, sizeof(float) * (size_t)(3 * span(s, s->rankBegin).n + 3 * (long long)s->nx * s->ny)));
+      MF_LAUNCH(s, k_soa_to_aos, ewBlocks(s, sp.n), 256, s->aosStage, g->comp(0) + sp.off, g->comp(1) + sp.off, g->comp(2) + sp.off, sp.n);
+      MF_LAUNCH_CHECK();
+      CUDA_CHECK(cudaMemcpyAsync((float*)host + 3 * hoff, s->aosStage, sizeof(float) * (size_t)(3 * sp.n), cudaMemcpyDeviceToHost, s->stream));
+    }
   }
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   CUDA_CHECK(cudaGetLastError());
-  MF_API_END
+  s->rankSync();                                 // peers may overwrite the grid only after everybody has read it
 }
+int mf_grid_upload(mf_grid* gp, const void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid upload: null argument"); gridUpload(G(gp), host, false); MF_API_END }
+int mf_grid_download(const mf_grid* gp, void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid download: null argument"); gridDownload(G(gp), host, false); MF_API_END }
+int mf_grid_upload_slab(mf_grid* gp, const void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid upload: null argument"); gridUpload(G(gp), host, true); MF_API_END }
+int mf_grid_download_slab(const mf_grid* gp, void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid download: null argument"); gridDownload(G(gp), host, true); MF_API_END }
 int mf_grid_set_const_real(mf_grid* gp, float v) {
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isReal(), "grid", "Grid<Real>::setConst");
   Grid* g = G(gp); Solver* s = g->s; s->use();
-  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->d, v, s->N); MF_LAUNCH_CHECK();
+  MF_EW(s, k_fill_f, g->d + sp.off, v, sp.n); s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }
 int mf_grid_set_const_int(mf_grid* gp, int v) {
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isInt(), "grid", "Grid<int>::setConst");
   Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
-  MF_LAUNCH(s, k_fill_i, ewBlocks(s, s->N), 256, g->di(), v, s->N); MF_LAUNCH_CHECK();
+  MF_EW(s, k_fill_i, g->di() + sp.off, v, sp.n); s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }
 int mf_grid_set_const_vec3(mf_grid* gp, float x, float y, float z) {
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isVec(), "grid", "Grid<Vec3>::setConst");
   Grid* g = G(gp); Solver* s = g->s; s->use();
-  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(0), x, s->N);
-  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(1), y, s->N);
-  MF_LAUNCH(s, k_fill_f, ewBlocks(s, s->N), 256, g->comp(2), z, s->N); MF_LAUNCH_CHECK();
+  const float f[3] = { x, y, z };
+  for (int c = 0; c < 3; c++) MF_EW(s, k_fill_f, g->comp(c) + sp.off, f[c], sp.n);
+  s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }
 int mf_grid_add_scaled(mf_grid* gp, const mf_grid* ap, float fx, float fy, float fz) {
@@ -422,12 +473,12 @@ int mf_grid_add_scaled(mf_grid* gp, const mf_grid* ap, float fx, float fy, float
   Grid* g = G(gp); const Grid* a = G(ap); Solver* s = g->s; s->use();
   check_same_solver(g, a, "Grid::addScaled");
   mfAssert(!g->isInt() && g->isVec() == a->isVec(), "Grid::addScaled: grid types do not match");
-  if (!g->isVec()) { MF_LAUNCH(s, k_scaled_add, ewBlocks(s, s->N), 256, g->d, a->d, fx, s->N); }
+  if (!g->isVec()) { MF_EW(s, k_scaled_add, g->d + sp.off, a->d + sp.off, fx, sp.n); }
   else {
     const float f[3] = { fx, fy, fz };
-    for (int c = 0; c < 3; c++) MF_LAUNCH(s, k_scaled_add, ewBlocks(s, s->N), 256, g->comp(c), a->comp(c), f[c], s->N);
+    for (int c = 0; c < 3; c++) MF_EW(s, k_scaled_add, g->comp(c) + sp.off, a->comp(c) + sp.off, f[c], sp.n);
   }
-  MF_LAUNCH_CHECK();
+  s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }
 int mf_grid_mult_const(mf_grid* gp, float fx, float fy, float fz) {
@@ -435,12 +486,12 @@ int mf_grid_mult_const(mf_grid* gp, float fx, float fy, float fz) {
   mfAssert(gp, "Grid::multConst: null grid");
   Grid* g = G(gp); Solver* s = g->s; s->use();
   mfAssert(!g->isInt(), "Grid::multConst: int grids not supported");
-  if (!g->isVec()) { MF_LAUNCH(s, k_mult_const, ewBlocks(s, s->N), 256, g->d, fx, s->N); }
+  if (!g->isVec()) { MF_EW(s, k_mult_const, g->d + sp.off, fx, sp.n); }
   else {
     const float f[3] = { fx, fy, fz };
-    for (int c = 0; c < 3; c++) MF_LAUNCH(s, k_mult_const, ewBlocks(s, s->N), 256, g->comp(c), f[c], s->N);
+    for (int c = 0; c < 3; c++) MF_EW(s, k_mult_const, g->comp(c) + sp.off, f[c], sp.n);
   }
-  MF_LAUNCH_CHECK();
+  s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }
 int mf_grid_max_abs(const mf_grid* gp, float* out) {
@@ -489,8 +540,12 @@ int mf_grid_max_diff(const mf_grid* ap, const mf_grid* bp, double* out) {
   const Grid* a = G(ap); const Grid* b = G(bp); Solver* s = a->s; s->use();
   check_same_solver(a, b, "gridMaxDiff");
   mfAssert(a->isVec() == b->isVec() && a->isInt() == b->isInt(), "gridMaxDiff: grid types do not match");
-  if (a->isInt()) { MF_LAUNCH(s, k_maxdiff_i, redBlocks(s, s->N), RED_THREADS, a->di(), b->di(), s->N, s->redScratch, s->redCounter, s->redOut); }
-  else { MF_LAUNCH(s, k_maxdiff, redBlocks(s, s->N), RED_THREADS, a->d, b->d, s->N, s->Np, a->isVec() ? 3 : 1, s->redScratch, s->redCounter, s->redOut); }
+  MF_RANKS(s, r) {
+    const Span sp = span(s, r);
+    if (a->isInt()) { MF_LAUNCH(s, k_maxdiff<int>, redBlocks(s, sp.n), RED_THREADS, a->di() + sp.off, b->di() + sp.off, sp.n, s->Np, 1, redCtx(s, r), s->redOut); }
+    else { MF_LAUNCH(s, k_maxdiff<float>, redBlocks(s, sp.n), RED_THREADS, a->d + sp.off, b->d + sp.off, sp.n, s->Np, a->isVec() ? 3 : 1, redCtx(s, r), s->redOut); }
+  }
+  redFinish<1>(s, RedOps<1>{ { 2 } }, FinStore<1>{ s->redOut });
   MF_LAUNCH_CHECK();
   fetchRed(s, 1);
   *out = s->redHost[0];
@@ -507,5 +562,7 @@ __global__ void k_norm_square(const float* x, const float* y, const float* z, fl
 }
 }
 void launch_norm_square(mf::Solver* s, const mf::Grid* g, float* o) {
-  MF_LAUNCH(s, mf::k_norm_square, mf::ewBlocks(s, s->N), 256, g->comp(0), g->comp(1), g->comp(2), o, s->N);
+  using namespace mf;
+  MF_EW(s, mf::k_norm_square, g->comp(0) + sp.off, g->comp(1) + sp.off, g->comp(2) + sp.off, o + sp.off, sp.n);
+  s->rankSync();
 }

@@ -157,12 +157,54 @@ def _plugin(fn):
     return wrapper
 
 
+# ---- multi-GPU: the team of ranks a solver is partitioned over (include/mantacuda.h "multi-GPU") ---------------
+class Comm(object):
+    """One process per GPU (`Comm.from_env()` under torchrun), or all ranks emulated in this process on one GPU
+    (`Comm.emulated(n)`, for testing the partitioned path).  Scenes stay unchanged: `setDefaultComm(comm)` makes every
+    Solver created afterwards a z-slab partitioned one."""
+
+    def __init__(self, handle, rank, nranks, emulated):
+        self._h, self.rank, self.nranks, self.emulated = handle, rank, nranks, emulated
+
+    @staticmethod
+    def emulated(nranks, device=0):
+        h = lib().mf_comm_create_emulated(int(nranks), int(device))
+        if not h:
+            raise MantaError(lib().mf_last_error().decode())
+        return Comm(h, 0, int(nranks), True)
+
+    @staticmethod
+    def from_env(session=None):
+        import os
+        rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+        local = int(os.environ.get("LOCAL_RANK", str(rank)))
+        session = session or ("job%s" % os.environ.get("MASTER_PORT", "0"))
+        h = lib().mf_comm_create(rank, world, local, session.encode())
+        if not h:
+            raise MantaError(lib().mf_last_error().decode())
+        return Comm(h, rank, world, False)
+
+    def destroy(self):
+        h, self._h = self._h, None
+        if h:
+            lib().mf_comm_destroy(h)
+
+
+_defaultComm = None
+
+
+def setDefaultComm(comm):
+    global _defaultComm
+    _defaultComm = comm
+
+
 # ---- FluidSolver -----------------------------------------------------------------------------------------
 class FluidSolver(object):
     """FluidSolver / Solver (source/fluidsolver.h:26-119, fluidsolver.cpp:107-166)."""
 
-    def __init__(self, name="solver", gridSize=None, dim=3, device=0, **kwargs):
+    def __init__(self, name="solver", gridSize=None, dim=3, device=0, comm=None, **kwargs):
         _checkArgs("Solver", kwargs, ())
+        comm = comm or _defaultComm
         if gridSize is None:
             raise MantaError("Argument 'gridSize' is not defined.")
         gs = _v3(gridSize)
@@ -174,7 +216,11 @@ class FluidSolver(object):
             raise MantaError("Trying to create 2D solver with size.z != 1")
         self._size = (nx, ny, nz)
         self._dim = dim
-        self._h = lib().mf_solver_create(nx, ny, nz, dim, device)
+        self.comm = comm
+        if comm is not None and comm.nranks > 1:
+            self._h = lib().mf_solver_create_dist(comm._h, nx, ny, nz, dim)
+        else:
+            self._h = lib().mf_solver_create(nx, ny, nz, dim, device)
         if not self._h:
             raise MantaError(lib().mf_last_error().decode())
         self._dt = np.float32(1.0)
@@ -241,6 +287,12 @@ class FluidSolver(object):
 
     def launchCount(self):
         return int(lib().mf_solver_launch_count(self._h))
+
+    def slab(self, rank=-1):
+        """z planes [k0, k1) of this process's (or `rank`'s) slab"""
+        k0, k1 = C.c_int(), C.c_int()
+        check(lib().mf_solver_slab(self._h, rank, C.byref(k0), C.byref(k1)))
+        return k0.value, k1.value
 
     def printMemInfo(self):
         print("Device temp-grid pool: %d bytes" % lib().mf_solver_pool_bytes(self._h))
