@@ -51,10 +51,12 @@ ALGO_BYTES_PER_CELL = {
     "k_cg_dot_beta": 8.0, "k_cg_dot_sigma": 8.0,
     "k_cg_search": 12.0,
     "k_correct_velocity": 32.0,  # flags 4 + p 4 + vel 12 r + 12 w
-    "k_mg_smooth0": 20.5,      # one colour: A couplings 12 + half of (A0 4, b 4, x-in 4, x-out 4) 8 + type 0.5
-    "k_mg_residual0": 29.0,    # A 16 + x 4 + b 4 + r 4 + type 1
-    "k_mg_restrict": 4.6,      # fine r 4 + type 1 (per FINE cell) + coarse b,x writes (1/8)
-    "k_mg_interp_add": 9.5,    # fine x r/w 8 + type 1 + coarse x (1/8)
+    # level-0 multigrid sweeps with the 16-bit operator code (sector granularity: a colour sweep touches every sector of the
+    # arrays it reads/writes): code 2 + x in 4 + b 4 + x out 4 = 14; the first sweep of a V-cycle (x == 0) has no x in: 10;
+    # 3 of the 4 sweeps per V-cycle are of the first kind -> 13 on average
+    "k_mg_smooth0": 13.0,
+    "k_mg_residual0": 14.0,    # code 2 + x 4 + b 4 + r 4
+    # k_mg_restrict / k_mg_interp_add / k_mg_smooth / k_mg_residual run on every level: no single bytes-per-cell figure
     "k_apply_cylinder": 4.0,
 }
 
@@ -64,7 +66,9 @@ def _parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--size", type=int, default=256, help="cubic grid edge (BASELINE configs[1]: 256)")
+    ap.add_argument("--size", type=int, default=256, help="grid edge (BASELINE configs[1]: 256); with N GPUs the grid is size x size x (size*N) "
+                                                       "(weak scaling, a size^3 z-slab per GPU) unless --strong")
+    ap.add_argument("--strong", action="store_true", help="N GPUs share ONE size^3 grid (BASELINE configs[4]: --size 1024 --strong)")
     ap.add_argument("--precond", default="mg", choices=["mg", "mic"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -156,12 +160,12 @@ def cpu_model():
 class Plume(object):
     """The synthetic smoke plume of SURVEY.md 8(d) on one GPU, driven through mantaflow_b200.manta (C-ABI -> CUDA)."""
 
-    def __init__(self, size, device, precond):
+    def __init__(self, size, device, precond, comm=None):
         from mantaflow_b200 import manta as M
         self.M = M
         nx, ny, nz = size
         gs = M.vec3(nx, ny, nz)
-        self.s = M.Solver(name="main", gridSize=gs, dim=3, device=device)
+        self.s = M.Solver(name="main", gridSize=gs, dim=3, device=device, comm=comm)
         self.s.timestep = 1.0
         self.flags = self.s.create(M.FlagGrid)
         self.vel = self.s.create(M.MACGrid)
@@ -190,20 +194,22 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    size = (a.size, a.size, a.size)
-    cells = a.size ** 3
+    strong = a.strong or world == 1
+    size = (a.size, a.size, a.size if strong else a.size * world)
+    cells = size[0] * size[1] * size[2]            # whole job
     pcname = "GridMg-preconditioned PCG (PcMGStatic)" if a.precond == "mg" else "red-black MIC PCG (PcMIC)"
-    config = {"workload": "smoke plume %d^3, MacCormack (order 2) advection of density+velocity, setWallBcs, addBuoyancy, "
-                          "solvePressure %s, cgAccuracy 1e-3, zeroPressureFixing" % (a.size, pcname),
-              "grid": list(size), "cells_per_gpu": cells, "dt": 1.0,
+    config = {"workload": "smoke plume %dx%dx%d, MacCormack (order 2) advection of density+velocity, setWallBcs, addBuoyancy, "
+                          "solvePressure %s, cgAccuracy 1e-3, zeroPressureFixing" % (size + (pcname,)),
+              "grid": list(size), "cells_per_gpu": cells // world, "dt": 1.0,
               "l2": "working set per step > 1 GiB (>> 126 MB L2), no flush needed" if a.size >= 256 else "L2-resident working set",
-              "parallelism": "replicas x%d" % world if world > 1 else "single GPU"}
+              "parallelism": ("z-slab x%d (one global address space over NVLink, device flag barrier per launch group), %s scaling"
+                              % (world, "strong" if a.strong else "weak")) if world > 1 else "single GPU"}
 
     if a.impl == "reference":
         if rank != 0:
             return 0
         pc = 3 if a.precond == "mg" else 1
-        ref_size = size
+        ref_size = (min(a.size, 256),) * 3      # bounded sample: one GPU's share of the (weak-scaled) workload
         # keep the whole run within a few minutes: a 256^3 reference step costs several seconds on the host cores
         if a.size > 128 and (a.steps + a.warmup) > 16:
             ref_size = (128, 128, 128)
@@ -225,11 +231,14 @@ def main():
     from mantaflow_b200._lib import lib, check
     L = lib()
     dist = None
+    comm = None
     if world > 1:
-        import torch
+        # torch.distributed is plumbing only (host barrier + max over ranks); the data path is the library's own
+        # peer-mapped address space and device barrier
         import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("gloo")
+        from mantaflow_b200 import manta as M
+        comm = M.Comm.from_env()
 
     def barrier():
         if dist is not None:
@@ -239,12 +248,13 @@ def main():
         if dist is None:
             return x
         import torch
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        t = torch.tensor([x], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    P = Plume(size, local, a.precond)
+    P = Plume(size, local, a.precond, comm)
     s = P.s
+    cells_gpu = cells // world
     for _ in range(max(a.warmup, 3)):
         P.step()
     s.sync()
@@ -268,7 +278,7 @@ def main():
     clk = clocks.stop()
     launches = s.launchCount() - l0
     dev_s = max_over_ranks(ms.value * 1e-3)
-    value = cells * world * a.steps / dev_s
+    value = cells * a.steps / dev_s
     iters = list(P.iterations)
 
     # ---- per-kernel CUDA-event profile (separate pass so the event pairs do not perturb `value`) -----------------
@@ -297,7 +307,7 @@ def main():
                  "share_of_step": tot / prof_ms, "avg_us": 1e3 * tot / n}
             if name in ALGO_BYTES_PER_CELL:
                 e["algo_bytes_per_cell"] = ALGO_BYTES_PER_CELL[name]
-                e["achieved_gbs"] = ALGO_BYTES_PER_CELL[name] * cells / (tot / n * 1e-3) / 1e9
+                e["achieved_gbs"] = ALGO_BYTES_PER_CELL[name] * cells_gpu / (tot / n * 1e-3) / 1e9
                 e["frac_of_peak"] = e["achieved_gbs"] / peak
             kernels.append(e)
         top = next((k for k in kernels if "achieved_gbs" in k), None)
@@ -310,37 +320,41 @@ def main():
                 pass
             roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak, "unit": "GB/s",
                         "frac": top["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
-                        "algo_bytes_per_launch": ALGO_BYTES_PER_CELL[top["kernel"]] * cells, "avg_launch_us": top["avg_us"],
+                        "algo_bytes_per_launch": ALGO_BYTES_PER_CELL[top["kernel"]] * cells_gpu, "avg_launch_us": top["avg_us"],
                         "share_of_step": top["share_of_step"], "timed": "CUDA events around every launch, %d extra steps after the timed region" % a.profile_steps}
 
     # ---- e2e: host buffers, copies inside the timed region -------------------------------------------------------
     e2e = None
     if not a.no_e2e:
         import numpy as np
-        nb_vel, nb_real = 12 * cells, 4 * cells
+        k0, k1 = s.slab()
+        slab_cells = size[0] * size[1] * (k1 - k0)
+        nb_vel, nb_real = 12 * slab_cells, 4 * slab_cells
 
         def pinned(nbytes, dtype, shape):
             p = L.mf_host_alloc(nbytes)
             if not p:
                 raise RuntimeError("mf_host_alloc failed")
             return p, np.ctypeslib.as_array((C.c_byte * nbytes).from_address(p)).view(dtype).reshape(shape)
-        pv, hv = pinned(nb_vel, np.float32, (a.size, a.size, a.size, 3))
-        pd, hd = pinned(nb_real, np.float32, (a.size,) * 3)
-        pp, hp = pinned(nb_real, np.float32, (a.size,) * 3)
-        check(L.mf_grid_download(P.vel._h, pv)); check(L.mf_grid_download(P.density._h, pd))
+        shp = (k1 - k0, size[1], size[0])
+        pv, hv = pinned(nb_vel, np.float32, shp + (3,))
+        pd, hd = pinned(nb_real, np.float32, shp)
+        pp, hp = pinned(nb_real, np.float32, shp)
+        # every rank moves its own z-slab between its pinned host buffers and its GPU (mf_grid_*_slab; the whole grid at N=1)
+        check(L.mf_grid_download_slab(P.vel._h, pv)); check(L.mf_grid_download_slab(P.density._h, pd))
         ke = max(2, min(a.steps, 5))
         barrier(); s.sync()
         t0 = time.perf_counter()
         for _ in range(ke):
-            check(L.mf_grid_upload(P.vel._h, pv)); check(L.mf_grid_upload(P.density._h, pd))
+            check(L.mf_grid_upload_slab(P.vel._h, pv)); check(L.mf_grid_upload_slab(P.density._h, pd))
             P.step()
-            check(L.mf_grid_download(P.vel._h, pv)); check(L.mf_grid_download(P.density._h, pd)); check(L.mf_grid_download(P.pressure._h, pp))
+            check(L.mf_grid_download_slab(P.vel._h, pv)); check(L.mf_grid_download_slab(P.density._h, pd)); check(L.mf_grid_download_slab(P.pressure._h, pp))
         s.sync()
         te = max_over_ranks(time.perf_counter() - t0)
         barrier()
-        e2e = {"value": cells * world * ke / te, "unit": UNIT, "h2d_bytes_per_step": nb_vel + nb_real, "d2h_bytes_per_step": nb_vel + 2 * nb_real,
-               "steps": ke, "ms_per_step": 1e3 * te / ke, "checksum": float(hp[a.size // 2, a.size // 2, a.size // 2]),
-               "path": "mf_grid_upload(vel,density) from pinned host -> plume step through mantaflow_b200.manta -> mf_grid_download(vel,density,pressure)"}
+        e2e = {"value": cells * ke / te, "unit": UNIT, "h2d_bytes_per_step": (nb_vel + nb_real) * world, "d2h_bytes_per_step": (nb_vel + 2 * nb_real) * world,
+               "steps": ke, "ms_per_step": 1e3 * te / ke, "checksum": float(hp[(k1 - k0) // 2, size[1] // 2, size[0] // 2]),
+               "path": "per rank: mf_grid_upload_slab(vel,density) from pinned host -> plume step through mantaflow_b200.manta -> mf_grid_download_slab(vel,density,pressure)"}
         for p in (pv, pd, pp):
             L.mf_host_free(p)
 
@@ -358,11 +372,19 @@ def main():
 
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-               "ms_per_step": 1e3 * dev_s / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "ms_per_step": 1e3 * dev_s / a.steps, "higher_is_better": True, "scaling": "strong" if (a.strong and world > 1) else "weak", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic", "config": config, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
                "roofline": roofline, "cpu_baseline": cpu, "pcg_iterations": iters,
-               "pcg_ms_per_iteration": None, "wall_ms_per_step": 1e3 * wall / a.steps, "kernels": kernels[:14]}
+               "pcg_ms_per_iteration": None, "wall_ms_per_step": 1e3 * wall / a.steps, "kernels": kernels[:14],
+               "device_barriers_per_step": (L.mf_solver_barrier_count(s._h) / float(max(a.warmup, 3) + a.steps + a.profile_steps + (0 if a.no_e2e else max(2, min(a.steps, 5))))) if world > 1 else 0}
         print(json.dumps(out))
+    del P
+    s = None
+    import gc
+    gc.collect()
+    if comm is not None:
+        barrier()
+        comm.destroy()
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -76,6 +76,7 @@ struct FinSigma { CgState* st; __device__ void operator()(double* r) const { st-
 
 // tmp = A * search ; dp = tmp . search ; alpha = sigma / dp        (conjugategrad.cpp:247-252)
 __global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* st, RedCtx ctx) {
+  MF_PDL_PROLOGUE
   __shared__ double sh[32];
   if (st->done) return;
   double acc[1] = { 0.0 };
@@ -93,6 +94,7 @@ __global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* s
 // PCNONE: also tmp := residual (implicitly) and sigmaNew = residual . residual, beta        (:279-286)
 template <bool PCNONE>
 __global__ void __launch_bounds__(256) k_cg_update(Span sp, CgVecs v, CgState* st, RedCtx ctx) {
+  MF_PDL_PROLOGUE
   __shared__ double sh[32];
   if (st->done) return;
   const float alpha = st->alpha, nalpha = -alpha;
@@ -115,6 +117,7 @@ __global__ void __launch_bounds__(256) k_cg_update(Span sp, CgVecs v, CgState* s
 // sigmaNew = tmp . residual ; beta = sigmaNew / sigma                 (conjugategrad.cpp:279-295), preconditioned path
 __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* __restrict__ tmp, const float* __restrict__ residual,
                                                      CgState* st, RedCtx ctx) {
+  MF_PDL_PROLOGUE
   __shared__ double sh[32];
   if (st->done) return;
   double acc[1] = { 0.0 };
@@ -139,6 +142,7 @@ __global__ void __launch_bounds__(256) k_cg_dot_sigma(long long n, const float* 
 
 // search = tmp + beta * search                                            (UpdateSearchVec, conjugategrad.cpp:193)
 __global__ void __launch_bounds__(256) k_cg_search(long long n, float* __restrict__ search, const float* __restrict__ tmp, const CgState* st) {
+  MF_PDL_PROLOGUE
   if (st->done) return;
   const float beta = st->beta;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;

@@ -164,7 +164,7 @@ static void connectAll(Comm* c, const char* session) {
 }
 
 // ---- global allocations ----------------------------------------------------------------------------------------
-void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp, size_t compStride) {
+void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp, size_t compStride, const size_t* byteSplit) {
   mfAssert(bytesPerComp > 0 && ncomp >= 1, "comm_alloc: bad size");
   if (c->emulated) {
     const size_t total = ncomp > 1 ? compStride * (size_t)(ncomp - 1) + bytesPerComp : bytesPerComp;
@@ -188,9 +188,17 @@ void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp, size_t compStride) {
   prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
   const int P = c->nranks;
+  // granule boundaries of the hosting split: rank r hosts granules [gb[r], gb[r+1]) of every component
+  size_t gb[COMM_MAX_RANKS + 1];
+  gb[0] = 0; gb[P] = G;
+  for (int r = 1; r < P; r++) {
+    gb[r] = byteSplit ? (byteSplit[r] >= bytesPerComp ? G : (byteSplit[r] + g / 2) / g) : G * (size_t)r / P;
+    if (gb[r] > G) gb[r] = G;
+    if (gb[r] < gb[r - 1]) gb[r] = gb[r - 1];
+  }
   for (int q = 0; q < ncomp; q++) {
     for (int owner = 0; owner < P; owner++) {
-      const size_t g0 = G * (size_t)owner / P, g1 = G * (size_t)(owner + 1) / P;
+      const size_t g0 = gb[owner], g1 = gb[owner + 1];
       if (g1 == g0) continue;
       Piece pc; pc.off = compStride * (size_t)q + g0 * g; pc.size = (g1 - g0) * g; pc.h = 0;
       if (owner == c->rank) {
@@ -214,7 +222,7 @@ void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp, size_t compStride) {
   for (const Piece& pc : rec.pieces) CU_CHECK(g_drv.MemSetAccess(base + pc.off, pc.size, &acc, 1));
   // every rank clears what it hosts
   for (int q = 0; q < ncomp; q++) {
-    const size_t g0 = G * (size_t)c->rank / P, g1 = G * (size_t)(c->rank + 1) / P;
+    const size_t g0 = gb[c->rank], g1 = gb[c->rank + 1];
     if (g1 > g0) CUDA_CHECK(cudaMemset((void*)(base + compStride * (size_t)q + g0 * g), 0, (g1 - g0) * g));
   }
   CUDA_CHECK(cudaDeviceSynchronize());
@@ -247,6 +255,7 @@ __device__ __forceinline__ unsigned long long ldAcquireSys(const unsigned long l
 }
 // thread t signals rank t (writes this rank's epoch into the flag array hosted on rank t) and then waits for rank t's signal
 __global__ void k_comm_barrier(char* shared, size_t stride, int rank, int nranks, unsigned long long epoch, int* err) {
+  MF_PDL_PROLOGUE
   const int t = threadIdx.x;
   if (t >= nranks || t == rank) return;
   __threadfence_system();
@@ -263,7 +272,7 @@ void comm_barrier(Comm* c, cudaStream_t stream) {
   if (c->emulated || c->nranks == 1) return;
   c->epoch++;
   c->barriers++;
-  k_comm_barrier<<<1, 32, 0, stream>>>(reinterpret_cast<char*>(c->shared), c->ctrlStride, c->rank, c->nranks, c->epoch, c->errDev);
+  launchPdl(stream, k_comm_barrier, dim3(1), dim3(32), reinterpret_cast<char*>(c->shared), c->ctrlStride, c->rank, c->nranks, c->epoch, c->errDev);
 }
 
 // ---- life cycle ---------------------------------------------------------------------------------------------------
@@ -409,6 +418,21 @@ int mf_comm_selftest(mf_comm* cp, long long bytesPerRank, int iters, double* out
   comm_barrier(c, st);
   out[5] = 2.0 * timeCopy(scratch, a + (size_t)me * n);
   out[4] = (double)g;
+  // launch-chain cost of tiny dependent kernels by the memory they touch: out[6] plain cudaMalloc, out[7] own slab of the
+  // peer-mapped array, out[8] the neighbour's slab (us per launch)
+  auto timeChain = [&](float* p) {
+    for (int i = 0; i < 20; i++) k_comm_fill<<<8, 128, 0, st>>>(p, 1024, 1.f);
+    CUDA_CHECK(cudaEventRecord(e0, st));
+    for (int i = 0; i < 500; i++) k_comm_fill<<<8, 128, 0, st>>>(p, 1024, (float)i);
+    CUDA_CHECK(cudaEventRecord(e1, st));
+    CUDA_CHECK(cudaEventSynchronize(e1)); CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    return 1e3 * ms / 500;
+  };
+  out[6] = timeChain(scratch);
+  out[7] = timeChain(a + (size_t)me * n);
+  comm_barrier(c, st);
+  out[8] = timeChain(a + (size_t)nb * n + n / 2);
+  comm_barrier(c, st);
   CUDA_CHECK(cudaStreamSynchronize(st));
   mfAssert(!comm_error(c), "mf_comm_selftest: a device barrier timed out");
   comm_host_barrier(c);

@@ -39,8 +39,9 @@ bool  comm_emulated(const Comm* c);
 size_t comm_granularity(const Comm* c);
 
 // Global array of ncomp components, component q at byte offset q*compStride (compStride a multiple of the granularity
-// when ncomp > 1); each component's granules are split evenly over the ranks in rank order.  Collective.  Zero-filled.
-void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp = 1, size_t compStride = 0);
+// when ncomp > 1).  Rank r hosts the granules nearest to bytes [byteSplit[r], byteSplit[r+1]) of every component
+// (byteSplit == nullptr: an even split), so that the hosting follows the z range the rank computes.  Collective.  Zero-filled.
+void* comm_alloc(Comm* c, size_t bytesPerComp, int ncomp = 1, size_t compStride = 0, const size_t* byteSplit = nullptr);
 void  comm_free(Comm* c, void* p);      // collective (host barrier first)
 
 // control block of rank r in the global address space (every rank can read/write every block)

@@ -10,6 +10,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstring>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -84,13 +85,17 @@ struct Solver {
   int zsplit[17];       // rank r owns planes [zsplit[r], zsplit[r+1])
   int redParity;        // alternates the cross-rank reduction slot set
   bool multi() const { return nranks > 1; }
-  void* galloc(size_t bytesPerComp, int ncomp = 1, size_t compStride = 0);   // global (all ranks map it) when multi, else cudaMalloc; zero-filled
+  // global (all ranks map it) when partitioned over GPUs, else cudaMalloc; zero-filled.  elemSplit[r] = first element (of
+  // elemSize bytes) of rank r's share (nranks+1 entries); nullptr = the z-slabs of a cell array with elemSize-byte cells
+  void* galloc(size_t bytesPerComp, int ncomp = 1, size_t compStride = 0, const long long* elemSplit = nullptr, int elemSize = 4);
   void  gfree(void* p);
   void  rankSync();      // device barrier across ranks on the solver stream (no-op on a single GPU / emulated)
   void  clearShared(void* p, size_t bytes);   // zero a small job-wide scratch array (one rank clears, then barrier)
   // per-kernel CUDA-event timing (mf_solver_profile_*): one event pair per launch while enabled
   bool profiling;
-  struct ProfRec { const char* name; cudaEvent_t a, b; };
+  struct ProfRec { const char* name; cudaEvent_t a, b; int tag; };
+  bool profLevels;      // MF_PROFILE_LEVELS set: split the profile of multigrid kernels by level
+  int profTag;          // appended to the kernel name in the profile when >= 0 (multigrid level)
   std::vector<ProfRec> profRecs;
   std::vector<cudaEvent_t> evPool;
   cudaEvent_t profEvent();
@@ -146,12 +151,27 @@ struct ProfScope {   // brackets one launch with events on the solver stream whe
   Solver* s; cudaEvent_t b;
   ProfScope(Solver* s_, const char* name) : s(s_), b(nullptr) {
     if (!s->profiling) return;
-    Solver::ProfRec r; r.name = name; r.a = s->profEvent(); r.b = s->profEvent(); b = r.b;
+    Solver::ProfRec r; r.name = name; r.a = s->profEvent(); r.b = s->profEvent(); b = r.b; r.tag = s->profTag;
     cudaEventRecord(r.a, s->stream); s->profRecs.push_back(r);
   }
   ~ProfScope() { if (b) cudaEventRecord(b, s->stream); }
 };
 #define MF_LAUNCH(s, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
+// Programmatic dependent launch (sm_90+): a kernel launched with MF_LAUNCH_PDL may be scheduled while its predecessor on the
+// stream is still draining; it must call pdlWait() before it touches global memory (waits for the predecessor's completion and
+// memory flush) and calls pdlTrigger() so that ITS successor can be scheduled early.  Hides the ~4 us launch gap between the
+// hundreds of small dependent launches of a V-cycle.  Kernels launched with plain MF_LAUNCH keep full stream ordering.
+template <class... KArgs, class... Args>
+inline void launchPdl(cudaStream_t st, void (*kern)(KArgs...), dim3 grid, dim3 block, Args... args) {
+  cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#define MF_LAUNCH_PDL(s, kern, grid, block, ...) do { if ((s)->profiling) { MF_LAUNCH(s, kern, grid, block, __VA_ARGS__); } \
+  else { mf::launchPdl((s)->stream, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } } while (0)
 #define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())
 // SPMD launch helpers: MF_RANKS iterates over the ranks this process executes; every group of per-rank launches is followed
 // by rankSync (dependent launches on other GPUs read/write the same global arrays).
@@ -177,6 +197,9 @@ __device__ __forceinline__ bool fIsEmpty(int f) { return (f & MF_EMPTY) != 0; }
 __device__ __forceinline__ bool fIsOutflow(int f) { return (f & MF_OUTFLOW) != 0; }
 __device__ __forceinline__ bool fIsStick(int f) { return (f & MF_STICK) != 0; }
 
+__device__ __forceinline__ void pdlWait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdlTrigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#define MF_PDL_PROLOGUE pdlTrigger(); pdlWait();
 __device__ __forceinline__ float warpSum(float v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
 __device__ __forceinline__ double warpSumD(double v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
 #endif

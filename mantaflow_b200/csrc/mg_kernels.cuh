@@ -203,6 +203,7 @@ __device__ __forceinline__ float mgOffdiag0(const OP& op, const typename OP::Row
 // so that no separate clear of x is needed.
 template <class OP, bool XZERO>
 __global__ void __launch_bounds__(256) k_mg_smooth0(LvlD L, MgDims D, float trivialScale, int color, int z0, int z1) {
+  MF_PDL_PROLOGUE
   const OP op(L, trivialScale);
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5) + z0 * L.sy;
   if (row >= L.sy * z1) return;
@@ -232,6 +233,7 @@ __global__ void __launch_bounds__(256) k_mg_smooth0(LvlD L, MgDims D, float triv
 // knCalcResidual, l == 0
 template <class OP>
 __global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D, float trivialScale, int z0, int z1) {
+  MF_PDL_PROLOGUE
   const OP op(L, trivialScale);
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5) + z0 * L.sy;
   if (row >= L.sy * z1) return;
@@ -284,19 +286,24 @@ __device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float
 // knSmoothColor, l > 0: one of the 8 (4) colours (multigrid.cpp:668-711)
 template <bool IS3D>
 __global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int lz1) {
+  MF_PDL_PROLOGUE
   BlkPos q;
   if (!mgBlockThread(L, c, lz0, lz1, q)) return;
-  if (L.type[q.p] == vtInactive) return;
+  // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
+  // reference's own division below would not be finite
+  const float diag = L.A[q.p];
+  if (diag == 0.f) return;
   const float sum = mgStencilSub<IS3D, false>(L, c, q.p, L.b[q.p]);
-  L.x[q.p] = sum / L.A[q.p];
+  L.x[q.p] = sum / diag;
 }
 // knCalcResidual, l > 0: blockIdx.y = colour
 template <bool IS3D>
 __global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {
+  MF_PDL_PROLOGUE
   BlkPos q;
   const int c = blockIdx.y;
   if (!mgBlockThread(L, c, lz0, lz1, q)) return;
-  if (L.type[q.p] == vtInactive) return;
+  // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
   L.r[q.p] = mgStencilSub<IS3D, true>(L, c, q.p, L.b[q.p]);
 }
 
@@ -305,12 +312,13 @@ __global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {
 // guarded) out-of-grid vertices.
 template <bool IS3D>
 __global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1) {
+  MF_PDL_PROLOGUE
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int vx = t % C.sx; const int u = t / C.sx; const int vy = u % C.sy, vz = z0 + u / C.sy;
   if (vz >= z1) return;
   const int v = mgIdx(C, vx, vy, vz);
   C.x[v] = 0.f;
-  if (C.type[v] == vtInactive) return;
+  if (C.A[v] == 0.f) return;          // inactive coarse vertex (all-zero row): b stays 0
   float sum = 0.f;
   const float* __restrict__ fr = F.r;
   if (F.perm) {
@@ -339,11 +347,12 @@ __global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int
 // knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse.  Threads run over the natural
 // coordinates of the fine level, z range [z0,z1) of the fine level; x_coarse is 0 at inactive / padding vertices.
 __global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, int z1) {
+  MF_PDL_PROLOGUE
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int vx = t % F.sx; const int u = t / F.sx; const int vy = u % F.sy, vz = z0 + u / F.sy;
   if (vz >= z1) return;
   const int v = mgIdx(F, vx, vy, vz);
-  if (F.type[v] == vtInactive) return;
+  if (F.perm ? (F.A[v] == 0.f) : (F.type[v] == vtInactive)) return;
   float sum = 0.f;
   const float* __restrict__ cx = C.x;
   for (int z = vz / 2; z <= (vz + 1) / 2; z++)

@@ -24,6 +24,7 @@ struct MgHierarchy {
   int* dFlags;              // job-wide device scratch: [0..3] activate flags, [4..5] coarsening flags
   int usedFallback;
   bool pendingSolo;         // a group of rank-0-only launches has not been followed by a cross-rank barrier yet
+  std::vector<std::vector<int>> pairSplit;   // blocked level l: rank r sweeps z pairs [pairSplit[l][r], pairSplit[l][r+1])
 };
 
 // ---- partition of a level over the ranks ----------------------------------------------------------------------
@@ -33,15 +34,15 @@ static bool lvlSolo(const MgHierarchy* mg, int l) {
   const Solver* s = mg->s;
   if (!s->multi() || l == 0) return false;
   const LvlD& L = mg->lv[l];
-  return L.n < 32768 || (L.PZ - 2) < 2 * s->nranks;
+  // below ~1M vertices a colour sweep takes about as long as one cross-GPU barrier
+  return L.n < (1 << 20) || (L.PZ - 2) < 2 * s->nranks;
 }
 // blocked level: range of z pairs of rank r
 static void lvlPairs(const MgHierarchy* mg, int l, int r, int& lz0, int& lz1) {
   const Solver* s = mg->s; const LvlD& L = mg->lv[l];
   const int BZ = mg->D.is3D ? L.PZ - 2 : 1;
   if (!s->multi()) { lz0 = 0; lz1 = BZ; return; }
-  if (lvlSolo(mg, l)) { lz0 = 0; lz1 = (r == 0) ? BZ : 0; return; }
-  lz0 = (int)((long long)BZ * r / s->nranks); lz1 = (int)((long long)BZ * (r + 1) / s->nranks);
+  lz0 = mg->pairSplit[l][r]; lz1 = mg->pairSplit[l][r + 1];
 }
 // natural z range of rank r on level l
 static void lvlPlanes(const MgHierarchy* mg, int l, int r, int& z0, int& z1) {
@@ -55,7 +56,10 @@ static void lvlStore(const MgHierarchy* mg, int l, int r, int& p0, int& p1) {
   const Solver* s = mg->s; const LvlD& L = mg->lv[l];
   if (!s->multi()) { p0 = 0; p1 = L.na; return; }
   if (lvlSolo(mg, l)) { p0 = 0; p1 = (r == 0) ? L.na : 0; return; }
-  p0 = (int)((long long)L.na * r / s->nranks); p1 = (int)((long long)L.na * (r + 1) / s->nranks);
+  if (l == 0) { const long long xy = (long long)L.sx * L.sy; p0 = (int)(xy * s->zsplit[r]); p1 = (int)(xy * s->zsplit[r + 1]); return; }
+  const int pair = L.NC * L.PY * L.PX;            // storage entries per z pair
+  p0 = (r == 0) ? 0 : (mg->pairSplit[l][r] + L.zoff) * pair;
+  p1 = (r == s->nranks - 1) ? L.na : (mg->pairSplit[l][r + 1] + L.zoff) * pair;
 }
 static void beginGroup(MgHierarchy* mg, bool solo) { if (!solo && mg->pendingSolo) { mg->s->rankSync(); mg->pendingSolo = false; } }
 static void endGroup(MgHierarchy* mg, bool solo) { if (!solo) mg->s->rankSync(); else if (mg->s->multi()) mg->pendingSolo = true; }
@@ -78,6 +82,7 @@ __device__ __forceinline__ void cgBlockSum2(double& a, double& b, double (*sh)[2
 
 template <bool LEVEL0>
 __global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
+  MF_PDL_PROLOGUE
   __shared__ double sh[2][2][32];
   __shared__ double vec[1024];
   constexpr int NS = LEVEL0 ? 7 : 27;
@@ -252,13 +257,42 @@ MgHierarchy* mg_create(Solver* s) {
     LvlD L; setLayout(L, sx, sy, sz, is3D, l > 0);
     // every array is zero-filled by galloc.  Operator planes are separate components, so that each plane is split over the
     // GPUs by z like the vectors; the plane stride is padded to the allocation granularity when the level is distributed.
-    L.r = (float*)s->galloc(sizeof(float) * (size_t)L.na);
-    L.type = (unsigned char*)s->galloc((size_t)L.na);
+    // Hosting follows the sweep partition: rank r hosts the granules nearest to its z pairs, rank 0 all of a solo level.
+    mg->lv.push_back(L);
+    const int P = s->nranks;
+    std::vector<int> ps(P + 1, 0);
+    std::vector<long long> es(P + 1, 0);
+    if (l > 0) {
+      const int BZ = is3D ? L.PZ - 2 : 1;
+      const long long pair = (long long)L.NC * L.PY * L.PX;
+      const bool solo = lvlSolo(mg, l);
+      for (int r = 0; r <= P; r++) ps[r] = solo ? (r == 0 ? 0 : BZ) : (int)((long long)BZ * r / P);
+      if (!solo && s->comm && !comm_emulated(s->comm)) {
+        // move the pair boundaries onto the allocation granules the vectors are split at (4-byte entries)
+        const long long gran = (long long)(comm_granularity(s->comm) / sizeof(float));
+        for (int r = 1; r < P; r++) {
+          const long long e = (ps[r] + L.zoff) * pair;                      // first entry of rank r's share
+          const long long eg = (e + gran / 2) / gran * gran;               // start of the granule rank r hosts from
+          int q = (int)((eg + pair - 1) / pair) - L.zoff;                   // first pair starting at or behind it
+          if (q < ps[r - 1]) q = ps[r - 1];
+          if (q > BZ) q = BZ;
+          ps[r] = q;
+        }
+      }
+      for (int r = 0; r <= P; r++) es[r] = (r == 0) ? 0 : (r == P ? (solo ? 0 : L.na) : (ps[r] + L.zoff) * pair);
+      if (solo) for (int r = 1; r <= P; r++) es[r] = L.na;
+    } else {
+      for (int r = 0; r <= P; r++) es[r] = (long long)L.sx * L.sy * s->zsplit[r];
+    }
+    mg->pairSplit.push_back(ps);
+    mg->lv.pop_back();
+    L.r = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
+    L.type = (unsigned char*)s->galloc((size_t)L.na, 1, 0, es.data(), 1);
     if (l > 0) {
       L.as = planeStride(s, L.na);
-      L.A = (float*)s->galloc(sizeof(float) * (size_t)L.na, mg->D.SS, sizeof(float) * (size_t)L.as);
-      L.x = (float*)s->galloc(sizeof(float) * (size_t)L.na);
-      L.b = (float*)s->galloc(sizeof(float) * (size_t)L.na);
+      L.A = (float*)s->galloc(sizeof(float) * (size_t)L.na, mg->D.SS, sizeof(float) * (size_t)L.as, es.data(), 4);
+      L.x = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
+      L.b = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
     }                                                      // level 0: A (float planes) or code0 are allocated by mg_set_a
     mg->lv.push_back(L);
   };
@@ -430,7 +464,7 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
   // planes because the coarsest-level CG reads them
   bool coded = false;
   if (maxLevel > 0) {
-    if (!mg->code0) mg->code0 = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)L0.n);
+    if (!mg->code0) mg->code0 = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)L0.n, 1, 0, nullptr, 2);
     s->clearShared(mg->dFlags, sizeof(int) * 4);
     MG_SETUP(mg, 0, k_mg_copy_activate<true>, 256, L0, mg->D, A0, Ai, Aj, Ak, mg->trivialScale, mg->code0, mg->dFlags);
     CUDA_CHECK(cudaMemcpyAsync(s->hostInts, mg->dFlags, sizeof(int) * 4, cudaMemcpyDeviceToHost, s->stream));
@@ -474,15 +508,15 @@ static void smooth0(MgHierarchy* mg, bool reversed, bool xzero) {
     MF_RANKS(s, r) {
       int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
       if (z1 <= z0) continue;
-      if (xzero && c == 0) { MF_LAUNCH(s, (k_mg_smooth0<OP, true>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
-      else                 { MF_LAUNCH(s, (k_mg_smooth0<OP, false>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+      if (xzero && c == 0) { MF_LAUNCH_PDL(s, (k_mg_smooth0<OP, true>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
+      else                 { MF_LAUNCH_PDL(s, (k_mg_smooth0<OP, false>), rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, color, z0, z1); }
     }
     endGroup(mg, false);
   }
 }
 
 static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
-  Solver* s = mg->s;
+  Solver* s = mg->s; s->profTag = l;
   LvlD& L = mg->lv[l];
   if (l == 0) {
     if (mg->useCode) smooth0<L0Code>(mg, reversed, xzero); else smooth0<L0Float>(mg, reversed, xzero);
@@ -496,15 +530,15 @@ static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
       const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0);
-      if (mg->D.is3D) { MF_LAUNCH(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
-      else            { MF_LAUNCH(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+      if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+      else            { MF_LAUNCH_PDL(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
     }
     endGroup(mg, solo);
   }
 }
 
 static void residual(MgHierarchy* mg, int l) {
-  Solver* s = mg->s;
+  Solver* s = mg->s; s->profTag = l;
   LvlD& L = mg->lv[l];
   const bool solo = lvlSolo(mg, l);
   beginGroup(mg, solo);
@@ -512,21 +546,21 @@ static void residual(MgHierarchy* mg, int l) {
     if (l == 0) {
       int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
       if (z1 <= z0) continue;
-      if (mg->useCode) { MF_LAUNCH(s, k_mg_residual0<L0Code>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
-      else             { MF_LAUNCH(s, k_mg_residual0<L0Float>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
+      if (mg->useCode) { MF_LAUNCH_PDL(s, k_mg_residual0<L0Code>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
+      else             { MF_LAUNCH_PDL(s, k_mg_residual0<L0Float>, rowsBlocks(L, z0, z1), 256, L, mg->D, mg->trivialScale, z0, z1); }
     } else {
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
       const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0), 128), L.NC);
-      if (mg->D.is3D) { MF_LAUNCH(s, k_mg_residual<true>, gr, 128, L, lz0, lz1); }
-      else            { MF_LAUNCH(s, k_mg_residual<false>, gr, 128, L, lz0, lz1); }
+      if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_residual<true>, gr, 128, L, lz0, lz1); }
+      else            { MF_LAUNCH_PDL(s, k_mg_residual<false>, gr, 128, L, lz0, lz1); }
     }
   }
   endGroup(mg, solo);
 }
 // coarse level l+1 <- fine level l; the coarse level's partition drives the launch
 static void restrictTo(MgHierarchy* mg, int l) {
-  Solver* s = mg->s;
+  Solver* s = mg->s; s->profTag = l;
   LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
   const bool solo = lvlSolo(mg, l + 1);
   beginGroup(mg, solo && lvlSolo(mg, l));     // reads the fine residual: the fine level's writers must have arrived
@@ -534,14 +568,14 @@ static void restrictTo(MgHierarchy* mg, int l) {
     int z0, z1; lvlPlanes(mg, l + 1, r, z0, z1);
     if (z1 <= z0) continue;
     const long long nt = (long long)C.sx * C.sy * (z1 - z0);
-    if (mg->D.is3D) { MF_LAUNCH(s, k_mg_restrict<true>, cdiv(nt, 128), 128, F, C, z0, z1); }
-    else            { MF_LAUNCH(s, k_mg_restrict<false>, cdiv(nt, 128), 128, F, C, z0, z1); }
+    if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_restrict<true>, cdiv(nt, 128), 128, F, C, z0, z1); }
+    else            { MF_LAUNCH_PDL(s, k_mg_restrict<false>, cdiv(nt, 128), 128, F, C, z0, z1); }
   }
   endGroup(mg, solo);
 }
 // fine level l += P * coarse level l+1; the fine level's partition drives the launch
 static void interpAdd(MgHierarchy* mg, int l) {
-  Solver* s = mg->s;
+  Solver* s = mg->s; s->profTag = l;
   LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
   const bool solo = lvlSolo(mg, l);
   beginGroup(mg, solo);
@@ -549,7 +583,7 @@ static void interpAdd(MgHierarchy* mg, int l) {
     int z0, z1; lvlPlanes(mg, l, r, z0, z1);
     if (z1 <= z0) continue;
     const long long nt = (long long)F.sx * F.sy * (z1 - z0);
-    MF_LAUNCH(s, k_mg_interp_add, cdiv(nt, 256), 256, F, C, z0, z1);
+    MF_LAUNCH_PDL(s, k_mg_interp_add, cdiv(nt, 256), 256, F, C, z0, z1);
   }
   endGroup(mg, solo);
 }
@@ -575,8 +609,8 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     const bool solo = s->multi();        // the coarsest level is always handled by rank 0
     beginGroup(mg, solo);
     if (s->rankBegin == 0) {
-      if (maxLevel == 0) { MF_LAUNCH(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
-      else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
+      if (maxLevel == 0) { MF_LAUNCH_PDL(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
+      else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH_PDL(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
     }
     endGroup(mg, solo);
   }
@@ -585,6 +619,7 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }
   flushGroups(mg);
+  s->profTag = -1;
   // the trailing calcResidual(0)/calcResidualNorm(0) of doVCycle only feed its return value, which the CG driver
   // ignores (conjugategrad.cpp:162-167) -- skipped.
 }

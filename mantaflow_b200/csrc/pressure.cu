@@ -101,20 +101,20 @@ struct CgDriver {
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
   }
   void iterate() {
-    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); }
+    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
     if (pcMethod == 0) {
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_update<true>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_update<true>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
       redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<true>{ st });
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
       s->rankSync();
     } else {
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_update<false>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_update<false>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
       redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<false>{ st });
       applyPrecond(false);
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_beta, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
       redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
       s->rankSync();
     }
   }

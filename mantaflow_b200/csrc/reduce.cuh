@@ -96,6 +96,7 @@ __device__ __forceinline__ void gridReduceK(double (&v)[K], const int (&ops)[K],
 }
 template <int K, class Fin>
 __global__ void k_red_finish(RedOps<K> ops, RedCtx ctx, Fin fin) {
+  MF_PDL_PROLOGUE
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   double r[K];
 #pragma unroll
@@ -116,7 +117,7 @@ inline void redFinish(Solver* s, const RedOps<K>& ops, Fin fin) {
   if (!s->multi()) return;
   s->rankSync();
   RedCtx c = redCtx(s, s->rankBegin);
-  k_red_finish<K, Fin><<<1, 32, 0, s->stream>>>(ops, c, fin);
+  launchPdl(s->stream, k_red_finish<K, Fin>, dim3(1), dim3(32), ops, c, fin);
   s->launches++;
   s->redParity ^= 1;
 }

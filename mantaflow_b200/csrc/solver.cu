@@ -22,8 +22,13 @@ void check_same_solver(const Grid* a, const Grid* b, const char* what) {
 void Solver::use() const { cudaSetDevice(device); }
 
 // ---- multi-GPU plumbing (comm.h) -------------------------------------------------------------------------
-void* Solver::galloc(size_t bytesPerComp, int ncomp, size_t compStride) {
-  if (comm && !comm_emulated(comm)) return comm_alloc(comm, bytesPerComp, ncomp, compStride);
+void* Solver::galloc(size_t bytesPerComp, int ncomp, size_t compStride, const long long* elemSplit, int elemSize) {
+  if (comm && !comm_emulated(comm)) {
+    size_t bs[COMM_MAX_RANKS + 1];
+    for (int r = 0; r <= nranks; r++)
+      bs[r] = (size_t)(elemSplit ? elemSplit[r] : (long long)nx * ny * zsplit[r]) * (size_t)elemSize;
+    return comm_alloc(comm, bytesPerComp, ncomp, compStride, bs);
+  }
   const size_t total = ncomp > 1 ? compStride * (size_t)(ncomp - 1) + bytesPerComp : bytesPerComp;
   void* p = nullptr;
   CUDA_CHECK(cudaMalloc(&p, total));
@@ -206,6 +211,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   int mx = nx > ny ? nx : ny; if (nz > mx) mx = nz;
   s->dx = (float)(1.0 / mx);       // grid.cpp:57
   s->device = device;
+  s->profTag = -1; s->profLevels = getenv("MF_PROFILE_LEVELS") != nullptr;
   s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->profiling = false;
   for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
   CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -305,6 +311,7 @@ int mf_solver_profile_end(mf_solver* sp, char* buf, int buflen) {
     size_t b0 = n.find_first_not_of("( "); if (b0 == std::string::npos) b0 = 0;
     size_t e0 = n.find_first_of("<)", b0); n = n.substr(b0, e0 == std::string::npos ? std::string::npos : e0 - b0);
     if (n.compare(0, 4, "mf::") == 0) n = n.substr(4);
+    if (r.tag >= 0 && s->profLevels) n += "@L" + std::to_string(r.tag);
     auto& a = agg[n]; a.first++; a.second += ms;
     s->evPool.push_back(r.a); s->evPool.push_back(r.b);
   }

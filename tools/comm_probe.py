@@ -20,11 +20,12 @@ def main():
     c = l.mf_comm_create(rank, world, local, session.encode())
     if not c:
         raise SystemExit("rank %d: mf_comm_create failed: %s" % (rank, l.mf_last_error().decode()))
-    out = (C.c_double * 8)()
+    out = (C.c_double * 16)()
     mb = int(os.environ.get("PROBE_MB", "256"))
     _lib.check(l.mf_comm_selftest(c, mb << 20, 2000, out))
     print(json.dumps({"rank": rank, "world": world, "mismatches": out[0], "barrier_us": out[1], "peer_read_gbs": out[2],
-                      "peer_write_gbs": out[3], "granularity": out[4], "local_copy_gbs": out[5], "slab_mb": mb}), flush=True)
+                      "peer_write_gbs": out[3], "granularity": out[4], "local_copy_gbs": out[5], "slab_mb": mb,
+                      "chain_us_plain": out[6], "chain_us_own_slab": out[7], "chain_us_peer_slab": out[8]}), flush=True)
     l.mf_comm_destroy(c)
 
 
