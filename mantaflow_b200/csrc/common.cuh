@@ -162,14 +162,19 @@ struct ProfScope {   // brackets one launch with events on the solver stream whe
 // memory flush) and calls pdlTrigger() so that ITS successor can be scheduled early.  Hides the ~4 us launch gap between the
 // hundreds of small dependent launches of a V-cycle.  Kernels launched with plain MF_LAUNCH keep full stream ordering.
 template <class... KArgs, class... Args>
-inline void launchPdl(cudaStream_t st, void (*kern)(KArgs...), dim3 grid, dim3 block, Args... args) {
-  cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+inline void launchPdlS(cudaStream_t st, size_t smem, void (*kern)(KArgs...), dim3 grid, dim3 block, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
+template <class... KArgs, class... Args>
+inline void launchPdl(cudaStream_t st, void (*kern)(KArgs...), dim3 grid, dim3 block, Args... args) { launchPdlS(st, 0, kern, grid, block, args...); }
+// with dynamic shared memory (profiling mode brackets the launch with events like MF_LAUNCH)
+#define MF_LAUNCH_PDL_SMEM(s, smem, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); \
+  mf::launchPdlS((s)->stream, smem, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } while (0)
 #define MF_LAUNCH_PDL(s, kern, grid, block, ...) do { if ((s)->profiling) { MF_LAUNCH(s, kern, grid, block, __VA_ARGS__); } \
   else { mf::launchPdl((s)->stream, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } } while (0)
 #define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())

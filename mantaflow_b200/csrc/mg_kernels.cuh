@@ -242,9 +242,11 @@ __global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D, float tr
   for (int vx = threadIdx.x & 31; vx < L.sx; vx += 32) {
     const int v = base + vx;
     const typename OP::Row r = op.row(v);
-    if (op.inactive(r)) continue;        // r stays 0 at inactive vertices (cleared at creation, never written)
-    float sum = mgOffdiag0(op, r, L, D, L.x, v, vx, vy, vz, op.rhs(r, L.b[v]));
-    sum -= op.diag(r, v) * L.x[v];
+    float sum = 0.f;                     // inactive vertices: r = 0 (the restriction adds them unconditionally)
+    if (!op.inactive(r)) {
+      sum = mgOffdiag0(op, r, L, D, L.x, v, vx, vy, vz, op.rhs(r, L.b[v]));
+      sum -= op.diag(r, v) * L.x[v];
+    }
     L.r[v] = sum;
   }
 }

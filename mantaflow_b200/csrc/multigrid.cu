@@ -3,6 +3,7 @@
 // knGenCoarseGridOperator :580-657, smoothGS :713-737, solveCG :796-902).
 #include "multigrid.h"
 #include "mg_kernels.cuh"
+#include "mg_fused0.cuh"
 #include "comm.h"
 #include <algorithm>
 #include <cmath>
@@ -588,6 +589,35 @@ static void interpAdd(MgHierarchy* mg, int l) {
   endGroup(mg, solo);
 }
 
+// level 0, first sweep: x = 0, smooth colour 0 then colour 1 in one kernel (x -> L0.x)
+template <class OP>
+static void fusedPresmooth0(MgHierarchy* mg) {
+  Solver* s = mg->s;
+  LvlD& L = mg->lv[0];
+  s->profTag = 0;
+  beginGroup(mg, false);
+  MF_RANKS(s, r) {
+    int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+    if (z1 > z0) { MF_LAUNCH_PDL(s, k_mg_presmooth0<OP>, rowsBlocks(L, z0, z1), 256, L, mg->trivialScale, 0, z0, z1); }
+  }
+  endGroup(mg, false);
+}
+// level 0, up leg: x += P x_coarse, smooth colour 1 then colour 0; reads x (in L0.r) and writes dst
+template <class OP>
+static void fusedUp0(MgHierarchy* mg, float* dst) {
+  Solver* s = mg->s;
+  LvlD& L = mg->lv[0]; LvlD& C = mg->lv[1];
+  s->profTag = 0;
+  beginGroup(mg, false);
+  MF_RANKS(s, r) {
+    int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+    if (z1 <= z0) continue;
+    const dim3 gr(cdiv(L.sx, UP_X), cdiv(L.sy, UP_Y), cdiv(z1 - z0, UP_Z));
+    MF_LAUNCH_PDL(s, k_mg_up0<OP>, gr, 256, L, C, mg->trivialScale, (const float*)L.r, dst, 1, z0, z1);
+  }
+  endGroup(mg, false);
+}
+
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
 void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
@@ -600,7 +630,17 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) CUDA_CHECK(cudaMemsetAsync(dst + sp.off, 0, sizeof(float) * (size_t)sp.n, s->stream)); }
     s->rankSync();
   }
-  for (int l = 0; l < maxLevel; l++) {
+  // level 0 of the standard V(1,1) cycle in 3-D uses the fused kernels of mg_fused0.cuh.  The down leg keeps x in the level's
+  // own array (L0.r) and puts the residual into dst, which is free until the tiled up-leg kernel writes it out of place.
+  const bool fused0 = mg->D.is3D && maxLevel > 0 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_UNFUSED");
+  float* const r0keep = L0.r;
+  if (fused0) {
+    L0.x = r0keep; L0.r = dst;
+    if (mg->useCode) fusedPresmooth0<L0Code>(mg); else fusedPresmooth0<L0Float>(mg);
+    residual(mg, 0);
+    restrictTo(mg, 0);
+  }
+  for (int l = fused0 ? 1 : 0; l < maxLevel; l++) {
     for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0);
     residual(mg, l);
     restrictTo(mg, l);
@@ -614,9 +654,13 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     }
     endGroup(mg, solo);
   }
-  for (int l = maxLevel - 1; l >= 0; l--) {
+  for (int l = maxLevel - 1; l >= (fused0 ? 1 : 0); l--) {
     interpAdd(mg, l);
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
+  }
+  if (fused0) {
+    L0.r = r0keep; L0.x = dst;
+    if (mg->useCode) fusedUp0<L0Code>(mg, dst); else fusedUp0<L0Float>(mg, dst);
   }
   flushGroups(mg);
   s->profTag = -1;
