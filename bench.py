@@ -45,8 +45,9 @@ ALGO_BYTES_PER_CELL = {
     "k_add_buoyancy": 32.0,    # flags 4 + density 4 + vel 12 r + 12 w
     "k_wall_buoyancy": 32.0,
     "k_make_rhs": 20.0,        # flags 4 + vel 12 + rhs 4
-    "k_make_laplace": 20.0,    # flags 4 + 4 coefficient grids 16
+    "k_make_laplace": 6.0,     # flags 4 + row code 2 (the 4 coefficient planes, +16, only when a preconditioner is (re)built)
     "k_cg_spmv_dot": 28.0,     # stored-A: flags 4 + src 4 + dst 4 + A 16
+    "k_cg_spmv_dot_code": 10.0,  # 16-bit row code 2 + src 4 + dst 4
     "k_cg_update": 24.0,       # x r/w 8 + search 4 + residual r/w 8 + tmp 4
     "k_cg_dot_beta": 8.0, "k_cg_dot_sigma": 8.0,
     "k_cg_search": 12.0,
@@ -56,6 +57,8 @@ ALGO_BYTES_PER_CELL = {
     # 3 of the 4 sweeps per V-cycle are of the first kind -> 13 on average
     "k_mg_smooth0": 13.0,
     "k_mg_residual0": 14.0,    # code 2 + x 4 + b 4 + r 4
+    "k_mg_presmooth0": 10.0,   # first sweep pair of a V-cycle (x == 0): code 2 + b 4 + x out 4
+    "k_mg_up0": 14.5,          # interpolate + add + both colour sweeps in one pass: code 2 + x 4 + b 4 + coarse x 0.5 + x out 4
     # k_mg_restrict / k_mg_interp_add / k_mg_smooth / k_mg_residual run on every level: no single bytes-per-cell figure
     "k_apply_cylinder": 4.0,
 }
@@ -74,6 +77,7 @@ def _parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
+    ap.add_argument("--kernels-out", default="", help="write the complete per-kernel table (JSON) to this file")
     return ap.parse_args()
 
 
@@ -305,11 +309,15 @@ def main():
             n, tot = int(n), float(tot)
             e = {"kernel": name, "launches_per_step": n / a.profile_steps, "ms_per_step": tot / a.profile_steps,
                  "share_of_step": tot / prof_ms, "avg_us": 1e3 * tot / n}
-            if name in ALGO_BYTES_PER_CELL:
-                e["algo_bytes_per_cell"] = ALGO_BYTES_PER_CELL[name]
-                e["achieved_gbs"] = ALGO_BYTES_PER_CELL[name] * cells_gpu / (tot / n * 1e-3) / 1e9
+            base = name[:-3] if name.endswith("@L0") else name     # MF_PROFILE_LEVELS=1 tags multigrid kernels with their level
+            if base in ALGO_BYTES_PER_CELL:
+                e["algo_bytes_per_cell"] = ALGO_BYTES_PER_CELL[base]
+                e["achieved_gbs"] = ALGO_BYTES_PER_CELL[base] * cells_gpu / (tot / n * 1e-3) / 1e9
                 e["frac_of_peak"] = e["achieved_gbs"] / peak
             kernels.append(e)
+        if a.kernels_out and rank == 0:
+            with open(a.kernels_out, "w") as f:
+                json.dump({"ms_per_step_profiled": prof_ms / a.profile_steps, "kernels": kernels}, f, indent=1)
         top = next((k for k in kernels if "achieved_gbs" in k), None)
         if top:
             traffic = None
@@ -320,7 +328,7 @@ def main():
                 pass
             roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak, "unit": "GB/s",
                         "frac": top["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
-                        "algo_bytes_per_launch": ALGO_BYTES_PER_CELL[top["kernel"]] * cells_gpu, "avg_launch_us": top["avg_us"],
+                        "algo_bytes_per_launch": top["algo_bytes_per_cell"] * cells_gpu, "avg_launch_us": top["avg_us"],
                         "share_of_step": top["share_of_step"], "timed": "CUDA events around every launch, %d extra steps after the timed region" % a.profile_steps}
 
     # ---- e2e: host buffers, copies inside the timed region -------------------------------------------------------

@@ -178,6 +178,9 @@ int          mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* 
                                     const mf_grid* fractions);          /* conjugategrad.h:154 */
 int          mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* src,
                              const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak); /* conjugategrad.h:118/136 */
+/* dst = A(flags) * src through the CG's 16-bit row codes (MakeLaplaceMatrix without fractions + ApplyMatrix fused; needs
+   nx % 4 == 0): must equal mf_make_laplace_matrix + mf_apply_matrix bit for bit. */
+int          mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* src);
 /* cgSolveDiffusion(flags, grid, alpha, cgMaxIterFac, cgAccuracy), conjugategrad.cpp:350 */
 int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float alpha, float cgMaxIterFac, float cgAccuracy);
 

@@ -101,6 +101,7 @@ SIGNATURES = {
     "mf_release_mg": (_i, [_P]),
     "mf_make_laplace_matrix": (_i, [_P, _P, _P, _P, _P, _P]),
     "mf_apply_matrix": (_i, [_P, _P, _P, _P, _P, _P, _P]),
+    "mf_apply_laplace_rowcode": (_i, [_P, _P, _P]),
     "mf_cg_solve_diffusion": (_i, [_P, _P, _f, _f, _f]),
     "mf_mg_info": (_i, [_P, C.POINTER(_i), C.POINTER(_i)]),
     "mf_mg_level_size": (_i, [_P, _i, C.POINTER(_i)]),

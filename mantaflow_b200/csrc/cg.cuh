@@ -31,6 +31,7 @@ struct CgVecs {
   float* dst; float* residual; float* search; float* tmp;
   const float* rhs;
   const float *A0, *Ai, *Aj, *Ak;
+  const unsigned short* code;   // 16-bit row codes (pressure_kernels.cuh CGC_*), or null: use the float planes
 };
 
 // finishing functors of the CG reductions: run once per process with the grid-wide (and rank-wide) results
@@ -90,9 +91,76 @@ __global__ void __launch_bounds__(256) k_cg_spmv_dot(Geo g, CgVecs v, CgState* s
   gridReduceK<1>(acc, ops, ctx, sh, FinAlpha{ st });
 }
 
+// The same with the 16-bit row codes, four x-consecutive cells per thread (needs nx % 4 == 0).  ApplyMatrix is a pure
+// linear-index stencil (conjugategrad.h:205-222), so the kernel is 1-D over quads of the rank's slab: one 8-byte code load, five
+// 16-byte loads of search (centre, +-Y, +-Z), the two x neighbours by shuffle, one 16-byte store: 10 B/cell of DRAM traffic.
+// The products use the reconstructed coefficients (-1 or 0) in the reference's order, so tmp is bit-identical to applyRow's.
+__device__ __forceinline__ float rowFromCode(int c, float s, float xm, float xp, float ym, float yp, float zm, float zp, bool is3D) {
+  float r = s * (float)((c >> CGC_DIAG_SHIFT) & 7);
+  r += xm * ((c & CGC_XM) ? -1.0f : 0.0f);
+  r += xp * ((c & CGC_XP) ? -1.0f : 0.0f);
+  r += ym * ((c & CGC_YM) ? -1.0f : 0.0f);
+  r += yp * ((c & CGC_YP) ? -1.0f : 0.0f);
+  if (is3D) {
+    r += zm * ((c & CGC_ZM) ? -1.0f : 0.0f);
+    r += zp * ((c & CGC_ZP) ? -1.0f : 0.0f);
+  }
+  return (c & CGC_FLUID) ? r : s;
+}
+__global__ void __launch_bounds__(256) k_cg_spmv_dot_code(Geo g, Span sp, CgVecs v, CgState* st, RedCtx ctx) {
+  MF_PDL_PROLOGUE
+  __shared__ double sh[32];
+  if (st->done) return;
+  double acc[1] = { 0.0 };
+  const long long Y = g.nx, Z = g.Z, N = g.N;
+  const long long q0 = sp.off >> 2, q1 = (sp.off + sp.n) >> 2;
+  const int lane = threadIdx.x & 31;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  // whole warps walk the range so that the shuffles below are always executed by all 32 lanes
+  for (long long qb = q0 + (blockIdx.x * (long long)blockDim.x + (threadIdx.x & ~31)); qb < q1; qb += (long long)gridDim.x * blockDim.x) {
+    const long long q = qb + lane;
+    const bool on = q < q1;
+    const long long idx = (on ? q : q1 - 1) << 2;
+    const float4 s = *reinterpret_cast<const float4*>(v.search + idx);
+    const uint2 cw = *reinterpret_cast<const uint2*>(v.code + idx);
+    const float4 ym = (idx - Y >= 0) ? *reinterpret_cast<const float4*>(v.search + idx - Y) : zero4;
+    const float4 yp = (idx + Y < N) ? *reinterpret_cast<const float4*>(v.search + idx + Y) : zero4;
+    float4 zm = zero4, zp = zero4;
+    if (g.is3D) {
+      if (idx - Z >= 0) zm = *reinterpret_cast<const float4*>(v.search + idx - Z);
+      if (idx + Z < N) zp = *reinterpret_cast<const float4*>(v.search + idx + Z);
+    }
+    float xm = __shfl_up_sync(0xffffffffu, s.w, 1), xp = __shfl_down_sync(0xffffffffu, s.x, 1);
+    if (lane == 0) xm = (idx - 1 >= 0) ? v.search[idx - 1] : 0.f;
+    if (lane == 31 || q + 1 >= q1) xp = (idx + 4 < N) ? v.search[idx + 4] : 0.f;
+    float4 t;
+    t.x = rowFromCode((int)(cw.x & 0xffffu), s.x, xm, s.y, ym.x, yp.x, zm.x, zp.x, g.is3D);
+    t.y = rowFromCode((int)(cw.x >> 16), s.y, s.x, s.z, ym.y, yp.y, zm.y, zp.y, g.is3D);
+    t.z = rowFromCode((int)(cw.y & 0xffffu), s.z, s.y, s.w, ym.z, yp.z, zm.z, zp.z, g.is3D);
+    t.w = rowFromCode((int)(cw.y >> 16), s.w, s.z, xp, ym.w, yp.w, zm.w, zp.w, g.is3D);
+    if (on) {
+      *reinterpret_cast<float4*>(v.tmp + idx) = t;
+      acc[0] += (double)(t.x * s.x); acc[0] += (double)(t.y * s.y); acc[0] += (double)(t.z * s.z); acc[0] += (double)(t.w * s.w);
+    }
+  }
+  const int ops[1] = { 0 };
+  gridReduceK<1>(acc, ops, ctx, sh, FinAlpha{ st });
+}
+
 // dst += alpha*search ; residual += -alpha*tmp ; norm(residual)     (conjugategrad.cpp:254-277)
 // PCNONE: also tmp := residual (implicitly) and sigmaNew = residual . residual, beta        (:279-286)
 template <bool PCNONE>
+__device__ __forceinline__ float cgUpdateCell(float& d, float se, float r0, float t, float alpha, float nalpha, int useL2, double* acc) {
+  d += alpha * se;
+  const float r = r0 + nalpha * t;
+  const double rd = (double)r;
+  if (useL2) acc[0] += rd * rd;
+  else { if (rd < acc[1]) acc[1] = rd; if (rd > acc[2]) acc[2] = rd; }
+  if (PCNONE) acc[3] += (double)(r * r);
+  return r;
+}
+// V4: the span starts and ends on a multiple of four cells (always the case when nx % 4 == 0): 16-byte accesses
+template <bool PCNONE, bool V4>
 __global__ void __launch_bounds__(256) k_cg_update(Span sp, CgVecs v, CgState* st, RedCtx ctx) {
   MF_PDL_PROLOGUE
   __shared__ double sh[32];
@@ -100,21 +168,35 @@ __global__ void __launch_bounds__(256) k_cg_update(Span sp, CgVecs v, CgState* s
   const float alpha = st->alpha, nalpha = -alpha;
   const int useL2 = st->useL2;
   double acc[4] = { 0.0, 1e300, -1e300, 0.0 };   // sumsqr, min, max, r.r (float products)
-  const long long i0 = sp.off + blockIdx.x * (long long)blockDim.x + threadIdx.x, iend = sp.off + sp.n;
   const long long st_ = (long long)gridDim.x * blockDim.x;
-  for (long long idx = i0; idx < iend; idx += st_) {
-    v.dst[idx] += alpha * v.search[idx];
-    const float r = v.residual[idx] + nalpha * v.tmp[idx];
-    v.residual[idx] = r;
-    if (useL2) { const double rd = (double)r; acc[0] += rd * rd; }
-    else { const double rd = (double)r; if (rd < acc[1]) acc[1] = rd; if (rd > acc[2]) acc[2] = rd; }
-    if (PCNONE) acc[3] += (double)(r * r);
+  if (V4) {
+    const long long q1 = (sp.off + sp.n) >> 2;
+    for (long long q = (sp.off >> 2) + blockIdx.x * (long long)blockDim.x + threadIdx.x; q < q1; q += st_) {
+      float4 d = reinterpret_cast<float4*>(v.dst)[q];
+      const float4 se = reinterpret_cast<const float4*>(v.search)[q];
+      float4 r = reinterpret_cast<float4*>(v.residual)[q];
+      const float4 t = reinterpret_cast<const float4*>(v.tmp)[q];
+      r.x = cgUpdateCell<PCNONE>(d.x, se.x, r.x, t.x, alpha, nalpha, useL2, acc);
+      r.y = cgUpdateCell<PCNONE>(d.y, se.y, r.y, t.y, alpha, nalpha, useL2, acc);
+      r.z = cgUpdateCell<PCNONE>(d.z, se.z, r.z, t.z, alpha, nalpha, useL2, acc);
+      r.w = cgUpdateCell<PCNONE>(d.w, se.w, r.w, t.w, alpha, nalpha, useL2, acc);
+      reinterpret_cast<float4*>(v.dst)[q] = d;
+      reinterpret_cast<float4*>(v.residual)[q] = r;
+    }
+  } else {
+    const long long i0 = sp.off + blockIdx.x * (long long)blockDim.x + threadIdx.x, iend = sp.off + sp.n;
+    for (long long idx = i0; idx < iend; idx += st_) {
+      float d = v.dst[idx];
+      v.residual[idx] = cgUpdateCell<PCNONE>(d, v.search[idx], v.residual[idx], v.tmp[idx], alpha, nalpha, useL2, acc);
+      v.dst[idx] = d;
+    }
   }
   const int ops[4] = { 0, 1, 2, 0 };
   gridReduceK<4>(acc, ops, ctx, sh, FinUpdate<PCNONE>{ st });
 }
 
 // sigmaNew = tmp . residual ; beta = sigmaNew / sigma                 (conjugategrad.cpp:279-295), preconditioned path
+template <bool V4>
 __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* __restrict__ tmp, const float* __restrict__ residual,
                                                      CgState* st, RedCtx ctx) {
   MF_PDL_PROLOGUE
@@ -123,7 +205,14 @@ __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* _
   double acc[1] = { 0.0 };
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long stp = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]);
+  if (V4) {
+    for (const long long nq = n >> 2; i < nq; i += stp) {
+      const float4 a = reinterpret_cast<const float4*>(tmp)[i], b = reinterpret_cast<const float4*>(residual)[i];
+      acc[0] += (double)(a.x * b.x); acc[0] += (double)(a.y * b.y); acc[0] += (double)(a.z * b.z); acc[0] += (double)(a.w * b.w);
+    }
+  } else {
+    for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]);
+  }
   const int ops[1] = { 0 };
   gridReduceK<1>(acc, ops, ctx, sh, FinBeta{ st });
 }
@@ -141,13 +230,23 @@ __global__ void __launch_bounds__(256) k_cg_dot_sigma(long long n, const float* 
 }
 
 // search = tmp + beta * search                                            (UpdateSearchVec, conjugategrad.cpp:193)
+template <bool V4>
 __global__ void __launch_bounds__(256) k_cg_search(long long n, float* __restrict__ search, const float* __restrict__ tmp, const CgState* st) {
   MF_PDL_PROLOGUE
   if (st->done) return;
   const float beta = st->beta;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long stp = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += stp) search[i] = tmp[i] + beta * search[i];
+  if (V4) {
+    for (const long long nq = n >> 2; i < nq; i += stp) {
+      float4 se = reinterpret_cast<float4*>(search)[i];
+      const float4 t = reinterpret_cast<const float4*>(tmp)[i];
+      se.x = t.x + beta * se.x; se.y = t.y + beta * se.y; se.z = t.z + beta * se.z; se.w = t.w + beta * se.w;
+      reinterpret_cast<float4*>(search)[i] = se;
+    }
+  } else {
+    for (; i < n; i += stp) search[i] = tmp[i] + beta * search[i];
+  }
 }
 
 // ---- red-black modified incomplete Cholesky: the parallel stand-in for the sequential MIC(0) --------

@@ -252,23 +252,25 @@ __global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D, float tr
 }
 
 // ---- levels > 0 (27-point, 14 stored), colour-blocked -----------------------------------------------------
-// storage position of the thread's vertex of colour c in the lz range [lz0, lz1); returns false outside
+// Every operation is a device function of a linear work index t, so that it can run as its own grid (one t per thread) or
+// inside the single-CTA kernel that walks several small levels (t strides over the CTA).
+// storage position of work item t among the vertices of colour c in the lz range [lz0, lz1); returns false outside
 struct BlkPos { int p; int lx, ly, lz; };
-__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int lz1, BlkPos& q) {
+__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int lz1, int t, BlkPos& q) {
   const int BX = L.PX - 2, BY = L.PY - 2;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
   q.lx = t % BX; const int u = t / BX; q.ly = u % BY; q.lz = lz0 + u / BY;
   if (q.lz >= lz1) return false;
   q.p = (((q.lz + L.zoff) * L.NC + c) * L.PY + q.ly + 1) * L.PX + q.lx + 1;
   return true;
 }
-// b - sum A x over the stencil in the reference's order (dz, dy, dx ascending; multigrid.cpp:691-706, :755-770)
+// b - sum A x over the stencil in the reference's order (dz, dy, dx ascending; multigrid.cpp:691-706, :755-770).
+// x is read through a plain pointer: the bottom-levels kernel writes x between sweeps of the same launch.
 template <bool IS3D, bool WITH_CENTER>
 __device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float sum) {
   constexpr int SS = IS3D ? 14 : 5;
   const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
   const int PXY = L.PX * L.PY;
-  const float* __restrict__ A = L.A; const float* __restrict__ x = L.x;
+  const float* __restrict__ A = L.A; const float* x = L.x;
   int s = 0;
 #pragma unroll
   for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
@@ -285,12 +287,11 @@ __device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float
       }
   return sum;
 }
-// knSmoothColor, l > 0: one of the 8 (4) colours (multigrid.cpp:668-711)
+// knSmoothColor, l > 0: one vertex of one of the 8 (4) colours (multigrid.cpp:668-711)
 template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int lz1) {
-  MF_PDL_PROLOGUE
+__device__ __forceinline__ void mgSmoothItem(const LvlD& L, int c, int lz0, int lz1, int t) {
   BlkPos q;
-  if (!mgBlockThread(L, c, lz0, lz1, q)) return;
+  if (!mgBlockThread(L, c, lz0, lz1, t, q)) return;
   // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
   // reference's own division below would not be finite
   const float diag = L.A[q.p];
@@ -298,31 +299,37 @@ __global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int l
   const float sum = mgStencilSub<IS3D, false>(L, c, q.p, L.b[q.p]);
   L.x[q.p] = sum / diag;
 }
-// knCalcResidual, l > 0: blockIdx.y = colour
 template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {
+__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int lz1) {
   MF_PDL_PROLOGUE
+  mgSmoothItem<IS3D>(L, c, lz0, lz1, blockIdx.x * blockDim.x + threadIdx.x);
+}
+// knCalcResidual, l > 0
+template <bool IS3D>
+__device__ __forceinline__ void mgResidualItem(const LvlD& L, int c, int lz0, int lz1, int t) {
   BlkPos q;
-  const int c = blockIdx.y;
-  if (!mgBlockThread(L, c, lz0, lz1, q)) return;
+  if (!mgBlockThread(L, c, lz0, lz1, t, q)) return;
   // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
   L.r[q.p] = mgStencilSub<IS3D, true>(L, c, q.p, L.b[q.p]);
 }
+template <bool IS3D>
+__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {   // blockIdx.y = colour
+  MF_PDL_PROLOGUE
+  mgResidualItem<IS3D>(L, blockIdx.y, lz0, lz1, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
-// knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472).  Threads run over the natural
+// knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472).  Work items run over the natural
 // coordinates of the coarse level, z range [z0,z1) of the coarse level.  r_fine is 0 at inactive / padding / (level 0:
 // guarded) out-of-grid vertices.
 template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1) {
-  MF_PDL_PROLOGUE
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int z0, int z1, int t) {
   const int vx = t % C.sx; const int u = t / C.sx; const int vy = u % C.sy, vz = z0 + u / C.sy;
   if (vz >= z1) return;
   const int v = mgIdx(C, vx, vy, vz);
   C.x[v] = 0.f;
   if (C.A[v] == 0.f) return;          // inactive coarse vertex (all-zero row): b stays 0
   float sum = 0.f;
-  const float* __restrict__ fr = F.r;
+  const float* fr = F.r;
   if (F.perm) {
 #pragma unroll
     for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
@@ -346,22 +353,29 @@ __global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int
   }
   C.b[v] = sum;
 }
-// knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse.  Threads run over the natural
-// coordinates of the fine level, z range [z0,z1) of the fine level; x_coarse is 0 at inactive / padding vertices.
-__global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, int z1) {
+template <bool IS3D>
+__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1) {
   MF_PDL_PROLOGUE
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  mgRestrictItem<IS3D>(F, C, z0, z1, blockIdx.x * blockDim.x + threadIdx.x);
+}
+// knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse.  Work items run over the natural
+// coordinates of the fine level, z range [z0,z1) of the fine level; x_coarse is 0 at inactive / padding vertices.
+__device__ __forceinline__ void mgInterpAddItem(const LvlD& F, const LvlD& C, int z0, int z1, int t) {
   const int vx = t % F.sx; const int u = t / F.sx; const int vy = u % F.sy, vz = z0 + u / F.sy;
   if (vz >= z1) return;
   const int v = mgIdx(F, vx, vy, vz);
   if (F.perm ? (F.A[v] == 0.f) : (F.type[v] == vtInactive)) return;
   float sum = 0.f;
-  const float* __restrict__ cx = C.x;
+  const float* cx = C.x;
   for (int z = vz / 2; z <= (vz + 1) / 2; z++)
     for (int y = vy / 2; y <= (vy + 1) / 2; y++)
       for (int x = vx / 2; x <= (vx + 1) / 2; x++) sum += cx[mgIdx(C, x, y, z)];
   const float iw = 1.0f / (float)(1 << ((vx % 2) + (vy % 2) + (vz % 2)));
   F.x[v] += iw * sum;
+}
+__global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, int z1) {
+  MF_PDL_PROLOGUE
+  mgInterpAddItem(F, C, z0, z1, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // ---- Galerkin coarse operators (setup) ---------------------------------------------------------------------

@@ -63,6 +63,7 @@ struct SolveTemps {   // the 7 (+4) temp grids of solvePressureSystem (pressure.
 struct CgDriver {
   Solver* s; CgVecs v; CgState* st; int pcMethod;   // 0 none, 1 red-black MIC, 2 multigrid
   float* P; MgHierarchy* mg;
+  bool v4 = false;      // nx % 4 == 0: every slab starts and ends on a 16-byte boundary -> vectorised kernels
   CgState host;
   void applyPrecond(bool init) {
     if (pcMethod == 1) {
@@ -100,24 +101,26 @@ struct CgDriver {
     MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, sp.n), 256, sp.n, z + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
   }
-  void iterate() {
-    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); }
+  template <bool V4> void iterateT() {
+    if (v.code) { MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n), 256, g, sp, v, st, redCtx(s, r)); } }
+    else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); } }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
     if (pcMethod == 0) {
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_update<true>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, (k_cg_update<true, V4>), redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
       redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<true>{ st });
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
       s->rankSync();
     } else {
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_update<false>, redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, (k_cg_update<false, V4>), redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
       redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<false>{ st });
       applyPrecond(false);
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta<V4>, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
       redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search, ewBlocks(s, sp.n), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
       s->rankSync();
     }
   }
+  void iterate() { if (v4) iterateT<true>(); else iterateT<false>(); }
   // for (iter < maxIter) if (!iterate()) break;   host polls the device flag every `batch` iterations
   void solve(int maxIter, int batch) {
     int it = 0;
@@ -148,21 +151,35 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "solvePressureSystem: grid too small");
   SolveTemps t(s);
   CV3 fr = p->fractions ? cv3(G(p->fractions)) : cv3(vel);
-  MF_LAUNCH_IJK(s, k_make_laplace, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0,
-                p->phi ? G(p->phi)->d : nullptr, p->gfClamp);
+  // Row codes instead of coefficient planes: the plain Laplace matrix (no fractions, no ghost fluid) has only 0/-1 couplings and
+  // an integer diagonal, and with nx % 4 == 0 the CG streams them four cells at a time.  The planes are then only written when
+  // somebody reads them: the red-black IC preconditioner, or a multigrid hierarchy that has to be (re)built.
+  const bool useCode = !p->fractions && !p->phi && (s->nx % 4 == 0) && !std::getenv("MF_CG_PLANES");
+  const bool mgPc = (preconditioner == MF_PC_MG_STATIC || preconditioner == MF_PC_MG_DYNAMIC);
+  if (mgPc && s->mg && preconditioner == MF_PC_MG_DYNAMIC) { mg_destroy(s->mg); s->mg = nullptr; }
+  const bool needPlanes = !useCode || (preconditioner == MF_PC_MIC && s->is3D) || (mgPc && !(s->mg && mg_is_a_set(s->mg)));
+  if (useCode && !s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
+  const float* phiD = p->phi ? G(p->phi)->d : nullptr;
+  if (useCode && needPlanes) MF_LAUNCH_IJK(s, (k_make_laplace<true, true>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
+  else if (useCode) MF_LAUNCH_IJK(s, (k_make_laplace<false, true>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
+  else MF_LAUNCH_IJK(s, (k_make_laplace<true, false>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0, phiD, p->gfClamp, (unsigned short*)nullptr);
   int* fixedDev = s->localInts + 2;
   bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
   if (fixing) {
     MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats, tileBlocks(s, g), 256, g, flags->di(), redCtx(s, r), s->redOut); }
     redFinish<2>(s, RedOps<2>{ { 0, 1 } }, FinStore<2>{ s->redOut });
     // every process applies the same single-cell fix (identical inputs, value 0: redundant peer writes are benign)
-    MF_LAUNCH(s, k_fix_pressure, 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, fixedDev);
+    if (useCode && needPlanes) MF_LAUNCH(s, (k_fix_pressure<true, true>), 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, s->cgCode, fixedDev);
+    else if (useCode) MF_LAUNCH(s, (k_fix_pressure<false, true>), 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, s->cgCode, fixedDev);
+    else MF_LAUNCH(s, (k_fix_pressure<true, false>), 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, (unsigned short*)nullptr, fixedDev);
     s->rankSync();
   }
   CgDriver cg;
   cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr;
   cg.v.flags = flags->di(); cg.v.dst = pressure->d; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
   cg.v.rhs = rhs; cg.v.A0 = t.A0; cg.v.Ai = t.Ai; cg.v.Aj = t.Aj; cg.v.Ak = t.Ak;
+  cg.v.code = useCode ? s->cgCode : nullptr;
+  cg.v4 = (s->nx % 4 == 0);
   int maxIter = 0, batch = 8;
   int mgLevels = 0, mgRebuilt = 0;
   int maxDim = s->nx > s->ny ? s->nx : s->ny; if (s->nz > maxDim) maxDim = s->nz;
@@ -177,7 +194,6 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   } else {
     maxIter = 100; batch = 1;
     cg.pcMethod = 2;
-    if (s->mg && preconditioner == MF_PC_MG_DYNAMIC) { mg_destroy(s->mg); s->mg = nullptr; }
     if (!s->mg) s->mg = mg_create(s);
     cg.mg = s->mg;
     // InitPreconditionMultigrid (conjugategrad.cpp:100-106)
@@ -315,7 +331,7 @@ int mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_gr
   Solver* s = G(flags)->s; s->use();
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "MakeLaplaceMatrix: grid too small");
   CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
-  MF_LAUNCH_IJK(s, k_make_laplace, G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f);
+  MF_LAUNCH_IJK(s, (k_make_laplace<true, false>), G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f, (unsigned short*)nullptr);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -329,6 +345,28 @@ int mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* src, cons
   mfAssert(G(dst)->d != G(src)->d, "ApplyMatrix: dst and src must differ");
   Solver* s = G(flags)->s; s->use();
   MF_LAUNCH_IJK(s, k_apply_matrix, G(flags)->di(), G(dst)->d, G(src)->d, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* src) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "mf_apply_laplace_rowcode");
+  REQ_GRID(dst, G(dst)->isReal(), "dst", "mf_apply_laplace_rowcode"); REQ_GRID(src, G(src)->isReal(), "src", "mf_apply_laplace_rowcode");
+  mfAssert(G(dst)->d != G(src)->d, "mf_apply_laplace_rowcode: dst and src must differ");
+  Solver* s = G(flags)->s; s->use();
+  mfAssert(s->nx % 4 == 0, "mf_apply_laplace_rowcode: nx must be a multiple of 4");
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "mf_apply_laplace_rowcode: grid too small");
+  if (!s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
+  CV3 fr; fr.x = fr.y = fr.z = nullptr;
+  MF_LAUNCH_IJK(s, (k_make_laplace<false, true>), G(flags)->di(), (float*)nullptr, (float*)nullptr, (float*)nullptr, (float*)nullptr, fr, 0,
+                (const float*)nullptr, 0.f, s->cgCode);
+  CgState* st = cgStateBuf(s);
+  CUDA_CHECK(cudaMemsetAsync(st, 0, sizeof(CgState), s->stream));
+  CgVecs v; memset(&v, 0, sizeof(v));
+  v.search = G(src)->d; v.tmp = G(dst)->d; v.code = s->cgCode;
+  MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH(s, k_cg_spmv_dot_code, redBlocks(s, sp.n), 256, g, sp, v, st, redCtx(s, r)); }
+  redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -354,6 +392,7 @@ int mf_cg_solve_diffusion(const mf_grid* flagsp, mf_grid* gridp, float alpha, fl
     cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr; cg.pcMethod = 0;
     cg.v.flags = flags->di(); cg.v.dst = u; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
     cg.v.rhs = rhs.p; cg.v.A0 = t.A0; cg.v.Ai = t.Ai; cg.v.Aj = t.Aj; cg.v.Ak = t.Ak;
+    cg.v.code = nullptr; cg.v4 = (s->nx % 4 == 0);
     cg.init(cgAccuracy, true);      // GridCgInterface() defaults to the L2 norm (conjugategrad.h:31)
     cg.solve(maxIter, 8);
   }

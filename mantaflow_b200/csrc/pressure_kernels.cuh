@@ -87,11 +87,19 @@ __global__ void k_add_scalar(float* d, float v, long long n) {
   for (; i < n; i += st) d[i] += v;
 }
 
+// 16-bit row code of the plain (no fractions, no ghost fluid) Laplace matrix: every coefficient is 0 or -1 and the diagonal a
+// small integer, so a row of ApplyMatrix is fully described by 10 bits.  The CG then streams 2 B/cell of matrix instead of the
+// four float planes (16 B/cell) + flags (4 B/cell).  Bits: coefficient towards +x,+y,+z (Ai/Aj/Ak at the cell), towards
+// -x,-y,-z (Ai/Aj/Ak at the lower neighbour), the diagonal (0..6), and "fluid" (non-fluid rows are identity rows, conjugategrad.h:217).
+enum { CGC_XP = 1, CGC_YP = 2, CGC_ZP = 4, CGC_XM = 8, CGC_YM = 16, CGC_ZM = 32, CGC_DIAG_SHIFT = 6, CGC_FLUID = 512 };
+
 // MakeLaplaceMatrix (+ ApplyGhostFluidDiagonal) -- writes all four coefficient grids for every cell
 // (the reference accumulates into cleared temp grids, conjugategrad.h:154-187, pressure.cpp:136-151)
+// PLANES: write A0/Ai/Aj/Ak; CODE: write the 16-bit row code (only valid without fractions / phi).
+template <bool PLANES, bool CODE>
 __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restrict__ flags, float* __restrict__ A0, float* __restrict__ Ai,
                                                       float* __restrict__ Aj, float* __restrict__ Ak, CV3 fr, int haveFractions,
-                                                      const float* __restrict__ phi, float gfClamp) {
+                                                      const float* __restrict__ phi, float gfClamp, unsigned short* __restrict__ code) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
   const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
@@ -131,7 +139,24 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
       }
     }
   }
-  A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak;
+  if (PLANES) { A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak; }
+  if (CODE) {
+    // the -x/-y/-z coefficients live in the lower neighbour's row: Ai[idx-X] = -1 iff that cell is an interior fluid cell and this
+    // one is fluid.  Neighbours outside the coordinate range map (by linear index) to border cells, whose rows are all zero.
+    int c = 0;
+    const int f = flags[idx];
+    if (fIsFluid(f)) {
+      c = CGC_FLUID | ((int)a0 << CGC_DIAG_SHIFT);
+      if (ai != 0.f) c |= CGC_XP;
+      if (aj != 0.f) c |= CGC_YP;
+      if (ak != 0.f) c |= CGC_ZP;
+      const long long Y = g.nx, Z = g.Z;
+      if (i >= 1 && interiorCell(g, i - 1, j, k) && fIsFluid(flags[idx - 1])) c |= CGC_XM;
+      if (j >= 1 && interiorCell(g, i, j - 1, k) && fIsFluid(flags[idx - Y])) c |= CGC_YM;
+      if (g.is3D && k >= 1 && interiorCell(g, i, j, k - 1) && fIsFluid(flags[idx - Z])) c |= CGC_ZM;
+    }
+    code[idx] = (unsigned short)c;
+  }
 }
 
 // CountEmptyCells (pressure.cpp:217) + "first interior fluid cell in FOR_IJK_BND order" (:371-381)
@@ -150,8 +175,9 @@ __global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict
 }
 
 // zeroPressureFixing: pick the cell (pressure.cpp:352-383) and apply fixPressure(idx, 0, ...) (:226-245); one thread
+template <bool PLANES, bool CODE>
 __global__ void k_fix_pressure(Geo g, const int* __restrict__ flags, const double* __restrict__ stats, float* rhs, float* A0, float* Ai,
-                               float* Aj, float* Ak, int* fixedOut) {
+                               float* Aj, float* Ak, unsigned short* code, int* fixedOut) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   long long fix = -1;
   if (stats[0] == 0.0) {
@@ -168,17 +194,26 @@ __global__ void k_fix_pressure(Geo g, const int* __restrict__ flags, const doubl
   if (fix < 0) return;
   const float value = 0.0f;
   const long long X = 1, Y = g.nx, Z = g.Z;
-  rhs[fix + X] -= Ai[fix] * value;
-  rhs[fix + Y] -= Aj[fix] * value;
-  rhs[fix - X] -= Ai[fix - X] * value;
-  rhs[fix - Y] -= Aj[fix - Y] * value;
-  if (g.is3D) { rhs[fix + Z] -= Ak[fix] * value; rhs[fix - Z] -= Ak[fix - Z] * value; }
-  rhs[fix] = value;
-  A0[fix] = 1.0f;
-  Ai[fix] = Aj[fix] = Ak[fix] = 0.0f;
-  Ai[fix - X] = 0.0f;
-  Aj[fix - Y] = 0.0f;
-  if (g.is3D) Ak[fix - Z] = 0.0f;
+  if (PLANES) {
+    rhs[fix + X] -= Ai[fix] * value;
+    rhs[fix + Y] -= Aj[fix] * value;
+    rhs[fix - X] -= Ai[fix - X] * value;
+    rhs[fix - Y] -= Aj[fix - Y] * value;
+    if (g.is3D) { rhs[fix + Z] -= Ak[fix] * value; rhs[fix - Z] -= Ak[fix - Z] * value; }
+    A0[fix] = 1.0f;
+    Ai[fix] = Aj[fix] = Ak[fix] = 0.0f;
+    Ai[fix - X] = 0.0f;
+    Aj[fix - Y] = 0.0f;
+    if (g.is3D) Ak[fix - Z] = 0.0f;
+  }
+  rhs[fix] = value;      // (without the planes the neighbour updates above are rhs -= (0 or -1) * 0, i.e. no-ops)
+  if (CODE) {
+    // same edits on the row codes: the row becomes (1, 0, 0, 0) and all six couplings to the cell are cut
+    code[fix] = (unsigned short)((code[fix] & CGC_FLUID) | (1 << CGC_DIAG_SHIFT));
+    code[fix + X] &= (unsigned short)~CGC_XM; code[fix - X] &= (unsigned short)~CGC_XP;
+    code[fix + Y] &= (unsigned short)~CGC_YM; code[fix - Y] &= (unsigned short)~CGC_YP;
+    if (g.is3D) { code[fix + Z] &= (unsigned short)~CGC_ZM; code[fix - Z] &= (unsigned short)~CGC_ZP; }
+  }
 }
 
 // ApplyMatrix / ApplyMatrix2D for one cell; neighbours outside the array contribute nothing

@@ -212,7 +212,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   s->dx = (float)(1.0 / mx);       // grid.cpp:57
   s->device = device;
   s->profTag = -1; s->profLevels = getenv("MF_PROFILE_LEVELS") != nullptr;
-  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->profiling = false;
+  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->profiling = false;
   for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
   CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
@@ -264,6 +264,7 @@ void mf_solver_destroy(mf_solver* sp) {
   release_mg(s);
   for (float* p : s->poolReal) s->gfree(p);
   for (float* p : s->poolVec) s->gfree(p);
+  if (s->cgCode) s->gfree(s->cgCode);
   cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);
   cudaFree(s->localInts); s->gfree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
   if (s->aosStage) cudaFree(s->aosStage);

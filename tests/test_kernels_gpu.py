@@ -1,0 +1,143 @@
+"""Kernel-level parity of the pressure-matrix pieces (C-ABI entries mf_make_laplace_matrix / mf_apply_matrix /
+mf_apply_laplace_rowcode) against a numpy restatement of MakeLaplaceMatrix (conjugategrad.h:154-187) and ApplyMatrix
+(conjugategrad.h:118-151, :205-222).  All comparisons are bit-exact: coefficients are small integers and the row sums are
+evaluated in the reference's order with separate multiplies and adds.
+"""
+import ctypes as Ct
+
+import numpy as np
+import pytest
+
+FLUID, OBSTACLE, EMPTY = 1, 2, 4
+
+
+def _flags(rs, size, dim, border_fluid=False):
+    nx, ny, nz = size
+    f = rs.choice([FLUID, OBSTACLE, EMPTY], size=(nz, ny, nx), p=[0.7, 0.15, 0.15]).astype(np.int32)
+    if not border_fluid:
+        f[:, :, 0] = f[:, :, -1] = OBSTACLE
+        f[:, 0, :] = f[:, -1, :] = OBSTACLE
+        if dim == 3:
+            f[0] = f[-1] = OBSTACLE
+    return f
+
+
+def _np_laplace(f, dim):
+    """MakeLaplaceMatrix without fractions: rows of interior (bnd 1) fluid cells only"""
+    nz, ny, nx = f.shape
+    A0 = np.zeros(f.shape, np.float32); Ai = np.zeros_like(A0); Aj = np.zeros_like(A0); Ak = np.zeros_like(A0)
+    inter = np.zeros(f.shape, bool)
+    if dim == 3:
+        inter[1:-1, 1:-1, 1:-1] = True
+    else:
+        inter[:, 1:-1, 1:-1] = True
+    row = inter & ((f & FLUID) != 0)
+    def sh(a, axis, d):   # value of the neighbour in direction d along axis (wrap is irrelevant: only interior rows are used)
+        return np.roll(a, -d, axis=axis)
+    axes = [(2, Ai), (1, Aj)] + ([(0, Ak)] if dim == 3 else [])
+    for ax, Ap in axes:
+        for d in (-1, 1):
+            nb = sh(f, ax, d)
+            A0 += (row & ((nb & OBSTACLE) == 0)).astype(np.float32)
+        Ap[row & ((sh(f, ax, 1) & FLUID) != 0)] = -1.0
+    return A0, Ai, Aj, Ak
+
+
+def _np_apply(f, src, A0, Ai, Aj, Ak, dim):
+    """ApplyMatrix: linear-index stencil, neighbours outside the array contribute nothing"""
+    nz, ny, nx = f.shape
+    N = f.size
+    s = src.ravel(); a0 = A0.ravel(); ai = Ai.ravel(); aj = Aj.ravel(); ak = Ak.ravel()
+    X, Y, Z = 1, nx, nx * ny
+    def lo(v, o):   # v[idx - o] (0 where idx - o < 0)
+        r = np.zeros_like(v); r[o:] = v[:N - o]; return r
+    def hi(v, o):   # v[idx + o] (0 where idx + o >= N)
+        r = np.zeros_like(v); r[:N - o] = v[o:]; return r
+    r = s * a0
+    r = r + lo(s, X) * lo(ai, X)
+    r = r + hi(s, X) * ai
+    r = r + lo(s, Y) * lo(aj, Y)
+    r = r + hi(s, Y) * aj
+    if dim == 3:
+        r = r + lo(s, Z) * lo(ak, Z)
+        r = r + hi(s, Z) * ak
+    out = np.where((f.ravel() & FLUID) != 0, r, s).astype(np.float32)
+    return out.reshape(f.shape)
+
+
+SIZES = [((64, 48, 40), 3), ((8, 8, 8), 3), ((4, 3, 3), 3), ((128, 20, 1), 2), ((36, 5, 7), 3)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size,dim", SIZES)
+@pytest.mark.parametrize("border_fluid", [False, True])
+def test_laplace_matrix_and_apply(size, dim, border_fluid):
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    rs = np.random.RandomState(11)
+    s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=dim)
+    f = _flags(rs, size, dim, border_fluid)
+    src = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
+    flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+    g = [s.create(manta.RealGrid) for _ in range(7)]
+    A0, Ai, Aj, Ak, S, D, D2 = g
+    S.from_numpy(src)
+    check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
+    ref = _np_laplace(f, dim)
+    for ours, r, nm in zip((A0, Ai, Aj, Ak), ref, "A0 Ai Aj Ak".split()):
+        assert np.array_equal(ours.to_numpy(), r), nm
+    check(lib().mf_apply_matrix(flags._h, D._h, S._h, A0._h, Ai._h, Aj._h, Ak._h))
+    want = _np_apply(f, src, *ref, dim)
+    got = D.to_numpy()
+    assert np.array_equal(got, want)
+    if size[0] % 4 == 0:
+        check(lib().mf_apply_laplace_rowcode(flags._h, D2._h, S._h))
+        got2 = D2.to_numpy()
+        assert np.array_equal(got2.view(np.int32), got.view(np.int32)), "row-code SpMV differs from the plane SpMV"
+    else:
+        assert lib().mf_apply_laplace_rowcode(flags._h, D2._h, S._h) != 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nranks", [2, 3])
+def test_rowcode_spmv_partitioned(nranks):
+    """z-slab partition (emulated ranks): the row-code SpMV reads the neighbour planes of other slabs"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    rs = np.random.RandomState(5)
+    size, dim = (32, 12, 14), 3
+    comm = manta.Comm.emulated(nranks)
+    try:
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=dim, comm=comm)
+        f = _flags(rs, size, dim, True)
+        src = rs.rand(*f.shape).astype(np.float32)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        S = s.create(manta.RealGrid); D = s.create(manta.RealGrid); S.from_numpy(src)
+        check(lib().mf_apply_laplace_rowcode(flags._h, D._h, S._h))
+        want = _np_apply(f, src, *_np_laplace(f, dim), dim)
+        assert np.array_equal(D.to_numpy(), want)
+        del flags, S, D, s
+    finally:
+        comm.destroy()
+
+
+@pytest.mark.gpu
+def test_pressure_solve_rowcode_vs_planes(monkeypatch):
+    """the CG with row codes and with coefficient planes converges to the same pressure (same iteration count)"""
+    from mantaflow_b200 import manta
+    rs = np.random.RandomState(2)
+    size = (32, 24, 16)
+    res = []
+    for planes in (False, True):
+        if planes:
+            monkeypatch.setenv("MF_CG_PLANES", "1")
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.initDomain(); flags.fillGrid()
+        vel = s.create(manta.MACGrid); p = s.create(manta.RealGrid)
+        rs2 = np.random.RandomState(9)
+        vel.from_numpy(rs2.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5))
+        manta.solvePressure(flags=flags, vel=vel, pressure=p, cgAccuracy=1e-6, preconditioner=manta.PcMGStatic, zeroPressureFixing=True)
+        res.append((p.to_numpy(), vel.to_numpy()))
+        manta.releaseMG(s)
+    assert np.allclose(res[0][0], res[1][0], rtol=0, atol=2e-5)
+    assert np.allclose(res[0][1], res[1][1], rtol=0, atol=2e-5)
