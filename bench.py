@@ -41,11 +41,14 @@ ALGO_BYTES_PER_CELL = {
     "k_mc_centered": 28.0,     # vel 12 + fwd 4 + orig 4 + flags 4 + dst 4
     "k_sl_mac": 24.0,          # self-advection: vel(=src) 12 + dst 12
     "k_mc_mac": 40.0,          # vel(=orig) 12 + fwd 12 + flags 4 + dst 12
-    "k_set_wall_bcs": 28.0,    # flags 4 + vel 12 r + 12 w
+    "k_set_wall_bcs": 4.0,     # streams the flags; velocities are only touched in the thin shell where a wall condition applies
     "k_add_buoyancy": 32.0,    # flags 4 + density 4 + vel 12 r + 12 w
     "k_wall_buoyancy": 32.0,
     "k_make_rhs": 20.0,        # flags 4 + vel 12 + rhs 4
-    "k_make_laplace": 6.0,     # flags 4 + row code 2 (the 4 coefficient planes, +16, only when a preconditioner is (re)built)
+    "k_make_rhs_plain": 20.0,
+    "k_flag_stats": 4.0,
+    "k_make_laplace_code": 6.0,  # flags 4 + row code 2
+    "k_make_laplace": 22.0,    # flags 4 + 4 coefficient planes 16 + row code 2 (only when a preconditioner is (re)built)
     "k_cg_spmv_dot": 28.0,     # stored-A: flags 4 + src 4 + dst 4 + A 16
     "k_cg_spmv_dot_code": 10.0,  # 16-bit row code 2 + src 4 + dst 4
     "k_cg_update": 24.0,       # x r/w 8 + search 4 + residual r/w 8 + tmp 4

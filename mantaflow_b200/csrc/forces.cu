@@ -5,6 +5,7 @@
 //            source/shapes.cpp (ApplyShapeToGrid :40, Box::isInside :151, Cylinder::isInside :324).
 #include "common.cuh"
 #include "sample.cuh"
+#include "quad.cuh"
 #include <cstring>
 #include <cmath>
 
@@ -115,19 +116,48 @@ __global__ void k_apply_cylinder(Geo g, float* __restrict__ d, float cx, float c
 }
 
 // ---- forces ---------------------------------------------------------------------------------------
-// KnAddBuoyancy (extforces.cpp:73-81): (0.5*strength) is a double product, the update is done in double
+// KnAddBuoyancy (extforces.cpp:73-81): (0.5*strength) is a double product, the update is done in double.
+// W x-consecutive cells per thread (quad.cuh); a component's cells are only stored when one of them changed.
+template <int W>
 __global__ void __launch_bounds__(256) k_add_buoyancy(Geo g, const int* __restrict__ flags, const float* __restrict__ factor, V3 vel,
                                                       float sx, float sy, float sz) {
-  IJK_FROM_BLOCK
-  if (!interior1(g, i, j, k)) return;
-  if (!fIsFluid(flags[idx])) return;
-  const float f0 = factor[idx];
-  if (fIsFluid(flags[idx - 1]))
-    vel.x[idx] = (float)((double)vel.x[idx] + (0.5 * (double)sx) * (double)(f0 + factor[idx - 1]));
-  if (fIsFluid(flags[idx - g.nx]))
-    vel.y[idx] = (float)((double)vel.y[idx] + (0.5 * (double)sy) * (double)(f0 + factor[idx - g.nx]));
-  if (g.is3D && fIsFluid(flags[idx - g.Z]))
-    vel.z[idx] = (float)((double)vel.z[idx] + (0.5 * (double)sz) * (double)(f0 + factor[idx - g.Z]));
+  MF_CELLS_W(g, W)
+  if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
+  const long long Y = g.nx, Z = g.Z;
+  int f[W], fx[W], fy[W], fz[W];
+  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
+  if (g.is3D) ldW<W>(fz, flags, idx - Z); else { for (int c = 0; c < W; c++) fz[c] = 0; }
+  xMinusW<W, int>(fx, f, flags, idx, i, 0);
+  float d0[W], dx[W], dy[W], dz[W];
+  ldW<W>(d0, factor, idx); ldW<W>(dy, factor, idx - Y);
+  if (g.is3D) ldW<W>(dz, factor, idx - Z); else { for (int c = 0; c < W; c++) dz[c] = 0.f; }
+  xMinusW<W, float>(dx, d0, factor, idx, i, 0.f);
+  if (!on) return;
+  bool mx = false, my = false, mz = false, cell[W];
+#pragma unroll
+  for (int c = 0; c < W; c++) {
+    cell[c] = (i + c >= 1) && (i + c < g.nx - 1) && fIsFluid(f[c]);
+    mx |= cell[c] && fIsFluid(fx[c]); my |= cell[c] && fIsFluid(fy[c]); mz |= cell[c] && g.is3D && fIsFluid(fz[c]);
+  }
+  float v[W];
+  if (mx) {
+    ldW<W>(v, vel.x, idx);
+#pragma unroll
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fx[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sx) * (double)(d0[c] + dx[c]));
+    stW<W>(vel.x, idx, v);
+  }
+  if (my) {
+    ldW<W>(v, vel.y, idx);
+#pragma unroll
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fy[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sy) * (double)(d0[c] + dy[c]));
+    stW<W>(vel.y, idx, v);
+  }
+  if (mz) {
+    ldW<W>(v, vel.z, idx);
+#pragma unroll
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fz[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sz) * (double)(d0[c] + dz[c]));
+    stW<W>(vel.z, idx, v);
+  }
 }
 // KnApplyForce (extforces.cpp:46-59), additive flag as in addGravity
 __global__ void __launch_bounds__(256) k_apply_force(Geo g, const int* __restrict__ flags, V3 vel, float fx, float fy, float fz,
@@ -153,22 +183,62 @@ __global__ void k_set_inflow(Geo g, V3 vel, int dim, int p0, float vx, float vy,
   if (p == p0 || p == p0 + 1) { vel.x[idx] = vx; vel.y[idx] = vy; vel.z[idx] = vz; }
 }
 
-// KnSetWallBcs (extforces.cpp:187-237): all cells, in place
+// KnSetWallBcs (extforces.cpp:187-237): all cells, in place.  W x-consecutive cells per thread (quad.cuh); the kernel streams
+// the flags and touches a velocity component only where a wall condition applies (a thin shell of the domain).
+template <int W>
 __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel) {
-  IJK_FROM_BLOCK
-  const int f = flags[idx];
-  const bool curFluid = fIsFluid(f), curObs = fIsObstacle(f);
-  if (!curFluid && !curObs) return;
-  float bx = 0.f, by = 0.f, bz = 0.f;
-  if (haveObvel) { bx = obvel.x[idx]; by = obvel.y[idx]; if (g.is3D) bz = obvel.z[idx]; }
-  if (i > 0) { const int fm = flags[idx - 1];    if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.x[idx] = bx; }
-  if (j > 0) { const int fm = flags[idx - g.nx]; if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.y[idx] = by; }
-  if (!g.is3D) vel.z[idx] = 0.0f;
-  else if (k > 0) { const int fm = flags[idx - g.Z]; if (fIsObstacle(fm) || (curObs && fIsFluid(fm))) vel.z[idx] = bz; }
-  if (curFluid) {
-    if ((i > 0 && fIsStick(flags[idx - 1])) || (i < g.nx - 1 && fIsStick(flags[idx + 1]))) { vel.y[idx] = 0.f; vel.z[idx] = 0.f; }
-    if ((j > 0 && fIsStick(flags[idx - g.nx])) || (j < g.ny - 1 && fIsStick(flags[idx + g.nx]))) { vel.x[idx] = 0.f; vel.z[idx] = 0.f; }
-    if (g.is3D && ((k > 0 && fIsStick(flags[idx - g.Z])) || (k < g.nz - 1 && fIsStick(flags[idx + g.Z])))) { vel.x[idx] = 0.f; vel.y[idx] = 0.f; }
+  MF_CELLS_W(g, W)
+  const long long Y = g.nx, Z = g.Z;
+  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  ldW<W>(f, flags, idx);
+  xMinusW<W, int>(fxm, f, flags, idx, i, 0);
+  xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0);
+  if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
+  if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
+  if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
+  if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  if (!on) return;
+  // what happens to each component of each cell: 0 keep, 1 set to the obstacle velocity, 2 set to zero (applied in this order)
+  int ax[W], ay[W], az[W];
+  bool anyx = false, anyy = false, anyz = false;
+#pragma unroll
+  for (int c = 0; c < W; c++) {
+    ax[c] = ay[c] = az[c] = 0;
+    const bool curFluid = fIsFluid(f[c]), curObs = fIsObstacle(f[c]);
+    if (!curFluid && !curObs) continue;
+    // (neighbours outside the grid were loaded as 0: no obstacle, no fluid, no stick bit -- the same as the index guards)
+    if (i + c > 0 && (fIsObstacle(fxm[c]) || (curObs && fIsFluid(fxm[c])))) ax[c] = 1;
+    if (j > 0 && (fIsObstacle(fym[c]) || (curObs && fIsFluid(fym[c])))) ay[c] = 1;
+    if (!g.is3D) az[c] = 2;
+    else if (k > 0 && (fIsObstacle(fzm[c]) || (curObs && fIsFluid(fzm[c])))) az[c] = 1;
+    if (curFluid) {
+      if (fIsStick(fxm[c]) || fIsStick(fxp[c])) { ay[c] = 2; az[c] = 2; }
+      if (fIsStick(fym[c]) || fIsStick(fyp[c])) { ax[c] = 2; az[c] = 2; }
+      if (g.is3D && (fIsStick(fzm[c]) || fIsStick(fzp[c]))) { ax[c] = 2; ay[c] = 2; }
+    }
+    anyx |= ax[c] != 0; anyy |= ay[c] != 0; anyz |= az[c] != 0;
+  }
+  float v[W], o[W];
+  if (anyx) {
+    ldW<W>(v, vel.x, idx);
+    if (haveObvel) ldW<W>(o, obvel.x, idx); else { for (int c = 0; c < W; c++) o[c] = 0.f; }
+#pragma unroll
+    for (int c = 0; c < W; c++) v[c] = ax[c] == 0 ? v[c] : (ax[c] == 1 ? o[c] : 0.f);
+    stW<W>(vel.x, idx, v);
+  }
+  if (anyy) {
+    ldW<W>(v, vel.y, idx);
+    if (haveObvel) ldW<W>(o, obvel.y, idx); else { for (int c = 0; c < W; c++) o[c] = 0.f; }
+#pragma unroll
+    for (int c = 0; c < W; c++) v[c] = ay[c] == 0 ? v[c] : (ay[c] == 1 ? o[c] : 0.f);
+    stW<W>(vel.y, idx, v);
+  }
+  if (anyz) {
+    ldW<W>(v, vel.z, idx);
+    if (haveObvel && g.is3D) ldW<W>(o, obvel.z, idx); else { for (int c = 0; c < W; c++) o[c] = 0.f; }
+#pragma unroll
+    for (int c = 0; c < W; c++) v[c] = az[c] == 0 ? v[c] : (az[c] == 1 ? o[c] : 0.f);
+    stW<W>(vel.z, idx, v);
   }
 }
 
@@ -388,7 +458,7 @@ int mf_add_buoyancy(const mf_grid* fp, const mf_grid* dp, mf_grid* vp, float gx,
   const float fx = ((-gx * dt) / gridScale) * coefficient;
   const float fy = ((-gy * dt) / gridScale) * coefficient;
   const float fz = ((-gz * dt) / gridScale) * coefficient;
-  MF_LAUNCH_IJK(s, k_add_buoyancy, flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
+  MF_LAUNCH_IJK_W(s, k_add_buoyancy, flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -433,7 +503,7 @@ int mf_set_wall_bcs(const mf_grid* fp, mf_grid* vp, const mf_grid* obvel, const 
   if (!phiObs || !fractions) {
     CV3 ov; ov.x = ov.y = ov.z = nullptr;
     if (obvel) ov = cv3(G(obvel));
-    MF_LAUNCH_IJK(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0);
+    MF_LAUNCH_IJK_W(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0);
   } else {
     mfAssert(s->nx >= 3 && s->ny >= 3, "setWallBcs: grid too small");
     float* tmp = s->getVec();

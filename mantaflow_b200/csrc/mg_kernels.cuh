@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(256) k_mg_copy_activate(LvlD L, MgDims D, cons
                                                           int* __restrict__ found /* [0]=nonZeroStencilSum, [1]=trivial, [2]=not codable */,
                                                           int p0, int p1) {
   MG_P_FROM_THREAD(L)
-  const int v = p, n = L.n;
+  const int v = p;
   float a[7];
   a[0] = A0[v]; a[1] = Ai[v]; a[2] = Aj[v]; a[3] = D.is3D ? Ak[v] : 0.f;
   a[4] = vx != 0 ? Ai[v - 1] : 0.f;

@@ -43,7 +43,10 @@ static void computeRhs(Solver* s, float* rhs, const Grid* vel, const Grid* flags
   a.phi = p->phi ? G(p->phi)->d : nullptr; a.curv = p->curv ? G(p->curv)->d : nullptr;
   a.surfTens = p->surfTens; a.gfClamp = p->gfClamp;
   a.writeBorder = freshTemp ? 1 : 0;
-  MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs, tileBlocks(s, g), 256, g, a, redCtx(s, r), s->redOut); }
+  const bool plain = !p->fractions && !p->obvel && !(p->phi && p->curv) && !p->perCellCorr;
+  if (plain && s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs_plain<4>, quadTileBlocks(s, g, 4), 256, g, a.flags, rhs, a.vel, a.writeBorder, redCtx(s, r), s->redOut); } }
+  else if (plain) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs_plain<1>, quadTileBlocks(s, g, 1), 256, g, a.flags, rhs, a.vel, a.writeBorder, redCtx(s, r), s->redOut); } }
+  else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs, tileBlocks(s, g), 256, g, a, redCtx(s, r), s->redOut); } }
   redFinish<2>(s, RedOps<2>{ { 0, 0 } }, FinStore<2>{ s->redOut });
   if (p->enforceCompatibility) {
     fetchRed(s, 2);
@@ -160,13 +163,14 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   const bool needPlanes = !useCode || (preconditioner == MF_PC_MIC && s->is3D) || (mgPc && !(s->mg && mg_is_a_set(s->mg)));
   if (useCode && !s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
   const float* phiD = p->phi ? G(p->phi)->d : nullptr;
-  if (useCode && needPlanes) MF_LAUNCH_IJK(s, (k_make_laplace<true, true>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
-  else if (useCode) MF_LAUNCH_IJK(s, (k_make_laplace<false, true>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
-  else MF_LAUNCH_IJK(s, (k_make_laplace<true, false>), flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0, phiD, p->gfClamp, (unsigned short*)nullptr);
+  if (useCode && needPlanes) MF_LAUNCH_IJK(s, k_make_laplace<true>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
+  else if (useCode) MF_LAUNCH_IJK_W(s, k_make_laplace_code, flags->di(), s->cgCode);
+  else MF_LAUNCH_IJK(s, k_make_laplace<false>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0, phiD, p->gfClamp, (unsigned short*)nullptr);
   int* fixedDev = s->localInts + 2;
   bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
   if (fixing) {
-    MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats, tileBlocks(s, g), 256, g, flags->di(), redCtx(s, r), s->redOut); }
+    if (s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<4>, quadTileBlocks(s, g, 4), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
+    else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<1>, quadTileBlocks(s, g, 1), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
     redFinish<2>(s, RedOps<2>{ { 0, 1 } }, FinStore<2>{ s->redOut });
     // every process applies the same single-cell fix (identical inputs, value 0: redundant peer writes are benign)
     if (useCode && needPlanes) MF_LAUNCH(s, (k_fix_pressure<true, true>), 1, 32, geo(s), flags->di(), s->redOut, rhs, t.A0, t.Ai, t.Aj, t.Ak, s->cgCode, fixedDev);
@@ -217,7 +221,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
 }
 
 static void correctVel(Solver* s, Grid* vel, const Grid* pressure, const Grid* flags, const mf_pressure_params* p) {
-  MF_LAUNCH_IJK(s, k_correct_velocity, flags->di(), v3(vel), pressure->d);
+  MF_LAUNCH_IJK_W(s, k_correct_velocity, flags->di(), v3(vel), pressure->d);
   if (p->phi) {
     MF_LAUNCH_IJK(s, k_correct_velocity_gf, flags->di(), v3(vel), pressure->d, G(p->phi)->d, p->gfClamp,
                   p->curv ? G(p->curv)->d : nullptr, p->surfTens);
@@ -331,7 +335,7 @@ int mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_gr
   Solver* s = G(flags)->s; s->use();
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "MakeLaplaceMatrix: grid too small");
   CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
-  MF_LAUNCH_IJK(s, (k_make_laplace<true, false>), G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f, (unsigned short*)nullptr);
+  MF_LAUNCH_IJK(s, k_make_laplace<false>, G(flags)->di(), G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d, fr, fractions ? 1 : 0, (const float*)nullptr, 0.f, (unsigned short*)nullptr);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -358,9 +362,7 @@ int mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* 
   mfAssert(s->nx % 4 == 0, "mf_apply_laplace_rowcode: nx must be a multiple of 4");
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "mf_apply_laplace_rowcode: grid too small");
   if (!s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
-  CV3 fr; fr.x = fr.y = fr.z = nullptr;
-  MF_LAUNCH_IJK(s, (k_make_laplace<false, true>), G(flags)->di(), (float*)nullptr, (float*)nullptr, (float*)nullptr, (float*)nullptr, fr, 0,
-                (const float*)nullptr, 0.f, s->cgCode);
+  MF_LAUNCH_IJK_W(s, k_make_laplace_code, G(flags)->di(), s->cgCode);
   CgState* st = cgStateBuf(s);
   CUDA_CHECK(cudaMemsetAsync(st, 0, sizeof(CgState), s->stream));
   CgVecs v; memset(&v, 0, sizeof(v));

@@ -6,6 +6,7 @@
 #pragma once
 #include "common.cuh"
 #include "reduce.cuh"
+#include "quad.cuh"
 
 namespace mf {
 
@@ -81,6 +82,46 @@ __global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, RedCtx ctx, 
   gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
 }
 
+// MakeRhs of the plain projection (no fractions, obstacle velocities, surface tension or per-cell correction):
+// W x-consecutive cells per thread (quad.cuh), same expression per cell
+template <int W>
+__global__ void __launch_bounds__(256) k_make_rhs_plain(Geo g, const int* __restrict__ flags, float* __restrict__ rhs, CV3 vel, int writeBorder,
+                                                        RedCtx ctx, double* out) {
+  __shared__ double sh[32];
+  double sum = 0.0, cnt = 0.0;
+  MF_QTILE_LOOP_BEGIN(g, W)
+    const long long Y = g.nx, Z = g.Z;
+    float r[W];
+    if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) {       // border row
+      if (writeBorder && on) { for (int c = 0; c < W; c++) r[c] = 0.f; stW<W>(rhs, idx, r); }
+      continue;
+    }
+    int f[W]; float vx[W], vxp[W], vy[W], vyp[W], vz[W], vzp[W];
+    ldW<W>(f, flags, idx);
+    ldW<W>(vx, vel.x, idx); xPlusW<W, float>(vxp, vx, vel.x, idx, i, g.nx, 0.f);
+    ldW<W>(vy, vel.y, idx); ldW<W>(vyp, vel.y, idx + Y);
+    if (g.is3D) { ldW<W>(vz, vel.z, idx); ldW<W>(vzp, vel.z, idx + Z); }
+    if (!on) continue;
+    const bool edgeQuad = (i == 0) || (i + W >= g.nx);
+    if (edgeQuad && !writeBorder) ldW<W>(r, rhs, idx);
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+      const int ic = i + c;
+      if (ic < 1 || ic >= g.nx - 1) { if (writeBorder) r[c] = 0.f; continue; }
+      if (!fIsFluid(f[c])) { r[c] = 0.f; continue; }
+      float set = vx[c] - vxp[c] + vy[c] - vyp[c];
+      if (g.is3D) set += vz[c] - vzp[c];
+      sum += (double)set;
+      cnt += 1.0;
+      r[c] = set;
+    }
+    stW<W>(rhs, idx, r);
+  MF_QTILE_LOOP_END
+  double acc[2] = { sum, cnt };
+  const int ops[2] = { 0, 0 };
+  gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
+}
+
 __global__ void k_add_scalar(float* d, float v, long long n) {
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long st = (long long)gridDim.x * blockDim.x;
@@ -95,8 +136,8 @@ enum { CGC_XP = 1, CGC_YP = 2, CGC_ZP = 4, CGC_XM = 8, CGC_YM = 16, CGC_ZM = 32,
 
 // MakeLaplaceMatrix (+ ApplyGhostFluidDiagonal) -- writes all four coefficient grids for every cell
 // (the reference accumulates into cleared temp grids, conjugategrad.h:154-187, pressure.cpp:136-151)
-// PLANES: write A0/Ai/Aj/Ak; CODE: write the 16-bit row code (only valid without fractions / phi).
-template <bool PLANES, bool CODE>
+// CODE: also write the 16-bit row code (only valid without fractions / phi).
+template <bool CODE>
 __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restrict__ flags, float* __restrict__ A0, float* __restrict__ Ai,
                                                       float* __restrict__ Aj, float* __restrict__ Ak, CV3 fr, int haveFractions,
                                                       const float* __restrict__ phi, float gfClamp, unsigned short* __restrict__ code) {
@@ -139,7 +180,7 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
       }
     }
   }
-  if (PLANES) { A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak; }
+  A0[idx] = a0; Ai[idx] = ai; Aj[idx] = aj; Ak[idx] = ak;
   if (CODE) {
     // the -x/-y/-z coefficients live in the lower neighbour's row: Ai[idx-X] = -1 iff that cell is an interior fluid cell and this
     // one is fluid.  Neighbours outside the coordinate range map (by linear index) to border cells, whose rows are all zero.
@@ -159,16 +200,65 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
   }
 }
 
+// Row codes only (no coefficient planes), W x-consecutive cells per thread: the matrix setup of a plain projection step whose
+// preconditioner is already built.  Same bits as k_make_laplace<false, true>.
+template <int W>
+__global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __restrict__ flags, unsigned short* __restrict__ code) {
+  MF_CELLS_W(g, W)
+  const long long Y = g.nx, Z = g.Z;
+  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  ldW<W>(f, flags, idx);
+  xMinusW<W, int>(fxm, f, flags, idx, i, 0);
+  xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0);
+  if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
+  if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
+  if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
+  if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  if (!on) return;
+  const bool rowJK = j >= 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+  int out[W];
+#pragma unroll
+  for (int c = 0; c < W; c++) {
+    int cd = 0;
+    if (fIsFluid(f[c])) {
+      cd = CGC_FLUID;
+      const int ic = i + c;
+      if (rowJK && ic >= 1 && ic < g.nx - 1) {          // an interior fluid cell has a Laplace row
+        int a0 = 0;
+        a0 += !fIsObstacle(fxm[c]); a0 += !fIsObstacle(fxp[c]); a0 += !fIsObstacle(fym[c]); a0 += !fIsObstacle(fyp[c]);
+        if (g.is3D) { a0 += !fIsObstacle(fzm[c]); a0 += !fIsObstacle(fzp[c]); }
+        cd |= a0 << CGC_DIAG_SHIFT;
+        if (fIsFluid(fxp[c])) cd |= CGC_XP;
+        if (fIsFluid(fyp[c])) cd |= CGC_YP;
+        if (g.is3D && fIsFluid(fzp[c])) cd |= CGC_ZP;
+      }
+      // couplings stored in the lower neighbours' rows (those cells must be interior fluid cells)
+      if (rowJK && ic >= 2 && ic < g.nx && fIsFluid(fxm[c])) cd |= CGC_XM;                         // (ic-1, j, k) interior
+      if (ic >= 1 && ic < g.nx - 1 && j >= 2 && (!g.is3D || (k >= 1 && k < g.nz - 1)) && fIsFluid(fym[c])) cd |= CGC_YM;   // (ic, j-1, k) interior
+      if (g.is3D && ic >= 1 && ic < g.nx - 1 && j >= 1 && j < g.ny - 1 && k >= 2 && fIsFluid(fzm[c])) cd |= CGC_ZM;       // (ic, j, k-1) interior
+    }
+    out[c] = cd;
+  }
+  stW<W>(code, idx, out);
+}
+
 // CountEmptyCells (pressure.cpp:217) + "first interior fluid cell in FOR_IJK_BND order" (:371-381)
 // out[0] = numEmpty, out[1] = min interior fluid index (or INT_MAX-ish)
+template <int W>
 __global__ void __launch_bounds__(256) k_flag_stats(Geo g, const int* __restrict__ flags, RedCtx ctx, double* out) {
   __shared__ double sh[32];
   double numEmpty = 0.0, minFluid = 1e300;
-  MF_TILE_LOOP_BEGIN(g)
-    const int f = flags[idx];
-    if (fIsEmpty(f)) numEmpty += 1.0;
-    if (fIsFluid(f) && interiorCell(g, i, j, k)) { const double v = (double)idx; if (v < minFluid) minFluid = v; }
-  MF_TILE_LOOP_END
+  MF_QTILE_LOOP_BEGIN(g, W)
+    if (!on) continue;
+    int f[W];
+    ldW<W>(f, flags, idx);
+    const bool rowJK = j >= 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+      if (fIsEmpty(f[c])) numEmpty += 1.0;
+      if (fIsFluid(f[c]) && rowJK && i + c >= 1 && i + c < g.nx - 1) { const double v = (double)(idx + c); if (v < minFluid) minFluid = v; }
+    }
+  MF_QTILE_LOOP_END
   double acc[2] = { numEmpty, minFluid };
   const int ops[2] = { 0, 1 };
   gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ out });
@@ -244,36 +334,44 @@ __global__ void __launch_bounds__(256) k_apply_matrix(Geo g, const int* __restri
   dst[idx] = fIsFluid(flags[idx]) ? applyRow(g, idx, src, A0, Ai, Aj, Ak) : src[idx];
 }
 
-// knCorrectVelocity (pressure.cpp:87-109), in place
+// knCorrectVelocity (pressure.cpp:87-109), in place; W x-consecutive cells per thread (quad.cuh)
+template <int W>
 __global__ void __launch_bounds__(256) k_correct_velocity(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
-  if (i >= g.nx || j >= g.ny || k >= g.k1) return;
-  if (!interiorCell(g, i, j, k)) return;
-  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
-  const long long X = 1, Y = g.nx, Z = g.Z;
-  const int f = flags[idx];
-  const int fx = flags[idx - X], fy = flags[idx - Y], fz = g.is3D ? flags[idx - Z] : 0;
-  if (fIsFluid(f)) {
-    const float pc = p[idx];
-    float vx = vel.x[idx], vy = vel.y[idx];
-    if (fIsFluid(fx)) vx -= (pc - p[idx - X]);
-    if (fIsFluid(fy)) vy -= (pc - p[idx - Y]);
-    if (fIsEmpty(fx)) vx -= pc;
-    if (fIsEmpty(fy)) vy -= pc;
-    vel.x[idx] = vx; vel.y[idx] = vy;
-    if (g.is3D) {
-      float vz = vel.z[idx];
-      if (fIsFluid(fz)) vz -= (pc - p[idx - Z]);
-      if (fIsEmpty(fz)) vz -= pc;
-      vel.z[idx] = vz;
+  MF_CELLS_W(g, W)
+  if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
+  const long long Y = g.nx, Z = g.Z;
+  int f[W], fx[W], fy[W], fz[W];
+  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
+  if (g.is3D) ldW<W>(fz, flags, idx - Z); else { for (int c = 0; c < W; c++) fz[c] = 0; }
+  xMinusW<W, int>(fx, f, flags, idx, i, 0);
+  float pc[W], px[W], py[W], pz[W];
+  ldW<W>(pc, p, idx); ldW<W>(py, p, idx - Y);
+  if (g.is3D) ldW<W>(pz, p, idx - Z); else { for (int c = 0; c < W; c++) pz[c] = 0.f; }
+  xMinusW<W, float>(px, pc, p, idx, i, 0.f);
+  float vx[W], vy[W], vz[W];
+  ldW<W>(vx, vel.x, idx); ldW<W>(vy, vel.y, idx);
+  if (g.is3D) ldW<W>(vz, vel.z, idx);
+#pragma unroll
+  for (int c = 0; c < W; c++) {
+    if (i + c < 1 || i + c >= g.nx - 1) continue;
+    if (fIsFluid(f[c])) {
+      if (fIsFluid(fx[c])) vx[c] -= (pc[c] - px[c]);
+      if (fIsFluid(fy[c])) vy[c] -= (pc[c] - py[c]);
+      if (fIsEmpty(fx[c])) vx[c] -= pc[c];
+      if (fIsEmpty(fy[c])) vy[c] -= pc[c];
+      if (g.is3D) {
+        if (fIsFluid(fz[c])) vz[c] -= (pc[c] - pz[c]);
+        if (fIsEmpty(fz[c])) vz[c] -= pc[c];
+      }
+    } else if (fIsEmpty(f[c]) && !fIsOutflow(f[c])) {
+      if (fIsFluid(fx[c])) vx[c] += px[c]; else vx[c] = 0.f;
+      if (fIsFluid(fy[c])) vy[c] += py[c]; else vy[c] = 0.f;
+      if (g.is3D) { if (fIsFluid(fz[c])) vz[c] += pz[c]; else vz[c] = 0.f; }
     }
-  } else if (fIsEmpty(f) && !fIsOutflow(f)) {
-    if (fIsFluid(fx)) vel.x[idx] += p[idx - X]; else vel.x[idx] = 0.f;
-    if (fIsFluid(fy)) vel.y[idx] += p[idx - Y]; else vel.y[idx] = 0.f;
-    if (g.is3D) { if (fIsFluid(fz)) vel.z[idx] += p[idx - Z]; else vel.z[idx] = 0.f; }
   }
+  if (!on) return;
+  stW<W>(vel.x, idx, vx); stW<W>(vel.y, idx, vy);
+  if (g.is3D) stW<W>(vel.z, idx, vz);
 }
 
 // knCorrectVelocityGhostFluid (pressure.cpp:154-187)

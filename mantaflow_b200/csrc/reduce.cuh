@@ -151,6 +151,33 @@ void fetchRed(Solver* s, int count);
         const long long idx = (long long)i + (long long)(g).nx * j + (long long)(g).nx * (g).ny * k;
 #define MF_TILE_LOOP_END }}}
 
+// The same with W x-consecutive cells per thread (quad.cuh): tiles of 32 threads x 4 x 2 rows; a warp is one row, so the row
+// test is warp-uniform and out-of-range lanes stay (clamped to the last cells of the row, on == false) for the shuffles.
+#define MF_QTILE_LOOP_BEGIN(g, W) \
+  { const int _ty = (g).is3D ? 4 : 8, _tz = (g).is3D ? 2 : 1; \
+    const unsigned _ntx = (unsigned)((((g).nx + (W) - 1) / (W) + 31) >> 5), _nty = (unsigned)(((g).ny + _ty - 1) / _ty); \
+    const unsigned _nt = _ntx * _nty * (unsigned)(((g).k1 - (g).k0 + _tz - 1) / _tz); \
+    const int _lx = threadIdx.x & 31; \
+    const int _ly = (g).is3D ? ((threadIdx.x >> 5) & 3) : (threadIdx.x >> 5); \
+    const int _lz = (g).is3D ? (threadIdx.x >> 7) : 0; \
+    for (unsigned _t = blockIdx.x; _t < _nt; _t += gridDim.x) { \
+      const unsigned _bx = _t % _ntx, _rr = _t / _ntx, _by = _rr % _nty, _bz = _rr / _nty; \
+      const int _i0 = (int)(_bx * 32 + _lx) * (W), j = (int)_by * _ty + _ly, k = (g).k0 + (int)_bz * _tz + _lz; \
+      if (j < (g).ny && k < (g).k1) { \
+        const bool on = _i0 < (g).nx; \
+        const int i = on ? _i0 : (g).nx - (W); \
+        const long long idx = (long long)i + (long long)(g).nx * j + (long long)(g).nx * (g).ny * k;
+#define MF_QTILE_LOOP_END }}}
+
+inline int quadTileBlocks(const Solver* s, const Geo& g, int W) {
+  const int ty = s->is3D ? 4 : 8, tz = s->is3D ? 2 : 1;
+  long long nt = (long long)(((s->nx + W - 1) / W + 31) / 32) * ((s->ny + ty - 1) / ty) * ((g.k1 - g.k0 + tz - 1) / tz);
+  if (nt < 1) nt = 1;
+  long long cap = (long long)s->numSMs * 8;
+  if (cap > RED_MAX_BLOCKS) cap = RED_MAX_BLOCKS;
+  return (int)(nt < cap ? nt : cap);
+}
+
 inline int tileBlocks(const Solver* s, const Geo& g) {
   const int ty = s->is3D ? 4 : 8, tz = s->is3D ? 2 : 1;
   long long nt = (long long)((s->nx + 31) / 32) * ((s->ny + ty - 1) / ty) * ((g.k1 - g.k0 + tz - 1) / tz);
