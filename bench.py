@@ -326,7 +326,7 @@ def main():
             traffic = None
             try:   # dram bytes per launch of the dominant kernel from the committed ncu capture, if any
                 tr = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
-                traffic = tr.get(str(a.size), {}).get(top["kernel"])
+                traffic = tr.get(str(a.size), {}).get(top["kernel"].split("@")[0])
             except Exception:
                 pass
             roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak, "unit": "GB/s",

@@ -41,6 +41,6 @@ def mg_level_pairs(size, level, rank, nranks):
     bz = (sz + 1) // 2
     if nranks == 1:
         return 0, bz
-    if sx * sy * sz < 32768 or bz < 2 * nranks:
+    if sx * sy * sz < (1 << 20) or bz < 2 * nranks:   # multigrid.cu lvlSolo
         return (0, bz) if rank == 0 else (0, 0)
     return bz * rank // nranks, bz * (rank + 1) // nranks
