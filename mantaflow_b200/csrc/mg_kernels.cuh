@@ -172,13 +172,20 @@ struct L0Code {
   __device__ __forceinline__ Row row(int v) const { Row r; r.c = code[v]; return r; }
   __device__ __forceinline__ bool inactive(const Row& r) const { return codeDiag(r.c) == 0; }
   __device__ __forceinline__ float rhs(const Row& r, float b) const { return (r.c & MGC_TRIVIAL) ? b * trivialScale : b; }
-  __device__ __forceinline__ float diag(const Row& r, int) const { const float d = (float)codeDiag(r.c); return (r.c & MGC_TRIVIAL) ? d * trivialScale : d; }
+  // (float)d for d in 0..7 without an int->float conversion: 2^23 + d is exact, subtracting 2^23 leaves d
+  __device__ __forceinline__ float diag(const Row& r, int) const {
+    const float d = __int_as_float(0x4B000000 | codeDiag(r.c)) - 8388608.0f;
+    return (r.c & MGC_TRIVIAL) ? d * trivialScale : d;
+  }
   template <int DIR> __device__ __forceinline__ float coef(const Row& r, int, int) const {
     constexpr int bit = (DIR == 0) ? MGC_XM : (DIR == 1) ? MGC_XP : (DIR == 2) ? MGC_YM : (DIR == 3) ? MGC_YP : (DIR == 4) ? MGC_ZM : MGC_ZP;
     return (r.c & bit) ? -1.0f : 0.0f;
   }
-  template <int DIR> __device__ __forceinline__ float sub(const Row& r, int v, int nb, float sum, float xn) const {
-    return sum - coef<DIR>(r, v, nb) * xn;      // 0 * xn = +-0 leaves sum bit-unchanged
+  // sum - coef * xn with coef in {-1, 0}: -(-1 * xn) is exactly +xn, and subtracting 0 * xn = +-0 leaves sum unchanged (up to
+  // the sign of a zero sum), so one predicated add replaces select + multiply + subtract
+  template <int DIR> __device__ __forceinline__ float sub(const Row& r, int, int, float sum, float xn) const {
+    constexpr int bit = (DIR == 0) ? MGC_XM : (DIR == 1) ? MGC_XP : (DIR == 2) ? MGC_YM : (DIR == 3) ? MGC_YP : (DIR == 4) ? MGC_ZM : MGC_ZP;
+    return (r.c & bit) ? sum + xn : sum;
   }
 };
 

@@ -4,6 +4,7 @@
 #include "multigrid.h"
 #include "mg_kernels.cuh"
 #include "mg_fused0.cuh"
+#include "mg_wave0.cuh"
 #include "comm.h"
 #include <algorithm>
 #include <cmath>
@@ -622,6 +623,59 @@ static void fusedUp0(MgHierarchy* mg, float* dst) {
   endGroup(mg, false);
 }
 
+// ---- z-marching wavefront legs (mg_wave0.cuh): 16-bit operator code, sx % 4 == 0; partitioned runs need a partitioned level 1
+static bool waveOk(const MgHierarchy* mg) {
+  const Solver* s = mg->s;
+  if (!mg->useCode || mg->lv[0].sx % 4 != 0 || getenv("MF_MG_NOWAVE")) return false;
+  return !s->multi() || !lvlSolo(mg, 1);
+}
+// total CTAs = a whole number of waves of the 2 CTAs an SM holds; chunks of at least ~16 planes (pipeline warm-up is 4-6 planes)
+static WvSched waveSched(const Solver* s, int tx, int ty, int planes, int& total) {
+  const int tiles = tx * ty, slots = 2 * s->numSMs;
+  int maxq = planes / 16; if (maxq < 1) maxq = 1;
+  const int waves = (tiles + slots - 1) / slots;
+  total = waves * slots;
+  if (total > tiles * maxq) total = tiles * maxq;
+  if (total < tiles) total = tiles;
+  WvSched S; S.tx = tx; S.ty = ty;
+  S.q = total / tiles;
+  S.nq = tiles - (total - S.q * tiles);           // the remaining total - q*tiles tiles get q+1 chunks
+  return S;
+}
+static void waveDown0(MgHierarchy* mg) {
+  Solver* s = mg->s;
+  LvlD& F = mg->lv[0]; LvlD& C = mg->lv[1];
+  s->profTag = 0;
+  beginGroup(mg, false);
+  MF_RANKS(s, r) {
+    int z0, z1, cz0, cz1; lvlPlanes(mg, 0, r, z0, z1); lvlPlanes(mg, 1, r, cz0, cz1);
+    if (z1 <= z0 && cz1 <= cz0) continue;
+    // planes whose x this rank writes, united with the planes 2K of the coarse vertices it writes
+    int U0 = z0, U1 = z1;
+    if (cz1 > cz0) { if (z1 <= z0) { U0 = 2 * cz0; U1 = 2 * cz1 - 1; } else { U0 = U0 < 2 * cz0 ? U0 : 2 * cz0; U1 = U1 > 2 * cz1 - 1 ? U1 : 2 * cz1 - 1; } }
+    U0 &= ~1;
+    const int tx = (int)cdiv(F.sx + 1, WV_TX), ty = (int)cdiv(F.sy + 1, WD_TY);
+    int total; const WvSched S = waveSched(s, tx, ty, U1 - U0, total);
+    MF_LAUNCH_PDL(s, k_mg_down0, total, WV_NT, F, C, mg->trivialScale, 0, U0, U1, S, z0, z1, cz0, cz1);
+  }
+  endGroup(mg, false);
+}
+static void waveUp0(MgHierarchy* mg, float* dst) {
+  Solver* s = mg->s;
+  LvlD& F = mg->lv[0]; LvlD& C = mg->lv[1];
+  s->profTag = 0;
+  beginGroup(mg, false);
+  MF_RANKS(s, r) {
+    int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+    if (z1 <= z0) continue;
+    const int U0 = z0 & ~1, U1 = z1;
+    const int tx = (int)cdiv(F.sx, WV_TX), ty = (int)cdiv(F.sy, WU_TY);
+    int total; const WvSched S = waveSched(s, tx, ty, U1 - U0, total);
+    MF_LAUNCH_PDL(s, k_mg_up0w, total, WV_NT, F, C, mg->trivialScale, 1, (const float*)F.r, dst, U0, U1, S, z0, z1);
+  }
+  endGroup(mg, false);
+}
+
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
 void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
@@ -638,11 +692,15 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   // own array (L0.r) and puts the residual into dst, which is free until the tiled up-leg kernel writes it out of place.
   const bool fused0 = mg->D.is3D && maxLevel > 0 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_UNFUSED");
   float* const r0keep = L0.r;
+  const bool wave = fused0 && waveOk(mg);
   if (fused0) {
     L0.x = r0keep; L0.r = dst;
-    if (mg->useCode) fusedPresmooth0<L0Code>(mg); else fusedPresmooth0<L0Float>(mg);
-    residual(mg, 0);
-    restrictTo(mg, 0);
+    if (wave) waveDown0(mg);          // both colours, residual and restriction in one pass; the residual stays on chip
+    else {
+      if (mg->useCode) fusedPresmooth0<L0Code>(mg); else fusedPresmooth0<L0Float>(mg);
+      residual(mg, 0);
+      restrictTo(mg, 0);
+    }
   }
   // (a single-CTA kernel walking all levels <= 17^3 plus the coarsest CG in one launch was measured: 229 us against ~256 us
   // for the separate PDL launches at 256^3, no gain on the step -- dropped)
@@ -668,7 +726,8 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   }
   if (fused0) {
     L0.r = r0keep; L0.x = dst;
-    if (mg->useCode) fusedUp0<L0Code>(mg, dst); else fusedUp0<L0Float>(mg, dst);
+    if (wave) waveUp0(mg, dst);
+    else if (mg->useCode) fusedUp0<L0Code>(mg, dst); else fusedUp0<L0Float>(mg, dst);
   }
   flushGroups(mg);
   s->profTag = -1;

@@ -141,3 +141,75 @@ def test_pressure_solve_rowcode_vs_planes(monkeypatch):
         manta.releaseMG(s)
     assert np.allclose(res[0][0], res[1][0], rtol=0, atol=2e-5)
     assert np.allclose(res[0][1], res[1][1], rtol=0, atol=2e-5)
+
+
+VC_SIZES = [(64, 50, 37), (8, 8, 8), (60, 29, 33), (120, 31, 18), (56, 26, 64), (116, 60, 41), (4, 70, 9)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size", VC_SIZES)
+def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
+    """one V(1,1)-cycle: the z-marching wavefront legs (mg_wave0.cuh), the tiled fused legs (mg_fused0.cuh) and the plain
+    per-colour sweeps give bit-identical results"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    rs = np.random.RandomState(21)
+    f = _flags(rs, size, 3)
+    f[f == EMPTY] = FLUID                 # closed box with obstacles
+    nz, ny, nx = f.shape
+    f[nz // 2, ny // 2, nx // 2] = EMPTY  # one Dirichlet neighbour keeps the operator regular
+    rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
+    outs = []
+    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}):
+        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        A0, Ai, Aj, Ak, R, D = [s.create(manta.RealGrid) for _ in range(6)]
+        R.from_numpy(rhs)
+        check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
+        check(lib().mf_mg_vcycle(s._h, A0._h, Ai._h, Aj._h, Ak._h, R._h, D._h, 1e-7))
+        outs.append(D.to_numpy())
+        manta.releaseMG(s)
+    assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
+    assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
+    assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nranks", [1, 2, 3])
+def test_vcycle_wavefront_partitioned(nranks, monkeypatch):
+    """a grid large enough for a partitioned level 1 (>= 2^20 vertices): wavefront legs on z-slabs (emulated ranks) against the
+    plain sweeps on one rank"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    size = (256, 128, 256)
+    rs = np.random.RandomState(4)
+    f = _flags(rs, size, 3)
+    f[f == EMPTY] = FLUID
+    f[128, 64, 128] = EMPTY
+    rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
+
+    def run(comm):
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3, comm=comm)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        A0, Ai, Aj, Ak, R, D = [s.create(manta.RealGrid) for _ in range(6)]
+        R.from_numpy(rhs)
+        check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
+        check(lib().mf_mg_vcycle(s._h, A0._h, Ai._h, Aj._h, Ak._h, R._h, D._h, 1e-7))
+        out = D.to_numpy()
+        manta.releaseMG(s)
+        return out
+
+    monkeypatch.setenv("MF_MG_UNFUSED", "1")
+    ref = run(None)
+    monkeypatch.delenv("MF_MG_UNFUSED")
+    comm = manta.Comm.emulated(nranks) if nranks > 1 else None
+    try:
+        got = run(comm)
+    finally:
+        if comm is not None:
+            comm.destroy()
+    assert np.array_equal(got.view(np.int32), ref.view(np.int32))
