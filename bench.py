@@ -62,6 +62,8 @@ ALGO_BYTES_PER_CELL = {
     "k_mg_residual0": 14.0,    # code 2 + x 4 + b 4 + r 4
     "k_mg_presmooth0": 10.0,   # first sweep pair of a V-cycle (x == 0): code 2 + b 4 + x out 4
     "k_mg_up0": 14.5,          # interpolate + add + both colour sweeps in one pass: code 2 + x 4 + b 4 + coarse x 0.5 + x out 4
+    "k_mg_up0w": 14.5,         # the same as a z-marching wavefront (mg_wave0.cuh)
+    "k_mg_down0": 10.5,        # both colours + residual + restriction in one pass: code 2 + b 4 + x out 4 + coarse b 0.5
     # k_mg_restrict / k_mg_interp_add / k_mg_smooth / k_mg_residual run on every level: no single bytes-per-cell figure
     "k_apply_cylinder": 4.0,
 }
