@@ -5,7 +5,6 @@
 #include "mg_kernels.cuh"
 #include "mg_fused0.cuh"
 #include "mg_wave0.cuh"
-#include <cooperative_groups.h>
 #include "comm.h"
 #include <algorithm>
 #include <cmath>
@@ -181,48 +180,6 @@ __global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float a
   __shared__ double sh[2][2][32];
   __shared__ double vec[1024];
   mgCoarseCg<LEVEL0>(L, D, accuracy, sh, vec);
-}
-
-// ---- a whole visit of a small level in ONE launch of a thread-block cluster ----------------------------------------------
-// Levels of a few thousand vertices per colour are pure launch latency as separate sweeps (8 colours + residual + restriction,
-// or interpolation + 8 colours: ~4.4 us per dependent launch).  One cluster of MG_CL_CTAS CTAs walks the phases with cluster
-// barriers (barrier.cluster arrive.release / wait.acquire orders the global-memory writes of one phase before the reads of
-// the next) -- the device functions are the ones the per-phase kernels call, so the arithmetic is identical.
-namespace cg = cooperative_groups;
-constexpr int MG_CL_CTAS = 8, MG_CL_THREADS = 512, MG_CL_MAXVERTS = 65536;
-template <bool IS3D, bool DOWN>
-__global__ void __launch_bounds__(MG_CL_THREADS) k_mg_level_cl(LvlD L, LvlD O) {   // O: the next coarser level
-  MF_PDL_PROLOGUE
-  cg::cluster_group cl = cg::this_cluster();
-  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-  const int lz1 = IS3D ? L.PZ - 2 : 1;
-  const int nt = (L.PX - 2) * (L.PY - 2) * lz1;
-  if (DOWN) {
-    for (int c = 0; c < L.NC; c++) {
-      for (int t = tid; t < nt; t += nth) mgSmoothItem<IS3D>(L, c, 0, lz1, t);
-      cl.sync();
-    }
-    for (int c = 0; c < L.NC; c++)
-      for (int t = tid; t < nt; t += nth) mgResidualItem<IS3D>(L, c, 0, lz1, t);
-    cl.sync();
-    for (int t = tid; t < O.n; t += nth) mgRestrictItem<IS3D>(L, O, 0, O.sz, t);
-  } else {
-    for (int t = tid; t < L.n; t += nth) mgInterpAddItem(L, O, 0, L.sz, t);
-    for (int c = L.NC - 1; c >= 0; c--) {
-      cl.sync();
-      for (int t = tid; t < nt; t += nth) mgSmoothItem<IS3D>(L, c, 0, lz1, t);
-    }
-  }
-}
-template <class... KArgs, class... Args>
-static void launchCluster(cudaStream_t st, void (*kern)(KArgs...), int ctas, int threads, Args... args) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-  cudaLaunchAttribute at[2];
-  at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = 2;
-  CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, KArgs(args)...));
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------
@@ -719,29 +676,6 @@ static void waveUp0(MgHierarchy* mg, float* dst) {
   endGroup(mg, false);
 }
 
-// small levels (not the finest, not the coarsest) of the standard V(1,1) cycle: one cluster launch per visit
-static bool clusterLevel(const MgHierarchy* mg, int l) {
-  const int maxLevel = (int)mg->lv.size() - 1;
-  if (l <= 0 || l >= maxLevel || mg->pre != 1 || mg->post != 1 || getenv("MF_MG_NOCLUSTER")) return false;
-  if (mg->lv[l].n > MG_CL_MAXVERTS) return false;
-  return !mg->s->multi() || (lvlSolo(mg, l) && lvlSolo(mg, l + 1));
-}
-static void levelCluster(MgHierarchy* mg, int l, bool down) {
-  Solver* s = mg->s; s->profTag = l;
-  LvlD& L = mg->lv[l]; LvlD& O = mg->lv[l + 1];
-  const bool solo = s->multi();
-  beginGroup(mg, solo);
-  if (s->rankBegin == 0) {
-    ProfScope ps(s, down ? "k_mg_level_cl_down" : "k_mg_level_cl_up");
-    if (mg->D.is3D) { if (down) launchCluster(s->stream, k_mg_level_cl<true, true>, MG_CL_CTAS, MG_CL_THREADS, L, O);
-                      else launchCluster(s->stream, k_mg_level_cl<true, false>, MG_CL_CTAS, MG_CL_THREADS, L, O); }
-    else            { if (down) launchCluster(s->stream, k_mg_level_cl<false, true>, MG_CL_CTAS, MG_CL_THREADS, L, O);
-                      else launchCluster(s->stream, k_mg_level_cl<false, false>, MG_CL_CTAS, MG_CL_THREADS, L, O); }
-    s->launches++;
-  }
-  endGroup(mg, solo);
-}
-
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
 void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
@@ -768,11 +702,12 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
       restrictTo(mg, 0);
     }
   }
-  // (a single-CTA kernel walking all levels <= 17^3 plus the coarsest CG in one launch was measured: 229 us against ~256 us
-  // for the separate PDL launches at 256^3, no gain on the step -- dropped)
+  // (measured and dropped: a single-CTA kernel walking all levels <= 17^3 plus the coarsest CG in one launch, 229 us against
+  // ~256 us for the separate PDL launches at 256^3; a thread-block cluster of 8 x 512 threads walking all phases of a 33^3 or
+  // 17^3 level with cluster barriers, 5-9 us per phase against ~4.4 us per dependent launch -- too few threads in flight for
+  // the latency of a 41-load stencil item)
   const int lb = maxLevel;
   for (int l = fused0 ? 1 : 0; l < lb; l++) {
-    if (clusterLevel(mg, l)) { levelCluster(mg, l, true); continue; }
     for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0);
     residual(mg, l);
     restrictTo(mg, l);
@@ -788,7 +723,6 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     endGroup(mg, solo);
   }
   for (int l = lb - 1; l >= (fused0 ? 1 : 0); l--) {
-    if (clusterLevel(mg, l)) { levelCluster(mg, l, false); continue; }
     interpAdd(mg, l);
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }
