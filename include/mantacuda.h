@@ -83,6 +83,19 @@ long long    mf_solver_barrier_count(const mf_solver* s);                      /
  * grid on every rank (upload: each rank copies its own slab from it; download: every rank receives the whole grid) */
 int          mf_grid_upload_slab(mf_grid* g, const void* host_slab);
 int          mf_grid_download_slab(const mf_grid* g, void* host_slab);
+/* Streaming transfers for pipelines whose data lives on the host (pinned memory from mf_host_alloc; slab layout as above).
+ * Copies run on two copy streams beside the solver stream through double-buffered device staging, so the upload of the next
+ * step's inputs and the download of the previous step's results overlap the kernels of the current step:
+ *   mf_grid_stage_upload    start the host->device copy of the slab (returns at once; at most 2 staged uploads per grid)
+ *   mf_grid_commit_upload   the solver stream waits for the oldest staged copy and moves it into the grid (AoS->SoA for vec grids)
+ *   mf_grid_download_async  snapshot the grid on the solver stream, copy it device->host on the copy-out stream
+ *   mf_solver_transfers_sync  wait for everything: host buffers are complete / reusable afterwards
+ * A host buffer passed to stage_upload / download_async must stay untouched until transfers_sync (or two further calls on the
+ * same grid have been followed by a solver sync). */
+int          mf_grid_stage_upload(mf_grid* g, const void* pinned_slab);
+int          mf_grid_commit_upload(mf_grid* g);
+int          mf_grid_download_async(const mf_grid* g, void* pinned_slab);
+int          mf_solver_transfers_sync(mf_solver* s);
 /* out[0] mismatches seen through peer mappings, out[1] device-barrier latency (us), out[2]/out[3] peer read/write GB/s,
  * out[4] allocation granularity (bytes), out[5] local copy GB/s */
 int          mf_comm_selftest(mf_comm* c, long long bytesPerRank, int iters, double* out);

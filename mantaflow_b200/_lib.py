@@ -59,6 +59,10 @@ SIGNATURES = {
     "mf_solver_barrier_count": (C.c_longlong, [_P]),
     "mf_grid_upload_slab": (_i, [_P, _P]),
     "mf_grid_download_slab": (_i, [_P, _P]),
+    "mf_grid_stage_upload": (_i, [_P, _P]),
+    "mf_grid_commit_upload": (_i, [_P]),
+    "mf_grid_download_async": (_i, [_P, _P]),
+    "mf_solver_transfers_sync": (_i, [_P]),
     "mf_comm_selftest": (_i, [_P, C.c_longlong, _i, C.POINTER(C.c_double)]),
     "mf_host_alloc": (_P, [C.c_longlong]),
     "mf_host_free": (None, [_P]),

@@ -354,8 +354,7 @@ bool flagsHaveOutflow(const Grid* flags) {
   s->clearShared(s->devFlagsScratch, sizeof(int));
   MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_scan_outflow, s->numSMs * 8, 256, flags->di() + sp.off, sp.n, s->devFlagsScratch); }
   s->rankSync();
-  CUDA_CHECK(cudaMemcpyAsync(s->hostInts, s->devFlagsScratch, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
-  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  s->readSmall(s->hostInts, s->devFlagsScratch, (int)sizeof(int));
   flags->outflowState = s->hostInts[0] ? 1 : 0;
   return flags->outflowState != 0;
 }

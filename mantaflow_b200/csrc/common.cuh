@@ -40,12 +40,14 @@ struct MgHierarchy;
 struct Comm;
 struct CommShared;
 
+struct GridXfer;      // staging of the streaming transfers (solver.cu), lazily created
 struct Grid {
   Solver* s;
   int type;          // MF_TYPE_* bits
   float* d;          // device storage (int grids reinterpret)
   bool pooled;       // storage came from the solver pool
   mutable int outflowState;  // flag grids: -1 unknown, 0 no TypeOutflow cell, 1 some (cache for applyOutflowBC)
+  mutable GridXfer* xfer;    // owned by the grid created through mf_grid_create (temporary Grid copies never touch it)
   bool isVec() const { return (type & MF_TYPE_VEC3) != 0; }
   bool isMAC() const { return (type & MF_TYPE_MAC) != 0; }
   bool isReal() const { return (type & MF_TYPE_REAL) != 0; }
@@ -63,6 +65,7 @@ struct Solver {
   float dt, dx;
   int device;
   cudaStream_t stream;
+  cudaStream_t copyIn, copyOut;   // streaming transfers (mf_grid_stage_upload / _download_async), lazily created
   long long launches;
   // temp-grid pool with the reference's stack discipline (fluidsolver.cpp:33-50)
   std::vector<float*> poolReal, poolVec;
@@ -92,6 +95,10 @@ struct Solver {
   void  gfree(void* p);
   void  rankSync();      // device barrier across ranks on the solver stream (no-op on a single GPU / emulated)
   void  clearShared(void* p, size_t bytes);   // zero a small job-wide scratch array (one rank clears, then barrier)
+  // small control transfers on the solver stream WITHOUT the copy engines (a 40-byte readback must not queue behind a bulk
+  // host copy of the streaming transfers): a one-warp kernel stores into mapped pinned memory / carries the payload as argument
+  void  readSmall(void* pinnedDst, const void* dev, int bytes);     // then synchronises the stream; bytes % 4 == 0, <= 256
+  void  writeSmall(void* dev, const void* hostSrc, int bytes);      // asynchronous; bytes % 4 == 0, <= 64
   // per-kernel CUDA-event timing (mf_solver_profile_*): one event pair per launch while enabled
   bool profiling;
   struct ProfRec { const char* name; cudaEvent_t a, b; int tag; };

@@ -380,8 +380,7 @@ int mf_flags_count_cells(const mf_grid* fp, int flag, int bnd, int* out) {
   s->clearShared(s->devFlagsScratch + 1, sizeof(int));
   MF_LAUNCH_IJK(s, k_count_cells, flags->di(), flag, bnd, s->devFlagsScratch + 1);
   MF_LAUNCH_CHECK();
-  CUDA_CHECK(cudaMemcpyAsync(s->hostInts, s->devFlagsScratch + 1, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
-  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  s->readSmall(s->hostInts, s->devFlagsScratch + 1, (int)sizeof(int));
   *out = s->hostInts[0];
   MF_API_END
 }

@@ -83,8 +83,7 @@ struct CgDriver {
     (void)init;
   }
   void fetch() {
-    CUDA_CHECK(cudaMemcpyAsync(s->hostInts, st, sizeof(CgState), cudaMemcpyDeviceToHost, s->stream));
-    CUDA_CHECK(cudaStreamSynchronize(s->stream));
+    s->readSmall(s->hostInts, st, (int)sizeof(CgState));
     memcpy(&host, s->hostInts, sizeof(CgState));
   }
   // doInit (conjugategrad.cpp:210-235)
@@ -92,9 +91,7 @@ struct CgDriver {
     const long long N = s->N;
     CgState h; memset(&h, 0, sizeof(h));
     h.accuracy = accuracy; h.useL2 = useL2 ? 1 : 0; h.resNorm = 1e20f;
-    memcpy(s->hostInts, &h, sizeof(h));
-    CUDA_CHECK(cudaMemcpyAsync(st, s->hostInts, sizeof(CgState), cudaMemcpyHostToDevice, s->stream));
-    CUDA_CHECK(cudaStreamSynchronize(s->stream));   // hostInts is reused below
+    s->writeSmall(st, &h, (int)sizeof(h));
     (void)N;
     slabZero(s, v.dst);
     slabCopy(s, v.residual, v.rhs);
@@ -212,8 +209,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     info->iterations = cg.host.iterations; info->resNorm = cg.host.resNorm; info->maxIter = maxIter;
     info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
     if (fixing) {
-      CUDA_CHECK(cudaMemcpyAsync(s->hostInts, fixedDev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
-      CUDA_CHECK(cudaStreamSynchronize(s->stream));
+      s->readSmall(s->hostInts, fixedDev, (int)sizeof(int));
       info->fixedCell = s->hostInts[0];
     }
   }

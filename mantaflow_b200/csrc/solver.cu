@@ -77,10 +77,26 @@ cudaEvent_t Solver::profEvent() {
   cudaEvent_t e; CUDA_CHECK(cudaEventCreate(&e)); return e;
 }
 
-void fetchRed(Solver* s, int count) {
-  CUDA_CHECK(cudaMemcpyAsync(s->redHost, s->redOut, sizeof(double) * count, cudaMemcpyDeviceToHost, s->stream));
-  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+struct SmallPayload { unsigned w[16]; };
+__global__ void k_read_small(unsigned* dst, const unsigned* __restrict__ src, int nwords) {
+  if ((int)threadIdx.x < nwords) dst[threadIdx.x] = src[threadIdx.x];
 }
+__global__ void k_write_small(unsigned* dst, SmallPayload p, int nwords) {
+  if ((int)threadIdx.x < nwords) dst[threadIdx.x] = p.w[threadIdx.x];
+}
+void Solver::readSmall(void* pinnedDst, const void* dev, int bytes) {
+  void* mapped = nullptr;
+  CUDA_CHECK(cudaHostGetDevicePointer(&mapped, pinnedDst, 0));
+  k_read_small<<<1, 64, 0, stream>>>((unsigned*)mapped, (const unsigned*)dev, bytes / 4);
+  launches++;
+  CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+void Solver::writeSmall(void* dev, const void* hostSrc, int bytes) {
+  SmallPayload p; memset(&p, 0, sizeof(p)); memcpy(&p, hostSrc, (size_t)bytes);
+  k_write_small<<<1, 32, 0, stream>>>((unsigned*)dev, p, bytes / 4);
+  launches++;
+}
+void fetchRed(Solver* s, int count) { s->readSmall(s->redHost, s->redOut, (int)sizeof(double) * count); }
 
 // ---- elementwise kernels ---------------------------------------------------------------
 __global__ void k_fill_f(float* d, float v, long long n) {
@@ -212,7 +228,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   s->dx = (float)(1.0 / mx);       // grid.cpp:57
   s->device = device;
   s->profTag = -1; s->profLevels = getenv("MF_PROFILE_LEVELS") != nullptr;
-  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->profiling = false;
+  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->profiling = false; s->copyIn = nullptr; s->copyOut = nullptr;
   for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
   CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
@@ -222,11 +238,11 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   CUDA_CHECK(cudaMemset(s->redCounter, 0, sizeof(unsigned int) * 4));
   CUDA_CHECK(cudaMalloc(&s->redOut, sizeof(double) * 16));
   CUDA_CHECK(cudaMemset(s->redOut, 0, sizeof(double) * 16));
-  CUDA_CHECK(cudaMallocHost(&s->redHost, sizeof(double) * 16));
+  CUDA_CHECK(cudaHostAlloc(&s->redHost, sizeof(double) * 16, cudaHostAllocMapped));
   CUDA_CHECK(cudaMalloc(&s->localInts, sizeof(int) * 16));
   CUDA_CHECK(cudaMemset(s->localInts, 0, sizeof(int) * 16));
   s->devFlagsScratch = (int*)s->galloc(sizeof(int) * 16);      // job-wide: kernels on any rank raise flags here
-  CUDA_CHECK(cudaMallocHost(&s->hostInts, sizeof(int) * 16));
+  CUDA_CHECK(cudaHostAlloc(&s->hostInts, sizeof(int) * 16, cudaHostAllocMapped));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   return s;
 }
@@ -271,6 +287,8 @@ void mf_solver_destroy(mf_solver* sp) {
   for (auto& r : s->profRecs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (cudaEvent_t e : s->evPool) cudaEventDestroy(e);
   for (int q = 0; q < 16; q++) if (s->userEvents[q]) cudaEventDestroy(s->userEvents[q]);
+  if (s->copyIn) cudaStreamDestroy(s->copyIn);
+  if (s->copyOut) cudaStreamDestroy(s->copyOut);
   cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -359,18 +377,22 @@ mf_grid* mf_grid_create(mf_solver* sp, int type) {
     mfAssert(sp, "Grid: null solver");
     Solver* s = S(sp); s->use();
     Grid* g = new Grid();
-    g->s = s; g->type = type; g->pooled = false; g->d = nullptr; g->outflowState = -1;
+    g->s = s; g->type = type; g->pooled = false; g->d = nullptr; g->outflowState = -1; g->xfer = nullptr;
     // Grid ctor clears (grid.cpp:58): galloc zero-fills
     if (type & MF_TYPE_VEC3) g->d = (float*)s->galloc(sizeof(float) * (size_t)s->Np, 3, sizeof(float) * (size_t)s->Np);
     else g->d = (float*)s->galloc(sizeof(float) * (size_t)(s->N + 64));
     return reinterpret_cast<mf_grid*>(g);
   } catch (const std::exception& e) { set_last_error(e.what()); return nullptr; }
 }
+}  // extern "C"
+namespace mf { void freeXfer(Grid* g); }
+extern "C" {
 void mf_grid_destroy(mf_grid* gp) {
   if (!gp) return;
   Grid* g = G(gp);
   g->s->use();
   cudaStreamSynchronize(g->s->stream);
+  freeXfer(g);
   g->s->gfree(g->d);
   delete g;
 }
@@ -414,7 +436,7 @@ static void gridUpload(Grid* g, const void* host, bool slabOnly) {
   MF_RANKS(s, r) {
     const Span sp = span(s, r);
     if (!sp.n) continue;
-    const long long hoff = slabOnly ? 0 : sp.off;
+    const long long hoff = slabOnly ? sp.off - span(s, s->rankBegin).off : sp.off;
     if (!g->isVec()) {
       CUDA_CHECK(cudaMemcpyAsync(g->d + sp.off, (const float*)host + hoff, sizeof(float) * (size_t)sp.n, cudaMemcpyHostToDevice, s->stream));
     } else {
@@ -434,7 +456,7 @@ static void gridDownload(const Grid* g, void* host, bool slabOnly) {
   for (int r = whole ? 0 : s->rankBegin; r < (whole ? s->nranks : s->rankEnd); r++) {
     const Span sp = span(s, r);
     if (!sp.n) continue;
-    const long long hoff = slabOnly ? 0 : sp.off;
+    const long long hoff = slabOnly ? sp.off - span(s, s->rankBegin).off : sp.off;
     if (!g->isVec()) {
       CUDA_CHECK(cudaMemcpyAsync((float*)host + hoff, g->d + sp.off, sizeof(float) * (size_t)sp.n, cudaMemcpyDeviceToHost, s->stream));
     } else {
@@ -447,6 +469,118 @@ static void gridDownload(const Grid* g, void* host, bool slabOnly) {
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   CUDA_CHECK(cudaGetLastError());
   s->rankSync();                                 // peers may overwrite the grid only after everybody has read it
+}
+// ---- streaming transfers: double-buffered staging, copies on their own streams ------------------------------------------
+// in[k] / out[k] hold the process' slab in host layout.  Events order the three streams: the copy-in stream refills a slot only
+// after the solver stream has consumed it (inFree), the solver stream overwrites an out slot only after the copy-out stream
+// has drained it (outFree).
+}  // extern "C"
+namespace mf {
+struct GridXfer {
+  float* in[2]; float* out[2];
+  cudaEvent_t inReady[2], inFree[2], outReady[2], outFree[2];
+  bool inFreeSet[2], outFreeSet[2];
+  int inHead, inCount, outNext;     // staged uploads form a queue of at most 2
+  size_t bytes;
+};
+static Span localSpan(const Solver* s) {
+  Span a = span(s, s->rankBegin), b = span(s, s->rankEnd - 1);
+  Span r; r.off = a.off; r.n = b.off + b.n - a.off; return r;
+}
+static GridXfer* xferOf(const Grid* g) {
+  Solver* s = g->s;
+  if (!s->copyIn) { CUDA_CHECK(cudaStreamCreateWithFlags(&s->copyIn, cudaStreamNonBlocking)); CUDA_CHECK(cudaStreamCreateWithFlags(&s->copyOut, cudaStreamNonBlocking)); }
+  if (g->xfer) return g->xfer;
+  GridXfer* x = new GridXfer();
+  memset(x, 0, sizeof(*x));
+  x->bytes = sizeof(float) * (size_t)localSpan(s).n * (g->isVec() ? 3 : 1);
+  for (int k = 0; k < 2; k++) {
+    CUDA_CHECK(cudaEventCreateWithFlags(&x->inReady[k], cudaEventDisableTiming)); CUDA_CHECK(cudaEventCreateWithFlags(&x->inFree[k], cudaEventDisableTiming));
+    CUDA_CHECK(cudaEventCreateWithFlags(&x->outReady[k], cudaEventDisableTiming)); CUDA_CHECK(cudaEventCreateWithFlags(&x->outFree[k], cudaEventDisableTiming));
+  }
+  g->xfer = x;
+  return x;
+}
+void freeXfer(Grid* g) {
+  GridXfer* x = g->xfer;
+  if (!x) return;
+  if (g->s->copyIn) { cudaStreamSynchronize(g->s->copyIn); cudaStreamSynchronize(g->s->copyOut); }
+  for (int k = 0; k < 2; k++) {
+    if (x->in[k]) cudaFree(x->in[k]);
+    if (x->out[k]) cudaFree(x->out[k]);
+    cudaEventDestroy(x->inReady[k]); cudaEventDestroy(x->inFree[k]); cudaEventDestroy(x->outReady[k]); cudaEventDestroy(x->outFree[k]);
+  }
+  delete x; g->xfer = nullptr;
+}
+}  // namespace mf
+extern "C" {
+int mf_grid_stage_upload(mf_grid* gp, const void* host) {
+  MF_API_BEGIN
+  mfAssert(gp && host, "Grid stage_upload: null argument");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  GridXfer* x = xferOf(g);
+  mfAssert(x->inCount < 2, "Grid stage_upload: two uploads are already staged -- commit one first");
+  const int k = (x->inHead + x->inCount) & 1;
+  if (!x->in[k]) CUDA_CHECK(cudaMalloc(&x->in[k], x->bytes));
+  if (x->inFreeSet[k]) CUDA_CHECK(cudaStreamWaitEvent(s->copyIn, x->inFree[k], 0));
+  CUDA_CHECK(cudaMemcpyAsync(x->in[k], host, x->bytes, cudaMemcpyHostToDevice, s->copyIn));
+  CUDA_CHECK(cudaEventRecord(x->inReady[k], s->copyIn));
+  x->inCount++;
+  MF_API_END
+}
+int mf_grid_commit_upload(mf_grid* gp) {
+  MF_API_BEGIN
+  mfAssert(gp, "Grid commit_upload: null argument");
+  Grid* g = G(gp); Solver* s = g->s; s->use();
+  GridXfer* x = xferOf(g);
+  mfAssert(x->inCount > 0, "Grid commit_upload: nothing staged");
+  const int k = x->inHead;
+  g->outflowState = -1;
+  CUDA_CHECK(cudaStreamWaitEvent(s->stream, x->inReady[k], 0));
+  const long long base = localSpan(s).off;
+  MF_RANKS(s, r) {
+    const Span sp = span(s, r);
+    if (!sp.n) continue;
+    const long long hoff = sp.off - base;
+    if (!g->isVec()) CUDA_CHECK(cudaMemcpyAsync(g->d + sp.off, x->in[k] + hoff, sizeof(float) * (size_t)sp.n, cudaMemcpyDeviceToDevice, s->stream));
+    else MF_LAUNCH(s, k_aos_to_soa, ewBlocks(s, sp.n), 256, x->in[k] + 3 * hoff, g->comp(0) + sp.off, g->comp(1) + sp.off, g->comp(2) + sp.off, sp.n);
+  }
+  CUDA_CHECK(cudaEventRecord(x->inFree[k], s->stream)); x->inFreeSet[k] = true;
+  x->inHead ^= 1; x->inCount--;
+  s->rankSync();
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_grid_download_async(const mf_grid* gp, void* host) {
+  MF_API_BEGIN
+  mfAssert(gp && host, "Grid download_async: null argument");
+  const Grid* g = G(gp); Solver* s = g->s; s->use();
+  GridXfer* x = xferOf(g);
+  const int k = x->outNext; x->outNext ^= 1;
+  if (!x->out[k]) CUDA_CHECK(cudaMalloc(&x->out[k], x->bytes));
+  if (x->outFreeSet[k]) CUDA_CHECK(cudaStreamWaitEvent(s->stream, x->outFree[k], 0));
+  const long long base = localSpan(s).off;
+  MF_RANKS(s, r) {
+    const Span sp = span(s, r);
+    if (!sp.n) continue;
+    const long long hoff = sp.off - base;
+    if (!g->isVec()) CUDA_CHECK(cudaMemcpyAsync(x->out[k] + hoff, g->d + sp.off, sizeof(float) * (size_t)sp.n, cudaMemcpyDeviceToDevice, s->stream));
+    else MF_LAUNCH(s, k_soa_to_aos, ewBlocks(s, sp.n), 256, x->out[k] + 3 * hoff, g->comp(0) + sp.off, g->comp(1) + sp.off, g->comp(2) + sp.off, sp.n);
+  }
+  CUDA_CHECK(cudaEventRecord(x->outReady[k], s->stream));
+  CUDA_CHECK(cudaStreamWaitEvent(s->copyOut, x->outReady[k], 0));
+  CUDA_CHECK(cudaMemcpyAsync(host, x->out[k], x->bytes, cudaMemcpyDeviceToHost, s->copyOut));
+  CUDA_CHECK(cudaEventRecord(x->outFree[k], s->copyOut)); x->outFreeSet[k] = true;
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+int mf_solver_transfers_sync(mf_solver* sp) {
+  MF_API_BEGIN
+  mfAssert(sp, "mf_solver_transfers_sync: null solver");
+  Solver* s = S(sp); s->use();
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  if (s->copyIn) { CUDA_CHECK(cudaStreamSynchronize(s->copyIn)); CUDA_CHECK(cudaStreamSynchronize(s->copyOut)); }
+  MF_API_END
 }
 int mf_grid_upload(mf_grid* gp, const void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid upload: null argument"); gridUpload(G(gp), host, false); MF_API_END }
 int mf_grid_download(const mf_grid* gp, void* host) { MF_API_BEGIN mfAssert(gp && host, "Grid download: null argument"); gridDownload(G(gp), host, false); MF_API_END }

@@ -282,6 +282,10 @@ class FluidSolver(object):
         if not (self._dt > self.timestepMin / 2.0):
             raise MantaError("Invalid dt encountered! Shouldnt happen...")
 
+    def transfersSync(self):
+        """wait for the solver stream and all streaming transfers"""
+        check(lib().mf_solver_transfers_sync(self._h))
+
     def sync(self):
         check(lib().mf_solver_sync(self._h))
 
@@ -384,6 +388,19 @@ class GridBase(object):
             a = a.reshape(self._shape())
         check(lib().mf_grid_upload(self._h, a.ctypes.data_as(C.c_void_p)))
         return self
+
+    # --- streaming transfers (pinned host slabs, double-buffered staging, copies overlap the solver stream) ---
+    def stageUpload(self, host_ptr):
+        """start the host->device copy of this process' slab (pointer from mf_host_alloc / a pinned array)"""
+        check(lib().mf_grid_stage_upload(self._h, C.c_void_p(host_ptr)))
+
+    def commitUpload(self):
+        """the solver stream takes over the oldest staged upload"""
+        check(lib().mf_grid_commit_upload(self._h))
+
+    def downloadAsync(self, host_ptr):
+        """snapshot the grid now (in stream order) and copy it to the host in the background"""
+        check(lib().mf_grid_download_async(self._h, C.c_void_p(host_ptr)))
 
     def get(self, i, j, k):
         v = self.to_numpy()[k, j, i]

@@ -102,3 +102,61 @@ def test_two_processes_two_gpus(tmp_path):
     rep = json.loads(out.read_text())
     assert rep["failed"] == [], rep
     assert sorted(rep["passed"]) == sorted(names)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nranks", [1, 2])
+def test_streaming_transfers(nranks):
+    """mf_grid_stage_upload / _commit_upload / _download_async: a pipelined loop returns, per step, exactly what a synchronous
+    upload -> kernel -> download returns"""
+    import ctypes as Ct
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    L = lib()
+    size = (12, 10, 8)
+    comm = manta.Comm.emulated(nranks)
+    bufs = []
+
+    def pinned(shape):
+        n = int(np.prod(shape)) * 4
+        p = L.mf_host_alloc(n)
+        assert p
+        bufs.append(p)
+        return p, np.ctypeslib.as_array((Ct.c_byte * n).from_address(p)).view(np.float32).reshape(shape)
+    try:
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3, comm=comm)
+        v = s.create(manta.MACGrid); d = s.create(manta.RealGrid)
+        rs = np.random.RandomState(1)
+        steps = 5
+        vin = [rs.rand(size[2], size[1], size[0], 3).astype(np.float32) for _ in range(steps)]
+        din = [rs.rand(size[2], size[1], size[0]).astype(np.float32) for _ in range(steps)]
+        hv = [pinned(vin[0].shape) for _ in range(2)]
+        hd = [pinned(din[0].shape) for _ in range(2)]
+        ov = [pinned(vin[0].shape) for _ in range(steps)]
+        od = [pinned(din[0].shape) for _ in range(steps)]
+        hv[0][1][...] = vin[0]; hd[0][1][...] = din[0]
+        v.stageUpload(hv[0][0]); d.stageUpload(hd[0][0])
+        for i in range(steps):
+            v.commitUpload(); d.commitUpload()
+            if i + 1 < steps:
+                if i >= 1:
+                    s.sync()          # the host buffer about to be refilled was consumed by the commit two steps ago
+                hv[(i + 1) & 1][1][...] = vin[i + 1]; hd[(i + 1) & 1][1][...] = din[i + 1]
+                v.stageUpload(hv[(i + 1) & 1][0]); d.stageUpload(hd[(i + 1) & 1][0])
+            v.multConst(manta.vec3(2.0, 3.0, 4.0)); d.multConst(0.5)
+            v.downloadAsync(ov[i][0]); d.downloadAsync(od[i][0])
+        s.transfersSync()
+        for i in range(steps):
+            assert np.array_equal(ov[i][1], vin[i] * np.array([2.0, 3.0, 4.0], np.float32)), i
+            assert np.array_equal(od[i][1], din[i] * np.float32(0.5)), i
+        # staging more than two uploads without a commit is refused
+        v.stageUpload(hv[0][0]); v.stageUpload(hv[1][0])
+        assert L.mf_grid_stage_upload(v._h, Ct.c_void_p(hv[0][0])) != 0
+        v.commitUpload(); v.commitUpload()
+        assert L.mf_grid_commit_upload(v._h) != 0
+        s.transfersSync()
+        del v, d, s
+    finally:
+        comm.destroy()
+        for p in bufs:
+            L.mf_host_free(p)
