@@ -171,7 +171,8 @@ class Plume(object):
 
     def __init__(self, size, device, precond, comm=None):
         from mantaflow_b200 import manta as M
-        self.M = M
+        from mantaflow_b200._lib import lib, check
+        self.M, self.L, self.check = M, lib(), check
         nx, ny, nz = size
         gs = M.vec3(nx, ny, nz)
         self.s = M.Solver(name="main", gridSize=gs, dim=3, device=device, comm=comm)
@@ -185,6 +186,7 @@ class Plume(object):
         self.source = M.Cylinder(parent=self.s, center=gs * M.vec3(0.5, 0.1, 0.5), radius=nx * 0.14, z=gs * M.vec3(0, 0.02, 0))
         self.pc = M.PcMGStatic if precond == "mg" else M.PcMIC
         self.iterations = []
+        self.solve_ms = None
 
     def step(self):
         M = self.M
@@ -193,7 +195,15 @@ class Plume(object):
         M.advectSemiLagrange(flags=self.flags, vel=self.vel, grid=self.vel, order=2)
         M.setWallBcs(flags=self.flags, vel=self.vel)
         M.addBuoyancy(density=self.density, vel=self.vel, gravity=M.vec3(0, -6e-4, 0), flags=self.flags)
+        if self.solve_ms is not None:      # PCG iteration time (SURVEY 8d metric ii): events around the projection only
+            self.check(self.L.mf_solver_event_record(self.s._h, 6))
         M.solvePressure(flags=self.flags, vel=self.vel, pressure=self.pressure, preconditioner=self.pc, zeroPressureFixing=True)
+        if self.solve_ms is not None:
+            self.check(self.L.mf_solver_event_record(self.s._h, 7))
+            ms = C.c_float()
+            self.s.sync()
+            self.check(self.L.mf_solver_event_elapsed_ms(self.s._h, 6, 7, C.byref(ms)))
+            self.solve_ms.append(ms.value)
         self.s.step()
         self.iterations.append(M.getSolveInfo()["iterations"])
 
@@ -336,6 +346,18 @@ def main():
                         "algo_bytes_per_launch": top["algo_bytes_per_cell"] * cells_gpu, "avg_launch_us": top["avg_us"],
                         "share_of_step": top["share_of_step"], "timed": "CUDA events around every launch, %d extra steps after the timed region" % a.profile_steps}
 
+    # ---- PCG iteration time: whole projection (RHS, matrix, solve, correction) / iterations, 3 extra steps ------------
+    pcg_ms = None
+    if a.profile_steps > 0:
+        P.solve_ms = []
+        n0 = len(P.iterations)
+        for _ in range(3):
+            P.step()
+        its = sum(P.iterations[n0:])
+        pcg_ms = {"ms_per_iteration": sum(P.solve_ms) / max(its, 1), "solve_ms_per_step": sum(P.solve_ms) / 3.0, "iterations_per_step": its / 3.0,
+                  "what": "mf_solve_pressure (MakeRhs + matrix + PCG incl. one V-cycle per iteration + correctVelocity) divided by the PCG iterations"}
+        P.solve_ms = None
+
     # ---- e2e: host buffers, copies inside the timed region -------------------------------------------------------
     e2e = None
     if not a.no_e2e:
@@ -414,8 +436,8 @@ def main():
                "ms_per_step": 1e3 * dev_s / a.steps, "higher_is_better": True, "scaling": "strong" if (a.strong and world > 1) else "weak", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic", "config": config, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
                "roofline": roofline, "cpu_baseline": cpu, "pcg_iterations": iters,
-               "pcg_ms_per_iteration": None, "wall_ms_per_step": 1e3 * wall / a.steps, "kernels": kernels[:14],
-               "device_barriers_per_step": (L.mf_solver_barrier_count(s._h) / float(max(a.warmup, 3) + a.steps + a.profile_steps + (0 if a.no_e2e else max(2, min(a.steps, 10)) + 2 + max(2, min(a.steps, 3))))) if world > 1 else 0}
+               "pcg_ms_per_iteration": pcg_ms, "wall_ms_per_step": 1e3 * wall / a.steps, "kernels": kernels[:14],
+               "device_barriers_per_step": (L.mf_solver_barrier_count(s._h) / float(max(a.warmup, 3) + a.steps + a.profile_steps + (3 if a.profile_steps > 0 else 0) + (0 if a.no_e2e else max(2, min(a.steps, 10)) + 2 + max(2, min(a.steps, 3))))) if world > 1 else 0}
         print(json.dumps(out))
     del P
     s = None

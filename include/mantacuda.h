@@ -186,6 +186,16 @@ int          mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* f
                                const mf_pressure_params* p, mf_solve_info* info);            /* :482 */
 int          mf_release_mg(mf_solver* s);                                                    /* :252 */
 
+/* ---- simple extrapolation (source/fastmarch.cpp) -- SURVEY 8(f) rank 2 ------------------------------------------------ */
+/* extrapolateMACSimple(flags, vel, distance=4, phiObs=NULL, intoObs=false), fastmarch.cpp:337 */
+int          mf_extrapolate_mac_simple(const mf_grid* flags, mf_grid* vel, int distance, const mf_grid* phiObs, int intoObs);
+/* extrapolateMACFromWeight(vel, weight, distance=2), fastmarch.cpp:410 (the weight grid is overwritten) */
+int          mf_extrapolate_mac_from_weight(mf_grid* vel, mf_grid* weight, int distance);
+/* extrapolateLsSimple(phi, distance=4, inside=false, include_walls=false), fastmarch.cpp:471 */
+int          mf_extrapolate_ls_simple(mf_grid* phi, int distance, int inside, int include_walls);
+/* extrapolateVec3Simple(vel, phi, distance=4, inside=false), fastmarch.cpp:525 */
+int          mf_extrapolate_vec3_simple(mf_grid* vel, const mf_grid* phi, int distance, int inside);
+
 /* pieces of the solver exposed for kernel-level parity tests */
 int          mf_make_laplace_matrix(const mf_grid* flags, mf_grid* A0, mf_grid* Ai, mf_grid* Aj, mf_grid* Ak,
                                     const mf_grid* fractions);          /* conjugategrad.h:154 */

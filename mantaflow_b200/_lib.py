@@ -103,6 +103,10 @@ SIGNATURES = {
     "mf_correct_velocity": (_i, [_P, _P, _P, C.POINTER(PressureParams)]),
     "mf_solve_pressure": (_i, [_P, _P, _P, C.POINTER(PressureParams), C.POINTER(SolveInfo)]),
     "mf_release_mg": (_i, [_P]),
+    "mf_extrapolate_mac_simple": (_i, [_P, _P, _i, _P, _i]),
+    "mf_extrapolate_mac_from_weight": (_i, [_P, _P, _i]),
+    "mf_extrapolate_ls_simple": (_i, [_P, _i, _i, _i]),
+    "mf_extrapolate_vec3_simple": (_i, [_P, _P, _i, _i]),
     "mf_make_laplace_matrix": (_i, [_P, _P, _P, _P, _P, _P]),
     "mf_apply_matrix": (_i, [_P, _P, _P, _P, _P, _P, _P]),
     "mf_apply_laplace_rowcode": (_i, [_P, _P, _P]),

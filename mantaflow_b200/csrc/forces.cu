@@ -242,13 +242,6 @@ __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restri
   }
 }
 
-__device__ __forceinline__ void normalize3(float& x, float& y, float& z) {   // vectorbase.h:421-434
-  const float l = x * x + y * y + z * z;
-  if (fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) { /* unit length */ }
-  else if (l > 1e-6f * 1e-6f) { const float nrm = sqrtf(l); const float inv = (float)(1. / (double)nrm); x *= inv; y *= inv; z *= inv; }
-  else { x = y = z = 0.f; }
-}
-
 // KnSetWallBcsFrac (extforces.cpp:240-323): writes velTarget for every cell
 __global__ void __launch_bounds__(256) k_set_wall_bcs_frac(Geo g, const int* __restrict__ flags, CV3 vel, V3 tgt, const float* __restrict__ phiObs) {
   IJK_FROM_BLOCK

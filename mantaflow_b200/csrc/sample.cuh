@@ -160,4 +160,12 @@ __device__ __forceinline__ float interpolCubic(const float* __restrict__ d, cons
   return cubicInterp<VEC>(zI, zp[0], zp[1], zp[2], zp[3]);
 }
 
+// normalize(Vec3&) (vectorbase.h:421-434): 1./norm is a double, rounded to Real before the multiply
+__device__ __forceinline__ void normalize3(float& x, float& y, float& z) {   // vectorbase.h:421-434
+  const float l = x * x + y * y + z * z;
+  if (fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) { /* unit length */ }
+  else if (l > 1e-6f * 1e-6f) { const float nrm = sqrtf(l); const float inv = (float)(1. / (double)nrm); x *= inv; y *= inv; z *= inv; }
+  else { x = y = z = 0.f; }
+}
+
 } // namespace mf

@@ -5,6 +5,7 @@ setWallBcs / addBuoyancy / addGravity / setInflowBcs / setOpenBound / resetOutfl
 computePressureRhs / solvePressureSystem / correctVelocity / solvePressure / releaseMG  source/plugin/pressure.cpp
 cgSolveDiffusion  source/conjugategrad.cpp:350
 gridMaxDiff / gridMaxDiffInt / gridMaxDiffVec3  source/grid.cpp:437-467
+extrapolateMACSimple / extrapolateMACFromWeight / extrapolateLsSimple / extrapolateVec3Simple  source/fastmarch.cpp:337-553
 """
 import ctypes as C
 
@@ -14,7 +15,7 @@ from ._lib import lib, check, MantaError, PressureParams, SolveInfo
 __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "addGravityNoScale", "setInflowBcs",
            "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
-           "getSolveInfo"]
+           "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple"]
 
 
 def _h(g):
@@ -205,3 +206,35 @@ def _maxDiff(g1, g2):
 def gridMaxDiff(g1, g2): return _maxDiff(g1, g2)
 def gridMaxDiffInt(g1, g2): return _maxDiff(g1, g2)
 def gridMaxDiffVec3(g1, g2): return _maxDiff(g1, g2)
+
+
+# ---- simple extrapolation (source/fastmarch.cpp) ---------------------------------------------------------------------
+@M._plugin
+def extrapolateMACSimple(flags=None, vel=None, distance=4, phiObs=None, intoObs=False, **kwargs):
+    M._checkArgs("extrapolateMACSimple", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "extrapolateMACSimple")
+    _req(vel, M.MACGrid, "vel", "extrapolateMACSimple")
+    check(lib().mf_extrapolate_mac_simple(flags._h, vel._h, int(distance), _h(phiObs), 1 if intoObs else 0))
+
+
+@M._plugin
+def extrapolateMACFromWeight(vel=None, weight=None, distance=2, **kwargs):
+    M._checkArgs("extrapolateMACFromWeight", kwargs, ())
+    _req(vel, M.MACGrid, "vel", "extrapolateMACFromWeight")
+    _req(weight, M.VecGrid, "weight", "extrapolateMACFromWeight")
+    check(lib().mf_extrapolate_mac_from_weight(vel._h, weight._h, int(distance)))
+
+
+@M._plugin
+def extrapolateLsSimple(phi=None, distance=4, inside=False, include_walls=False, **kwargs):
+    M._checkArgs("extrapolateLsSimple", kwargs, ())
+    _req(phi, M.RealGrid, "phi", "extrapolateLsSimple")
+    check(lib().mf_extrapolate_ls_simple(phi._h, int(distance), 1 if inside else 0, 1 if include_walls else 0))
+
+
+@M._plugin
+def extrapolateVec3Simple(vel=None, phi=None, distance=4, inside=False, **kwargs):
+    M._checkArgs("extrapolateVec3Simple", kwargs, ())
+    _req(vel, M.VecGrid, "vel", "extrapolateVec3Simple")
+    _req(phi, M.RealGrid, "phi", "extrapolateVec3Simple")
+    check(lib().mf_extrapolate_vec3_simple(vel._h, phi._h, int(distance), 1 if inside else 0))

@@ -58,6 +58,18 @@ def gen_fractions(size, seed):
     return f.astype(np.float32)
 
 
+def gen_weight(size, seed):
+    """Vec3 weights as left by mapPartsToMAC: positive in a blob, exactly 0 elsewhere"""
+    r = np.random.RandomState(seed)
+    nx, ny, nz = size
+    x, y, z = _coords(size)
+    w = np.zeros((nz, ny, nx, 3), np.float32)
+    for c in range(3):
+        blob = ((x - nx * (0.4 + 0.05 * c)) ** 2 + (y - ny * 0.45) ** 2 + (z - nz * 0.5) ** 2) < (0.27 * min(nx, ny, max(nz, ny))) ** 2
+        w[..., c] = np.where(blob, 0.1 + 3 * r.rand(nz, ny, nx), 0.0)
+    return w
+
+
 def gen_flags_liquid(size, fill=0.55, dim=3):
     """walls on the border, fluid below a height, empty above, one obstacle block"""
     nx, ny, nz = size
@@ -311,3 +323,33 @@ _PLUME_STEP_MG = [op if op[1] != "solvePressure" else ["call", "solvePressure", 
 CASES["plume3d_mg"] = {"size": [24, 32, 20], "dim": 3, "dt": 1.0, "grids": dict(BASEGRIDS), "load": [], "inputs": {},
                        "ops": DOMAIN + [["repeat", 15, _PLUME_STEP_MG]], "save": ["density", "vel"], "exact": False,
                        "abs_tol": {"density": 1e-3, "vel": 5e-3}}
+
+
+# ---- simple extrapolation plugins (fastmarch.cpp:337-553), SURVEY 8(f) rank 2: bit-exact ------------------------------
+def _ex_case(size, dim, call, kw, load, inputs, save, grids):
+    g = dict(BASEGRIDS); g.update(grids)
+    return {"size": size, "dim": dim, "dt": 1.0, "grids": g, "load": load, "inputs": inputs, "ops": [["call", call, kw]], "save": save, "exact": True}
+
+
+CASES["extrap_mac_simple"] = _ex_case(S3, 3, "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel"}, ["vel", "flags"],
+                                      {"vel": ["gen_vel", 120, 1.0, 3], "flags": ["gen_flags_liquid"]}, ["vel"], {})
+CASES["extrap_mac_simple_d2"] = _ex_case(S3, 3, "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel", "distance": 2}, ["vel", "flags"],
+                                         {"vel": ["gen_vel", 121, 1.0, 3], "flags": ["gen_flags_liquid", 0.35]}, ["vel"], {})
+CASES["extrap_mac_intoobs_phi"] = _ex_case(S3, 3, "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel", "distance": 3, "phiObs": "@phiObs", "intoObs": True},
+                                           ["vel", "flags", "phiObs"],
+                                           {"vel": ["gen_vel", 122, 1.0, 3], "flags": ["gen_flags_liquid"], "phiObs": ["gen_phi_sphere", 7.0, 6.5, 6.0, 3.4]},
+                                           ["vel"], {"phiObs": "LevelsetGrid"})
+CASES["extrap_mac_simple_2d"] = _ex_case(S2, 2, "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel", "distance": 5}, ["vel", "flags"],
+                                         {"vel": ["gen_vel", 123, 1.0, 2], "flags": ["gen_flags_liquid", 0.5, 2]}, ["vel"], {})
+CASES["extrap_mac_weight"] = _ex_case(S3, 3, "extrapolateMACFromWeight", {"vel": "@vel", "weight": "@weight", "distance": 3}, ["vel", "weight"],
+                                      {"vel": ["gen_vel", 124, 1.0, 3], "weight": ["gen_weight", 125]}, ["vel", "weight"], {"weight": "VecGrid"})
+CASES["extrap_mac_weight_2d"] = _ex_case(S2, 2, "extrapolateMACFromWeight", {"vel": "@vel", "weight": "@weight"}, ["vel", "weight"],
+                                         {"vel": ["gen_vel", 126, 1.0, 2], "weight": ["gen_weight", 127]}, ["vel", "weight"], {"weight": "VecGrid"})
+CASES["extrap_ls_simple"] = _ex_case(S3, 3, "extrapolateLsSimple", {"phi": "@phi", "distance": 5}, ["phi"],
+                                     {"phi": ["gen_phi_sphere", 8.0, 10.5, 7.0, 3.7]}, ["phi"], {"phi": "LevelsetGrid"})
+CASES["extrap_ls_inside_walls"] = _ex_case(S3, 3, "extrapolateLsSimple", {"phi": "@phi", "distance": 3, "inside": True, "include_walls": True}, ["phi"],
+                                           {"phi": ["gen_phi_sphere", 8.0, 10.5, 7.0, 5.2]}, ["phi"], {"phi": "LevelsetGrid"})
+CASES["extrap_ls_simple_2d"] = _ex_case(S2, 2, "extrapolateLsSimple", {"phi": "@phi", "distance": 4, "inside": True}, ["phi"],
+                                        {"phi": ["gen_phi_sphere", 12.0, 9.5, 0.5, 5.5]}, ["phi"], {"phi": "LevelsetGrid"})
+CASES["extrap_vec3_simple"] = _ex_case(S3, 3, "extrapolateVec3Simple", {"vel": "@vec", "phi": "@phi", "distance": 4}, ["vec", "phi"],
+                                       {"vec": ["gen_vec", 128], "phi": ["gen_phi_sphere", 8.0, 10.5, 7.0, 3.7]}, ["vec"], {"vec": "VecGrid", "phi": "LevelsetGrid"})

@@ -12,7 +12,7 @@ if [ "$N" -ge 8 ]; then
 timeout 300 $TR --nproc-per-node 8 --master-port 29542 tools/dist_cases.py --out gpurun_out/${TAG}_cases8.json \
   plume3d_mg > gpurun_out/${TAG}_cases8.log 2>&1; echo "cases8 rc=$?"
 fi
-timeout 600 $TR --nproc-per-node $N --master-port 29543 bench.py --gpus $N --steps 10 --warmup 5 \
+timeout 600 $TR --nproc-per-node $N --master-port 29543 bench.py --gpus $N --steps 10 --warmup 5 --kernels-out gpurun_out/${TAG}_weak${N}_kernels.json \
   > gpurun_out/${TAG}_weak${N}.json 2> gpurun_out/${TAG}_weak${N}.log; echo "weak rc=$?"; tail -c 1500 gpurun_out/${TAG}_weak${N}.json
 timeout 900 $TR --nproc-per-node $N --master-port 29544 bench.py --gpus $N --steps 5 --warmup 3 --size 1024 --strong --no-e2e \
   > gpurun_out/${TAG}_strong1024_${N}.json 2> gpurun_out/${TAG}_strong1024_${N}.log; echo "strong rc=$?"; tail -c 1500 gpurun_out/${TAG}_strong1024_${N}.json
