@@ -186,6 +186,24 @@ int          mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* f
                                const mf_pressure_params* p, mf_solve_info* info);            /* :482 */
 int          mf_release_mg(mf_solver* s);                                                    /* :252 */
 
+/* ---- scene-setup plugins that run inside the step loop -- SURVEY 8(f) rank 1 ---------------------------------------------- */
+enum { MF_SHAPE_BOX = 0, MF_SHAPE_SPHERE = 1, MF_SHAPE_CYLINDER = 2 };
+/* Box: a = p0, b = p1.  Sphere: a = center, b = scale, r = radius.  Cylinder: a = center, b = z (axis, its length is the half
+ * height, normalised by the library as Cylinder::Cylinder does), r = radius.          source/shapes.h:93,120,139 */
+typedef struct mf_shape { int type; float a[3]; float b[3]; float r; } mf_shape;
+/* Shape::applyToGrid(grid, value, respectFlags=NULL), shapes.cpp:72: int grids take ivalue, Real grids vx, Vec3 / MAC grids
+ * (vx, vy, vz) */
+int          mf_shape_apply(const mf_shape* shape, mf_grid* grid, float vx, float vy, float vz, int ivalue, const mf_grid* respectFlags);
+/* Shape::computeLevelset() / generateLevelset(phi), shapes.cpp:29 (BoxSDF :178, SphereSDF :309, CylinderSDF :367) */
+int          mf_shape_levelset(const mf_shape* shape, mf_grid* phi);
+int          mf_flags_update_from_levelset(mf_grid* flags, const mf_grid* levelset);     /* grid.cpp:910 */
+int          mf_levelset_join(mf_grid* a, const mf_grid* b);                             /* levelset.cpp:111 */
+/* updateFractions(flags, phiObs, fractions, boundaryWidth=0, fracThreshold=0.01), plugin/initplugins.cpp:437 */
+int          mf_update_fractions(const mf_grid* flags, const mf_grid* phiObs, mf_grid* fractions, int boundaryWidth, float fracThreshold);
+/* setObstacleFlags(flags, phiObs, fractions=NULL, phiOut=NULL, phiIn=NULL, boundaryWidth=1), plugin/initplugins.cpp:473 */
+int          mf_set_obstacle_flags(mf_grid* flags, const mf_grid* phiObs, const mf_grid* fractions, const mf_grid* phiOut,
+                                   const mf_grid* phiIn, int boundaryWidth);
+
 /* ---- simple extrapolation (source/fastmarch.cpp) -- SURVEY 8(f) rank 2 ------------------------------------------------ */
 /* extrapolateMACSimple(flags, vel, distance=4, phiObs=NULL, intoObs=false), fastmarch.cpp:337 */
 int          mf_extrapolate_mac_simple(const mf_grid* flags, mf_grid* vel, int distance, const mf_grid* phiObs, int intoObs);

@@ -23,6 +23,10 @@ class PressureParams(C.Structure):
     ]
 
 
+class ShapeDesc(C.Structure):          # mf_shape
+    _fields_ = [("type", C.c_int), ("a", C.c_float * 3), ("b", C.c_float * 3), ("r", C.c_float)]
+
+
 class SolveInfo(C.Structure):
     _fields_ = [("iterations", C.c_int), ("resNorm", C.c_float), ("maxIter", C.c_int), ("fixedCell", C.c_int),
                 ("mgLevels", C.c_int), ("mgRebuilt", C.c_int)]
@@ -103,6 +107,12 @@ SIGNATURES = {
     "mf_correct_velocity": (_i, [_P, _P, _P, C.POINTER(PressureParams)]),
     "mf_solve_pressure": (_i, [_P, _P, _P, C.POINTER(PressureParams), C.POINTER(SolveInfo)]),
     "mf_release_mg": (_i, [_P]),
+    "mf_shape_apply": (_i, [_P, _P, _f, _f, _f, _i, _P]),
+    "mf_shape_levelset": (_i, [_P, _P]),
+    "mf_flags_update_from_levelset": (_i, [_P, _P]),
+    "mf_levelset_join": (_i, [_P, _P]),
+    "mf_update_fractions": (_i, [_P, _P, _P, _i, _f]),
+    "mf_set_obstacle_flags": (_i, [_P, _P, _P, _P, _P, _i]),
     "mf_extrapolate_mac_simple": (_i, [_P, _P, _i, _P, _i]),
     "mf_extrapolate_mac_from_weight": (_i, [_P, _P, _i]),
     "mf_extrapolate_ls_simple": (_i, [_P, _i, _i, _i]),

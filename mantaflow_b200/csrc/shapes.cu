@@ -1,0 +1,300 @@
+// shapes.cu -- scene-setup plugins that run inside the step loop of the reference's scenes, SURVEY 8(f) rank 1:
+// Shape::applyToGrid / computeLevelset for Box, Sphere, Cylinder (source/shapes.cpp: ApplyShapeToGrid :40, ApplyShapeToMACGrid :62,
+// Box::isInside :151, BoxSDF :178, Sphere::isInside :240, SphereSDF :309, Cylinder::isInside :324, CylinderSDF :367),
+// FlagGrid::updateFromLevelset (grid.cpp:910), LevelsetGrid::join (levelset.cpp:108), updateFractions / setObstacleFlags
+// (plugin/initplugins.cpp:437, :473).  Float expressions keep the reference's order (the library is built with -fmad=false).
+#include "common.cuh"
+#include "sample.cuh"
+#include <cmath>
+
+namespace mf {
+
+#define IJK_ALL \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x; \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y; \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0; \
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return; \
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+
+struct ShapeD { int type; float a[3]; float b[3]; float r; float zlen; };   // see mf_shape; zlen = |z| of a cylinder (b normalised)
+
+__device__ __forceinline__ float vnorm(float x, float y, float z) {          // norm(Vec3), vectorbase.h:385-389
+  const float l = x * x + y * y + z * z;
+  if (l <= 1e-6f * 1e-6f) return 0.f;
+  return (fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) ? 1.f : sqrtf(l);
+}
+__device__ __forceinline__ float fmax2(float a, float b) { return (a < b) ? b : a; }   // std::max
+__device__ __forceinline__ float fmin2(float a, float b) { return (b < a) ? b : a; }   // std::min
+
+__device__ __forceinline__ bool shapeInside(const ShapeD& s, float px, float py, float pz) {
+  if (s.type == MF_SHAPE_BOX)
+    return px >= s.a[0] && py >= s.a[1] && pz >= s.a[2] && px <= s.b[0] && py <= s.b[1] && pz <= s.b[2];
+  if (s.type == MF_SHAPE_SPHERE) {
+    const float x = (px - s.a[0]) / s.b[0], y = (py - s.a[1]) / s.b[1], z = (pz - s.a[2]) / s.b[2];
+    return x * x + y * y + z * z <= s.r * s.r;
+  }
+  const float dx = px - s.a[0], dy = py - s.a[1], dz = pz - s.a[2];
+  const float z = dx * s.b[0] + dy * s.b[1] + dz * s.b[2];
+  if (fabsf(z) > s.zlen) return false;
+  const float r2 = (dx * dx + dy * dy + dz * dz) - z * z;
+  return r2 < s.r * s.r;
+}
+
+// ApplyShapeToGrid<T>: NC components of a cell-centred grid (int / Real / Vec3)
+template <class T, int NC>
+__global__ void __launch_bounds__(256) k_shape_apply(Geo g, ShapeD s, T* __restrict__ d, long long np, T v0, T v1, T v2, const int* __restrict__ respect) {
+  IJK_ALL
+  if (respect && fIsObstacle(respect[idx])) return;
+  if (!shapeInside(s, i + 0.5f, j + 0.5f, k + 0.5f)) return;
+  d[idx] = v0;
+  if (NC == 3) { d[idx + np] = v1; d[idx + 2 * np] = v2; }
+}
+// ApplyShapeToMACGrid: each face tested at its own position
+__global__ void __launch_bounds__(256) k_shape_apply_mac(Geo g, ShapeD s, V3 d, float vx, float vy, float vz, const int* __restrict__ respect) {
+  IJK_ALL
+  if (respect && fIsObstacle(respect[idx])) return;
+  if (shapeInside(s, (float)i, j + 0.5f, k + 0.5f)) d.x[idx] = vx;
+  if (shapeInside(s, i + 0.5f, (float)j, k + 0.5f)) d.y[idx] = vy;
+  if (shapeInside(s, i + 0.5f, j + 0.5f, (float)k)) d.z[idx] = vz;
+}
+// BoxSDF / SphereSDF / CylinderSDF
+__global__ void __launch_bounds__(256) k_shape_sdf(Geo g, ShapeD s, float* __restrict__ phi) {
+  IJK_ALL
+  const float px = i + 0.5f, py = j + 0.5f, pz = k + 0.5f;
+  float out;
+  if (s.type == MF_SHAPE_SPHERE) {
+    out = vnorm((px - s.a[0]) / s.b[0], (py - s.a[1]) / s.b[1], (pz - s.a[2]) / s.b[2]) - s.r;
+  } else if (s.type == MF_SHAPE_CYLINDER) {
+    const float dx = px - s.a[0], dy = py - s.a[1], dz = pz - s.a[2];
+    const float z = fabsf(dx * s.b[0] + dy * s.b[1] + dz * s.b[2]);
+    const float r = sqrtf((dx * dx + dy * dy + dz * dz) - z * z);
+    if (z < s.zlen) out = (r < s.r) ? fmax2(r - s.r, z - s.zlen) : r - s.r;
+    else if (r < s.r) out = fabsf(z - s.zlen);
+    else { const float a = z - s.zlen, b = r - s.r; out = sqrtf(a * a + b * b); }
+  } else {
+    const float x1 = s.a[0], y1 = s.a[1], z1 = s.a[2], x2 = s.b[0], y2 = s.b[1], z2 = s.b[2];
+    const bool inx = px <= x2 && px >= x1, iny = py <= y2 && py >= y1, inz = pz <= z2 && pz >= z1;
+    auto sq = [](float a) { return a * a; };
+    if (inx && iny && inz) {
+      const float mx = fmax2(px - x2, x1 - px), my = fmax2(py - y2, y1 - py);
+      float mz = fmax2(pz - z2, z1 - pz);
+      if (!g.is3D) mz = mx;
+      out = fmax2(mx, fmax2(my, mz));
+    } else if (iny && inz) out = fmax2(px - x2, x1 - px);
+    else if (inx && inz) out = fmax2(py - y2, y1 - py);
+    else if (inx && iny) out = fmax2(pz - z2, z1 - pz);
+    else if (px > x1 && px < x2) {
+      const float m1 = sqrtf(sq(y1 - py) + sq(z1 - pz)), m2 = sqrtf(sq(y2 - py) + sq(z1 - pz));
+      const float m3 = sqrtf(sq(y1 - py) + sq(z2 - pz)), m4 = sqrtf(sq(y2 - py) + sq(z2 - pz));
+      out = fmin2(m1, fmin2(m2, fmin2(m3, m4)));
+    } else if (py > y1 && py < y2) {
+      const float m1 = sqrtf(sq(x1 - px) + sq(z1 - pz)), m2 = sqrtf(sq(x2 - px) + sq(z1 - pz));
+      const float m3 = sqrtf(sq(x1 - px) + sq(z2 - pz)), m4 = sqrtf(sq(x2 - px) + sq(z2 - pz));
+      out = fmin2(m1, fmin2(m2, fmin2(m3, m4)));
+    } else if (pz > x1 && pz < z2) {        // sic: the reference compares p.z with p1.x (shapes.cpp:208)
+      const float m1 = sqrtf(sq(y1 - py) + sq(x1 - px)), m2 = sqrtf(sq(y2 - py) + sq(x1 - px));
+      const float m3 = sqrtf(sq(y1 - py) + sq(x2 - px)), m4 = sqrtf(sq(y2 - py) + sq(x2 - px));
+      out = fmin2(m1, fmin2(m2, fmin2(m3, m4)));
+    } else {
+      float m = vnorm(px - x1, py - y1, pz - z1);
+      m = fmin2(m, vnorm(px - x1, py - y1, pz - z2));
+      m = fmin2(m, vnorm(px - x1, py - y2, pz - z1));
+      m = fmin2(m, vnorm(px - x1, py - y2, pz - z2));
+      m = fmin2(m, vnorm(px - x2, py - y1, pz - z1));
+      m = fmin2(m, vnorm(px - x2, py - y1, pz - z2));
+      m = fmin2(m, vnorm(px - x2, py - y2, pz - z1));
+      m = fmin2(m, vnorm(px - x2, py - y2, pz - z2));
+      out = m;
+    }
+  }
+  phi[idx] = out;
+}
+
+// FlagGrid::updateFromLevelset (grid.cpp:910-920); invalidTimeValue() = -1000 (fastmarch.h:134)
+__global__ void __launch_bounds__(256) k_flags_from_levelset(Geo g, int* __restrict__ flags, const float* __restrict__ phi) {
+  IJK_ALL
+  int f = flags[idx];
+  if (fIsObstacle(f) || fIsOutflow(f)) return;
+  const float p = phi[idx];
+  if (p <= -1000.f) return;
+  f &= ~(MF_EMPTY | MF_FLUID);
+  f |= (p <= 0.f) ? MF_FLUID : MF_EMPTY;
+  flags[idx] = f;
+}
+// KnJoin (levelset.cpp:108): a = min(a, b)
+__global__ void __launch_bounds__(256) k_ls_join(Geo g, float* __restrict__ a, const float* __restrict__ b) {
+  IJK_ALL
+  a[idx] = fmin2(a[idx], b[idx]);
+}
+
+// calcFraction (initplugins.cpp:356-370)
+__device__ __forceinline__ float calcFraction(float phi1, float phi2, float fracThreshold) {
+  if (phi1 > 0.f && phi2 > 0.f) return 1.f;
+  if (phi1 < 0.f && phi2 < 0.f) return 0.f;
+  if (phi2 < phi1) { const float t = phi1; phi1 = phi2; phi2 = t; }
+  const float denom = phi1 - phi2;
+  if ((double)denom > -1e-04) return 0.5f;
+  float frac = (float)(1. - (double)(phi1 / denom));
+  if (frac < fracThreshold) frac = 0.f;
+  return fmin2(1.f, frac);
+}
+__device__ __forceinline__ bool fOpenish(int f) { return (f & (MF_INFLOW | MF_OUTFLOW | MF_OPEN)) != 0; }
+// KnUpdateFractions (initplugins.cpp:372-434), restated for the reference's SERIAL ijk order: a cell's "max side" writes go to
+// the next cell along that axis, which is visited later and overwrites them unless it lies on the domain border (bnd = 1 skips
+// it) -- so only border targets keep them.  The cell's own values: calcFraction, then 1 if a "min side" condition holds.
+__global__ void __launch_bounds__(256) k_update_fractions(Geo g, const int* __restrict__ flags, const float* __restrict__ phi, V3 fr, int w, float thr) {
+  IJK_ALL
+  const long long Y = g.nx, Z = g.Z;
+  const bool interior = i >= 1 && j >= 1 && i < g.nx - 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+  if (interior) {
+    const float p = phi[idx];
+    float fx = calcFraction(p, phi[idx - 1], thr), fy = calcFraction(p, phi[idx - Y], thr), fz = g.is3D ? calcFraction(p, phi[idx - Z], thr) : 0.f;
+    if (!(p < 0.f)) {
+      bool one = false;
+      if (i <= w + 1 && fOpenish(flags[idx - 1])) one = true;
+      if (j <= w + 1 && fOpenish(flags[idx - Y])) one = true;
+      if (g.is3D && k <= w + 1 && fOpenish(flags[idx - Z])) one = true;
+      if (one) { fx = 1.f; fy = 1.f; if (g.is3D) fz = 1.f; }
+    }
+    fr.x[idx] = fx; fr.y[idx] = fy; fr.z[idx] = fz;
+    return;
+  }
+  // border cell: 0 (setConst), or 1 when the interior neighbour below it along an axis has a "max side" hit
+  float v = 0.f;
+  auto srcOk = [&](int si, int sj, int sk) {   // the writing cell must be interior, outside the obstacle, and satisfy its range test
+    const bool in = si >= 1 && sj >= 1 && si < g.nx - 1 && sj < g.ny - 1 && (!g.is3D || (sk >= 1 && sk < g.nz - 1));
+    if (!in) return false;
+    return !(phi[(long long)si + Y * sj + (long long)g.nx * g.ny * sk] < 0.f);
+  };
+  const bool openHere = fOpenish(flags[idx]);
+  if (openHere) {
+    if (i >= 1 && srcOk(i - 1, j, k) && (i - 1) >= g.nx - w - 2) v = 1.f;                 // max x: source (i-1,j,k) tests flags(i,j,k)
+    if (j >= 1 && srcOk(i, j - 1, k) && (j - 1) >= g.ny - w - 2) v = 1.f;                 // max y
+    if (g.is3D && k >= 1 && srcOk(i, j, k - 1) && j >= g.nz - w - 2) v = 1.f;             // max z (sic: the reference tests j, :423)
+  }
+  fr.x[idx] = v; fr.y[idx] = v; fr.z[idx] = g.is3D ? v : 0.f;
+}
+// KnUpdateFlagsObs (initplugins.cpp:441-468), bnd = boundaryWidth
+__global__ void __launch_bounds__(256) k_set_obstacle_flags(Geo g, int* __restrict__ flags, CV3 fr, int haveFr, const float* __restrict__ phiObs,
+                                                            const float* __restrict__ phiOut, const float* __restrict__ phiIn, int bnd) {
+  IJK_ALL
+  if (i < bnd || j < bnd || i >= g.nx - bnd || j >= g.ny - bnd || (g.is3D && (k < bnd || k >= g.nz - bnd))) return;
+  bool isObs = false;
+  if (haveFr) {
+    float f = 0.f;
+    f += fr.x[idx]; f += fr.x[idx + 1]; f += fr.y[idx]; f += fr.y[idx + g.nx];
+    if (g.is3D) { f += fr.z[idx]; f += fr.z[idx + g.Z]; }
+    if (f == 0.f) isObs = true;
+  } else if (phiObs[idx] < 0.f) isObs = true;
+  const bool isOut = phiOut && phiOut[idx] < 0.f, isIn = phiIn && phiIn[idx] < 0.f;
+  int f;
+  if (isObs) f = MF_OBSTACLE;
+  else if (isIn) f = MF_FLUID | MF_INFLOW;
+  else if (isOut) f = MF_EMPTY | MF_OUTFLOW;
+  else f = MF_EMPTY;
+  flags[idx] = f;
+}
+
+static ShapeD shapeOf(const mf_shape* sh) {
+  mfAssert(sh, "Shape: null shape");
+  mfAssert(sh->type == MF_SHAPE_BOX || sh->type == MF_SHAPE_SPHERE || sh->type == MF_SHAPE_CYLINDER, "Shape: unknown shape type " << sh->type);
+  ShapeD d; d.type = sh->type; d.r = sh->r; d.zlen = 0.f;
+  for (int c = 0; c < 3; c++) { d.a[c] = sh->a[c]; d.b[c] = sh->b[c]; }
+  if (sh->type == MF_SHAPE_CYLINDER) {
+    // Cylinder ctor: mZDir = z; mZ = normalize(mZDir)  (shapes.cpp:316-322, vectorbase.h:421-434)
+    float zx = d.b[0], zy = d.b[1], zz = d.b[2];
+    const float l = zx * zx + zy * zy + zz * zz;
+    if (std::fabs((double)l - 1.) < (double)(1e-6f * 1e-6f)) d.zlen = 1.f;
+    else if (l > 1e-6f * 1e-6f) { d.zlen = std::sqrt(l); const float inv = (float)(1. / (double)d.zlen); zx *= inv; zy *= inv; zz *= inv; }
+    else { zx = zy = zz = 0.f; d.zlen = 0.f; }
+    d.b[0] = zx; d.b[1] = zy; d.b[2] = zz;
+  }
+  return d;
+}
+
+} // namespace mf
+
+using namespace mf;
+
+extern "C" {
+
+int mf_shape_apply(const mf_shape* sh, mf_grid* gp, float vx, float vy, float vz, int ivalue, const mf_grid* respectFlags) {
+  MF_API_BEGIN
+  mfAssert(gp, "Shape::applyToGrid: argument 'grid' is missing");
+  if (respectFlags) REQ_GRID(respectFlags, G(respectFlags)->isInt(), "respectFlags", "Shape::applyToGrid");
+  Grid* gr = G(gp); Solver* s = gr->s; s->use();
+  const ShapeD d = shapeOf(sh);
+  const int* rf = respectFlags ? G(respectFlags)->di() : nullptr;
+  if (gr->isInt()) { gr->outflowState = -1; MF_LAUNCH_IJK(s, (k_shape_apply<int, 1>), d, gr->di(), 0LL, ivalue, 0, 0, rf); }
+  else if (gr->isReal()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 1>), d, gr->d, 0LL, vx, 0.f, 0.f, rf);
+  else if (gr->isMAC()) MF_LAUNCH_IJK(s, k_shape_apply_mac, d, v3(gr), vx, vy, vz, rf);
+  else if (gr->isVec()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 3>), d, gr->d, s->Np, vx, vy, vz, rf);
+  else mfErr("Shape::applyToGrid(): unknown grid type");
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_shape_levelset(const mf_shape* sh, mf_grid* phi) {
+  MF_API_BEGIN
+  REQ_GRID(phi, G(phi)->isReal(), "phi", "Shape::computeLevelset");
+  Grid* gr = G(phi); Solver* s = gr->s; s->use();
+  const ShapeD d = shapeOf(sh);
+  MF_LAUNCH_IJK(s, k_shape_sdf, d, gr->d);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_flags_update_from_levelset(mf_grid* flags, const mf_grid* phi) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "FlagGrid::updateFromLevelset");
+  REQ_GRID(phi, G(phi)->isReal(), "levelset", "FlagGrid::updateFromLevelset");
+  Grid* f = G(flags); Solver* s = f->s; s->use();
+  check_same_solver(f, G(phi), "FlagGrid::updateFromLevelset");
+  f->outflowState = -1;
+  MF_LAUNCH_IJK(s, k_flags_from_levelset, f->di(), G(phi)->d);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_levelset_join(mf_grid* a, const mf_grid* b) {
+  MF_API_BEGIN
+  REQ_GRID(a, G(a)->isReal(), "this", "LevelsetGrid::join");
+  REQ_GRID(b, G(b)->isReal(), "o", "LevelsetGrid::join");
+  Grid* ga = G(a); Solver* s = ga->s; s->use();
+  check_same_solver(ga, G(b), "LevelsetGrid::join");
+  MF_LAUNCH_IJK(s, k_ls_join, ga->d, G(b)->d);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_update_fractions(const mf_grid* flags, const mf_grid* phiObs, mf_grid* fractions, int boundaryWidth, float fracThreshold) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "updateFractions");
+  REQ_GRID(phiObs, G(phiObs)->isReal(), "phiObs", "updateFractions");
+  REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "updateFractions");
+  const Grid* f = G(flags); Solver* s = f->s; s->use();
+  check_same_solver(f, G(phiObs), "updateFractions"); check_same_solver(f, G(fractions), "updateFractions");
+  mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "updateFractions: grid too small");
+  MF_LAUNCH_IJK(s, k_update_fractions, f->di(), G(phiObs)->d, v3(G(fractions)), boundaryWidth, fracThreshold);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+int mf_set_obstacle_flags(mf_grid* flags, const mf_grid* phiObs, const mf_grid* fractions, const mf_grid* phiOut, const mf_grid* phiIn, int boundaryWidth) {
+  MF_API_BEGIN
+  REQ_GRID(flags, G(flags)->isInt(), "flags", "setObstacleFlags");
+  REQ_GRID(phiObs, G(phiObs)->isReal(), "phiObs", "setObstacleFlags");
+  if (fractions) REQ_GRID(fractions, G(fractions)->isMAC(), "fractions", "setObstacleFlags");
+  if (phiOut) REQ_GRID(phiOut, G(phiOut)->isReal(), "phiOut", "setObstacleFlags");
+  if (phiIn) REQ_GRID(phiIn, G(phiIn)->isReal(), "phiIn", "setObstacleFlags");
+  Grid* f = G(flags); Solver* s = f->s; s->use();
+  check_same_solver(f, G(phiObs), "setObstacleFlags");
+  f->outflowState = -1;
+  CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
+  MF_LAUNCH_IJK(s, k_set_obstacle_flags, f->di(), fr, fractions ? 1 : 0, G(phiObs)->d, phiOut ? G(phiOut)->d : (const float*)nullptr,
+                phiIn ? G(phiIn)->d : (const float*)nullptr, boundaryWidth);
+  MF_LAUNCH_CHECK();
+  MF_API_END
+}
+
+} // extern "C"

@@ -463,6 +463,10 @@ class RealGrid(GridBase):
 class LevelsetGrid(RealGrid):
     _type = _TYPE_REAL | _TYPE_LEVELSET
 
+    def join(self, o):
+        """levelset union (levelset.cpp:111)"""
+        check(lib().mf_levelset_join(self._h, o._h))
+
 
 class IntGrid(GridBase):
     _type = _TYPE_INT
@@ -509,6 +513,10 @@ class FlagGrid(IntGrid):
     def fillGrid(self, type=TypeFluid):
         check(lib().mf_flags_fill_grid(self._h, int(type)))
 
+    def updateFromLevelset(self, levelset):
+        """fluid / empty from the sign of a levelset (grid.cpp:910)"""
+        check(lib().mf_flags_update_from_levelset(self._h, levelset._h))
+
     def countCells(self, flag, bnd=0, mask=None):
         out = C.c_int()
         check(lib().mf_flags_count_cells(self._h, int(flag), int(bnd), C.byref(out)))
@@ -517,11 +525,51 @@ class FlagGrid(IntGrid):
 
 # ---- shapes used by the config scenes (source/shapes.cpp) -------------------------------------------------
 class Shape(object):
+    """Shape base (source/shapes.h:27): applyToGrid / computeLevelset run on the device"""
+    _kind = -1
+
     def __init__(self, parent):
         self.parent = parent
 
+    def _desc(self):
+        raise MantaError("Shape: abstract")
+
+    def _struct(self):
+        from ._lib import ShapeDesc
+        a, b, r = self._desc()
+        d = ShapeDesc()
+        d.type = self._kind
+        d.a[0], d.a[1], d.a[2] = float(a.x), float(a.y), float(a.z)
+        d.b[0], d.b[1], d.b[2] = float(b.x), float(b.y), float(b.z)
+        d.r = float(r)
+        return d
+
+    def applyToGrid(self, grid=None, value=0, respectFlags=None, **kwargs):
+        _checkArgs("Shape::applyToGrid", kwargs, ())
+        if grid is None:
+            raise MantaError("Argument 'grid' is not defined.")
+        d = self._struct()
+        rf = respectFlags._h if respectFlags is not None else None
+        if isinstance(grid, IntGrid):
+            check(lib().mf_shape_apply(C.byref(d), grid._h, 0.0, 0.0, 0.0, int(value), rf))
+        elif isinstance(grid, RealGrid):
+            check(lib().mf_shape_apply(C.byref(d), grid._h, float(value), 0.0, 0.0, 0, rf))
+        elif isinstance(grid, VecGrid):
+            v = _v3(value)
+            check(lib().mf_shape_apply(C.byref(d), grid._h, float(v.x), float(v.y), float(v.z), 0, rf))
+        else:
+            raise MantaError("Shape::applyToGrid(): unknown grid type")
+
+    def computeLevelset(self):
+        phi = LevelsetGrid(self.parent)
+        d = self._struct()
+        check(lib().mf_shape_levelset(C.byref(d), phi._h))
+        return phi
+
 
 class Box(Shape):
+    _kind = 0
+
     def __init__(self, parent, center=None, p0=None, p1=None, size=None, **kwargs):
         _checkArgs("Box", kwargs, ())
         Shape.__init__(self, parent)
@@ -532,28 +580,33 @@ class Box(Shape):
         else:
             raise MantaError("Box: specify either p0,p1 or size,center")
 
-    def applyToGrid(self, grid, value=0, respectFlags=None):
-        a, b = self.p0, self.p1
-        if isinstance(grid, IntGrid):
-            check(lib().mf_apply_box_to_flags(grid._h, float(a.x), float(a.y), float(a.z), float(b.x), float(b.y), float(b.z), int(value)))
-        elif isinstance(grid, RealGrid):
-            check(lib().mf_apply_box_to_real(grid._h, float(a.x), float(a.y), float(a.z), float(b.x), float(b.y), float(b.z), float(value)))
-        else:
-            raise MantaError("Shape::applyToGrid(): unknown grid type")
+    def _desc(self):
+        return self.p0, self.p1, 0.0
+
+
+class Sphere(Shape):
+    _kind = 1
+
+    def __init__(self, parent, center=None, radius=None, scale=None, **kwargs):
+        _checkArgs("Sphere", kwargs, ())
+        Shape.__init__(self, parent)
+        self.center, self.radius = _v3(center), np.float32(radius)
+        self.scale = _v3(scale) if scale is not None else vec3(1, 1, 1)
+
+    def _desc(self):
+        return self.center, self.scale, self.radius
 
 
 class Cylinder(Shape):
+    _kind = 2
+
     def __init__(self, parent, center=None, radius=None, z=None, **kwargs):
         _checkArgs("Cylinder", kwargs, ())
         Shape.__init__(self, parent)
         self.center, self.radius, self.z = _v3(center), np.float32(radius), _v3(z)
 
-    def applyToGrid(self, grid, value=0, respectFlags=None):
-        if not isinstance(grid, RealGrid):
-            raise MantaError("Shape::applyToGrid(): unknown grid type")
-        c, z = self.center, self.z
-        check(lib().mf_apply_cylinder_to_real(grid._h, float(c.x), float(c.y), float(c.z), float(self.radius),
-                                              float(z.x), float(z.y), float(z.z), float(value)))
+    def _desc(self):
+        return self.center, self.z, self.radius
 
 
 from .plugins import *  # noqa: E402,F401,F403  (plugin functions of the hot path)

@@ -6,6 +6,7 @@ computePressureRhs / solvePressureSystem / correctVelocity / solvePressure / rel
 cgSolveDiffusion  source/conjugategrad.cpp:350
 gridMaxDiff / gridMaxDiffInt / gridMaxDiffVec3  source/grid.cpp:437-467
 extrapolateMACSimple / extrapolateMACFromWeight / extrapolateLsSimple / extrapolateVec3Simple  source/fastmarch.cpp:337-553
+updateFractions / setObstacleFlags  source/plugin/initplugins.cpp:437,473
 """
 import ctypes as C
 
@@ -15,7 +16,8 @@ from ._lib import lib, check, MantaError, PressureParams, SolveInfo
 __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "addGravityNoScale", "setInflowBcs",
            "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
-           "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple"]
+           "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
+           "updateFractions", "setObstacleFlags"]
 
 
 def _h(g):
@@ -238,3 +240,21 @@ def extrapolateVec3Simple(vel=None, phi=None, distance=4, inside=False, **kwargs
     _req(vel, M.VecGrid, "vel", "extrapolateVec3Simple")
     _req(phi, M.RealGrid, "phi", "extrapolateVec3Simple")
     check(lib().mf_extrapolate_vec3_simple(vel._h, phi._h, int(distance), 1 if inside else 0))
+
+
+# ---- obstacle fractions / flags from levelsets (source/plugin/initplugins.cpp) -----------------------------------------
+@M._plugin
+def updateFractions(flags=None, phiObs=None, fractions=None, boundaryWidth=0, fracThreshold=0.01, **kwargs):
+    M._checkArgs("updateFractions", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "updateFractions")
+    _req(phiObs, M.RealGrid, "phiObs", "updateFractions")
+    _req(fractions, M.MACGrid, "fractions", "updateFractions")
+    check(lib().mf_update_fractions(flags._h, phiObs._h, fractions._h, int(boundaryWidth), float(fracThreshold)))
+
+
+@M._plugin
+def setObstacleFlags(flags=None, phiObs=None, fractions=None, phiOut=None, phiIn=None, boundaryWidth=1, **kwargs):
+    M._checkArgs("setObstacleFlags", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "setObstacleFlags")
+    _req(phiObs, M.RealGrid, "phiObs", "setObstacleFlags")
+    check(lib().mf_set_obstacle_flags(flags._h, phiObs._h, _h(fractions), _h(phiOut), _h(phiIn), int(boundaryWidth)))

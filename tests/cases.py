@@ -353,3 +353,57 @@ CASES["extrap_ls_simple_2d"] = _ex_case(S2, 2, "extrapolateLsSimple", {"phi": "@
                                         {"phi": ["gen_phi_sphere", 12.0, 9.5, 0.5, 5.5]}, ["phi"], {"phi": "LevelsetGrid"})
 CASES["extrap_vec3_simple"] = _ex_case(S3, 3, "extrapolateVec3Simple", {"vel": "@vec", "phi": "@phi", "distance": 4}, ["vec", "phi"],
                                        {"vec": ["gen_vec", 128], "phi": ["gen_phi_sphere", 8.0, 10.5, 7.0, 3.7]}, ["vec"], {"vec": "VecGrid", "phi": "LevelsetGrid"})
+
+
+# ---- scene-setup plugins inside the step loop: shapes, levelset flags, fractions -- bit-exact ----------
+_BOX = {"p0": V(4.3, 5.1, 3.2), "p1": V(11.6, 12.4, 9.9)}
+_BOX2 = {"p0": V(6.2, 4.4, 0), "p1": V(15.7, 12.3, 1)}
+_SPH = {"center": V(8.3, 10.2, 6.7), "radius": 4.1}
+_SPHS = {"center": V(8.3, 10.2, 6.7), "radius": 3.3, "scale": V(1.0, 1.7, 0.8)}
+_CYL = {"center": V(8.3, 10.2, 6.7), "radius": 3.1, "z": V(0.6, 2.0, 0.9)}
+
+
+def _shape_case(size, dim, ops, save, grids, load=(), inputs=None):
+    g = dict(BASEGRIDS); g.update(grids)
+    return {"size": size, "dim": dim, "dt": 1.0, "grids": g, "load": list(load), "inputs": inputs or {}, "ops": ops, "save": save, "exact": True}
+
+
+CASES["shape_box_sdf"] = _shape_case(S3, 3, [["shape_ls", "Box", _BOX, "phi"]], ["phi"], {"phi": "LevelsetGrid"})
+CASES["shape_box_sdf_2d"] = _shape_case(S2, 2, [["shape_ls", "Box", _BOX2, "phi"]], ["phi"], {"phi": "LevelsetGrid"})
+CASES["shape_sphere_sdf"] = _shape_case(S3, 3, [["shape_ls", "Sphere", _SPHS, "phi"]], ["phi"], {"phi": "LevelsetGrid"})
+CASES["shape_cylinder_sdf"] = _shape_case(S3, 3, [["shape_ls", "Cylinder", _CYL, "phi"]], ["phi"], {"phi": "LevelsetGrid"})
+CASES["shape_apply_mix"] = _shape_case(S3, 3, DOMAIN + OBST3 + [
+    ["shape", "Sphere", _SPH, "applyToGrid", {"grid": "@density", "value": 0.75, "respectFlags": "@flags"}],
+    ["shape", "Sphere", _SPHS, "applyToGrid", {"grid": "@vel", "value": V(0.5, -1.5, 2.5)}],
+    ["shape", "Cylinder", _CYL, "applyToGrid", {"grid": "@vec", "value": V(1.0, 2.0, 3.0), "respectFlags": "@flags"}],
+    ["shape", "Cylinder", _CYL, "applyToGrid", {"grid": "@flags", "value": 4}],
+    ["shape", "Box", _BOX, "applyToGrid", {"grid": "@pressure", "value": -2.0}],
+    ["shape", "Box", {"center": V(9, 11, 7), "size": V(3.5, 2.5, 4.5)}, "applyToGrid", {"grid": "@vel", "value": V(7.0, 8.0, 9.0), "respectFlags": "@flags"}]],
+    ["density", "vel", "vec", "flags", "pressure"], {"vec": "VecGrid"}, load=["vel"], inputs={"vel": ["gen_vel", 130, 1.0, 3]})
+CASES["flags_from_levelset"] = _shape_case(S3, 3, [
+    ["method", "flags", "initDomain", {"boundaryWidth": 0, "outflow": "Y"}], ["method", "flags", "fillGrid", {}]] + OBST3 + [
+    ["shape_ls", "Sphere", _SPH, "phi"], ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(18, 5.5, 14)}, "phi2"],
+    ["method", "phi", "join", {"o": "@phi2"}],
+    ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}]],
+    ["flags", "phi"], {"phi": "LevelsetGrid", "phi2": "LevelsetGrid"})
+_FRAC_OPS = [["method", "flags", "initDomain", {"boundaryWidth": 0, "open": "xY", "inflow": "Z", "outflow": "y"}], ["method", "flags", "fillGrid", {}],
+             ["shape_ls", "Sphere", _SPH, "phiObs"]]
+CASES["update_fractions"] = _shape_case(S3, 3, _FRAC_OPS + [
+    ["call", "updateFractions", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions"}]],
+    ["fractions"], {"phiObs": "LevelsetGrid", "fractions": "MACGrid"})
+CASES["update_fractions_bw1"] = _shape_case(S3, 3, [["method", "flags", "initDomain", {"boundaryWidth": 1, "open": "XyzZ"}], ["method", "flags", "fillGrid", {}],
+    ["shape_ls", "Box", _BOX, "phiObs"],
+    ["call", "updateFractions", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions", "boundaryWidth": 1, "fracThreshold": 0.2}]],
+    ["fractions"], {"phiObs": "LevelsetGrid", "fractions": "MACGrid"})
+CASES["update_fractions_2d"] = _shape_case(S2, 2, [["method", "flags", "initDomain", {"boundaryWidth": 0, "open": "XY"}], ["method", "flags", "fillGrid", {}],
+    ["shape_ls", "Sphere", {"center": V(12.4, 9.7, 0.5), "radius": 4.2}, "phiObs"],
+    ["call", "updateFractions", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions"}]],
+    ["fractions"], {"phiObs": "LevelsetGrid", "fractions": "MACGrid"})
+CASES["set_obstacle_flags"] = _shape_case(S3, 3, _FRAC_OPS + [
+    ["call", "updateFractions", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions"}],
+    ["shape_ls", "Box", {"p0": V(0, 18.5, 0), "p1": V(18, 22, 14)}, "phiOut"], ["shape_ls", "Cylinder", _CYL, "phiIn"],
+    ["call", "setObstacleFlags", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions", "phiOut": "@phiOut", "phiIn": "@phiIn"}]],
+    ["flags"], {"phiObs": "LevelsetGrid", "fractions": "MACGrid", "phiOut": "LevelsetGrid", "phiIn": "LevelsetGrid"})
+CASES["set_obstacle_flags_phi"] = _shape_case(S3, 3, DOMAIN + [["shape_ls", "Sphere", _SPHS, "phiObs"],
+    ["call", "setObstacleFlags", {"flags": "@flags", "phiObs": "@phiObs", "boundaryWidth": 2}]],
+    ["flags"], {"phiObs": "LevelsetGrid"})

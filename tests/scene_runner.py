@@ -68,6 +68,10 @@ def _run_ops(ops, grids, api, solver, log):
             shp = api[op[1]](parent=solver, **ckw)
             kw = {k: _resolve(v, grids, api) for k, v in op[4].items()}
             getattr(shp, op[3])(**kw)
+        elif kind == "shape_ls":   # ["shape_ls", "Sphere", {ctor kwargs}, "phi"]: phi.copyFrom(shape.computeLevelset())
+            ckw = {k: _resolve(v, grids, api) for k, v in op[2].items()}
+            shp = api[op[1]](parent=solver, **ckw)
+            grids[op[3]].copyFrom(shp.computeLevelset())
         elif kind == "repeat":
             for _ in range(op[1]):
                 _run_ops(op[2], grids, api, solver, log)
