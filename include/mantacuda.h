@@ -230,6 +230,9 @@ int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float al
 int          mf_mg_info(mf_solver* s, int* levels, int* usedHostFallback);
 /* size3[0..2] = vertex counts of level l; returns non-zero if there is no such level */
 int          mf_mg_level_size(mf_solver* s, int l, int* size3);
+/* *bytesPerEntry = storage width of level l's operator on the device: 2 (level 0: 16-bit row code; level 1: binary16 when every
+ * entry converts exactly) or 4 (float) */
+int          mf_mg_level_format(mf_solver* s, int l, int* bytesPerEntry);
 /* type: n bytes of GridMg::VertexType; A: n*stencil floats in the reference's interleaved order mA[l][v*stencil+e] */
 int          mf_mg_download_level(mf_solver* s, int l, void* type, void* A);
 /* GridMg(size); setA(A0..Ak); setCoarsestLevelAccuracy(acc); setSmoothing(1,1); setRhs(rhs); doVCycle(dst)

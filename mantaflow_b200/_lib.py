@@ -123,6 +123,7 @@ SIGNATURES = {
     "mf_cg_solve_diffusion": (_i, [_P, _P, _f, _f, _f]),
     "mf_mg_info": (_i, [_P, C.POINTER(_i), C.POINTER(_i)]),
     "mf_mg_level_size": (_i, [_P, _i, C.POINTER(_i)]),
+    "mf_mg_level_format": (_i, [_P, _i, C.POINTER(_i)]),
     "mf_mg_download_level": (_i, [_P, _i, _P, _P]),
     "mf_mg_vcycle": (_i, [_P, _P, _P, _P, _P, _P, _P, _f]),
 }

@@ -17,6 +17,7 @@
 // Arithmetic (summation order, float products) is the reference's; only the storage order differs.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include "reduce.cuh"
 
 namespace mf {
@@ -34,6 +35,8 @@ struct LvlD {
   float* A; float* x; float* b; float* r;
   unsigned char* type;
   const unsigned short* code;   // level 0 only: compact operator (or nullptr)
+  unsigned bxMagic;    // blocked: ceil(2^32 / (PX-2)), see mgBlockThread
+  const __half* Ah; long long ash;   // blocked levels: the operator in binary16 when every entry converts exactly (else nullptr)
 };
 
 struct MgDims { int is3D; int dim; int SS; int SS0; int zmin; int zmax; };   // mStencilSize, mStencilSize0, mStencilMin/Max.z
@@ -58,6 +61,10 @@ __device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, 
   const int c = q % L.NC; const int lz = q / L.NC - L.zoff;
   x = 2 * lx + (c & 1); y = 2 * ly + ((c >> 1) & 1); z = 2 * lz + ((c >> 2) & 1);
   return lx >= 0 && ly >= 0 && lz >= 0 && x < L.sx && y < L.sy && z < L.sz;
+}
+// all-zero row (inactive vertex or padding) of a blocked level: the diagonal is 0
+__device__ __forceinline__ bool mgRowZero(const LvlD& L, int p) {
+  return L.Ah ? (__half_as_ushort(L.Ah[p]) & 0x7fffu) == 0 : L.A[p] == 0.f;
 }
 // setup kernels walk the storage range [p0, p1) (a rank's share of the level)
 #define MG_P_FROM_THREAD(L) \
@@ -259,70 +266,74 @@ __global__ void __launch_bounds__(256) k_mg_residual0(LvlD L, MgDims D, float tr
 }
 
 // ---- levels > 0 (27-point, 14 stored), colour-blocked -----------------------------------------------------
-// Every operation is a device function of a linear work index t, so that it can run as its own grid (one t per thread) or
-// inside the single-CTA kernel that walks several small levels (t strides over the CTA).
-// storage position of work item t among the vertices of colour c in the lz range [lz0, lz1); returns false outside
+// The sweeps are instruction-issue and latency bound (one vertex = 27 coefficient loads, 27 loads of x, 54 dependent float
+// operations), so the address arithmetic is taken out of them: the host tabulates, per colour and stencil term, the byte offsets
+// of the coefficient and of the neighbour's x relative to the vertex' own entries (MgOff1, a kernel parameter: the offsets are
+// constant-bank operands of one 64-bit add per load).
+struct MgOff1 { long long xo[27]; long long ao[27]; };   // terms in the reference's order (dz, dy, dx ascending)
+struct MgOff8 { MgOff1 t[8]; };
 struct BlkPos { int p; int lx, ly, lz; };
-__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int lz1, int t, BlkPos& q) {
+// work item -> storage position among the vertices of colour c: blockIdx.y = z pair (from lz0), t = position in the pair's
+// BX x BY block of the colour (t / BX by multiplication: t * BX < 2^32)
+__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int t, BlkPos& q) {
   const int BX = L.PX - 2, BY = L.PY - 2;
-  q.lx = t % BX; const int u = t / BX; q.ly = u % BY; q.lz = lz0 + u / BY;
-  if (q.lz >= lz1) return false;
+  if (t >= BX * BY) return false;
+  q.ly = (BX == 1) ? t : (int)__umulhi((unsigned)t, L.bxMagic);
+  q.lx = t - q.ly * BX; q.lz = lz0 + blockIdx.y;
   q.p = (((q.lz + L.zoff) * L.NC + c) * L.PY + q.ly + 1) * L.PX + q.lx + 1;
   return true;
 }
-// b - sum A x over the stencil in the reference's order (dz, dy, dx ascending; multigrid.cpp:691-706, :755-770).
-// x is read through a plain pointer: the bottom-levels kernel writes x between sweeps of the same launch.
-template <bool IS3D, bool WITH_CENTER>
-__device__ __forceinline__ float mgStencilSub(const LvlD& L, int c, int p, float sum) {
-  constexpr int SS = IS3D ? 14 : 5;
-  const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
-  const int PXY = L.PX * L.PY;
-  const float* __restrict__ A = L.A; const float* x = L.x;
-  int s = 0;
+// b - sum A x over the stencil in the reference's order (multigrid.cpp:691-706, :755-770); ap / xp = the vertex' own entries of
+// operator plane 0 and of x.  The lower half of the stencil is read from the neighbours' rows (symmetric storage).
+template <bool IS3D, bool WITH_CENTER, bool HALF>
+__device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const char* xp, const MgOff1& o, float sum) {
+  constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
 #pragma unroll
-  for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
-#pragma unroll
-    for (int dy = -1; dy <= 1; dy++)
-#pragma unroll
-      for (int dx = -1; dx <= 1; dx++, s++) {
-        if (s == SS - 1) { if (WITH_CENTER) sum -= A[p] * x[p]; continue; }
-        const int ncx = (cx + dx) & 1, ncy = (cy + dy) & 1, ncz = (cz + dz) & 1;
-        const int nc = ncx | (ncy << 1) | (ncz << 2);
-        const int pn = p + ((cz + dz) >> 1) * L.NC * PXY + (nc - c) * PXY + ((cy + dy) >> 1) * L.PX + ((cx + dx) >> 1);
-        const float a = (s < SS) ? A[(SS - 1 - s) * L.as + pn] : A[(s - SS + 1) * L.as + p];
-        sum -= a * x[pn];
-      }
+  for (int s = 0; s < NS; s++) {
+    if (s == SS - 1 && !WITH_CENTER) continue;
+    const float a = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
+    sum -= a * *reinterpret_cast<const float*>(xp + o.xo[s]);
+  }
   return sum;
 }
+template <bool HALF> __device__ __forceinline__ const char* mgRowPtr(const LvlD& L, int p) {
+  return HALF ? reinterpret_cast<const char*>(L.Ah + p) : reinterpret_cast<const char*>(L.A + p);
+}
 // knSmoothColor, l > 0: one vertex of one of the 8 (4) colours (multigrid.cpp:668-711)
-template <bool IS3D>
-__device__ __forceinline__ void mgSmoothItem(const LvlD& L, int c, int lz0, int lz1, int t) {
+template <bool IS3D, bool HALF>
+__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0) {
+  MF_PDL_PROLOGUE
   BlkPos q;
-  if (!mgBlockThread(L, c, lz0, lz1, t, q)) return;
+  if (!mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
   // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
   // reference's own division below would not be finite
-  const float diag = L.A[q.p];
+  const char* ap = mgRowPtr<HALF>(L, q.p);
+  const float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
   if (diag == 0.f) return;
-  const float sum = mgStencilSub<IS3D, false>(L, c, q.p, L.b[q.p]);
+  const float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
   L.x[q.p] = sum / diag;
 }
-template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, int c, int lz0, int lz1) {
-  MF_PDL_PROLOGUE
-  mgSmoothItem<IS3D>(L, c, lz0, lz1, blockIdx.x * blockDim.x + threadIdx.x);
-}
-// knCalcResidual, l > 0
-template <bool IS3D>
-__device__ __forceinline__ void mgResidualItem(const LvlD& L, int c, int lz0, int lz1, int t) {
+// knCalcResidual, l > 0; blockIdx.z = colour
+template <bool IS3D, bool HALF, int C>
+__device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, int lz0) {
   BlkPos q;
-  if (!mgBlockThread(L, c, lz0, lz1, t, q)) return;
+  if (!mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
   // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
-  L.r[q.p] = mgStencilSub<IS3D, true>(L, c, q.p, L.b[q.p]);
+  L.r[q.p] = mgStencilSub<IS3D, true, HALF>(mgRowPtr<HALF>(L, q.p), reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
 }
-template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, int lz0, int lz1) {   // blockIdx.y = colour
+template <bool IS3D, bool HALF>
+__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0) {
   MF_PDL_PROLOGUE
-  mgResidualItem<IS3D>(L, blockIdx.y, lz0, lz1, blockIdx.x * blockDim.x + threadIdx.x);
+  switch (blockIdx.z) {       // the colour selects compile-time positions in the offset table
+    case 0: mgResidualItem<IS3D, HALF, 0>(L, O, lz0); break;
+    case 1: mgResidualItem<IS3D, HALF, 1>(L, O, lz0); break;
+    case 2: mgResidualItem<IS3D, HALF, 2>(L, O, lz0); break;
+    case 3: mgResidualItem<IS3D, HALF, 3>(L, O, lz0); break;
+    case 4: if (IS3D) mgResidualItem<IS3D, HALF, 4>(L, O, lz0); break;
+    case 5: if (IS3D) mgResidualItem<IS3D, HALF, 5>(L, O, lz0); break;
+    case 6: if (IS3D) mgResidualItem<IS3D, HALF, 6>(L, O, lz0); break;
+    default: if (IS3D) mgResidualItem<IS3D, HALF, 7>(L, O, lz0); break;
+  }
 }
 
 // knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472).  Work items run over the natural
@@ -334,7 +345,7 @@ __device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int
   if (vz >= z1) return;
   const int v = mgIdx(C, vx, vy, vz);
   C.x[v] = 0.f;
-  if (C.A[v] == 0.f) return;          // inactive coarse vertex (all-zero row): b stays 0
+  if (mgRowZero(C, v)) return;        // inactive coarse vertex (all-zero row): b stays 0
   float sum = 0.f;
   const float* fr = F.r;
   if (F.perm) {
@@ -371,7 +382,7 @@ __device__ __forceinline__ void mgInterpAddItem(const LvlD& F, const LvlD& C, in
   const int vx = t % F.sx; const int u = t / F.sx; const int vy = u % F.sy, vz = z0 + u / F.sy;
   if (vz >= z1) return;
   const int v = mgIdx(F, vx, vy, vz);
-  if (F.perm ? (F.A[v] == 0.f) : (F.type[v] == vtInactive)) return;
+  if (F.perm ? mgRowZero(F, v) : (F.type[v] == vtInactive)) return;
   float sum = 0.f;
   const float* cx = C.x;
   for (int z = vz / 2; z <= (vz + 1) / 2; z++)
@@ -471,6 +482,21 @@ __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D, i
     }
   }
   for (int e = 0; e < SS; e++) C.A[e * C.as + v] = acc[e];
+}
+
+// binary16 copy of a blocked level's operator; *inexact is set when an entry does not survive the round trip.  The level-1
+// Galerkin operator of a 0 / -1 / small-integer Laplacian consists of multiples of 1/64 below 32 and converts exactly.
+__global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* __restrict__ Ah, int* __restrict__ inexact, int p0, int p1) {
+  const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= p1) return;
+  bool bad = false;
+  for (int e = 0; e < D.SS; e++) {
+    const float a = L.A[e * L.as + p];
+    const __half h = __float2half_rn(a);
+    bad |= !(__half2float(h) == a);
+    Ah[e * L.ash + p] = h;
+  }
+  if (bad) *inexact = 1;
 }
 
 } // namespace mf

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float tri
             if (2 * K >= c0 && 2 * K < c1 && K >= cz0 && K < cz1) {
               const int v = mgIdx(C, CX0 + X, CY0 + Y, K);
               C.x[v] = 0.f;
-              if (C.A[v] != 0.f) C.b[v] = a;                       // inactive coarse vertex (all-zero row): b stays 0
+              if (!mgRowZero(C, v)) C.b[v] = a;                       // inactive coarse vertex (all-zero row): b stays 0
             }
             a = 0.f;
 #pragma unroll

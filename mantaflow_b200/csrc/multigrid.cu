@@ -27,6 +27,8 @@ struct MgHierarchy {
   int usedFallback;
   bool pendingSolo;         // a group of rank-0-only launches has not been followed by a cross-rank barrier yet
   std::vector<std::vector<int>> pairSplit;   // blocked level l: rank r sweeps z pairs [pairSplit[l][r], pairSplit[l][r+1])
+  std::vector<MgOff8> offs;                  // blocked level l: stencil offset tables of the sweeps (buildOffsets)
+  __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when exact)
 };
 
 // ---- partition of a level over the ranks ----------------------------------------------------------------------
@@ -232,9 +234,9 @@ static void buildPaths(MgHierarchy* mg) {
 
 // stride (in floats) between operator planes: every plane is split over the GPUs by z like the vectors, so on a distributed
 // solver a plane covers a whole number of allocation granules
-static long long planeStride(const Solver* s, long long n) {
+static long long planeStride(const Solver* s, long long n, size_t elem = sizeof(float)) {
   if (!(s->comm && !comm_emulated(s->comm))) return n;
-  const long long unit = (long long)(comm_granularity(s->comm) / sizeof(float));
+  const long long unit = (long long)(comm_granularity(s->comm) / elem);
   return (n + unit - 1) / unit * unit;
 }
 
@@ -246,7 +248,35 @@ static void setLayout(LvlD& L, int sx, int sy, int sz, bool is3D, bool blocked) 
   const long long na = blocked ? (long long)L.PZ * L.NC * L.PY * L.PX : (long long)L.n;
   mfAssert(na * 14 < (1LL << 40) && na < (1LL << 31), "GridMg: level too large for 32-bit vertex indices");
   L.na = (int)na; L.as = na;
-  L.A = L.x = L.b = L.r = nullptr; L.type = nullptr; L.code = nullptr;
+  L.A = L.x = L.b = L.r = nullptr; L.type = nullptr; L.code = nullptr; L.Ah = nullptr; L.ash = 0;
+  const unsigned long long BX = (unsigned long long)(L.PX - 2);
+  L.bxMagic = BX > 1 ? (unsigned)(((1ULL << 32) + BX - 1) / BX) : 0u;
+}
+
+// byte offsets of the stencil terms of a blocked level, per colour (MgOff1); depends on the operator's storage format
+static void buildOffsets(MgHierarchy* mg, int l) {
+  const LvlD& L = mg->lv[l];
+  if ((int)mg->offs.size() <= l) mg->offs.resize(l + 1);
+  MgOff8& O = mg->offs[l];
+  memset(&O, 0, sizeof(O));
+  const bool is3D = mg->D.is3D != 0;
+  const int SS = mg->D.SS;
+  const long long PXY = (long long)L.PX * L.PY;
+  const long long elem = L.Ah ? 2 : 4, as = L.Ah ? L.ash : L.as;
+  for (int c = 0; c < L.NC; c++) {
+    const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
+    int s = 0;
+    for (int dz = is3D ? -1 : 0; dz <= (is3D ? 1 : 0); dz++)
+      for (int dy = -1; dy <= 1; dy++)
+        for (int dx = -1; dx <= 1; dx++, s++) {
+          const int nc = ((cx + dx) & 1) | (((cy + dy) & 1) << 1) | (((cz + dz) & 1) << 2);
+          // floor((c + d) / 2) for c + d in -1..2
+          const long long dp = (long long)((cz + dz + 2) / 2 - 1) * L.NC * PXY + (long long)(nc - c) * PXY
+                             + (long long)((cy + dy + 2) / 2 - 1) * L.PX + ((cx + dx + 2) / 2 - 1);
+          O.t[c].xo[s] = 4 * dp;
+          O.t[c].ao[s] = elem * ((s < SS) ? (SS - 1 - s) * as + dp : (long long)(s - SS + 1) * as);
+        }
+  }
 }
 
 MgHierarchy* mg_create(Solver* s) {
@@ -254,6 +284,7 @@ MgHierarchy* mg_create(Solver* s) {
   MgHierarchy* mg = new MgHierarchy();
   mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
+  mg->half1 = nullptr; mg->ash1 = 0;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
   mg->D.zmin = is3D ? -1 : 0; mg->D.zmax = is3D ? 1 : 0;
@@ -299,6 +330,10 @@ MgHierarchy* mg_create(Solver* s) {
       L.A = (float*)s->galloc(sizeof(float) * (size_t)L.na, mg->D.SS, sizeof(float) * (size_t)L.as, es.data(), 4);
       L.x = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
       L.b = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
+      if (l == 1 && is3D && !getenv("MF_MG_NOHALF")) {
+        mg->ash1 = planeStride(s, L.na, sizeof(__half));
+        mg->half1 = (__half*)s->galloc(sizeof(__half) * (size_t)L.na, mg->D.SS, sizeof(__half) * (size_t)mg->ash1, es.data(), 2);
+      }
     }                                                      // level 0: A (float planes) or code0 are allocated by mg_set_a
     mg->lv.push_back(L);
   };
@@ -327,6 +362,7 @@ void mg_destroy(MgHierarchy* mg) {
     if (l > 0) { s->gfree(L.x); s->gfree(L.b); }
   }
   if (mg->code0) mg->s->gfree(mg->code0);
+  if (mg->half1) mg->s->gfree(mg->half1);
   mg->s->gfree(mg->dFlags); cudaFree(mg->dPaths);
   delete mg;
 }
@@ -336,6 +372,7 @@ void mg_set_coarsest_accuracy(MgHierarchy* mg, float acc) { mg->coarsestAcc = ac
 void mg_set_smoothing(MgHierarchy* mg, int pre, int post) { mg->pre = pre; mg->post = post; }
 int mg_num_levels(const MgHierarchy* mg) { return (int)mg->lv.size(); }
 int mg_used_host_fallback(const MgHierarchy* mg) { return mg->usedFallback; }
+int mg_level_format(const MgHierarchy* mg, int l) { return (l == 0 ? mg->useCode : mg->lv[l].Ah != nullptr) ? 2 : 4; }
 int mg_level_size(const MgHierarchy* mg, int l, int* sx, int* sy, int* sz) {
   if (l < 0 || l >= (int)mg->lv.size()) return 0;
   *sx = mg->lv[l].sx; *sy = mg->lv[l].sy; *sz = mg->lv[l].sz; return mg->lv[l].n;
@@ -496,6 +533,19 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
       else       MG_SETUP(mg, l, k_mg_galerkin1<L0Float>, 128, F, C, mg->D, mg->dPaths, mg->npaths, mg->trivialScale);
     } else MG_SETUP(mg, l, k_mg_galerkin, 128, F, C, mg->D);
     flushGroups(mg);
+    if (l == 1 && mg->half1) {
+      // level 1 carries most of the coarse-level traffic (14 planes, every entry read twice per sweep): keep it in binary16
+      // when that is exact, so that the whole level stays resident in L2 between the sweeps of a V-cycle
+      int* inexact = mg->dFlags + 6;
+      s->clearShared(inexact, sizeof(int));
+      C.Ah = nullptr; C.ash = mg->ash1;
+      MG_SETUP(mg, l, k_mg_pack_half, 256, C, mg->D, mg->half1, inexact);
+      flushGroups(mg);
+      CUDA_CHECK(cudaMemcpyAsync(s->hostInts + 6, inexact, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+      CUDA_CHECK(cudaStreamSynchronize(s->stream));
+      if (s->hostInts[6] == 0) C.Ah = mg->half1;
+    }
+    buildOffsets(mg, l);
   }
   MF_LAUNCH_CHECK();
   mg->aSet = true;
@@ -532,12 +582,14 @@ static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
   for (int c = 0; c < L.NC; c++) {
     const int color = reversed ? L.NC - 1 - c : c;
     beginGroup(mg, solo);
+    const MgOff1& o = mg->offs[l].t[color];
     MF_RANKS(s, r) {
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
-      const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0);
-      if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_smooth<true>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
-      else            { MF_LAUNCH_PDL(s, k_mg_smooth<false>, cdiv(nt, 128), 128, L, color, lz0, lz1); }
+      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2), 128), lz1 - lz0);
+      if (L.Ah)            { MF_LAUNCH_PDL(s, (k_mg_smooth<true, true>), gr, 128, L, o, color, lz0); }
+      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_smooth<true, false>), gr, 128, L, o, color, lz0); }
+      else                 { MF_LAUNCH_PDL(s, (k_mg_smooth<false, false>), gr, 128, L, o, color, lz0); }
     }
     endGroup(mg, solo);
   }
@@ -557,9 +609,11 @@ static void residual(MgHierarchy* mg, int l) {
     } else {
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
-      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2) * (lz1 - lz0), 128), L.NC);
-      if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_residual<true>, gr, 128, L, lz0, lz1); }
-      else            { MF_LAUNCH_PDL(s, k_mg_residual<false>, gr, 128, L, lz0, lz1); }
+      const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2), 128), lz1 - lz0, L.NC);
+      const MgOff8& O = mg->offs[l];
+      if (L.Ah)            { MF_LAUNCH_PDL(s, (k_mg_residual<true, true>), gr, 128, L, O, lz0); }
+      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_residual<true, false>), gr, 128, L, O, lz0); }
+      else                 { MF_LAUNCH_PDL(s, (k_mg_residual<false, false>), gr, 128, L, O, lz0); }
     }
   }
   endGroup(mg, solo);

@@ -19,5 +19,6 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs);
 int  mg_level_size(const MgHierarchy* mg, int l, int* sx, int* sy, int* sz);
 void mg_download_level(MgHierarchy* mg, int l, unsigned char* type, float* A);  // A: n*stencil floats in the reference's interleaved order
 int  mg_used_host_fallback(const MgHierarchy* mg);
+int  mg_level_format(const MgHierarchy* mg, int l);   // bytes per stored operator entry
 
 } // namespace mf

@@ -413,6 +413,14 @@ int mf_mg_level_size(mf_solver* sp, int l, int* size3) {
   mfAssert(mg_level_size(s->mg, l, &size3[0], &size3[1], &size3[2]) > 0, "mf_mg_level_size: no such level");
   MF_API_END
 }
+int mf_mg_level_format(mf_solver* sp, int l, int* bytesPerEntry) {
+  MF_API_BEGIN
+  mfAssert(sp && bytesPerEntry, "mf_mg_level_format: null argument");
+  Solver* s = S(sp);
+  mfAssert(s->mg && l >= 0 && l < mg_num_levels(s->mg), "mf_mg_level_format: no such level");
+  *bytesPerEntry = mg_level_format(s->mg, l);
+  MF_API_END
+}
 int mf_mg_download_level(mf_solver* sp, int l, void* type, void* A) {
   MF_API_BEGIN
   mfAssert(sp, "mf_mg_download_level: null solver");

@@ -150,7 +150,7 @@ VC_SIZES = [(64, 50, 37), (8, 8, 8), (60, 29, 33), (120, 31, 18), (56, 26, 64), 
 @pytest.mark.parametrize("size", VC_SIZES)
 def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     """one V(1,1)-cycle: the z-marching wavefront legs (mg_wave0.cuh), the tiled fused legs (mg_fused0.cuh) and the plain
-    per-colour sweeps give bit-identical results"""
+    per-colour sweeps give bit-identical results; so does the binary16 copy of the level-1 operator (exact by construction)"""
     from mantaflow_b200 import manta
     from mantaflow_b200._lib import lib, check
     rs = np.random.RandomState(21)
@@ -160,8 +160,9 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     f[nz // 2, ny // 2, nx // 2] = EMPTY  # one Dirichlet neighbour keeps the operator regular
     rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
     outs = []
-    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}):
-        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED"):
+    fmt = []
+    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}):
+        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -172,7 +173,14 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
         check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
         check(lib().mf_mg_vcycle(s._h, A0._h, Ai._h, Aj._h, Ak._h, R._h, D._h, 1e-7))
         outs.append(D.to_numpy())
+        b = Ct.c_int(0); nl = Ct.c_int(0); fb = Ct.c_int(0)
+        check(lib().mf_mg_info(s._h, Ct.byref(nl), Ct.byref(fb)))
+        if nl.value > 1:
+            check(lib().mf_mg_level_format(s._h, 1, Ct.byref(b)))
+        fmt.append(b.value)
         manta.releaseMG(s)
+    assert fmt in ([2, 2, 2, 4], [0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
+    assert np.array_equal(outs[3].view(np.int32), outs[2].view(np.int32)), "binary16 level-1 operator changes the V-cycle"
     assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
     assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
     assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
