@@ -236,7 +236,7 @@ int          mf_mg_level_format(mf_solver* s, int l, int* bytesPerEntry);
 /* type: n bytes of GridMg::VertexType; A: n*stencil floats in the reference's interleaved order mA[l][v*stencil+e] */
 int          mf_mg_download_level(mf_solver* s, int l, void* type, void* A);
 /* GridMg(size); setA(A0..Ak); setCoarsestLevelAccuracy(acc); setSmoothing(1,1); setRhs(rhs); doVCycle(dst)
- * -- the hierarchy stays cached on the solver like PcMGStatic's */
+ * -- the hierarchy stays cached on the solver like PcMGStatic's; A0 == NULL re-applies the cached hierarchy (setRhs + doVCycle only) */
 int          mf_mg_vcycle(mf_solver* s, const mf_grid* A0, const mf_grid* Ai, const mf_grid* Aj, const mf_grid* Ak,
                           const mf_grid* rhs, mf_grid* dst, float coarsestAccuracy);
 

@@ -66,6 +66,7 @@ __device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, 
 __device__ __forceinline__ bool mgRowZero(const LvlD& L, int p) {
   return L.Ah ? (__half_as_ushort(L.Ah[p]) & 0x7fffu) == 0 : L.A[p] == 0.f;
 }
+__device__ __forceinline__ float mgDiag(const LvlD& L, int p) { return L.Ah ? __half2float(L.Ah[p]) : L.A[p]; }
 // setup kernels walk the storage range [p0, p1) (a rank's share of the level)
 #define MG_P_FROM_THREAD(L) \
   const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x; \
@@ -339,13 +340,17 @@ __global__ void __launch_bounds__(128) k_mg_residual(LvlD L, const __grid_consta
 // knRestrict (multigrid.cpp:904-927): b_coarse = R r_fine ; also x_coarse = 0 (knSet, :472).  Work items run over the natural
 // coordinates of the coarse level, z range [z0,z1) of the coarse level.  r_fine is 0 at inactive / padding / (level 0:
 // guarded) out-of-grid vertices.
+// fold: the pre-smoothing sweep of colour 0 that follows on x == 0 is x = b / diag (every stencil term is a * 0) -- done here,
+// and the sweep starts at colour 1.
+__device__ __forceinline__ float mgFoldFirst(const LvlD& C, int v, int vx, int vy, int vz, float b, bool fold) {
+  return (fold && ((vx | vy | vz) & 1) == 0) ? b / mgDiag(C, v) : 0.f;
+}
 template <bool IS3D>
-__device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int z0, int z1, int t) {
+__device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int z0, int z1, int t, bool fold) {
   const int vx = t % C.sx; const int u = t / C.sx; const int vy = u % C.sy, vz = z0 + u / C.sy;
   if (vz >= z1) return;
   const int v = mgIdx(C, vx, vy, vz);
-  C.x[v] = 0.f;
-  if (mgRowZero(C, v)) return;        // inactive coarse vertex (all-zero row): b stays 0
+  if (mgRowZero(C, v)) { C.x[v] = 0.f; return; }       // inactive coarse vertex (all-zero row): b stays 0
   float sum = 0.f;
   const float* fr = F.r;
   if (F.perm) {
@@ -370,11 +375,12 @@ __device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int
         }
   }
   C.b[v] = sum;
+  C.x[v] = mgFoldFirst(C, v, vx, vy, vz, sum, fold);
 }
 template <bool IS3D>
-__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1) {
+__global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1, int fold) {
   MF_PDL_PROLOGUE
-  mgRestrictItem<IS3D>(F, C, z0, z1, blockIdx.x * blockDim.x + threadIdx.x);
+  mgRestrictItem<IS3D>(F, C, z0, z1, blockIdx.x * blockDim.x + threadIdx.x, fold != 0);
 }
 // knInterpolate + knAddAssign (multigrid.cpp:934-954, :445-446): x_fine += P x_coarse.  Work items run over the natural
 // coordinates of the fine level, z range [z0,z1) of the fine level; x_coarse is 0 at inactive / padding vertices.

@@ -93,7 +93,7 @@ __device__ __forceinline__ float wvOffdiagAt(const L0Code& op, const L0Code::Row
 // the rank's coarse range [cz0, cz1).  Tiles cover [0, sx] x [0, sy] and the chunks [U0, U1) reach plane sz when the last coarse
 // plane needs it, so the coarse vertices at 2X == sx (even sizes) have an owner too.
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float trivialScale, int firstColor, int U0, int U1, WvSched S,
-                                                  int z0, int z1, int cz0, int cz1) {
+                                                  int z0, int z1, int cz0, int cz1, int foldFirst) {
   MF_PDL_PROLOGUE
   __shared__ float xs[4][WV_RY][WV_RX];
   __shared__ float rs[WV_RY][WV_RX];
@@ -163,8 +163,12 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float tri
             const int K = (q - 1) >> 1;
             if (2 * K >= c0 && 2 * K < c1 && K >= cz0 && K < cz1) {
               const int v = mgIdx(C, CX0 + X, CY0 + Y, K);
-              C.x[v] = 0.f;
-              if (!mgRowZero(C, v)) C.b[v] = a;                       // inactive coarse vertex (all-zero row): b stays 0
+              float x0 = 0.f;
+              if (!mgRowZero(C, v)) {                                  // inactive coarse vertex (all-zero row): b stays 0
+                C.b[v] = a;
+                x0 = mgFoldFirst(C, v, CX0 + X, CY0 + Y, K, a, foldFirst != 0);
+              }
+              C.x[v] = x0;
             }
             a = 0.f;
 #pragma unroll

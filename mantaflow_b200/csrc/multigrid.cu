@@ -571,7 +571,7 @@ static void smooth0(MgHierarchy* mg, bool reversed, bool xzero) {
   }
 }
 
-static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
+static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero, bool firstDone = false) {
   Solver* s = mg->s; s->profTag = l;
   LvlD& L = mg->lv[l];
   if (l == 0) {
@@ -579,7 +579,7 @@ static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero) {
     return;
   }
   const bool solo = lvlSolo(mg, l);
-  for (int c = 0; c < L.NC; c++) {
+  for (int c = firstDone ? 1 : 0; c < L.NC; c++) {     // firstDone: colour 0 was folded into the restriction (mgFoldFirst)
     const int color = reversed ? L.NC - 1 - c : c;
     beginGroup(mg, solo);
     const MgOff1& o = mg->offs[l].t[color];
@@ -619,7 +619,7 @@ static void residual(MgHierarchy* mg, int l) {
   endGroup(mg, solo);
 }
 // coarse level l+1 <- fine level l; the coarse level's partition drives the launch
-static void restrictTo(MgHierarchy* mg, int l) {
+static void restrictTo(MgHierarchy* mg, int l, bool fold) {
   Solver* s = mg->s; s->profTag = l;
   LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
   const bool solo = lvlSolo(mg, l + 1);
@@ -628,8 +628,8 @@ static void restrictTo(MgHierarchy* mg, int l) {
     int z0, z1; lvlPlanes(mg, l + 1, r, z0, z1);
     if (z1 <= z0) continue;
     const long long nt = (long long)C.sx * C.sy * (z1 - z0);
-    if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_restrict<true>, cdiv(nt, 128), 128, F, C, z0, z1); }
-    else            { MF_LAUNCH_PDL(s, k_mg_restrict<false>, cdiv(nt, 128), 128, F, C, z0, z1); }
+    if (mg->D.is3D) { MF_LAUNCH_PDL(s, k_mg_restrict<true>, cdiv(nt, 128), 128, F, C, z0, z1, (int)fold); }
+    else            { MF_LAUNCH_PDL(s, k_mg_restrict<false>, cdiv(nt, 128), 128, F, C, z0, z1, (int)fold); }
   }
   endGroup(mg, solo);
 }
@@ -696,7 +696,7 @@ static WvSched waveSched(const Solver* s, int tx, int ty, int planes, int& total
   S.nq = tiles - (total - S.q * tiles);           // the remaining total - q*tiles tiles get q+1 chunks
   return S;
 }
-static void waveDown0(MgHierarchy* mg) {
+static void waveDown0(MgHierarchy* mg, bool fold) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[0]; LvlD& C = mg->lv[1];
   s->profTag = 0;
@@ -710,7 +710,7 @@ static void waveDown0(MgHierarchy* mg) {
     U0 &= ~1;
     const int tx = (int)cdiv(F.sx + 1, WV_TX), ty = (int)cdiv(F.sy + 1, WD_TY);
     int total; const WvSched S = waveSched(s, tx, ty, U1 - U0, total);
-    MF_LAUNCH_PDL(s, k_mg_down0, total, WV_NT, F, C, mg->trivialScale, 0, U0, U1, S, z0, z1, cz0, cz1);
+    MF_LAUNCH_PDL(s, k_mg_down0, total, WV_NT, F, C, mg->trivialScale, 0, U0, U1, S, z0, z1, cz0, cz1, (int)fold);
   }
   endGroup(mg, false);
 }
@@ -744,16 +744,20 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   }
   // level 0 of the standard V(1,1) cycle in 3-D uses the fused kernels of mg_fused0.cuh.  The down leg keeps x in the level's
   // own array (L0.r) and puts the residual into dst, which is free until the tiled up-leg kernel writes it out of place.
+  // the restriction onto level l also performs the first pre-smoothing sweep of colour 0 there (not on the coarsest level,
+  // whose x is the initial guess of the CG solve)
+  const bool noFold = getenv("MF_MG_NOFOLD") != nullptr;
+  auto foldTo = [&](int l) { return l > 0 && l < maxLevel && mg->pre >= 1 && !noFold; };
   const bool fused0 = mg->D.is3D && maxLevel > 0 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_UNFUSED");
   float* const r0keep = L0.r;
   const bool wave = fused0 && waveOk(mg);
   if (fused0) {
     L0.x = r0keep; L0.r = dst;
-    if (wave) waveDown0(mg);          // both colours, residual and restriction in one pass; the residual stays on chip
+    if (wave) waveDown0(mg, foldTo(1));   // both colours, residual and restriction in one pass; the residual stays on chip
     else {
       if (mg->useCode) fusedPresmooth0<L0Code>(mg); else fusedPresmooth0<L0Float>(mg);
       residual(mg, 0);
-      restrictTo(mg, 0);
+      restrictTo(mg, 0, foldTo(1));
     }
   }
   // (measured and dropped: a single-CTA kernel walking all levels <= 17^3 plus the coarsest CG in one launch, 229 us against
@@ -762,9 +766,9 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   // the latency of a 41-load stencil item)
   const int lb = maxLevel;
   for (int l = fused0 ? 1 : 0; l < lb; l++) {
-    for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0);
+    for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0, i == 0 && foldTo(l));
     residual(mg, l);
-    restrictTo(mg, l);
+    restrictTo(mg, l, foldTo(l + 1));
   }
   {
     const bool solo = s->multi();        // the bottom levels are always handled by rank 0

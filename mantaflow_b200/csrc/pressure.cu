@@ -434,14 +434,16 @@ int mf_mg_vcycle(mf_solver* sp, const mf_grid* A0, const mf_grid* Ai, const mf_g
   MF_API_BEGIN
   mfAssert(sp, "mf_mg_vcycle: null solver");
   Solver* s = S(sp); s->use();
-  REQ_GRID(A0, G(A0)->isReal(), "A0", "mf_mg_vcycle"); REQ_GRID(Ai, G(Ai)->isReal(), "Ai", "mf_mg_vcycle");
-  REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "mf_mg_vcycle"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "mf_mg_vcycle");
   REQ_GRID(rhs, G(rhs)->isReal(), "rhs", "mf_mg_vcycle"); REQ_GRID(dst, G(dst)->isReal(), "dst", "mf_mg_vcycle");
-  release_mg(s);
-  s->mg = mg_create(s);
-  mg_set_a(s->mg, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+  if (A0) {
+    REQ_GRID(A0, G(A0)->isReal(), "A0", "mf_mg_vcycle"); REQ_GRID(Ai, G(Ai)->isReal(), "Ai", "mf_mg_vcycle");
+    REQ_GRID(Aj, G(Aj)->isReal(), "Aj", "mf_mg_vcycle"); REQ_GRID(Ak, G(Ak)->isReal(), "Ak", "mf_mg_vcycle");
+    release_mg(s);
+    s->mg = mg_create(s);
+    mg_set_a(s->mg, G(A0)->d, G(Ai)->d, G(Aj)->d, G(Ak)->d);
+    mg_set_smoothing(s->mg, 1, 1);
+  } else mfAssert(s->mg && mg_is_a_set(s->mg), "mf_mg_vcycle: no cached hierarchy to re-apply (A0 == NULL)");
   mg_set_coarsest_accuracy(s->mg, coarsestAccuracy);
-  mg_set_smoothing(s->mg, 1, 1);
   mg_apply(s->mg, G(dst)->d, G(rhs)->d);
   MF_LAUNCH_CHECK();
   MF_API_END

@@ -161,8 +161,8 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
     outs = []
     fmt = []
-    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}):
-        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF"):
+    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}, {"MF_MG_NOFOLD": "1"}):
+        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF", "MF_MG_NOFOLD"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -179,8 +179,9 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
             check(lib().mf_mg_level_format(s._h, 1, Ct.byref(b)))
         fmt.append(b.value)
         manta.releaseMG(s)
-    assert fmt in ([2, 2, 2, 4], [0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
+    assert fmt in ([2, 2, 2, 4, 2], [0, 0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
     assert np.array_equal(outs[3].view(np.int32), outs[2].view(np.int32)), "binary16 level-1 operator changes the V-cycle"
+    assert np.array_equal(outs[4].view(np.int32), outs[0].view(np.int32)), "folding the first colour-0 sweep into the restriction changes the V-cycle"
     assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
     assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
     assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
