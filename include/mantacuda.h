@@ -225,6 +225,31 @@ int          mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const 
 /* cgSolveDiffusion(flags, grid, alpha, cgMaxIterFac, cgAccuracy), conjugategrad.cpp:350 */
 int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float alpha, float cgMaxIterFac, float cgAccuracy);
 
+/* ---- wavelet noise and noise-driven sources (source/noisefield.h:26-97, source/plugin/initplugins.cpp:26-50) ---- */
+typedef struct mf_noise mf_noise;
+/* the python-visible members of WaveletNoiseField (noisefield.h:49-60); passed with every call, like attribute reads */
+typedef struct mf_noise_params {
+  float posOffset[3]; float posScale[3];
+  float valOffset; float valScale;
+  int clamp; float clampNeg; float clampPos;
+  float timeAnim;
+} mf_noise_params;
+/* WaveletNoiseField(parent, fixedSeed=-1, loadFromFile=false), noisefield.cpp:65-84: seed offset from the seeded stream, the
+ * 3 x 128^3 tile generated once per process (or read from / written to ./waveletNoiseTile.bin when loadFromFile) */
+mf_noise*    mf_noise_create(mf_solver* s, int fixedSeed, int loadFromFile);
+void         mf_noise_destroy(mf_noise* n);
+/* host-only: WaveletNoiseField::generateTile (noisefield.cpp:97-181) into out[3 * 128^3]; no device needed */
+int          mf_noise_generate_tile(float* out);
+int          mf_noise_seed_offset(const mf_noise* n, float* out3);
+/* WaveletNoiseField::evaluate(pos) at `count` host positions (xyz interleaved) -> host values; solverTime = FluidSolver::getTime() */
+int          mf_noise_evaluate(const mf_noise* n, const mf_noise_params* p, float solverTime, const float* pos, int count, float* out);
+/* densityInflow(flags, density, noise, shape, scale=1, sigma=0), initplugins.cpp:39 */
+int          mf_density_inflow(const mf_grid* flags, mf_grid* density, const mf_noise* n, const mf_noise_params* p, const mf_shape* shape,
+                               float scale, float sigma, float solverTime);
+/* addNoise(flags, density, noise, sdf=NULL, scale=1), initplugins.cpp:49 */
+int          mf_add_noise(const mf_grid* flags, mf_grid* density, const mf_noise* n, const mf_noise_params* p, const mf_grid* sdf, float scale,
+                          float solverTime);
+
 /* ---- GridMg inspection hooks for parity tests (source/multigrid.h:31-137 keeps these private) ---- */
 /* levels / host-fallback count of the solver's cached hierarchy (the gMapMG entry, pressure.cpp:250) */
 int          mf_mg_info(mf_solver* s, int* levels, int* usedHostFallback);

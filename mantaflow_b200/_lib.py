@@ -27,6 +27,11 @@ class ShapeDesc(C.Structure):          # mf_shape
     _fields_ = [("type", C.c_int), ("a", C.c_float * 3), ("b", C.c_float * 3), ("r", C.c_float)]
 
 
+class NoiseParams(C.Structure):        # mf_noise_params
+    _fields_ = [("posOffset", C.c_float * 3), ("posScale", C.c_float * 3), ("valOffset", C.c_float), ("valScale", C.c_float),
+                ("clamp", C.c_int), ("clampNeg", C.c_float), ("clampPos", C.c_float), ("timeAnim", C.c_float)]
+
+
 class SolveInfo(C.Structure):
     _fields_ = [("iterations", C.c_int), ("resNorm", C.c_float), ("maxIter", C.c_int), ("fixedCell", C.c_int),
                 ("mgLevels", C.c_int), ("mgRebuilt", C.c_int)]
@@ -113,6 +118,13 @@ SIGNATURES = {
     "mf_levelset_join": (_i, [_P, _P]),
     "mf_update_fractions": (_i, [_P, _P, _P, _i, _f]),
     "mf_set_obstacle_flags": (_i, [_P, _P, _P, _P, _P, _i]),
+    "mf_noise_create": (_P, [_P, _i, _i]),
+    "mf_noise_destroy": (None, [_P]),
+    "mf_noise_generate_tile": (_i, [C.POINTER(_f)]),
+    "mf_noise_seed_offset": (_i, [_P, C.POINTER(_f)]),
+    "mf_noise_evaluate": (_i, [_P, C.POINTER(NoiseParams), _f, C.POINTER(_f), _i, C.POINTER(_f)]),
+    "mf_density_inflow": (_i, [_P, _P, _P, C.POINTER(NoiseParams), _P, _f, _f, _f]),
+    "mf_add_noise": (_i, [_P, _P, _P, C.POINTER(NoiseParams), _P, _f, _f]),
     "mf_extrapolate_mac_simple": (_i, [_P, _P, _i, _P, _i]),
     "mf_extrapolate_mac_from_weight": (_i, [_P, _P, _i]),
     "mf_extrapolate_ls_simple": (_i, [_P, _i, _i, _i]),

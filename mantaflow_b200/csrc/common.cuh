@@ -80,6 +80,7 @@ struct Solver {
   int* hostInts;        // pinned
   float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
+  float* noiseTile;         // 3 x 128^3 wavelet-noise tile (noise.cu), uploaded on first use
   unsigned short* cgCode;   // 16-bit Laplace row codes for the CG's ApplyMatrix (pressure_kernels.cuh CGC_*), lazily allocated
   int numSMs;
   // ---- z-slab partition over GPUs (comm.h).  Single GPU: nranks = 1, comm = nullptr.

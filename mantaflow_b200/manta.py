@@ -571,7 +571,7 @@ class Box(Shape):
     _kind = 0
 
     def __init__(self, parent, center=None, p0=None, p1=None, size=None, **kwargs):
-        _checkArgs("Box", kwargs, ())
+        _checkArgs("Box", kwargs, ("name",))
         Shape.__init__(self, parent)
         if center is not None and size is not None:
             self.p0, self.p1 = _v3(center) - _v3(size), _v3(center) + _v3(size)
@@ -588,7 +588,7 @@ class Sphere(Shape):
     _kind = 1
 
     def __init__(self, parent, center=None, radius=None, scale=None, **kwargs):
-        _checkArgs("Sphere", kwargs, ())
+        _checkArgs("Sphere", kwargs, ("name",))
         Shape.__init__(self, parent)
         self.center, self.radius = _v3(center), np.float32(radius)
         self.scale = _v3(scale) if scale is not None else vec3(1, 1, 1)
@@ -601,12 +601,62 @@ class Cylinder(Shape):
     _kind = 2
 
     def __init__(self, parent, center=None, radius=None, z=None, **kwargs):
-        _checkArgs("Cylinder", kwargs, ())
+        _checkArgs("Cylinder", kwargs, ("name",))
         Shape.__init__(self, parent)
         self.center, self.radius, self.z = _v3(center), np.float32(radius), _v3(z)
 
     def _desc(self):
         return self.center, self.z, self.radius
+
+
+# ---- wavelet noise (source/noisefield.h) ----------------------------------------------------------------------------
+class NoiseField(object):
+    """WaveletNoiseField (noisefield.h:26-97): python-visible members as attributes, evaluation on the device"""
+
+    def __init__(self, parent, fixedSeed=-1, loadFromFile=False, name="", **kwargs):
+        _checkArgs("NoiseField", kwargs, ())
+        self.parent = parent
+        self._name = name
+        self.posOffset = vec3(0.0)
+        self.posScale = vec3(1.0)
+        self.valOffset = 0.0
+        self.valScale = 1.0
+        self.clamp = False
+        self.clampNeg = 0.0
+        self.clampPos = 1.0
+        self.timeAnim = 0.0
+        self._h = lib().mf_noise_create(parent._h, int(fixedSeed), 1 if loadFromFile else 0)
+        if not self._h:
+            check(1)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().mf_noise_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _params(self):
+        from ._lib import NoiseParams
+        p = NoiseParams()
+        po, ps = _v3(self.posOffset), _v3(self.posScale)
+        p.posOffset[0], p.posOffset[1], p.posOffset[2] = float(po.x), float(po.y), float(po.z)
+        p.posScale[0], p.posScale[1], p.posScale[2] = float(ps.x), float(ps.y), float(ps.z)
+        p.valOffset, p.valScale = float(self.valOffset), float(self.valScale)
+        p.clamp = 1 if self.clamp else 0
+        p.clampNeg, p.clampPos = float(self.clampNeg), float(self.clampPos)
+        p.timeAnim = float(self.timeAnim)
+        return p
+
+    def evaluate(self, positions):
+        """WaveletNoiseField::evaluate at an (n, 3) array of positions (a test hook: the reference evaluates inside its kernels)"""
+        pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        out = np.empty(pos.shape[0], np.float32)
+        p = self._params()
+        fp = C.POINTER(C.c_float)
+        check(lib().mf_noise_evaluate(self._h, C.byref(p), float(self.parent.timeTotal), pos.ctypes.data_as(fp), pos.shape[0], out.ctypes.data_as(fp)))
+        return out
 
 
 from .plugins import *  # noqa: E402,F401,F403  (plugin functions of the hot path)

@@ -17,7 +17,7 @@ __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "add
            "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
            "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
-           "updateFractions", "setObstacleFlags"]
+           "updateFractions", "setObstacleFlags", "densityInflow", "addNoise"]
 
 
 def _h(g):
@@ -258,3 +258,30 @@ def setObstacleFlags(flags=None, phiObs=None, fractions=None, phiOut=None, phiIn
     _req(flags, M.FlagGrid, "flags", "setObstacleFlags")
     _req(phiObs, M.RealGrid, "phiObs", "setObstacleFlags")
     check(lib().mf_set_obstacle_flags(flags._h, phiObs._h, _h(fractions), _h(phiOut), _h(phiIn), int(boundaryWidth)))
+
+
+# ---- noise-driven sources (source/plugin/initplugins.cpp:26-50) -------------------------------------------------------
+@M._plugin
+def densityInflow(flags=None, density=None, noise=None, shape=None, scale=1.0, sigma=0, **kwargs):
+    M._checkArgs("densityInflow", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "densityInflow")
+    _req(density, M.RealGrid, "density", "densityInflow")
+    if not isinstance(noise, M.NoiseField):
+        raise MantaError("densityInflow: argument 'noise' is missing or not a NoiseField")
+    if not isinstance(shape, M.Shape):
+        raise MantaError("densityInflow: argument 'shape' is missing or not a Shape")
+    p = noise._params()
+    d = shape._struct()
+    check(lib().mf_density_inflow(flags._h, density._h, noise._h, C.byref(p), C.byref(d), float(scale), float(sigma),
+                                  float(flags.parent.timeTotal)))
+
+
+@M._plugin
+def addNoise(flags=None, density=None, noise=None, sdf=None, scale=1.0, **kwargs):
+    M._checkArgs("addNoise", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "addNoise")
+    _req(density, M.RealGrid, "density", "addNoise")
+    if not isinstance(noise, M.NoiseField):
+        raise MantaError("addNoise: argument 'noise' is missing or not a NoiseField")
+    p = noise._params()
+    check(lib().mf_add_noise(flags._h, density._h, noise._h, C.byref(p), _h(sdf), float(scale), float(flags.parent.timeTotal)))

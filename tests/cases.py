@@ -407,3 +407,49 @@ CASES["set_obstacle_flags"] = _shape_case(S3, 3, _FRAC_OPS + [
 CASES["set_obstacle_flags_phi"] = _shape_case(S3, 3, DOMAIN + [["shape_ls", "Sphere", _SPHS, "phiObs"],
     ["call", "setObstacleFlags", {"flags": "@flags", "phiObs": "@phiObs", "boundaryWidth": 2}]],
     ["flags"], {"phiObs": "LevelsetGrid"})
+
+
+# ---- wavelet noise sources: densityInflow / addNoise with the reference's NoiseField ------------------
+_NZ_PLUME = {"posScale": V(45, 45, 45), "clamp": True, "clampNeg": 0, "clampPos": 1, "valOffset": 0.75, "timeAnim": 0.2}   # simpleplume.py:22-28
+_NZ_FREE = {"posScale": V(7.5, 11.0, 3.25), "posOffset": V(0.3, -1.7, 2.2), "valScale": 1.5, "valOffset": -0.1, "timeAnim": 1.3}
+CASES["noise_inflow"] = _shape_case(S3, 3, DOMAIN + OBST3 + [
+    ["object", "nz", "NoiseField", {}, _NZ_PLUME], ["object", "src", "Cylinder", _CYL],
+    ["repeat", 3, [["call", "densityInflow", {"flags": "@flags", "density": "@density", "noise": "@nz", "shape": "@src", "scale": 1, "sigma": 0.5}]]]],
+    ["density"], {})
+CASES["noise_inflow_sigma0"] = _shape_case(S3, 3, DOMAIN + [
+    ["object", "nz", "NoiseField", {"fixedSeed": 42}, _NZ_FREE], ["object", "src", "Sphere", _SPH],
+    ["repeat", 2, [["call", "densityInflow", {"flags": "@flags", "density": "@density", "noise": "@nz", "shape": "@src", "scale": 0.8}]]]],
+    ["density"], {}, load=["density"], inputs={"density": ["gen_real", 140, -0.5, 0.5]})
+CASES["noise_inflow_2d"] = _shape_case(S2, 2, DOMAIN + [
+    ["object", "nz", "NoiseField", {"fixedSeed": 7}, _NZ_PLUME], ["object", "src", "Box", {"p0": V(6.5, 3.0, 0), "p1": V(17.0, 9.5, 1)}],
+    ["repeat", 2, [["call", "densityInflow", {"flags": "@flags", "density": "@density", "noise": "@nz", "shape": "@src", "scale": 1.25, "sigma": 1.5}]]]],
+    ["density"], {})
+CASES["noise_add"] = _shape_case(S3, 3, DOMAIN + OBST3 + [
+    ["object", "nz", "NoiseField", {}, _NZ_FREE], ["shape_ls", "Sphere", _SPH, "phi"],
+    ["repeat", 2, [["call", "addNoise", {"flags": "@flags", "density": "@density", "noise": "@nz", "sdf": "@phi", "scale": 0.6}],
+                   ["call", "addNoise", {"flags": "@flags", "density": "@pressure", "noise": "@nz"}]]]],
+    ["density", "pressure"], {"phi": "LevelsetGrid"}, load=["density"], inputs={"density": ["gen_real", 141]})
+CASES["noise_add_2d"] = _shape_case(S2, 2, DOMAIN + [
+    ["object", "nz", "NoiseField", {"fixedSeed": 99}, _NZ_FREE],
+    ["repeat", 2, [["call", "addNoise", {"flags": "@flags", "density": "@density", "noise": "@nz", "scale": 2.0}]]]],
+    ["density"], {})
+
+# the reference's hello-world scene (scenes/simpleplume.py: noise-textured smoke source, MacCormack advection, buoyancy,
+# pressure projection) on a 24 x 36 x 24 grid, 12 steps; tolerances as for plume3d_mic / plume3d_mg above
+_SIMPLEPLUME_STEP = [
+    ["call", "densityInflow", {"flags": "@flags", "density": "@density", "noise": "@nz", "shape": "@src", "scale": 1, "sigma": 0.5}],
+    ["call", "advectSemiLagrange", {"flags": "@flags", "vel": "@vel", "grid": "@density", "order": 2}],
+    ["call", "advectSemiLagrange", {"flags": "@flags", "vel": "@vel", "grid": "@vel", "order": 2, "strength": 1.0}],
+    ["call", "setWallBcs", {"flags": "@flags", "vel": "@vel"}],
+    ["call", "addBuoyancy", {"density": "@density", "vel": "@vel", "gravity": V(0, -6e-4, 0), "flags": "@flags"}],
+    ["call", "solvePressure", {"flags": "@flags", "vel": "@vel", "pressure": "@pressure"}],
+]
+_SIMPLEPLUME_SETUP = [["object", "nz", "NoiseField", {"loadFromFile": True}, _NZ_PLUME],
+                      ["object", "src", "Cylinder", {"center": V(12, 3.6, 12), "radius": 3.36, "z": V(0, 0.72, 0)}]] + DOMAIN
+CASES["simpleplume_noise"] = {"size": [24, 36, 24], "dim": 3, "dt": 1.0, "grids": dict(BASEGRIDS), "load": [], "inputs": {},
+                              "ops": _SIMPLEPLUME_SETUP + [["repeat", 12, _SIMPLEPLUME_STEP]], "save": ["density", "vel"], "exact": False,
+                              "abs_tol": {"density": 3e-3, "vel": 5e-3}}
+_SIMPLEPLUME_STEP_MG = [op if op[1] != "solvePressure" else ["call", "solvePressure", dict(op[2], preconditioner="$PcMGStatic", zeroPressureFixing=True)]
+                        for op in _SIMPLEPLUME_STEP]
+CASES["simpleplume_noise_mg"] = dict(CASES["simpleplume_noise"], ops=_SIMPLEPLUME_SETUP + [["repeat", 12, _SIMPLEPLUME_STEP_MG]],
+                                     abs_tol={"density": 1e-3, "vel": 5e-3})

@@ -72,6 +72,12 @@ def _run_ops(ops, grids, api, solver, log):
             ckw = {k: _resolve(v, grids, api) for k, v in op[2].items()}
             shp = api[op[1]](parent=solver, **ckw)
             grids[op[3]].copyFrom(shp.computeLevelset())
+        elif kind == "object":   # ["object", "src", "Cylinder", {ctor kwargs}, {attributes}]: grids["src"] = solver.create(Cylinder, ...)
+            ckw = {k: _resolve(v, grids, api) for k, v in op[3].items()}
+            obj = solver.create(api[op[2]], **ckw)
+            for k, v in (op[4] if len(op) > 4 else {}).items():
+                setattr(obj, k, _resolve(v, grids, api))
+            grids[op[1]] = obj
         elif kind == "repeat":
             for _ in range(op[1]):
                 _run_ops(op[2], grids, api, solver, log)
