@@ -107,6 +107,8 @@ int          mf_grid_type(const mf_grid* g);
 int          mf_grid_clear(mf_grid* g);                                   /* Grid::clear  grid.cpp:95 */
 int          mf_grid_copy(mf_grid* dst, const mf_grid* src);             /* Grid::copyFrom grid.cpp:228 */
 int          mf_grid_swap(mf_grid* a, mf_grid* b);                       /* Grid::swap   grid.cpp:100 */
+int          mf_grid_get_component(const mf_grid* source, mf_grid* target, int component);   /* getComponent grid.cpp:746 */
+int          mf_grid_set_component(const mf_grid* source, mf_grid* target, int component);   /* setComponent grid.cpp:751 */
 int          mf_grid_upload(mf_grid* g, const void* host);               /* host -> device, reference layout */
 int          mf_grid_download(const mf_grid* g, void* host);             /* device -> host, reference layout */
 int          mf_grid_set_const_real(mf_grid* g, float v);                /* Grid::setConst grid.cpp:288 */

@@ -81,6 +81,8 @@ SIGNATURES = {
     "mf_grid_clear": (_i, [_P]),
     "mf_grid_copy": (_i, [_P, _P]),
     "mf_grid_swap": (_i, [_P, _P]),
+    "mf_grid_get_component": (_i, [_P, _P, _i]),
+    "mf_grid_set_component": (_i, [_P, _P, _i]),
     "mf_grid_upload": (_i, [_P, _P]),
     "mf_grid_download": (_i, [_P, _P]),
     "mf_grid_set_const_real": (_i, [_P, _f]),

@@ -418,6 +418,30 @@ int mf_grid_copy(mf_grid* dp, const mf_grid* sp_) {
   d->outflowState = a->outflowState;
   MF_API_END
 }
+// getComponent / setComponent (grid.cpp:743-751): one plane of the SoA vector grid <-> a real grid
+static void componentCopy(const Grid* vec, const Grid* real, int component, bool toVec, const char* fn) {
+  mfAssert(vec && real && vec->isVec() && real->isReal(), fn << ": needs a Vec3 grid and a Real grid");
+  mfAssert(component >= 0 && component < 3, fn << ": component out of range");
+  check_same_solver(vec, real, fn);
+  Solver* s = vec->s; s->use();
+  MF_RANKS(s, r) {
+    const Span sp = span(s, r);
+    if (!sp.n) continue;
+    float* v = vec->comp(component) + sp.off; float* q = real->d + sp.off;
+    CUDA_CHECK(cudaMemcpyAsync(toVec ? v : q, toVec ? q : v, sizeof(float) * sp.n, cudaMemcpyDeviceToDevice, s->stream));
+  }
+  s->rankSync();
+}
+int mf_grid_get_component(const mf_grid* source, mf_grid* target, int component) {
+  MF_API_BEGIN
+  componentCopy(G(source), G(target), component, false, "getComponent");
+  MF_API_END
+}
+int mf_grid_set_component(const mf_grid* source, mf_grid* target, int component) {
+  MF_API_BEGIN
+  componentCopy(G(target), G(source), component, true, "setComponent");
+  MF_API_END
+}
 int mf_grid_swap(mf_grid* ap, mf_grid* bp) {
   MF_API_BEGIN
   mfAssert(ap && bp, "Grid::swap: null grid");

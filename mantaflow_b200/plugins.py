@@ -17,7 +17,7 @@ __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "add
            "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
            "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
-           "updateFractions", "setObstacleFlags", "densityInflow", "addNoise"]
+           "updateFractions", "setObstacleFlags", "densityInflow", "addNoise", "getComponent", "setComponent"]
 
 
 def _h(g):
@@ -285,3 +285,20 @@ def addNoise(flags=None, density=None, noise=None, sdf=None, scale=1.0, **kwargs
         raise MantaError("addNoise: argument 'noise' is missing or not a NoiseField")
     p = noise._params()
     check(lib().mf_add_noise(flags._h, density._h, noise._h, C.byref(p), _h(sdf), float(scale), float(flags.parent.timeTotal)))
+
+
+# ---- Real <-> Vec3 component transfer (source/grid.cpp:741-751) ---------------------------------------------------------
+@M._plugin
+def getComponent(source=None, target=None, component=None, **kwargs):
+    M._checkArgs("getComponent", kwargs, ())
+    _req(source, M.VecGrid, "source", "getComponent")
+    _req(target, M.RealGrid, "target", "getComponent")
+    check(lib().mf_grid_get_component(source._h, target._h, int(component)))
+
+
+@M._plugin
+def setComponent(source=None, target=None, component=None, **kwargs):
+    M._checkArgs("setComponent", kwargs, ())
+    _req(source, M.RealGrid, "source", "setComponent")
+    _req(target, M.VecGrid, "target", "setComponent")
+    check(lib().mf_grid_set_component(source._h, target._h, int(component)))

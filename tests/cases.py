@@ -453,3 +453,41 @@ _SIMPLEPLUME_STEP_MG = [op if op[1] != "solvePressure" else ["call", "solvePress
                         for op in _SIMPLEPLUME_STEP]
 CASES["simpleplume_noise_mg"] = dict(CASES["simpleplume_noise"], ops=_SIMPLEPLUME_SETUP + [["repeat", 12, _SIMPLEPLUME_STEP_MG]],
                                      abs_tol={"density": 1e-3, "vel": 5e-3})
+
+# the reference's von Karman vortex street scene (scenes/karman.py, 2-D, second-order obstacle boundaries: fractions from the
+# obstacle levelset, extrapolation into the obstacle, noise-perturbed inflow) on a 48 x 24 grid, 8 steps
+_KC, _KZ = V(12, 12, 0.5), V(0, 0, 1.0)
+_KARMAN_SETUP = [
+    ["method", "flags", "initDomain", {"inflow": "xX", "phiWalls": "@phiWalls", "boundaryWidth": 0}],
+    ["shape_ls", "Cylinder", {"center": _KC, "radius": 4.8, "z": _KZ}, "phiObs"],
+    ["object", "densInflow", "Cylinder", {"center": _KC, "radius": 5.04, "z": _KZ}],
+    ["method", "phiObs", "join", {"o": "@phiWalls"}],
+    ["call", "updateFractions", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions"}],
+    ["call", "setObstacleFlags", {"flags": "@flags", "phiObs": "@phiObs", "fractions": "@fractions"}],
+    ["method", "flags", "fillGrid", {}],
+    ["method", "vel", "setConst", {"s": V(0.9, 0, 0)}],
+    ["object", "nz", "NoiseField", {"loadFromFile": True}, {"posScale": V(75, 75, 75), "clamp": True, "clampNeg": -1.0, "clampPos": 1.0}],
+    ["method", "testall", "setConst", {"s": -1.0}],
+    ["call", "addNoise", {"flags": "@flags", "density": "@density", "noise": "@nz", "sdf": "@testall", "scale": 0.1}],
+    ["call", "setComponent", {"target": "@vel", "source": "@density", "component": 1}],
+    ["method", "density", "setConst", {"s": 0.0}],
+]
+_KIN = {"vel": "@vel", "dir": "xX", "value": V(0.9, 0, 0)}
+_KWALL = {"flags": "@flags", "vel": "@vel", "fractions": "@fractions", "phiObs": "@phiObs"}
+_KARMAN_STEP = [
+    ["method", "densInflow", "applyToGrid", {"grid": "@density", "value": 2.0}],
+    ["call", "advectSemiLagrange", {"flags": "@flags", "vel": "@vel", "grid": "@density", "order": 2, "orderSpace": 1}],
+    ["call", "advectSemiLagrange", {"flags": "@flags", "vel": "@vel", "grid": "@vel", "order": 2, "strength": 1.0}],
+    ["call", "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel", "distance": 2, "intoObs": True}],
+    ["call", "setWallBcs", _KWALL],
+    ["call", "setInflowBcs", _KIN],
+    ["call", "solvePressure", {"flags": "@flags", "vel": "@vel", "pressure": "@pressure", "fractions": "@fractions", "cgAccuracy": 1e-4, "cgMaxIterFac": 5}],
+    ["call", "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel", "distance": 5, "intoObs": True}],
+    ["call", "setWallBcs", _KWALL],
+    ["call", "setInflowBcs", _KIN],
+]
+CASES["karman2d"] = {"size": [48, 24, 1], "dim": 2, "dt": 1.0,
+                     "grids": dict(BASEGRIDS, fractions="MACGrid", phiWalls="LevelsetGrid", phiObs="LevelsetGrid", testall="RealGrid"),
+                     "load": [], "inputs": {}, "ops": _KARMAN_SETUP + [["repeat", 8, _KARMAN_STEP]],
+                     "save": ["density", "vel", "flags", "fractions"], "exact": False,
+                     "abs_tol": {"density": 5e-3, "vel": 5e-3, "flags": 0, "fractions": 0}}
