@@ -252,6 +252,32 @@ int          mf_density_inflow(const mf_grid* flags, mf_grid* density, const mf_
 int          mf_add_noise(const mf_grid* flags, mf_grid* density, const mf_noise* n, const mf_noise_params* p, const mf_grid* sdf, float scale,
                           float solverTime);
 
+/* ---- FLIP particle system (source/particle.h:32-180,198; source/plugin/flip.cpp) ---- */
+typedef struct mf_parts mf_parts;
+enum { MF_INT_EULER = 0, MF_INT_RK2 = 1, MF_INT_RK4 = 2 };            /* IntegrationMode, util/integrator.h:23 */
+mf_parts*    mf_parts_create(mf_solver* s);                             /* BasicParticleSystem(parent), particle.h:200 */
+void         mf_parts_destroy(mf_parts* p);
+long long    mf_parts_size(const mf_parts* p);
+/* ParticleSystem::create(PdataReal | PdataVec3 | PdataInt): ncomp 1, 3 or -1; *index identifies the data in later calls */
+int          mf_parts_create_pdata(mf_parts* p, int ncomp, int* index);
+/* host <-> device: positions n x 3 interleaved, flags n ints (ParticleBase::ParticleStatus), particle data n x ncomp */
+int          mf_parts_upload(mf_parts* p, const float* pos, const int* flag, long long n);
+int          mf_parts_download(const mf_parts* p, float* pos, int* flag);
+int          mf_pdata_upload(mf_parts* p, int pdata, const void* in);
+int          mf_pdata_download(const mf_parts* p, int pdata, void* out);
+/* sampleFlagsWithParticles(flags, parts, discretization, randomness), flip.cpp:32 */
+int          mf_sample_flags_with_particles(const mf_grid* flags, mf_parts* parts, int discretization, float randomness);
+/* parts.advectInGrid(flags, vel, integrationMode, deleteInObstacle, stopInObstacle, skipNew), particle.h:527 */
+int          mf_parts_advect_in_grid(mf_parts* parts, const mf_grid* flags, const mf_grid* vel, int integrationMode, int deleteInObstacle,
+                                     int stopInObstacle, int skipNew);
+/* mapPartsToMAC(flags, vel, velOld, parts, partVel, weight=NULL), flip.cpp:637 */
+int          mf_map_parts_to_mac(const mf_grid* flags, mf_grid* vel, mf_grid* velOld, const mf_parts* parts, int partVel, mf_grid* weight);
+/* markFluidCells(parts, flags, phiObs=NULL), flip.cpp:166 */
+int          mf_mark_fluid_cells(const mf_parts* parts, mf_grid* flags, const mf_grid* phiObs);
+/* mapMACToParts(flags, vel, parts, partVel), flip.cpp:717; flipVelocityUpdate(flags, vel, velOld, parts, partVel, flipRatio), flip.cpp:738 */
+int          mf_map_mac_to_parts(const mf_grid* flags, const mf_grid* vel, const mf_parts* parts, int partVel);
+int          mf_flip_velocity_update(const mf_grid* flags, const mf_grid* vel, const mf_grid* velOld, const mf_parts* parts, int partVel, float flipRatio);
+
 /* ---- GridMg inspection hooks for parity tests (source/multigrid.h:31-137 keeps these private) ---- */
 /* levels / host-fallback count of the solver's cached hierarchy (the gMapMG entry, pressure.cpp:250) */
 int          mf_mg_info(mf_solver* s, int* levels, int* usedHostFallback);

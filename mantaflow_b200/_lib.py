@@ -120,6 +120,20 @@ SIGNATURES = {
     "mf_levelset_join": (_i, [_P, _P]),
     "mf_update_fractions": (_i, [_P, _P, _P, _i, _f]),
     "mf_set_obstacle_flags": (_i, [_P, _P, _P, _P, _P, _i]),
+    "mf_parts_create": (_P, [_P]),
+    "mf_parts_destroy": (None, [_P]),
+    "mf_parts_size": (C.c_longlong, [_P]),
+    "mf_parts_create_pdata": (_i, [_P, _i, C.POINTER(_i)]),
+    "mf_parts_upload": (_i, [_P, C.POINTER(_f), C.POINTER(_i), C.c_longlong]),
+    "mf_parts_download": (_i, [_P, C.POINTER(_f), C.POINTER(_i)]),
+    "mf_pdata_upload": (_i, [_P, _i, _P]),
+    "mf_pdata_download": (_i, [_P, _i, _P]),
+    "mf_sample_flags_with_particles": (_i, [_P, _P, _i, _f]),
+    "mf_parts_advect_in_grid": (_i, [_P, _P, _P, _i, _i, _i, _i]),
+    "mf_map_parts_to_mac": (_i, [_P, _P, _P, _P, _i, _P]),
+    "mf_mark_fluid_cells": (_i, [_P, _P, _P]),
+    "mf_map_mac_to_parts": (_i, [_P, _P, _P, _i]),
+    "mf_flip_velocity_update": (_i, [_P, _P, _P, _P, _i, _f]),
     "mf_noise_create": (_P, [_P, _i, _i]),
     "mf_noise_destroy": (None, [_P]),
     "mf_noise_generate_tile": (_i, [C.POINTER(_f)]),

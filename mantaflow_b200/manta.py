@@ -659,4 +659,102 @@ class NoiseField(object):
         return out
 
 
+# ---- FLIP particles (source/particle.h) -------------------------------------------------------------------------------
+IntEuler, IntRK2, IntRK4 = 0, 1, 2           # IntegrationMode (util/integrator.h:23)
+
+
+class ParticleDataBase(object):
+    """ParticleDataImpl<T> (particle.h:310): one value per particle, stored on the device next to the positions"""
+    _ncomp = 0
+
+    def __init__(self, parts, index, name=""):
+        self.parts, self._index, self._name = parts, index, name
+
+    def to_numpy(self):
+        n = self.parts.size()
+        nc = 3 if self._ncomp == 3 else 1
+        out = np.empty((n, nc), np.int32 if self._ncomp == -1 else np.float32)
+        if n:
+            check(lib().mf_pdata_download(self.parts._h, self._index, out.ctypes.data_as(C.c_void_p)))
+        return out if nc == 3 else out[:, 0]
+
+    def from_numpy(self, a):
+        n = self.parts.size()
+        nc = 3 if self._ncomp == 3 else 1
+        a = np.ascontiguousarray(a, np.int32 if self._ncomp == -1 else np.float32).reshape(n, nc)
+        if n:
+            check(lib().mf_pdata_upload(self.parts._h, self._index, a.ctypes.data_as(C.c_void_p)))
+
+
+class PdataReal(ParticleDataBase):
+    _ncomp = 1
+
+
+class PdataVec3(ParticleDataBase):
+    _ncomp = 3
+
+
+class PdataInt(ParticleDataBase):
+    _ncomp = -1
+
+
+class BasicParticleSystem(object):
+    """BasicParticleSystem (particle.h:198): positions + status flags on the device"""
+
+    def __init__(self, parent, name="", **kwargs):
+        _checkArgs("BasicParticleSystem", kwargs, ())
+        self.parent, self._name = parent, name
+        self._h = lib().mf_parts_create(parent._h)
+        if not self._h:
+            check(1)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().mf_parts_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def create(self, type=None, name="", **kwargs):
+        if type is None or not issubclass(type, ParticleDataBase) or type is ParticleDataBase:
+            raise MantaError("ParticleSystem::create: need a particle data type (PdataReal, PdataVec3, PdataInt)")
+        idx = C.c_int(-1)
+        check(lib().mf_parts_create_pdata(self._h, type._ncomp, C.byref(idx)))
+        return type(self, idx.value, name)
+
+    def size(self): return int(lib().mf_parts_size(self._h))
+    def pySize(self): return self.size()
+
+    def advectInGrid(self, flags=None, vel=None, integrationMode=None, deleteInObstacle=True, stopInObstacle=True, skipNew=False,
+                     ptype=None, exclude=0, **kwargs):
+        _checkArgs("advectInGrid", kwargs, ())
+        if ptype is not None:
+            raise MantaError("advectInGrid: ptype / exclude are not supported")
+        if integrationMode is None:
+            raise MantaError("Argument 'integrationMode' is not defined.")
+        check(lib().mf_parts_advect_in_grid(self._h, flags._h, vel._h, int(integrationMode), 1 if deleteInObstacle else 0,
+                                            1 if stopInObstacle else 0, 1 if skipNew else 0))
+
+    def getPosPdata(self, target=None):
+        pos, _ = self.to_numpy()
+        target.from_numpy(pos)
+
+    def to_numpy(self):
+        """(positions (n, 3) float32, status flags (n,) int32)"""
+        n = self.size()
+        pos = np.empty((n, 3), np.float32); flag = np.empty(n, np.int32)
+        if n:
+            check(lib().mf_parts_download(self._h, pos.ctypes.data_as(C.POINTER(C.c_float)), flag.ctypes.data_as(C.POINTER(C.c_int))))
+        return pos, flag
+
+    def from_numpy(self, pos, flag=None):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        fp = None
+        if flag is not None:
+            flag = np.ascontiguousarray(flag, np.int32)
+            fp = flag.ctypes.data_as(C.POINTER(C.c_int))
+        check(lib().mf_parts_upload(self._h, pos.ctypes.data_as(C.POINTER(C.c_float)), fp, pos.shape[0]))
+
+
 from .plugins import *  # noqa: E402,F401,F403  (plugin functions of the hot path)

@@ -17,7 +17,8 @@ __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "add
            "setOpenBound", "resetOutflow", "computePressureRhs", "solvePressureSystem", "correctVelocity",
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
            "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
-           "updateFractions", "setObstacleFlags", "densityInflow", "addNoise", "getComponent", "setComponent"]
+           "updateFractions", "setObstacleFlags", "densityInflow", "addNoise", "getComponent", "setComponent",
+           "sampleFlagsWithParticles", "mapPartsToMAC", "markFluidCells", "mapMACToParts", "flipVelocityUpdate"]
 
 
 def _h(g):
@@ -302,3 +303,68 @@ def setComponent(source=None, target=None, component=None, **kwargs):
     _req(source, M.RealGrid, "source", "setComponent")
     _req(target, M.VecGrid, "target", "setComponent")
     check(lib().mf_grid_set_component(source._h, target._h, int(component)))
+
+
+# ---- FLIP (source/plugin/flip.cpp) --------------------------------------------------------------------------------------
+def _parts(p, name, fn):
+    if not isinstance(p, M.BasicParticleSystem):
+        raise MantaError("%s: argument '%s' is missing or not a BasicParticleSystem" % (fn, name))
+    return p
+
+
+def _pvec(pd, parts, name, fn):
+    if not isinstance(pd, M.PdataVec3) or pd.parts is not parts:
+        raise MantaError("%s: argument '%s' is missing or not a PdataVec3 of 'parts'" % (fn, name))
+    return pd._index
+
+
+def _noPtype(fn, ptype):
+    if ptype is not None:
+        raise MantaError("%s: ptype / exclude are not supported" % fn)
+
+
+@M._plugin
+def sampleFlagsWithParticles(flags=None, parts=None, discretization=None, randomness=None, **kwargs):
+    M._checkArgs("sampleFlagsWithParticles", kwargs, ())
+    _req(flags, M.FlagGrid, "flags", "sampleFlagsWithParticles")
+    _parts(parts, "parts", "sampleFlagsWithParticles")
+    check(lib().mf_sample_flags_with_particles(flags._h, parts._h, int(discretization), float(randomness)))
+
+
+@M._plugin
+def mapPartsToMAC(flags=None, vel=None, velOld=None, parts=None, partVel=None, weight=None, ptype=None, exclude=0, **kwargs):
+    M._checkArgs("mapPartsToMAC", kwargs, ())
+    _noPtype("mapPartsToMAC", ptype)
+    _req(flags, M.FlagGrid, "flags", "mapPartsToMAC")
+    _req(vel, M.MACGrid, "vel", "mapPartsToMAC")
+    _req(velOld, M.MACGrid, "velOld", "mapPartsToMAC")
+    _parts(parts, "parts", "mapPartsToMAC")
+    check(lib().mf_map_parts_to_mac(flags._h, vel._h, velOld._h, parts._h, _pvec(partVel, parts, "partVel", "mapPartsToMAC"), _h(weight)))
+
+
+@M._plugin
+def markFluidCells(parts=None, flags=None, phiObs=None, ptype=None, exclude=0, **kwargs):
+    M._checkArgs("markFluidCells", kwargs, ())
+    _noPtype("markFluidCells", ptype)
+    _req(flags, M.FlagGrid, "flags", "markFluidCells")
+    _parts(parts, "parts", "markFluidCells")
+    check(lib().mf_mark_fluid_cells(parts._h, flags._h, _h(phiObs)))
+
+
+@M._plugin
+def mapMACToParts(flags=None, vel=None, parts=None, partVel=None, ptype=None, exclude=0, **kwargs):
+    M._checkArgs("mapMACToParts", kwargs, ())
+    _noPtype("mapMACToParts", ptype)
+    _req(vel, M.MACGrid, "vel", "mapMACToParts")
+    _parts(parts, "parts", "mapMACToParts")
+    check(lib().mf_map_mac_to_parts(_h(flags), vel._h, parts._h, _pvec(partVel, parts, "partVel", "mapMACToParts")))
+
+
+@M._plugin
+def flipVelocityUpdate(flags=None, vel=None, velOld=None, parts=None, partVel=None, flipRatio=None, ptype=None, exclude=0, **kwargs):
+    M._checkArgs("flipVelocityUpdate", kwargs, ())
+    _noPtype("flipVelocityUpdate", ptype)
+    _req(vel, M.MACGrid, "vel", "flipVelocityUpdate")
+    _req(velOld, M.MACGrid, "velOld", "flipVelocityUpdate")
+    _parts(parts, "parts", "flipVelocityUpdate")
+    check(lib().mf_flip_velocity_update(_h(flags), vel._h, velOld._h, parts._h, _pvec(partVel, parts, "partVel", "flipVelocityUpdate"), float(flipRatio)))

@@ -491,3 +491,69 @@ CASES["karman2d"] = {"size": [48, 24, 1], "dim": 2, "dt": 1.0,
                      "load": [], "inputs": {}, "ops": _KARMAN_SETUP + [["repeat", 8, _KARMAN_STEP]],
                      "save": ["density", "vel", "flags", "fractions"], "exact": False,
                      "abs_tol": {"density": 5e-3, "vel": 5e-3, "flags": 0, "fractions": 0}}
+
+
+# ---- FLIP particles: sampling, RK advection, particle <-> MAC grid transfers, the flip01_simple scene --------
+_PGRIDS = {"pp": "BasicParticleSystem", "pVel": "PdataVec3:pp", "velOld": "MACGrid", "tmpVec3": "VecGrid", "phi": "LevelsetGrid"}
+
+
+def _flip_case(size, dim, ops, save, load=(), inputs=None, exact=True, abs_tol=None, grids=None):
+    g = dict(BASEGRIDS); g.update(_PGRIDS); g.update(grids or {})
+    c = {"size": size, "dim": dim, "dt": 0.5, "grids": g, "load": list(load), "inputs": inputs or {}, "ops": ops, "save": save, "exact": exact}
+    if abs_tol:
+        c["abs_tol"] = abs_tol
+    return c
+
+
+_DAM3 = [["method", "flags", "initDomain", {"boundaryWidth": 0}], ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(7.2, 13.2, 14)}, "phi"],
+         ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}]]
+_DAM2 = [["method", "flags", "initDomain", {"boundaryWidth": 0}], ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(10.4, 12.0, 1)}, "phi"],
+         ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}]]
+_SAMPLE3 = ["call", "sampleFlagsWithParticles", {"flags": "@flags", "parts": "@pp", "discretization": 2, "randomness": 0.4}]
+_SAMPLE2 = ["call", "sampleFlagsWithParticles", {"flags": "@flags", "parts": "@pp", "discretization": 3, "randomness": 0.2}]
+CASES["flip_sample"] = _flip_case(S3, 3, _DAM3 + OBST3 + [_SAMPLE3], ["pp", "flags"])
+CASES["flip_sample_2d"] = _flip_case(S2, 2, _DAM2 + [_SAMPLE2], ["pp", "flags"])
+_ADV = {"flags": "@flags", "vel": "@vel", "deleteInObstacle": False}
+CASES["flip_advect_rk4"] = _flip_case(S3, 3, _DAM3 + OBST3 + [_SAMPLE3, ["repeat", 3, [["method", "pp", "advectInGrid", dict(_ADV, integrationMode="$IntRK4")]]]],
+                                      ["pp"], load=["vel"], inputs={"vel": ["gen_vel", 150, 1.9, 3]})
+CASES["flip_advect_rk2_stop"] = _flip_case(S3, 3, _DAM3 + OBST3 + [_SAMPLE3, ["repeat", 3, [
+    ["method", "pp", "advectInGrid", {"flags": "@flags", "vel": "@vel", "integrationMode": "$IntRK2"}]]]],
+    ["pp"], load=["vel"], inputs={"vel": ["gen_vel", 151, 2.6, 3]})
+CASES["flip_advect_euler_2d"] = _flip_case(S2, 2, _DAM2 + [_SAMPLE2, ["repeat", 4, [
+    ["method", "pp", "advectInGrid", dict(_ADV, integrationMode="$IntEuler", stopInObstacle=False)]]]],
+    ["pp"], load=["vel"], inputs={"vel": ["gen_vel", 152, 2.2, 2]})
+_TRANSFER = [["call", "mapMACToParts", {"flags": "@flags", "vel": "@vel", "parts": "@pp", "partVel": "@pVel"}],
+             ["method", "pp", "advectInGrid", dict(_ADV, integrationMode="$IntRK4")],
+             ["call", "mapPartsToMAC", {"vel": "@vel2", "flags": "@flags", "velOld": "@velOld", "parts": "@pp", "partVel": "@pVel", "weight": "@tmpVec3"}],
+             ["call", "markFluidCells", {"parts": "@pp", "flags": "@flags"}],
+             ["call", "flipVelocityUpdate", {"vel": "@vel", "velOld": "@velOld", "flags": "@flags", "parts": "@pp", "partVel": "@pVel", "flipRatio": 0.97}]]
+CASES["flip_transfer"] = _flip_case(S3, 3, _DAM3 + OBST3 + [_SAMPLE3] + _TRANSFER, ["vel2", "velOld", "tmpVec3", "flags", "pVel", "pp"],
+                                    load=["vel"], inputs={"vel": ["gen_vel", 153, 1.4, 3]}, grids={"vel2": "MACGrid"})
+CASES["flip_transfer_2d"] = _flip_case(S2, 2, _DAM2 + [_SAMPLE2] + _TRANSFER, ["vel2", "velOld", "tmpVec3", "flags", "pVel", "pp"],
+                                       load=["vel"], inputs={"vel": ["gen_vel", 154, 1.4, 2]}, grids={"vel2": "MACGrid"})
+CASES["flip_map_noweight"] = _flip_case(S3, 3, _DAM3 + [_SAMPLE3, _TRANSFER[0],
+    ["call", "mapPartsToMAC", {"vel": "@vel2", "flags": "@flags", "velOld": "@velOld", "parts": "@pp", "partVel": "@pVel"}]], ["vel2", "velOld"],
+    load=["vel"], inputs={"vel": ["gen_vel", 155, 1.0, 3]}, grids={"vel2": "MACGrid"})
+
+# the reference's scenes/flip01_simple.py (breaking dam, FLIP without levelset or resampling), 2-D as shipped and a 3-D variant
+_FLIP01_STEP = [
+    ["method", "pp", "advectInGrid", dict(_ADV, integrationMode="$IntRK4")],
+    ["call", "mapPartsToMAC", {"vel": "@vel", "flags": "@flags", "velOld": "@velOld", "parts": "@pp", "partVel": "@pVel", "weight": "@tmpVec3"}],
+    ["call", "extrapolateMACFromWeight", {"vel": "@vel", "distance": 2, "weight": "@tmpVec3"}],
+    ["call", "markFluidCells", {"parts": "@pp", "flags": "@flags"}],
+    ["call", "addGravity", {"flags": "@flags", "vel": "@vel", "gravity": V(0, -0.002, 0)}],
+    ["call", "setWallBcs", {"flags": "@flags", "vel": "@vel"}],
+    ["call", "solvePressure", {"flags": "@flags", "vel": "@vel", "pressure": "@pressure"}],
+    ["call", "setWallBcs", {"flags": "@flags", "vel": "@vel"}],
+    ["call", "extrapolateMACSimple", {"flags": "@flags", "vel": "@vel"}],
+    ["call", "flipVelocityUpdate", {"vel": "@vel", "velOld": "@velOld", "flags": "@flags", "parts": "@pp", "partVel": "@pVel", "flipRatio": 0.97}],
+]
+CASES["flip01_2d"] = _flip_case([32, 32, 1], 2, [["method", "flags", "initDomain", {"boundaryWidth": 0}],
+    ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(12.8, 19.2, 1)}, "phi"], ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}],
+    _SAMPLE2, ["repeat", 20, _FLIP01_STEP]], ["vel", "flags", "pp", "pVel"], exact=False,
+    abs_tol={"vel": 2e-3, "flags": 0, "pp": 2e-3, "pVel": 2e-3})
+CASES["flip01_3d"] = _flip_case([20, 20, 20], 3, [["method", "flags", "initDomain", {"boundaryWidth": 0}],
+    ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(8, 12, 20)}, "phi"], ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}],
+    ["call", "sampleFlagsWithParticles", {"flags": "@flags", "parts": "@pp", "discretization": 2, "randomness": 0.2}],
+    ["repeat", 10, _FLIP01_STEP]], ["vel", "flags", "pp", "pVel"], exact=False,
+    abs_tol={"vel": 2e-3, "flags": 0, "pp": 2e-3, "pVel": 2e-3})

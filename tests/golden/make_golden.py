@@ -40,6 +40,9 @@ def run_reference(name, case, threads="1"):
         out = {}
         for g in case["save"]:
             gt = case["grids"][g]
+            if sr.is_particle_type(gt):
+                out["out_" + g] = sr.read_pdata_uni(os.path.join(d, "out_%s.uni" % g), 1 if gt.startswith("PdataReal") else 3)
+                continue
             dt = np.int32 if gt in ("FlagGrid", "IntGrid") else np.float32
             out["out_" + g] = sr.read_raw(os.path.join(d, "out_%s.raw" % g), dt, sr.grid_shape(case, gt))
         its = [int(m) for m in re.findall(r"solvePressure done\. Iterations:(\d+)", p.stdout)]

@@ -17,7 +17,14 @@ def loader(name, grid, gtype):
     grid.load(os.path.join(d, "in_%s.raw" % name))
 
 def saver(name, grid, gtype):
-    grid.save(os.path.join(d, "out_%s.raw" % name))
+    if gtype == "BasicParticleSystem":       # positions through a particle-data copy (the particle .uni writer is unusable in this fork)
+        tmp = grid.create(PdataVec3)
+        grid.getPosPdata(target=tmp)
+        tmp.save(os.path.join(d, "out_%s.uni" % name))
+    elif sr.is_particle_type(gtype):
+        grid.save(os.path.join(d, "out_%s.uni" % name))
+    else:
+        grid.save(os.path.join(d, "out_%s.raw" % name))
     return None
 
 out, log = sr.run_case(case, globals(), loader, saver)

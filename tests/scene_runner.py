@@ -29,6 +29,26 @@ def grid_shape(case, gtype):
     return (nz, ny, nx, 3) if NCOMP.get(gtype, 1) == 3 else (nz, ny, nx)
 
 
+PART_HEADER = 4 + 6 * 4 + 256 + 8      # "PD01" + UniPartHeader (fileio/ioparticles.cpp:37-43)
+
+
+def read_pdata_uni(path, ncomp=3):
+    """particle data written by ParticleDataImpl::save (writePdataUni, fileio/ioparticles.cpp:226): float32 values after the header"""
+    import numpy as np
+    import struct
+    with gzip.open(path, "rb") as f:
+        raw = f.read()
+    assert raw[:4] == b"PD01", raw[:4]
+    n, = struct.unpack("<i", raw[4:8])
+    a = np.frombuffer(raw[PART_HEADER:], dtype=np.float32)
+    assert a.size == n * ncomp, (a.size, n, ncomp)
+    return a.reshape(n, ncomp).copy() if ncomp > 1 else a.copy()
+
+
+def is_particle_type(gtype):
+    return gtype.split(":")[0] in ("BasicParticleSystem", "PdataVec3", "PdataReal")
+
+
 def write_raw(path, arr):
     import numpy as np
     with gzip.open(path, "wb", compresslevel=1) as f:
@@ -93,7 +113,11 @@ def run_case(case, api, loader, saver):
     s.timestep = case.get("dt", 1.0)
     grids = {}
     for name, gtype in case["grids"].items():
-        grids[name] = s.create(api[gtype])
+        if ":" in gtype:     # "PdataVec3:pp": particle data created by its particle system
+            t, owner = gtype.split(":")
+            grids[name] = grids[owner].create(api[t])
+        else:
+            grids[name] = s.create(api[gtype])
     for name in case.get("load", []):
         loader(name, grids[name], case["grids"][name])
     log = []

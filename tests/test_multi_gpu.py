@@ -24,7 +24,9 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
 def _cases_for(nranks):
-    return [n for n, c in C.CASES.items() if c.get("dim", 3) == 3 and c["size"][2] >= 2 * nranks]
+    # particle systems are not z-slab partitioned yet (mf_parts_create refuses a partitioned solver)
+    return [n for n, c in C.CASES.items() if c.get("dim", 3) == 3 and c["size"][2] >= 2 * nranks
+            and "BasicParticleSystem" not in c["grids"].values()]
 
 
 def _run_partitioned(name, comm):

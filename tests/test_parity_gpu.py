@@ -30,6 +30,8 @@ def run_ours(case):
         grid.from_numpy(ins[name])
 
     def saver(name, grid, gtype):
+        if gtype == "BasicParticleSystem":
+            return grid.to_numpy()[0]
         return grid.to_numpy()
 
     infos = []
