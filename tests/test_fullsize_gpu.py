@@ -303,12 +303,40 @@ def test_flip01_128_properties():
     assert all(1 <= it <= 192 for it in A["its"]), A["its"]       # maxIter = 1.5 * 128 (pressure.cpp:410)
     if A["its"][-1] < 192:
         assert div.size > 100000 and div.max() < 2e-3, div.max()
-    assert np.isfinite(A["pvel"]).all() and np.abs(A["pvel"]).max() < 1.0
+    assert np.isfinite(A["pvel"]).all() and np.abs(A["pvel"]).max() < 4.0      # the reference itself reaches 1.1 after 3 steps
     # determinism of the whole particle <-> grid loop (sorted scatter, fixed-order reductions)
     B = _flip01(res, steps)
     for k in ("pos", "pvel", "vel", "pressure", "flags"):
         assert np.array_equal(A[k], B[k]), "run-to-run difference in " + k
     assert A["its"] == B["its"]
+
+
+@pytest.mark.gpu
+def test_live_oracle_flip01_128():
+    """configs[3]: scenes/flip01_simple.py with dim=3, res=128 (3.8 M particles), three steps through the unmodified reference and
+    through the device path, the free-surface projection with PcMGDynamic on both sides (the V-cycle is the reference's
+    operation for operation; with the default preconditioner the reference runs its sequential MIC(0), this library the
+    red-black variant, and the two stop at different iterates of a cgAccuracy=1e-3 solve).  Sampling, RK4 advection, the
+    particle -> grid scatter, extrapolation, cell marking and the FLIP update must reproduce the reference's particles."""
+    _need_oracle()
+    res = 128
+    V = C.V
+    step = [op if op[1] != "solvePressure" else ["call", "solvePressure", dict(op[2], preconditioner="$PcMGDynamic")] for op in C._FLIP01_STEP]
+    case = C._flip_case([res, res, res], 3, [
+        ["method", "flags", "initDomain", {"boundaryWidth": 0}],
+        ["shape_ls", "Box", {"p0": V(0, 0, 0), "p1": V(0.4 * res, 0.6 * res, res)}, "phi"],
+        ["method", "flags", "updateFromLevelset", {"levelset": "@phi"}],
+        ["call", "sampleFlagsWithParticles", {"flags": "@flags", "parts": "@pp", "discretization": 2, "randomness": 0.2}],
+        ["repeat", 3, step]], ["vel", "flags", "pp", "pVel", "pressure"], exact=False)
+    ref = _live_reference("fullsize_flip01", case)
+    ins, out, infos = T.run_ours(case)
+    assert out["pp"].shape == ref["out_pp"].shape
+    assert np.array_equal(out["flags"], ref["out_flags"])
+    worst = {g: float(np.abs(out[g].astype(np.float64) - ref["out_" + g]).max()) for g in ("vel", "pp", "pVel", "pressure")}
+    print("flip01 128^3 vs reference, max |diff|:", worst, "iterations", [i["iterations"] for i in infos], ref["ref_iterations"].tolist())
+    assert worst["pp"] <= 2e-3 and worst["pVel"] <= 2e-3 and worst["vel"] <= 2e-3, worst
+    assert worst["pressure"] <= 1e-3 * float(np.abs(ref["out_pressure"]).max()), worst
+    assert [i["iterations"] for i in infos] == ref["ref_iterations"].tolist()
 
 
 @pytest.mark.gpu
