@@ -11,6 +11,7 @@
 //   (cached per flag grid, invalidated by every flag-writing entry point).
 #include "common.cuh"
 #include "sample.cuh"
+#include "advect_fast.cuh"
 #include <cfloat>
 
 namespace mf {
@@ -369,17 +370,27 @@ static void applyOutflowBC(Solver* s, const Grid* flags, V3 vel, CV3 velPrev, fl
   MF_LAUNCH_IJK(s, k_outflow_copy, flags->di(), cv3(velDst), vel);
 }
 
+// the 32-bit-index kernels of advect_fast.cuh: 3-D, linear interpolation, first-order trace (MF_ADVECT_GENERIC=1: tests compare
+// them with the generic kernels)
+static bool fastPath(const Solver* s, int OS, int OT) {
+  return s->is3D && OS == 1 && OT == 1 && s->N < (1LL << 31) && !getenv("MF_ADVECT_GENERIC");
+}
+
 template <int NC, int OS, int OT>
 static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* grid, int order, float strength, int clampMode) {
   const long long np = s->Np;
   const float dt = s->dt;
+  const bool fast = NC == 1 && fastPath(s, OS, OT);
   float* fwd = (NC == 1) ? s->getReal() : s->getVec();
-  MF_LAUNCH_IJK(s, (k_sl<NC, OS, OT>), cv3(vel), grid->d, fwd, dt, np);
+  if (fast) MF_LAUNCH_IJK(s, k_sl_f, cv3(vel), grid->d, fwd, dt);
+  else MF_LAUNCH_IJK(s, (k_sl<NC, OS, OT>), cv3(vel), grid->d, fwd, dt, np);
   if (order == 1) {
     float* old = grid->d; grid->d = fwd; fwd = old;       // orig.swap(fwd)
   } else {
     float* nw = (NC == 1) ? s->getReal() : s->getVec();
-    MF_LAUNCH_IJK(s, (k_mc_centered<NC, OS, OT>), flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
+    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_centered_f<1>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength);
+    else if (fast) MF_LAUNCH_IJK(s, k_mc_centered_f<2>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength);
+    else MF_LAUNCH_IJK(s, (k_mc_centered<NC, OS, OT>), flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
     float* old = grid->d; grid->d = nw;                   // orig.swap(newGrid)
     if (NC == 1) s->putReal(old); else s->putVec(old);
   }
@@ -392,14 +403,18 @@ static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid,
   const bool self = (vel == grid) || (vel->d == grid->d);
   float* fwd = s->getVec();
   Grid fw = *grid; fw.d = fwd;
-  MF_LAUNCH_IJK(s, (k_sl_mac<OS, OT>), cv3(vel), cv3(grid), v3(&fw), dt);
+  const bool fast = fastPath(s, OS, OT);
+  if (fast) MF_LAUNCH_IJK(s, k_sl_mac_f, cv3(vel), cv3(grid), v3(&fw), dt);
+  else MF_LAUNCH_IJK(s, (k_sl_mac<OS, OT>), cv3(vel), cv3(grid), v3(&fw), dt);
   if (order == 1) {
     applyOutflowBC(s, flags, v3(&fw), cv3(grid), dt);
     float* old = grid->d; grid->d = fwd; fwd = old;
   } else {
     float* nw = s->getVec();
     Grid ng = *grid; ng.d = nw;
-    MF_LAUNCH_IJK(s, (k_mc_mac<OS, OT>), flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
+    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_mac_f<1>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength);
+    else if (fast) MF_LAUNCH_IJK(s, k_mc_mac_f<2>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength);
+    else MF_LAUNCH_IJK(s, (k_mc_mac<OS, OT>), flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
     applyOutflowBC(s, flags, v3(&ng), cv3(grid), dt);
     float* old = grid->d; grid->d = nw;
     s->putVec(old);

@@ -5,6 +5,7 @@
 #include "mg_kernels.cuh"
 #include "mg_fused0.cuh"
 #include "mg_wave0.cuh"
+#include "mg_tail.cuh"
 #include "comm.h"
 #include <algorithm>
 #include <cmath>
@@ -29,6 +30,9 @@ struct MgHierarchy {
   std::vector<std::vector<int>> pairSplit;   // blocked level l: rank r sweeps z pairs [pairSplit[l][r], pairSplit[l][r+1])
   std::vector<MgOff8> offs;                  // blocked level l: stencil offset tables of the sweeps (buildOffsets)
   __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when exact)
+  // persistent kernels for the small levels (mg_tail.cuh): grid-barrier counter, its host-tracked value, time-out flag
+  unsigned* tailBar; unsigned tailBase; int* tailErrHost; int* tailErrDev; MgOff8* tailOffs;
+  int tailFirst;            // first level swept by the tail kernels, or -1
 };
 
 // ---- partition of a level over the ranks ----------------------------------------------------------------------
@@ -72,20 +76,28 @@ static void flushGroups(MgHierarchy* mg) { if (mg->pendingSolo) { mg->s->rankSyn
 // ---- coarsest level: Jacobi-preconditioned CG in double, one CTA (solveCG, multigrid.cpp:796-902) ---------
 // One thread per vertex (n <= 1024).  The 27 (7) coefficients of the thread's row are loaded once into registers, the
 // search vector lives in shared memory; 3 block barriers per iteration.
-__device__ __forceinline__ void cgBlockSum2(double& a, double& b, double (*sh)[2][32], int& buf) {
+// block-wide sums of (a, b): warp tree, one partial per warp in shared memory, then warp 0 alone combines the partials (the same
+// xor tree every warp used to run redundantly, so the sums are bit-identical) and runs `fin(a, b)` -- the scalar double
+// divisions / square root of the iteration, which would otherwise occupy the FP64 pipe once per warp -- before the results
+// are published through shared memory.  Two block barriers per call.
+template <class Fin>
+__device__ __forceinline__ void cgBlockSum2(double a, double b, double (*sh)[32], double* out, Fin fin) {
   for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  if (l == 0) { sh[buf][0][w] = a; sh[buf][1][w] = b; }
+  if (l == 0) { sh[0][w] = a; sh[1][w] = b; }
   __syncthreads();
-  const int nw = (blockDim.x + 31) >> 5;
-  a = (l < nw) ? sh[buf][0][l] : 0.0;
-  b = (l < nw) ? sh[buf][1][l] : 0.0;
-  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
-  buf ^= 1;     // the next reduction writes the other buffer: no barrier needed before it
+  if (w == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    a = (l < nw) ? sh[0][l] : 0.0;
+    b = (l < nw) ? sh[1][l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (l == 0) fin(a, b, out);
+  }
+  __syncthreads();
 }
 
 template <bool LEVEL0>
-__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[2][32], double* vec) {
+__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[32], double* out, double* vec) {
   constexpr int NS = LEVEL0 ? 7 : 27;
   const int v = threadIdx.x;
   const bool in = v < L.n;
@@ -146,7 +158,6 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
   };
   const double diag = active ? (double)L.A[p] : 1.0;
   double x = in ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
-  int buf = 0;
   vec[v] = x;
   __syncthreads();
   if (active) {
@@ -154,24 +165,24 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
     z = r / diag;
     pp = z;
   }
-  double rr = active ? r * r : 0.0, rz = active ? r * z : 0.0;
-  cgBlockSum2(rr, rz, sh, buf);
-  const double initialResidual = sqrt(rr);
-  double alphaTop = rz;
+  // out[0] = sqrt(sum r.r), out[1] = sum r.z
+  cgBlockSum2(active ? r * r : 0.0, active ? r * z : 0.0, sh, out, [](double rr, double rz, double* o) { o[0] = sqrt(rr); o[1] = rz; });
+  const double initialResidual = out[0];
+  double alphaTop = out[1];
   const double acc = (double)accuracy;
   for (int iter = 0; iter < 10000 && initialResidual > 1E-12; iter++) {
-    vec[v] = pp;              // all reads of the previous vec happened before the last reduction barrier
+    vec[v] = pp;              // the previous contents were last read before the barriers of the reduction above
     __syncthreads();
     if (active) z = applyA();
-    double pz = active ? pp * z : 0.0, dummy = 0.0;
-    cgBlockSum2(pz, dummy, sh, buf);
-    const double alpha = alphaTop / pz;
+    cgBlockSum2(active ? pp * z : 0.0, 0.0, sh, out, [alphaTop](double pz, double, double* o) { o[0] = alphaTop / pz; });
+    const double alpha = out[0];
     if (active) { x += alpha * pp; r -= alpha * z; z = r / diag; }
-    rr = active ? r * r : 0.0; rz = active ? r * z : 0.0;
-    cgBlockSum2(rr, rz, sh, buf);
-    if (sqrt(rr) / initialResidual < acc) break;
-    const double beta = rz / alphaTop;
-    alphaTop = rz;
+    // out[0] = beta, out[1] = new alphaTop, out[2] = converged
+    cgBlockSum2(active ? r * r : 0.0, active ? r * z : 0.0, sh, out, [alphaTop, initialResidual, acc](double rr, double rz, double* o) {
+      o[0] = rz / alphaTop; o[1] = rz; o[2] = (sqrt(rr) / initialResidual < acc) ? 1.0 : 0.0; });
+    if (out[2] != 0.0) break;
+    const double beta = out[0];
+    alphaTop = out[1];
     pp = z + beta * pp;
   }
   if (in) L.x[p] = (float)x;
@@ -179,12 +190,14 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
 template <bool LEVEL0>
 __global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
   MF_PDL_PROLOGUE
-  __shared__ double sh[2][2][32];
+  __shared__ double sh[2][32];
+  __shared__ double out[4];
   __shared__ double vec[1024];
-  mgCoarseCg<LEVEL0>(L, D, accuracy, sh, vec);
+  mgCoarseCg<LEVEL0>(L, D, accuracy, sh, out, vec);
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------
+static void planTail(MgHierarchy* mg);
 static void buildPaths(MgHierarchy* mg) {
   // restatement of the path enumeration in GridMg::GridMg (multigrid.cpp:286-318)
   struct P { int N[3], U[3], W[3]; int sc, sf; float rw, iw; bool inU; };
@@ -285,6 +298,7 @@ MgHierarchy* mg_create(Solver* s) {
   mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
   mg->half1 = nullptr; mg->ash1 = 0;
+  mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
   mg->D.zmin = is3D ? -1 : 0; mg->D.zmax = is3D ? 1 : 0;
@@ -364,6 +378,9 @@ void mg_destroy(MgHierarchy* mg) {
   if (mg->code0) mg->s->gfree(mg->code0);
   if (mg->half1) mg->s->gfree(mg->half1);
   mg->s->gfree(mg->dFlags); cudaFree(mg->dPaths);
+  if (mg->tailBar) cudaFree(mg->tailBar);
+  if (mg->tailOffs) cudaFree(mg->tailOffs);
+  if (mg->tailErrHost) cudaFreeHost(mg->tailErrHost);
   delete mg;
 }
 
@@ -549,6 +566,7 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
   }
   MF_LAUNCH_CHECK();
   mg->aSet = true;
+  planTail(mg);
 }
 
 // ---- V-cycle launches: every group = the same kernel on every local rank's z range of the level, then the barrier ----
@@ -730,10 +748,81 @@ static void waveUp0(MgHierarchy* mg, float* dst) {
   endGroup(mg, false);
 }
 
+// ---- small levels in two persistent kernels (mg_tail.cuh) ---------------------------------------------------------------------
+// The tail starts at the first level whose colour sweep is at most ~one vertex per thread of a one-CTA-per-SM grid; every level
+// from there to the coarsest one must be a float, colour-blocked 3-D level and (partitioned solvers) be hosted by rank 0 alone.
+static void planTail(MgHierarchy* mg) {
+  Solver* s = mg->s;
+  mg->tailFirst = -1;
+  const int maxLevel = (int)mg->lv.size() - 1;
+  // opt-in (MF_MG_TAIL=1): measured at 256^3 the persistent kernels need ~2.7-3.2 us per phase (1.25 us of it the grid barrier,
+  // the rest one L2 round trip and the 52-operation dependent chain of a vertex) against ~3.4 us per programmatic dependent
+  // launch -- 6.83 vs 6.78 ms per step, no gain; kept for the parity test and as the starting point of a shared-memory variant
+  if (!mg->D.is3D || maxLevel < 2 || !getenv("MF_MG_TAIL") || getenv("MF_MG_NOTAIL")) return;
+  const long long cap = (long long)s->numSMs * MG_TAIL_THREADS;
+  int tf = -1;
+  for (int l = 1; l < maxLevel; l++) {
+    const LvlD& L = mg->lv[l];
+    if ((long long)(L.PX - 2) * (L.PY - 2) * (L.PZ - 2) <= cap && !L.Ah) { tf = l; break; }
+  }
+  if (tf < 0 || maxLevel - tf + 1 > MG_TAIL_MAXL) return;
+  for (int l = tf; l <= maxLevel; l++) {
+    const LvlD& L = mg->lv[l];
+    if (!L.perm || L.Ah || L.NC != 8 || (s->multi() && !lvlSolo(mg, l))) return;
+  }
+  if (!mg->tailBar) {
+    CUDA_CHECK(cudaMalloc(&mg->tailBar, sizeof(unsigned)));
+    CUDA_CHECK(cudaMemset(mg->tailBar, 0, sizeof(unsigned)));
+    CUDA_CHECK(cudaHostAlloc(&mg->tailErrHost, sizeof(int), cudaHostAllocMapped));
+    *mg->tailErrHost = 0;
+    CUDA_CHECK(cudaHostGetDevicePointer(&mg->tailErrDev, mg->tailErrHost, 0));
+    mg->tailBase = 0;
+    CUDA_CHECK(cudaMalloc(&mg->tailOffs, sizeof(MgOff8) * MG_TAIL_MAXL));
+  }
+  // (stream-ordered behind the kernels of an earlier hierarchy that may still read the tables)
+  CUDA_CHECK(cudaMemcpyAsync(mg->tailOffs, &mg->offs[tf], sizeof(MgOff8) * (size_t)(maxLevel - tf), cudaMemcpyHostToDevice, s->stream));
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  mg->tailFirst = tf;
+}
+void mg_check_errors(const MgHierarchy* mg) {
+  mfAssert(!(mg && mg->tailErrHost && *mg->tailErrHost), "GridMg: a grid barrier of the small-level kernel timed out");
+}
+static void tailLeg(MgHierarchy* mg, bool down, bool fold) {
+  Solver* s = mg->s;
+  const int maxLevel = (int)mg->lv.size() - 1, tf = mg->tailFirst;
+  const bool solo = s->multi();
+  s->profTag = tf;
+  beginGroup(mg, solo);
+  if (s->rankBegin == 0) {
+    TailArgs T;
+    memset(&T, 0, sizeof(T));
+    T.nl = maxLevel - tf + 1; T.fold = fold ? 1 : 0; T.base = mg->tailBase; T.bar = mg->tailBar; T.err = mg->tailErrDev; T.off = mg->tailOffs; T.prefetch = (down && !getenv("MF_MG_TAILNOPF")) ? 1 : 0;
+    static unsigned long long* dbgBuf = nullptr;
+    if (getenv("MF_MG_TAILDBG") && !dbgBuf) CUDA_CHECK(cudaMalloc(&dbgBuf, 64 * sizeof(unsigned long long)));
+    T.dbg = getenv("MF_MG_TAILDBG") ? dbgBuf : nullptr;
+    for (int l = tf; l <= maxLevel; l++) T.lv[l - tf] = mg->lv[l];
+    const int G = s->numSMs;
+    if (down) { MF_LAUNCH_PDL(s, k_mg_tail<true>, G, MG_TAIL_THREADS, T); }
+    else      { MF_LAUNCH_PDL(s, k_mg_tail<false>, G, MG_TAIL_THREADS, T); }
+    mg->tailBase += (unsigned)G * (unsigned)mgTailBarriers(T.nl, down, fold);
+    if (T.dbg) {     // MF_MG_TAILDBG: per-phase times of this launch (development)
+      unsigned long long h[64];
+      CUDA_CHECK(cudaStreamSynchronize(s->stream));
+      CUDA_CHECK(cudaMemcpy(h, T.dbg, sizeof(h), cudaMemcpyDeviceToHost));
+      const int nb = mgTailBarriers(T.nl, down, fold);
+      fprintf(stderr, "k_mg_tail<%s> phases (ns):", down ? "down" : "up");
+      for (int i = 1; i <= nb && i < 64; i++) fprintf(stderr, " %llu", h[i] - h[i - 1]);
+      fprintf(stderr, "\n");
+    }
+  }
+  endGroup(mg, solo);
+}
+
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
 void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   Solver* s = mg->s;
   mfAssert(mg->aSet, "GridMg::setRhs Error: A has not been set.");
+  mg_check_errors(mg);
   const int maxLevel = (int)mg->lv.size() - 1;
   LvlD& L0 = mg->lv[0];
   L0.b = const_cast<float*>(rhs);      // knSetRhs' trivial-row scaling is applied on the fly (OP::rhs)
@@ -765,7 +854,10 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   // 17^3 level with cluster barriers, 5-9 us per phase against ~4.4 us per dependent launch -- too few threads in flight for
   // the latency of a 41-load stencil item)
   const int lb = maxLevel;
+  // levels tail .. maxLevel-1: both legs as one persistent kernel each (mg_tail.cuh)
+  const int tail = (mg->tailFirst >= 1 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_NOTAIL") && !getenv("MF_MG_UNFUSED")) ? mg->tailFirst : -1;
   for (int l = fused0 ? 1 : 0; l < lb; l++) {
+    if (l == tail) { tailLeg(mg, true, foldTo(l)); break; }
     for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0, i == 0 && foldTo(l));
     residual(mg, l);
     restrictTo(mg, l, foldTo(l + 1));
@@ -780,7 +872,8 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     }
     endGroup(mg, solo);
   }
-  for (int l = lb - 1; l >= (fused0 ? 1 : 0); l--) {
+  if (tail >= 0) tailLeg(mg, false, false);
+  for (int l = (tail >= 0 ? tail : lb) - 1; l >= (fused0 ? 1 : 0); l--) {
     interpAdd(mg, l);
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }

@@ -15,6 +15,7 @@ void mg_set_smoothing(MgHierarchy* mg, int pre, int post); // setSmoothing
 int  mg_num_levels(const MgHierarchy* mg);
 // ApplyPreconditionMultigrid (conjugategrad.cpp:162-167): dst = one V-cycle on A*dst = rhs from dst = 0
 void mg_apply(MgHierarchy* mg, float* dst, const float* rhs);
+void mg_check_errors(const MgHierarchy* mg);               // raises if a device-side barrier of the V-cycle timed out (call after a stream sync)
 // test hooks
 int  mg_level_size(const MgHierarchy* mg, int l, int* sx, int* sy, int* sz);
 void mg_download_level(MgHierarchy* mg, int l, unsigned char* type, float* A);  // A: n*stencil floats in the reference's interleaved order

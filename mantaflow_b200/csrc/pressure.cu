@@ -85,6 +85,7 @@ struct CgDriver {
   void fetch() {
     s->readSmall(s->hostInts, st, (int)sizeof(CgState));
     memcpy(&host, s->hostInts, sizeof(CgState));
+    if (pcMethod == 2) mg_check_errors(mg);
   }
   // doInit (conjugategrad.cpp:210-235)
   void init(float accuracy, bool useL2) {

@@ -143,14 +143,15 @@ def test_pressure_solve_rowcode_vs_planes(monkeypatch):
     assert np.allclose(res[0][1], res[1][1], rtol=0, atol=2e-5)
 
 
-VC_SIZES = [(64, 50, 37), (8, 8, 8), (60, 29, 33), (120, 31, 18), (56, 26, 64), (116, 60, 41), (4, 70, 9)]
+VC_SIZES = [(64, 50, 37), (8, 8, 8), (60, 29, 33), (120, 31, 18), (56, 26, 64), (116, 60, 41), (4, 70, 9), (128, 96, 80)]
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("size", VC_SIZES)
 def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     """one V(1,1)-cycle: the z-marching wavefront legs (mg_wave0.cuh), the tiled fused legs (mg_fused0.cuh) and the plain
-    per-colour sweeps give bit-identical results; so does the binary16 copy of the level-1 operator (exact by construction)"""
+    per-colour sweeps give bit-identical results; so does the binary16 copy of the level-1 operator (exact by construction)
+    and so do the opt-in persistent small-level kernels (mg_tail.cuh, MF_MG_TAIL=1)"""
     from mantaflow_b200 import manta
     from mantaflow_b200._lib import lib, check
     rs = np.random.RandomState(21)
@@ -161,8 +162,8 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
     outs = []
     fmt = []
-    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}, {"MF_MG_NOFOLD": "1"}):
-        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF", "MF_MG_NOFOLD"):
+    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}, {"MF_MG_NOFOLD": "1"}, {"MF_MG_TAIL": "1"}):
+        for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF", "MF_MG_NOFOLD", "MF_MG_TAIL"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -179,9 +180,10 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
             check(lib().mf_mg_level_format(s._h, 1, Ct.byref(b)))
         fmt.append(b.value)
         manta.releaseMG(s)
-    assert fmt in ([2, 2, 2, 4, 2], [0, 0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
+    assert fmt in ([2, 2, 2, 4, 2, 2], [0, 0, 0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
     assert np.array_equal(outs[3].view(np.int32), outs[2].view(np.int32)), "binary16 level-1 operator changes the V-cycle"
     assert np.array_equal(outs[4].view(np.int32), outs[0].view(np.int32)), "folding the first colour-0 sweep into the restriction changes the V-cycle"
+    assert np.array_equal(outs[5].view(np.int32), outs[0].view(np.int32)), "persistent small-level kernels change the V-cycle"
     assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
     assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
     assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
@@ -222,3 +224,35 @@ def test_vcycle_wavefront_partitioned(nranks, monkeypatch):
         if comm is not None:
             comm.destroy()
     assert np.array_equal(got.view(np.int32), ref.view(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gridtype", ["RealGrid", "MACGrid"])
+@pytest.mark.parametrize("order,clampMode", [(1, 2), (2, 2), (2, 1)])
+def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
+    """the 32-bit-index advection kernels (advect_fast.cuh: 3-D, linear interpolation, first-order trace) against the generic
+    ones (MF_ADVECT_GENERIC=1) on a grid with obstacles, empty cells and velocities of up to ~6 cells per step (so that traces
+    leave the grid and hit every edge case of BUILD_INDEX and of the clamp lookups): bit-identical"""
+    from mantaflow_b200 import manta
+    size = (70, 45, 38)
+    rs = np.random.RandomState(31)
+    f = _flags(rs, size, 3)
+    vel0 = ((rs.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5)) * np.float32(12.0))
+    vel0[rs.rand(size[2], size[1], size[0]) < 0.5] *= np.float32(0.05)
+    d0 = rs.rand(size[2], size[1], size[0]).astype(np.float32)
+    outs = []
+    for generic in (False, True):
+        monkeypatch.delenv("MF_ADVECT_GENERIC", raising=False)
+        if generic:
+            monkeypatch.setenv("MF_ADVECT_GENERIC", "1")
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        vel = s.create(manta.MACGrid); vel.from_numpy(vel0)
+        if gridtype == "RealGrid":
+            g = s.create(manta.RealGrid); g.from_numpy(d0)
+        else:
+            g = vel
+        manta.advectSemiLagrange(flags=flags, vel=vel, grid=g, order=order, clampMode=clampMode)
+        outs.append(g.to_numpy())
+    assert np.isfinite(outs[0]).all()
+    assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32))
