@@ -302,17 +302,19 @@ template <bool HALF> __device__ __forceinline__ const char* mgRowPtr(const LvlD&
 }
 // knSmoothColor, l > 0: one vertex of one of the 8 (4) colours (multigrid.cpp:668-711)
 template <bool IS3D, bool HALF>
-__global__ void __launch_bounds__(128) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0) {
+__global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0) {
   MF_PDL_PROLOGUE
   BlkPos q;
   if (!mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
   // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
   // reference's own division below would not be finite
+  // The diagonal is loaded with the rest of the row and only the store is predicated: a vertex is one batch of loads (one trip
+  // to L2 / DRAM instead of two) -- the sweeps of the small levels are pure latency.  (128, 6): up to 80 registers, enough for
+  // the compiler to issue all 54 loads before the first use (with 32 registers it interleaved them in three dependent rounds).
   const char* ap = mgRowPtr<HALF>(L, q.p);
   const float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
-  if (diag == 0.f) return;
   const float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
-  L.x[q.p] = sum / diag;
+  if (diag != 0.f) L.x[q.p] = sum / diag;
 }
 // knCalcResidual, l > 0; blockIdx.z = colour
 template <bool IS3D, bool HALF, int C>
@@ -323,7 +325,7 @@ __device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, i
   L.r[q.p] = mgStencilSub<IS3D, true, HALF>(mgRowPtr<HALF>(L, q.p), reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
 }
 template <bool IS3D, bool HALF>
-__global__ void __launch_bounds__(128) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0) {
+__global__ void __launch_bounds__(128, 6) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0) {
   MF_PDL_PROLOGUE
   switch (blockIdx.z) {       // the colour selects compile-time positions in the offset table
     case 0: mgResidualItem<IS3D, HALF, 0>(L, O, lz0); break;
@@ -350,7 +352,7 @@ __device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int
   const int vx = t % C.sx; const int u = t / C.sx; const int vy = u % C.sy, vz = z0 + u / C.sy;
   if (vz >= z1) return;
   const int v = mgIdx(C, vx, vy, vz);
-  if (mgRowZero(C, v)) { C.x[v] = 0.f; return; }       // inactive coarse vertex (all-zero row): b stays 0
+  const float diag = mgDiag(C, v);        // loaded with the residuals (one trip to memory), tested after the sum
   float sum = 0.f;
   const float* fr = F.r;
   if (F.perm) {
@@ -374,8 +376,9 @@ __device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int
           sum += rw * fr[mgIdx(F, x, y, z)];
         }
   }
+  if (diag == 0.f) { C.x[v] = 0.f; return; }           // inactive coarse vertex (all-zero row): b stays 0
   C.b[v] = sum;
-  C.x[v] = mgFoldFirst(C, v, vx, vy, vz, sum, fold);
+  C.x[v] = (fold && ((vx | vy | vz) & 1) == 0) ? sum / diag : 0.f;      // mgFoldFirst
 }
 template <bool IS3D>
 __global__ void __launch_bounds__(128) k_mg_restrict(LvlD F, LvlD C, int z0, int z1, int fold) {
@@ -388,14 +391,15 @@ __device__ __forceinline__ void mgInterpAddItem(const LvlD& F, const LvlD& C, in
   const int vx = t % F.sx; const int u = t / F.sx; const int vy = u % F.sy, vz = z0 + u / F.sy;
   if (vz >= z1) return;
   const int v = mgIdx(F, vx, vy, vz);
-  if (F.perm ? mgRowZero(F, v) : (F.type[v] == vtInactive)) return;
+  const bool off = F.perm ? mgRowZero(F, v) : (F.type[v] == vtInactive);     // tested after the loads (one trip to memory)
+  const float xo = F.x[v];
   float sum = 0.f;
   const float* cx = C.x;
   for (int z = vz / 2; z <= (vz + 1) / 2; z++)
     for (int y = vy / 2; y <= (vy + 1) / 2; y++)
       for (int x = vx / 2; x <= (vx + 1) / 2; x++) sum += cx[mgIdx(C, x, y, z)];
   const float iw = 1.0f / (float)(1 << ((vx % 2) + (vy % 2) + (vz % 2)));
-  F.x[v] += iw * sum;
+  if (!off) F.x[v] = xo + iw * sum;
 }
 __global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, int z1) {
   MF_PDL_PROLOGUE
