@@ -204,7 +204,7 @@ __device__ __forceinline__ float mcMacCompF(const GeoF& g, const int* __restrict
 }
 
 template <int CM>
-__global__ void __launch_bounds__(256) k_mc_mac_f(Geo gg, const int* __restrict__ flags, CV3 vel, CV3 orig, CV3 fwd, V3 dst, float dt, float strength) {
+__global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restrict__ flags, CV3 vel, CV3 orig, CV3 fwd, V3 dst, float dt, float strength) {
   IJK_FROM_BLOCK_F
   const int f = flags[idx];
   const int fxm = (i > 0) ? flags[idx - 1] : MF_FLUID, fym = (j > 0) ? flags[idx - g.nx] : MF_FLUID, fzm = (k > 0) ? flags[idx - g.Z] : MF_FLUID;
