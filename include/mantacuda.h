@@ -224,6 +224,27 @@ int          mf_apply_matrix(const mf_grid* flags, mf_grid* dst, const mf_grid* 
 /* dst = A(flags) * src through the CG's 16-bit row codes (MakeLaplaceMatrix without fractions + ApplyMatrix fused; needs
    nx % 4 == 0): must equal mf_make_laplace_matrix + mf_apply_matrix bit for bit. */
 int          mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* src);
+/* ---- GridCg as an object: the interface the reference's C++-side clients drive directly (GridCgInterface, conjugategrad.h:27-58;
+   callers: pressure.cpp:372-452, fluidguiding.cpp:276-334, waves.cpp:129-133, vortexplugins.cpp:279).
+   mf_cg_create = GridCg<ApplyMatrix>(dst, rhs, residual, search, flags, tmp, A0, Ai, Aj, Ak) (conjugategrad.cpp:201; ApplyMatrix2D on a
+   2-D solver): all grids stay owned by the caller and must outlive the object; accuracy starts at VECTOR_EPSILON (1e-6), the norm
+   is the L2 one (GridCgInterface() :31) until mf_cg_set_use_l2_norm(cg, 0).  iterate / solve follow conjugategrad.cpp:238-308:
+   the first call initialises (dst = 0, residual = rhs, preconditioner set-up, sigma); *notConverged = iterate()'s return value.
+   method: 0 PC_None, 1 PC_ICP, 2 PC_mICP (both run the red-black modified IC(0) of this library, 3-D only as in the reference:
+   silently disabled in 2-D, conjugategrad.cpp:315-321), 3 PC_MGP (the solver's cached GridMg -- gMapMG, pressure.cpp:250 -- is
+   created / set up from A0..Ak on first use; rebuild != 0 drops a cached hierarchy first, like passing a fresh GridMg). */
+typedef struct mf_cg mf_cg;
+mf_cg*       mf_cg_create(mf_grid* dst, mf_grid* rhs, mf_grid* residual, mf_grid* search, const mf_grid* flags, mf_grid* tmp,
+                          mf_grid* A0, mf_grid* Ai, mf_grid* Aj, mf_grid* Ak);
+void         mf_cg_destroy(mf_cg* cg);
+int          mf_cg_set_ic_preconditioner(mf_cg* cg, int method);                 /* setICPreconditioner, conjugategrad.cpp:311 */
+int          mf_cg_set_mg_preconditioner(mf_cg* cg, int method, int rebuild);    /* setMGPreconditioner, conjugategrad.cpp:329 */
+int          mf_cg_set_accuracy(mf_cg* cg, float accuracy);                      /* setAccuracy */
+int          mf_cg_set_use_l2_norm(mf_cg* cg, int useL2);                        /* setUseL2Norm */
+int          mf_cg_force_reinit(mf_cg* cg);                                      /* forceReinit */
+int          mf_cg_iterate(mf_cg* cg, int* notConverged);                        /* iterate, conjugategrad.cpp:238 */
+int          mf_cg_solve(mf_cg* cg, int maxIter);                                /* solve, conjugategrad.cpp:302 */
+int          mf_cg_get(mf_cg* cg, float* sigma, float* iterations, float* resNorm, float* accuracy);   /* getSigma / getIterations / getResNorm / getAccuracy */
 /* cgSolveDiffusion(flags, grid, alpha, cgMaxIterFac, cgAccuracy), conjugategrad.cpp:350 */
 int          mf_cg_solve_diffusion(const mf_grid* flags, mf_grid* grid, float alpha, float cgMaxIterFac, float cgAccuracy);
 

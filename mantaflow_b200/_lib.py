@@ -149,6 +149,16 @@ SIGNATURES = {
     "mf_apply_matrix": (_i, [_P, _P, _P, _P, _P, _P, _P]),
     "mf_apply_laplace_rowcode": (_i, [_P, _P, _P]),
     "mf_cg_solve_diffusion": (_i, [_P, _P, _f, _f, _f]),
+    "mf_cg_create": (_P, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "mf_cg_destroy": (None, [_P]),
+    "mf_cg_set_ic_preconditioner": (_i, [_P, _i]),
+    "mf_cg_set_mg_preconditioner": (_i, [_P, _i, _i]),
+    "mf_cg_set_accuracy": (_i, [_P, _f]),
+    "mf_cg_set_use_l2_norm": (_i, [_P, _i]),
+    "mf_cg_force_reinit": (_i, [_P]),
+    "mf_cg_iterate": (_i, [_P, C.POINTER(_i)]),
+    "mf_cg_solve": (_i, [_P, _i]),
+    "mf_cg_get": (_i, [_P, C.POINTER(_f), C.POINTER(_f), C.POINTER(_f), C.POINTER(_f)]),
     "mf_mg_info": (_i, [_P, C.POINTER(_i), C.POINTER(_i)]),
     "mf_mg_level_size": (_i, [_P, _i, C.POINTER(_i)]),
     "mf_mg_level_format": (_i, [_P, _i, C.POINTER(_i)]),

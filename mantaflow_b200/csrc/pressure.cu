@@ -103,7 +103,7 @@ struct CgDriver {
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
   }
   template <bool V4> void iterateT() {
-    if (v.code) { MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n), 256, g, sp, v, st, redCtx(s, r)); } }
+    if (v.code) { MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n, 5), 256, g, sp, v, st, redCtx(s, r)); } }
     else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); } }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
     if (pcMethod == 0) {
@@ -395,6 +395,149 @@ int mf_cg_solve_diffusion(const mf_grid* flagsp, mf_grid* gridp, float alpha, fl
     cg.init(cgAccuracy, true);      // GridCgInterface() defaults to the L2 norm (conjugategrad.h:31)
     cg.solve(maxIter, 8);
   }
+  MF_API_END
+}
+
+// ---- GridCg as an object (GridCgInterface, conjugategrad.h:27-58) ----------------------------------------------------------
+namespace mf {
+struct CgObject {
+  Solver* s;
+  CgDriver drv;
+  CgState* state;       // this object's device state (several GridCg objects may be alive on one solver)
+  const Grid *A0, *Ai, *Aj, *Ak; const Grid* flags;
+  float accuracy; bool useL2; bool inited; int method; bool rebuildMg;
+  float* pc;            // red-black IC diagonal (from the solver's pool while a preconditioned solve is set up)
+};
+static void cgObjInit(CgObject* c) {
+  Solver* s = c->s;
+  CgDriver& d = c->drv;
+  d.pcMethod = 0; d.P = nullptr; d.mg = nullptr;
+  if ((c->method == 1 || c->method == 2) && s->is3D) {
+    if (!c->pc) c->pc = s->getReal();
+    d.pcMethod = 1; d.P = c->pc;
+    MF_LAUNCH_IJK(s, k_rbic_init, c->flags->di(), d.P, c->A0->d, c->Ai->d, c->Aj->d, c->Ak->d);
+  } else if (c->method == 3) {
+    if (c->rebuildMg && s->mg) { mg_destroy(s->mg); s->mg = nullptr; }
+    c->rebuildMg = false;
+    if (!s->mg) s->mg = mg_create(s);
+    d.pcMethod = 2; d.mg = s->mg;
+    if (!mg_is_a_set(d.mg)) mg_set_a(d.mg, c->A0->d, c->Ai->d, c->Aj->d, c->Ak->d);      // InitPreconditionMultigrid (conjugategrad.cpp:100-106)
+    mg_set_coarsest_accuracy(d.mg, c->accuracy * 1E-4f);
+    mg_set_smoothing(d.mg, 1, 1);
+  }
+  d.init(c->accuracy, c->useL2);
+  c->inited = true;
+}
+}
+
+mf_cg* mf_cg_create(mf_grid* dst, mf_grid* rhs, mf_grid* residual, mf_grid* search, const mf_grid* flags, mf_grid* tmp,
+                    mf_grid* A0, mf_grid* Ai, mf_grid* Aj, mf_grid* Ak) {
+  mf_cg* out = nullptr;
+  auto body = [&]() -> int {
+    MF_API_BEGIN
+    REQ_GRID(flags, G(flags)->isInt(), "flags", "GridCg");
+    const mf_grid* gs[9] = { dst, rhs, residual, search, tmp, A0, Ai, Aj, Ak };
+    const char* names[9] = { "dst", "rhs", "residual", "search", "tmp", "A0", "Ai", "Aj", "Ak" };
+    for (int i = 0; i < 9; i++) {
+      mfAssert(gs[i] && G(gs[i])->isReal(), "GridCg: argument '" << names[i] << "' has the wrong grid type or is missing");
+      check_same_solver(G(flags), G(gs[i]), "GridCg");
+    }
+    Solver* s = G(flags)->s; s->use();
+    mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "GridCg: grid too small");
+    CgObject* c = new CgObject();
+    c->s = s; c->A0 = G(A0); c->Ai = G(Ai); c->Aj = G(Aj); c->Ak = G(Ak); c->flags = G(flags);
+    c->accuracy = 1e-6f; c->useL2 = true; c->inited = false; c->method = 0; c->rebuildMg = false; c->pc = nullptr;
+    CUDA_CHECK(cudaMalloc(&c->state, sizeof(CgState)));
+    CUDA_CHECK(cudaMemset(c->state, 0, sizeof(CgState)));
+    CgDriver& d = c->drv;
+    d.s = s; d.st = c->state; d.P = nullptr; d.mg = nullptr; d.pcMethod = 0;
+    d.v.flags = G(flags)->di(); d.v.dst = G(dst)->d; d.v.residual = G(residual)->d; d.v.search = G(search)->d; d.v.tmp = G(tmp)->d;
+    d.v.rhs = G(rhs)->d; d.v.A0 = G(A0)->d; d.v.Ai = G(Ai)->d; d.v.Aj = G(Aj)->d; d.v.Ak = G(Ak)->d;
+    d.v.code = nullptr; d.v4 = (s->nx % 4 == 0);
+    memset(&d.host, 0, sizeof(d.host)); d.host.resNorm = 1e20f;
+    out = reinterpret_cast<mf_cg*>(c);
+    MF_API_END
+  };
+  return body() == 0 ? out : nullptr;
+}
+void mf_cg_destroy(mf_cg* cg) {
+  if (!cg) return;
+  CgObject* c = reinterpret_cast<CgObject*>(cg);
+  cudaStreamSynchronize(c->s->stream);
+  if (c->pc) c->s->putReal(c->pc);
+  cudaFree(c->state);
+  delete c;
+}
+#define CG_OBJ(fn) mfAssert(cg, fn ": null GridCg"); CgObject* c = reinterpret_cast<CgObject*>(cg); c->s->use();
+int mf_cg_set_ic_preconditioner(mf_cg* cg, int method) {
+  MF_API_BEGIN
+  CG_OBJ("setICPreconditioner")
+  mfAssert(method == 1 || method == 2, "GridCg<APPLYMAT>::setICPreconditioner: Invalid method specified.");
+  c->method = c->s->is3D ? method : 0;      // 2-D: disabled (conjugategrad.cpp:315-321)
+  MF_API_END
+}
+int mf_cg_set_mg_preconditioner(mf_cg* cg, int method, int rebuild) {
+  MF_API_BEGIN
+  CG_OBJ("setMGPreconditioner")
+  mfAssert(method == 3, "GridCg<APPLYMAT>::setMGPreconditioner: Invalid method specified.");
+  c->method = 3; c->rebuildMg = rebuild != 0;
+  MF_API_END
+}
+int mf_cg_set_accuracy(mf_cg* cg, float accuracy) {
+  MF_API_BEGIN
+  CG_OBJ("setAccuracy")
+  c->accuracy = accuracy;
+  if (c->inited) {        // takes effect on the next iterate(), as mAccuracy does
+    c->drv.fetch();
+    CgState h = c->drv.host; h.accuracy = accuracy;
+    c->s->writeSmall(c->state, &h, (int)sizeof(h));
+  }
+  MF_API_END
+}
+int mf_cg_set_use_l2_norm(mf_cg* cg, int useL2) {
+  MF_API_BEGIN
+  CG_OBJ("setUseL2Norm")
+  c->useL2 = useL2 != 0;
+  if (c->inited) {
+    c->drv.fetch();
+    CgState h = c->drv.host; h.useL2 = useL2 ? 1 : 0;
+    c->s->writeSmall(c->state, &h, (int)sizeof(h));
+  }
+  MF_API_END
+}
+int mf_cg_force_reinit(mf_cg* cg) {
+  MF_API_BEGIN
+  CG_OBJ("forceReinit")
+  c->inited = false;
+  MF_API_END
+}
+int mf_cg_iterate(mf_cg* cg, int* notConverged) {
+  MF_API_BEGIN
+  CG_OBJ("iterate")
+  if (!c->inited) cgObjInit(c);
+  c->drv.iterate();
+  MF_LAUNCH_CHECK();
+  c->drv.fetch();
+  if (c->drv.host.diverged) mfErr("GridCg::iterate: The CG solver diverged, residual norm > 1e30, stopping.");
+  if (notConverged) *notConverged = c->drv.host.done ? 0 : 1;
+  MF_API_END
+}
+int mf_cg_solve(mf_cg* cg, int maxIter) {
+  MF_API_BEGIN
+  CG_OBJ("solve")
+  if (maxIter > 0) {
+    if (!c->inited) cgObjInit(c);
+    c->drv.solve(maxIter, c->drv.pcMethod == 2 ? 1 : 8);
+  }
+  MF_API_END
+}
+int mf_cg_get(mf_cg* cg, float* sigma, float* iterations, float* resNorm, float* accuracy) {
+  MF_API_BEGIN
+  CG_OBJ("get")
+  if (sigma) *sigma = c->drv.host.sigma;
+  if (iterations) *iterations = (float)c->drv.host.iterations;
+  if (resNorm) *resNorm = c->drv.host.resNorm;
+  if (accuracy) *accuracy = c->accuracy;
   MF_API_END
 }
 

@@ -122,9 +122,10 @@ inline void redFinish(Solver* s, const RedOps<K>& ops, Fin fin) {
   s->redParity ^= 1;
 }
 
-inline int redBlocks(const Solver* s, long long n) {
+// perSM: CTAs of the kernel one SM holds (grid-stride kernels: a grid of exactly the resident CTAs has no partial last wave)
+inline int redBlocks(const Solver* s, long long n, int perSM = 8) {
   long long b = (n + RED_THREADS * 4 - 1) / (RED_THREADS * 4);
-  long long cap = (long long)s->numSMs * 8;
+  long long cap = (long long)s->numSMs * perSM;
   if (cap > RED_MAX_BLOCKS) cap = RED_MAX_BLOCKS;
   if (b > cap) b = cap;
   if (b < 1) b = 1;

@@ -18,7 +18,7 @@ __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "add
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
            "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
            "updateFractions", "setObstacleFlags", "densityInflow", "addNoise", "getComponent", "setComponent",
-           "sampleFlagsWithParticles", "mapPartsToMAC", "markFluidCells", "mapMACToParts", "flipVelocityUpdate"]
+           "sampleFlagsWithParticles", "mapPartsToMAC", "markFluidCells", "mapMACToParts", "flipVelocityUpdate", "GridCg"]
 
 
 def _h(g):
@@ -198,6 +198,50 @@ def cgSolveDiffusion(flags=None, grid=None, alpha=0.25, cgMaxIterFac=1.0, cgAccu
     M._checkArgs("cgSolveDiffusion", kwargs, ())
     _req(flags, M.FlagGrid, "flags", "cgSolveDiffusion"); _req(grid, M.GridBase, "grid", "cgSolveDiffusion")
     check(lib().mf_cg_solve_diffusion(flags._h, grid._h, float(alpha), float(cgMaxIterFac), float(cgAccuracy)))
+
+
+class GridCg(object):
+    """GridCg<ApplyMatrix> (conjugategrad.h:65-116) for C++-style clients of the solver: the reference does not expose this class to
+    Python, its plugins drive it directly (pressure.cpp:372-452, waves.cpp:129, vortexplugins.cpp:279, fluidguiding.cpp:276).  Same
+    method names and semantics; the grids stay owned by the caller."""
+    PC_None, PC_ICP, PC_mICP, PC_MGP = 0, 1, 2, 3
+
+    def __init__(self, dst, rhs, residual, search, flags, tmp, A0, Ai, Aj, Ak):
+        self._keep = (dst, rhs, residual, search, flags, tmp, A0, Ai, Aj, Ak)
+        self._h = lib().mf_cg_create(dst._h, rhs._h, residual._h, search._h, flags._h, tmp._h, A0._h, Ai._h, Aj._h, Ak._h)
+        if not self._h:
+            check(1)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().mf_cg_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def setICPreconditioner(self, method, A0=None, Ai=None, Aj=None, Ak=None): check(lib().mf_cg_set_ic_preconditioner(self._h, int(method)))
+    def setMGPreconditioner(self, method, MG=None, rebuild=False): check(lib().mf_cg_set_mg_preconditioner(self._h, int(method), 1 if rebuild else 0))
+    def setAccuracy(self, a): check(lib().mf_cg_set_accuracy(self._h, float(a)))
+    def setUseL2Norm(self, b): check(lib().mf_cg_set_use_l2_norm(self._h, 1 if b else 0))
+    def forceReinit(self): check(lib().mf_cg_force_reinit(self._h))
+
+    def iterate(self):
+        r = C.c_int()
+        check(lib().mf_cg_iterate(self._h, C.byref(r)))
+        return bool(r.value)
+
+    def solve(self, maxIter): check(lib().mf_cg_solve(self._h, int(maxIter)))
+
+    def _get(self, i):
+        v = [C.c_float() for _ in range(4)]
+        check(lib().mf_cg_get(self._h, *[C.byref(x) for x in v]))
+        return v[i].value
+
+    def getSigma(self): return self._get(0)
+    def getIterations(self): return self._get(1)
+    def getResNorm(self): return self._get(2)
+    def getAccuracy(self): return self._get(3)
 
 
 def _maxDiff(g1, g2):

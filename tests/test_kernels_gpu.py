@@ -256,3 +256,70 @@ def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
         outs.append(g.to_numpy())
     assert np.isfinite(outs[0]).all()
     assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pc", ["none", "mic", "mg"])
+@pytest.mark.parametrize("dim", [3, 2])
+def test_gridcg_object_matches_solve_pressure(pc, dim, monkeypatch):
+    """GridCg driven as an object, the way the reference's C++ plugins do (solvePressureSystem, pressure.cpp:372-452: matrix,
+    GridCg(dst, rhs, residual, search, flags, tmp, A0..Ak), setAccuracy, setUseL2Norm(false), set*Preconditioner, iterate until
+    it returns false), must produce the pressure of the solvePressureSystem plugin bit for bit, with the same iteration count;
+    then the accessors, forceReinit and solve(maxIter)."""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    monkeypatch.setattr(manta, "allowPcNone", True)    # the plugin refuses precondition=False like the reference (pressure.cpp:417)
+    monkeypatch.setenv("MF_CG_PLANES", "1")      # the plugin's CG reads the float coefficient planes too (same kernels, same reduction grids)
+    size = (28, 22, 18) if dim == 3 else (40, 30, 1)
+    rs = np.random.RandomState(17)
+    f = _flags(rs, size, dim)
+    f[f == EMPTY] = FLUID
+    nz, ny, nx = f.shape
+    f[nz // 2, ny // 2, nx // 2] = EMPTY
+    vel0 = (rs.rand(nz, ny, nx, 3).astype(np.float32) - np.float32(0.5))
+    if dim == 2:
+        vel0[..., 2] = 0
+    s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=dim)
+    flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+    vel = s.create(manta.MACGrid); vel.from_numpy(vel0)
+    p_ref = s.create(manta.RealGrid); rhs = s.create(manta.RealGrid)
+    pcs = {"none": dict(precondition=False), "mic": dict(preconditioner=manta.PcMIC), "mg": dict(preconditioner=manta.PcMGDynamic)}[pc]
+    manta.computePressureRhs(rhs=rhs, vel=vel, pressure=p_ref, flags=flags)
+    manta.solvePressureSystem(rhs=rhs, vel=vel, pressure=p_ref, flags=flags, cgAccuracy=1e-5, **pcs)
+    info = dict(manta.getSolveInfo())
+    manta.releaseMG(s)
+    # the same through the object
+    dst, residual, search, tmp, A0, Ai, Aj, Ak = [s.create(manta.RealGrid) for _ in range(8)]
+    check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
+    cg = manta.GridCg(dst, rhs, residual, search, flags, tmp, A0, Ai, Aj, Ak)
+    assert cg.getAccuracy() == np.float32(1e-6) and cg.getIterations() == 0
+    cg.setAccuracy(1e-5)
+    cg.setUseL2Norm(False)
+    if pc == "mic":
+        cg.setICPreconditioner(manta.GridCg.PC_mICP, A0, Ai, Aj, Ak)
+    elif pc == "mg":
+        cg.setMGPreconditioner(manta.GridCg.PC_MGP, None, rebuild=True)
+    it = 0
+    while it < info["maxIter"]:
+        it += 1
+        if not cg.iterate():
+            break
+    assert cg.getIterations() == it == info["iterations"]
+    assert np.array_equal(dst.to_numpy().view(np.int32), p_ref.to_numpy().view(np.int32))
+    assert abs(cg.getResNorm() - info["resNorm"]) <= 1e-12
+    if cg.getResNorm() < 1e-5:                         # (the unpreconditioned solve may stop at maxIter instead)
+        assert cg.getSigma() == cg.getResNorm()        # mSigma = mResNorm on convergence (conjugategrad.cpp:276)
+    else:
+        assert it == info["maxIter"]
+    if pc == "mg":
+        assert cg.getResNorm() < 1e-5
+    # a second solve with the same object: forceReinit + solve(maxIter) reproduces it
+    first = dst.to_numpy()
+    cg.forceReinit()
+    cg.solve(info["maxIter"])
+    assert cg.getIterations() == info["iterations"]
+    assert np.array_equal(dst.to_numpy().view(np.int32), first.view(np.int32))
+    with pytest.raises(manta.MantaError):
+        cg.setICPreconditioner(manta.GridCg.PC_MGP)
+    del cg
+    manta.releaseMG(s)
