@@ -82,6 +82,8 @@ def _parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--code-cache", action="store_true", help="let solvePressure reuse the CG's Laplace row codes while the flag grid is unchanged "
+                    "(library default; the bench rebuilds the matrix every step like the reference does, so that no work of the step is skipped)")
     ap.add_argument("--profile-steps", type=int, default=3)
     ap.add_argument("--kernels-out", default="", help="write the complete per-kernel table (JSON) to this file")
     return ap.parse_args()
@@ -211,6 +213,8 @@ class Plume(object):
 
 def main():
     a = _parse()
+    if not a.code_cache:
+        os.environ["MF_CG_NOCODECACHE"] = "1"     # every step builds its matrix, as the reference's solvePressureSystem does
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -221,6 +225,7 @@ def main():
     config = {"workload": "smoke plume %dx%dx%d, MacCormack (order 2) advection of density+velocity, setWallBcs, addBuoyancy, "
                           "solvePressure %s, cgAccuracy 1e-3, zeroPressureFixing" % (size + (pcname,)),
               "grid": list(size), "cells_per_gpu": cells // world, "dt": 1.0,
+              "matrix": "row codes reused while the flags are unchanged" if a.code_cache else "rebuilt every step (MF_CG_NOCODECACHE=1)",
               "l2": "working set per step > 1 GiB (>> 126 MB L2), no flush needed" if a.size >= 256 else "L2-resident working set",
               "parallelism": ("z-slab x%d (one global address space over NVLink, device flag barrier per launch group), %s scaling"
                               % (world, "strong" if a.strong else "weak")) if world > 1 else "single GPU"}

@@ -47,6 +47,7 @@ struct Grid {
   float* d;          // device storage (int grids reinterpret)
   bool pooled;       // storage came from the solver pool
   mutable int outflowState;  // flag grids: -1 unknown, 0 no TypeOutflow cell, 1 some (cache for applyOutflowBC)
+  mutable unsigned long long version;   // changes whenever an entry point may have written the grid's cells as flags (markFlagsChanged)
   mutable GridXfer* xfer;    // owned by the grid created through mf_grid_create (temporary Grid copies never touch it)
   bool isVec() const { return (type & MF_TYPE_VEC3) != 0; }
   bool isMAC() const { return (type & MF_TYPE_MAC) != 0; }
@@ -82,6 +83,9 @@ struct Solver {
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
   float* noiseTile;         // 3 x 128^3 wavelet-noise tile (noise.cu), uploaded on first use
   unsigned short* cgCode;   // 16-bit Laplace row codes for the CG's ApplyMatrix (pressure_kernels.cuh CGC_*), lazily allocated
+  // the row codes (and the pinned cell of zeroPressureFixing) depend on the flags only: kept while the same flag storage holds
+  // the same version (single-GPU solvers)
+  const void* codeFlags; unsigned long long codeVersion; int codeFixing; int codeFixedCell;
   int numSMs;
   // ---- z-slab partition over GPUs (comm.h).  Single GPU: nranks = 1, comm = nullptr.
   Comm* comm;           // not owned
@@ -118,6 +122,10 @@ struct Solver {
 };
 
 inline float* Grid::comp(int c) const { return d + (long long)c * s->Np; }
+// every entry point that writes a flag (int) grid calls this: drops the caches derived from the flags (outflow scan of
+// applyOutflowBC, the CG's Laplace row codes and flag statistics of solvePressureSystem)
+unsigned long long nextGridVersion();
+inline void markFlagsChanged(const Grid* g) { g->outflowState = -1; g->version = nextGridVersion(); }
 
 // RAII temp grids
 struct TmpReal { Solver* s; float* p; TmpReal(Solver* s_) : s(s_), p(s_->getReal()) {} ~TmpReal() { s->putReal(p); } operator float*() const { return p; } };

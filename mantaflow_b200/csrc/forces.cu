@@ -328,7 +328,7 @@ int mf_flags_init_domain(mf_grid* fp, int boundaryWidth, const char* wallIn, con
   MF_API_BEGIN
   REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::initDomain");
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
-  flags->outflowState = -1;
+  markFlagsChanged(flags);
   std::string wall = wallIn ? wallIn : "xXyYzZ", open = openIn ? openIn : "", inflow = inflowIn ? inflowIn : "", outflow = outflowIn ? outflowIn : "";
   wall.append("      "); open.append("      "); inflow.append("      "); outflow.append("      ");
   Types6 types; bool set[6] = { false, false, false, false, false, false };
@@ -358,7 +358,7 @@ int mf_flags_fill_grid(mf_grid* fp, int type) {
   MF_API_BEGIN
   REQ_GRID(fp, G(fp)->isInt(), "flags", "FlagGrid::fillGrid");
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
-  flags->outflowState = -1;
+  markFlagsChanged(flags);
   MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_fill_grid, s->numSMs * 8, 256, flags->di() + sp.off, type, sp.n); }
   s->rankSync();
   MF_LAUNCH_CHECK();
@@ -383,7 +383,7 @@ int mf_flags_set_open_bound(mf_grid* fp, int bWidth, const char* openBound, int 
   REQ_GRID(fp, G(fp)->isInt(), "flags", "setOpenBound");
   if (!openBound || !*openBound) return 0;
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
-  flags->outflowState = -1;
+  markFlagsChanged(flags);
   int lo, up; parseDesc(openBound, lo, up, "setOpenBound");
   MF_LAUNCH_IJK(s, k_set_open_bound, flags->di(), bWidth, lo, up, type);
   MF_LAUNCH_CHECK();
@@ -415,7 +415,7 @@ int mf_apply_box_to_flags(mf_grid* gp, float x0, float y0, float z0, float x1, f
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isInt(), "grid", "Shape::applyToGrid");
   Grid* gr = G(gp); Solver* s = gr->s; s->use();
-  gr->outflowState = -1;
+  markFlagsChanged(gr);
   MF_LAUNCH_IJK(s, k_apply_box<int>, gr->di(), x0, y0, z0, x1, y1, z1, value);
   MF_LAUNCH_CHECK();
   MF_API_END

@@ -496,7 +496,7 @@ int mf_mark_fluid_cells(const mf_parts* pp, mf_grid* flagsG, const mf_grid* phiO
   const Parts* p = P(pp); Solver* s = p->s; s->use();
   Grid* fg = G(flagsG);
   mfAssert(fg->s == s, "markFluidCells: flags and parts belong to different solvers");
-  fg->outflowState = -1;
+  markFlagsChanged(fg);
   const Geo g = geo(s, 0);
   MF_LAUNCH(s, k_clear_fluid_flags, pblocks(s->N), 256, s->N, fg->di());
   if (p->n) MF_LAUNCH(s, k_mark_fluid, pblocks(p->n), 256, g, p->n, (const float*)p->px(), (const float*)p->py(), (const float*)p->pz(), (const int*)p->flag, fg->di());

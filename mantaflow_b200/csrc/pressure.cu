@@ -161,12 +161,19 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   const bool needPlanes = !useCode || (preconditioner == MF_PC_MIC && s->is3D) || (mgPc && !(s->mg && mg_is_a_set(s->mg)));
   if (useCode && !s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
   const float* phiD = p->phi ? G(p->phi)->d : nullptr;
+  int* fixedDev = s->localInts + 2;
+  bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
+  // the row codes and the choice of the pinned cell depend on the flags only: reuse them while the flag grid is unchanged
+  const bool codeCached = useCode && !needPlanes && !s->multi() && s->codeFlags == (const void*)flags->d && s->codeVersion == flags->version &&
+                          s->codeFixing == (fixing ? 1 : 0) && !std::getenv("MF_CG_NOCODECACHE");
+  s->codeFlags = nullptr;
+  if (codeCached) {
+    if (fixing && s->codeFixedCell >= 0) CUDA_CHECK(cudaMemsetAsync(rhs + s->codeFixedCell, 0, sizeof(float), s->stream));   // fixPressure: rhs(cell) = 0
+  } else
   if (useCode && needPlanes) MF_LAUNCH_IJK(s, k_make_laplace<true>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
   else if (useCode) MF_LAUNCH_IJK_W(s, k_make_laplace_code, flags->di(), s->cgCode);
   else MF_LAUNCH_IJK(s, k_make_laplace<false>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0, phiD, p->gfClamp, (unsigned short*)nullptr);
-  int* fixedDev = s->localInts + 2;
-  bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
-  if (fixing) {
+  if (fixing && !codeCached) {
     if (s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<4>, quadTileBlocks(s, g, 4), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
     else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<1>, quadTileBlocks(s, g, 1), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
     redFinish<2>(s, RedOps<2>{ { 0, 1 } }, FinStore<2>{ s->redOut });
@@ -209,10 +216,16 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   if (info) {
     info->iterations = cg.host.iterations; info->resNorm = cg.host.resNorm; info->maxIter = maxIter;
     info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
-    if (fixing) {
+    if (fixing && codeCached) info->fixedCell = s->codeFixedCell;
+    else if (fixing) {
       s->readSmall(s->hostInts, fixedDev, (int)sizeof(int));
       info->fixedCell = s->hostInts[0];
     }
+  }
+  // remember what the row codes were built from (a solve that also wrote the planes rebuilt them, which is just as valid)
+  if (useCode && !s->multi() && (!fixing || codeCached || info)) {
+    if (fixing && !codeCached) s->codeFixedCell = info->fixedCell;
+    s->codeFlags = flags->d; s->codeVersion = flags->version; s->codeFixing = fixing ? 1 : 0;
   }
   if (cg.mg && preconditioner == MF_PC_MG_DYNAMIC) { mg_destroy(s->mg); s->mg = nullptr; }
 }
@@ -359,6 +372,7 @@ int mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* 
   mfAssert(s->nx % 4 == 0, "mf_apply_laplace_rowcode: nx must be a multiple of 4");
   mfAssert(s->nx >= 3 && s->ny >= 3 && (!s->is3D || s->nz >= 3), "mf_apply_laplace_rowcode: grid too small");
   if (!s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
+  s->codeFlags = nullptr;       // the solver's cached row codes are overwritten here
   MF_LAUNCH_IJK_W(s, k_make_laplace_code, G(flags)->di(), s->cgCode);
   CgState* st = cgStateBuf(s);
   CUDA_CHECK(cudaMemsetAsync(st, 0, sizeof(CgState), s->stream));

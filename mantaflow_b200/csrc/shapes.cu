@@ -138,7 +138,7 @@ int mf_shape_apply(const mf_shape* sh, mf_grid* gp, float vx, float vy, float vz
   Grid* gr = G(gp); Solver* s = gr->s; s->use();
   const ShapeD d = shapeOf(sh);
   const int* rf = respectFlags ? G(respectFlags)->di() : nullptr;
-  if (gr->isInt()) { gr->outflowState = -1; MF_LAUNCH_IJK(s, (k_shape_apply<int, 1>), d, gr->di(), 0LL, ivalue, 0, 0, rf); }
+  if (gr->isInt()) { markFlagsChanged(gr); MF_LAUNCH_IJK(s, (k_shape_apply<int, 1>), d, gr->di(), 0LL, ivalue, 0, 0, rf); }
   else if (gr->isReal()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 1>), d, gr->d, 0LL, vx, 0.f, 0.f, rf);
   else if (gr->isMAC()) MF_LAUNCH_IJK(s, k_shape_apply_mac, d, v3(gr), vx, vy, vz, rf);
   else if (gr->isVec()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 3>), d, gr->d, s->Np, vx, vy, vz, rf);
@@ -163,7 +163,7 @@ int mf_flags_update_from_levelset(mf_grid* flags, const mf_grid* phi) {
   REQ_GRID(phi, G(phi)->isReal(), "levelset", "FlagGrid::updateFromLevelset");
   Grid* f = G(flags); Solver* s = f->s; s->use();
   check_same_solver(f, G(phi), "FlagGrid::updateFromLevelset");
-  f->outflowState = -1;
+  markFlagsChanged(f);
   MF_LAUNCH_IJK(s, k_flags_from_levelset, f->di(), G(phi)->d);
   MF_LAUNCH_CHECK();
   MF_API_END
@@ -202,7 +202,7 @@ int mf_set_obstacle_flags(mf_grid* flags, const mf_grid* phiObs, const mf_grid* 
   if (phiIn) REQ_GRID(phiIn, G(phiIn)->isReal(), "phiIn", "setObstacleFlags");
   Grid* f = G(flags); Solver* s = f->s; s->use();
   check_same_solver(f, G(phiObs), "setObstacleFlags");
-  f->outflowState = -1;
+  markFlagsChanged(f);
   CV3 fr; fr.x = fr.y = fr.z = nullptr; if (fractions) fr = cv3(G(fractions));
   MF_LAUNCH_IJK(s, k_set_obstacle_flags, f->di(), fr, fractions ? 1 : 0, G(phiObs)->d, phiOut ? G(phiOut)->d : (const float*)nullptr,
                 phiIn ? G(phiIn)->d : (const float*)nullptr, boundaryWidth);

@@ -11,6 +11,7 @@ namespace mf { struct Grid; struct Solver; }
 void launch_norm_square(mf::Solver* s, const mf::Grid* g, float* o);
 
 namespace mf {
+unsigned long long nextGridVersion() { static unsigned long long v = 0; return ++v; }   // (API calls are single-threaded per process)
 
 static thread_local std::string g_lastError;
 void set_last_error(const std::string& s) { g_lastError = s; }
@@ -228,7 +229,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   s->dx = (float)(1.0 / mx);       // grid.cpp:57
   s->device = device;
   s->profTag = -1; s->profLevels = getenv("MF_PROFILE_LEVELS") != nullptr;
-  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->noiseTile = nullptr; s->profiling = false; s->copyIn = nullptr; s->copyOut = nullptr;
+  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->codeFlags = nullptr; s->codeVersion = 0; s->codeFixing = 0; s->codeFixedCell = -1; s->noiseTile = nullptr; s->profiling = false; s->copyIn = nullptr; s->copyOut = nullptr;
   for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
   CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
@@ -378,7 +379,7 @@ mf_grid* mf_grid_create(mf_solver* sp, int type) {
     mfAssert(sp, "Grid: null solver");
     Solver* s = S(sp); s->use();
     Grid* g = new Grid();
-    g->s = s; g->type = type; g->pooled = false; g->d = nullptr; g->outflowState = -1; g->xfer = nullptr;
+    g->s = s; g->type = type; g->pooled = false; g->d = nullptr; markFlagsChanged(g); g->xfer = nullptr;
     // Grid ctor clears (grid.cpp:58): galloc zero-fills
     if (type & MF_TYPE_VEC3) g->d = (float*)s->galloc(sizeof(float) * (size_t)s->Np, 3, sizeof(float) * (size_t)s->Np);
     else g->d = (float*)s->galloc(sizeof(float) * (size_t)(s->N + 64));
@@ -402,7 +403,7 @@ int mf_grid_type(const mf_grid* g) { return g ? G(g)->type : 0; }
 int mf_grid_clear(mf_grid* gp) {
   MF_API_BEGIN
   mfAssert(gp, "Grid::clear: null grid");
-  Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
+  Grid* g = G(gp); Solver* s = g->s; s->use(); markFlagsChanged(g);
   forSlabs(s, g, [&](float* p, long long n, int, const Span&) { CUDA_CHECK(cudaMemsetAsync(p, 0, sizeof(float) * n, s->stream)); });
   MF_API_END
 }
@@ -415,7 +416,7 @@ int mf_grid_copy(mf_grid* dp, const mf_grid* sp_) {
   forSlabs(s, d, [&](float* p, long long n, int c, const Span& sp) {
     const float* src = (a->isVec() ? a->comp(c) : a->d) + sp.off;
     CUDA_CHECK(cudaMemcpyAsync(p, src, sizeof(float) * n, cudaMemcpyDeviceToDevice, s->stream)); });
-  d->outflowState = a->outflowState;
+  { const int o = a->outflowState; markFlagsChanged(d); d->outflowState = o; }
   MF_API_END
 }
 // getComponent / setComponent (grid.cpp:743-751): one plane of the SoA vector grid <-> a real grid
@@ -449,7 +450,7 @@ int mf_grid_swap(mf_grid* ap, mf_grid* bp) {
   check_same_solver(a, b, "Grid::swap");
   mfAssert(a->isVec() == b->isVec() && a->isInt() == b->isInt(), "Grid::swap(): Grid types mismatch.");
   float* t = a->d; a->d = b->d; b->d = t;
-  int o = a->outflowState; a->outflowState = b->outflowState; b->outflowState = o;
+  { const int oa = a->outflowState, ob = b->outflowState; markFlagsChanged(a); markFlagsChanged(b); a->outflowState = ob; b->outflowState = oa; }
   MF_API_END
 }
 // host <-> device.  `host` is the FULL grid in the reference layout on every rank (slabOnly == 0: each rank uploads its own
@@ -457,7 +458,7 @@ int mf_grid_swap(mf_grid* ap, mf_grid* bp) {
 // z-slab [k0,k1) (slabOnly == 1; mf_solver_slab).
 static void gridUpload(Grid* g, const void* host, bool slabOnly) {
   Solver* s = g->s; s->use();
-  g->outflowState = -1;
+  markFlagsChanged(g);
   MF_RANKS(s, r) {
     const Span sp = span(s, r);
     if (!sp.n) continue;
@@ -560,7 +561,7 @@ int mf_grid_commit_upload(mf_grid* gp) {
   GridXfer* x = xferOf(g);
   mfAssert(x->inCount > 0, "Grid commit_upload: nothing staged");
   const int k = x->inHead;
-  g->outflowState = -1;
+  markFlagsChanged(g);
   CUDA_CHECK(cudaStreamWaitEvent(s->stream, x->inReady[k], 0));
   const long long base = localSpan(s).off;
   MF_RANKS(s, r) {
@@ -621,7 +622,7 @@ int mf_grid_set_const_real(mf_grid* gp, float v) {
 int mf_grid_set_const_int(mf_grid* gp, int v) {
   MF_API_BEGIN
   REQ_GRID(gp, G(gp)->isInt(), "grid", "Grid<int>::setConst");
-  Grid* g = G(gp); Solver* s = g->s; s->use(); g->outflowState = -1;
+  Grid* g = G(gp); Solver* s = g->s; s->use(); markFlagsChanged(g);
   MF_EW(s, k_fill_i, g->di() + sp.off, v, sp.n); s->rankSync(); MF_LAUNCH_CHECK();
   MF_API_END
 }

@@ -323,3 +323,43 @@ def test_gridcg_object_matches_solve_pressure(pc, dim, monkeypatch):
         cg.setICPreconditioner(manta.GridCg.PC_MGP)
     del cg
     manta.releaseMG(s)
+
+
+@pytest.mark.gpu
+def test_rowcode_cache_follows_flag_changes(monkeypatch):
+    """solvePressureSystem keeps the CG's Laplace row codes (and the pinned cell) while the flag grid is unchanged; every way of
+    writing flags must drop them: the solves with the cache are bit-identical to solves with MF_CG_NOCODECACHE=1"""
+    from mantaflow_b200 import manta
+    size = (32, 24, 20)
+    rs = np.random.RandomState(3)
+    vel0 = (rs.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5))
+
+    def run():
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); vel = s.create(manta.MACGrid); p = s.create(manta.RealGrid); other = s.create(manta.FlagGrid)
+        flags.initDomain(); flags.fillGrid()
+        out = []
+
+        def solve():
+            vel.from_numpy(vel0)
+            manta.setWallBcs(flags=flags, vel=vel)
+            manta.solvePressure(flags=flags, vel=vel, pressure=p, preconditioner=manta.PcMGStatic, zeroPressureFixing=True, cgAccuracy=1e-5)
+            out.append((p.to_numpy(), vel.to_numpy(), manta.getSolveInfo()["iterations"]))
+        solve(); solve()                                   # second solve: cached codes
+        manta.Box(parent=s, p0=manta.vec3(8, 6, 5), p1=manta.vec3(14, 12, 11)).applyToGrid(grid=flags, value=manta.FlagObstacle)
+        manta.releaseMG(s); solve(); solve()               # shape written into the flags
+        f = flags.to_numpy(); f[10:14, 14:18, 20:26] = manta.FlagObstacle; flags.from_numpy(f)
+        manta.releaseMG(s); solve()                        # upload
+        other.initDomain(); other.fillGrid(); flags.swap(other)
+        manta.releaseMG(s); solve()                        # swap
+        flags.copyFrom(other)
+        manta.releaseMG(s); solve(); solve()               # copy
+        return out
+
+    a = run()
+    monkeypatch.setenv("MF_CG_NOCODECACHE", "1")
+    b = run()
+    assert len(a) == len(b) == 8
+    for (pa, va, ia), (pb, vb, ib) in zip(a, b):
+        assert ia == ib and np.array_equal(pa.view(np.int32), pb.view(np.int32)) and np.array_equal(va.view(np.int32), vb.view(np.int32))
+    assert not np.array_equal(a[1][0], a[2][0]) and not np.array_equal(a[3][0], a[4][0]) and not np.array_equal(a[4][0], a[5][0])
