@@ -102,27 +102,59 @@ struct CgDriver {
     MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, sp.n), 256, sp.n, z + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
   }
-  template <bool V4> void iterateT() {
+  // tmp = A search, alpha (conjugategrad.cpp:246-252)
+  void spmv() {
     if (v.code) { MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n, 5), 256, g, sp, v, st, redCtx(s, r)); } }
     else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); } }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
+  }
+  // preconditioned iteration, first half: matrix product, x / residual update, norm and stop test (:246-277; the reference applies
+  // the preconditioner before it tests the norm, but the test does not depend on it)
+  template <bool V4> void headT() {
+    spmv();
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, (k_cg_update<false, V4>), redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
+    redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<false>{ st });
+  }
+  // second half: tmp = M^-1 residual, sigmaNew, beta, new search direction (:262-295)
+  template <bool V4> void tailT() {
+    applyPrecond(false);
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta<V4>, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+    redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
+    s->rankSync();
+  }
+  template <bool V4> void iterateT() {
     if (pcMethod == 0) {
+      spmv();
       MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, (k_cg_update<true, V4>), redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
       redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<true>{ st });
       MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.residual + sp.off, st); }
       s->rankSync();
     } else {
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, (k_cg_update<false, V4>), redBlocks(s, sp.n), 256, sp, v, st, redCtx(s, r)); }
-      redFinish<4>(s, RedOps<4>{ { 0, 1, 2, 0 } }, FinUpdate<false>{ st });
-      applyPrecond(false);
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta<V4>, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
-      redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
-      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
-      s->rankSync();
+      headT<V4>();
+      tailT<V4>();
     }
   }
   void iterate() { if (v4) iterateT<true>(); else iterateT<false>(); }
   // for (iter < maxIter) if (!iterate()) break;   host polls the device flag every `batch` iterations
+  // Multigrid-preconditioned solve: the host reads the stop flag once per iteration anyway (a V-cycle is too expensive to
+  // run ahead of it), so it reads it BETWEEN the two halves: the V-cycle, dot product and search update of the iteration that
+  // converged -- which the reference computes into its temporary grids and never uses -- are not launched.  Same results, one
+  // V-cycle less per solve.  (The GridCg object keeps whole iterations: its caller owns tmp / search and may look at them.)
+  void solveSplit(int maxIter) {
+    host.done = 0; host.diverged = 0; host.iterations = 0;
+    bool fresh = false;
+    for (int it = 0; it < maxIter; it++) {
+      if (v4) headT<true>(); else headT<false>();
+      MF_LAUNCH_CHECK();
+      fetch(); fresh = true;
+      if (host.done) break;
+      if (v4) tailT<true>(); else tailT<false>();
+      fresh = false;
+    }
+    if (!fresh) { MF_LAUNCH_CHECK(); fetch(); }
+    if (host.diverged) mfErr("GridCg::iterate: The CG solver diverged, residual norm > 1e30, stopping.");
+  }
   void solve(int maxIter, int batch) {
     int it = 0;
     host.done = 0; host.diverged = 0; host.iterations = 0;
@@ -212,7 +244,8 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     mgLevels = mg_num_levels(cg.mg);
   }
   cg.init(p->cgAccuracy, p->useL2Norm != 0);
-  cg.solve(maxIter, batch);
+  if (cg.pcMethod == 2 && !std::getenv("MF_CG_WHOLE_ITERATIONS")) cg.solveSplit(maxIter);
+  else cg.solve(maxIter, batch);
   if (info) {
     info->iterations = cg.host.iterations; info->resNorm = cg.host.resNorm; info->maxIter = maxIter;
     info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
