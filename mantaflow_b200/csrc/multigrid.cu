@@ -187,8 +187,10 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
   }
   if (in) L.x[p] = (float)x;
 }
-template <bool LEVEL0>
-__global__ void __launch_bounds__(1024) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
+// MAXT = 768: up to 85 registers per thread -- with 1024 threads (64 registers) the 27 coefficients and the double state of the
+// iteration spill to local memory inside the loop
+template <bool LEVEL0, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
   MF_PDL_PROLOGUE
   __shared__ double sh[2][32];
   __shared__ double out[4];
@@ -867,8 +869,12 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
     beginGroup(mg, solo);
     s->profTag = lb;
     if (s->rankBegin == 0) {
-      if (maxLevel == 0) { MF_LAUNCH_PDL(s, k_mg_coarse_cg<true>, 1, (unsigned)((L0.n + 31) / 32 * 32), L0, mg->D, mg->coarsestAcc); }
-      else { LvlD& B = mg->lv[maxLevel]; MF_LAUNCH_PDL(s, k_mg_coarse_cg<false>, 1, (unsigned)((B.n + 31) / 32 * 32), B, mg->D, mg->coarsestAcc); }
+      const LvlD& B = mg->lv[maxLevel];
+      const unsigned nt = (unsigned)((B.n + 31) / 32 * 32);
+      if (maxLevel == 0) { if (nt <= 768) { MF_LAUNCH_PDL(s, (k_mg_coarse_cg<true, 768>), 1, nt, B, mg->D, mg->coarsestAcc); }
+                           else { MF_LAUNCH_PDL(s, (k_mg_coarse_cg<true, 1024>), 1, nt, B, mg->D, mg->coarsestAcc); } }
+      else { if (nt <= 768) { MF_LAUNCH_PDL(s, (k_mg_coarse_cg<false, 768>), 1, nt, B, mg->D, mg->coarsestAcc); }
+             else { MF_LAUNCH_PDL(s, (k_mg_coarse_cg<false, 1024>), 1, nt, B, mg->D, mg->coarsestAcc); } }
     }
     endGroup(mg, solo);
   }
