@@ -142,21 +142,36 @@ __global__ void __launch_bounds__(256) k_add_buoyancy(Geo g, const int* __restri
   float v[W];
   if (mx) {
     ldW<W>(v, vel.x, idx);
+    bool ch = false;
 #pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fx[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sx) * (double)(d0[c] + dx[c]));
-    stW<W>(vel.x, idx, v);
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fx[c])) {
+      const float o = v[c];
+      v[c] = (float)((double)o + (0.5 * (double)sx) * (double)(d0[c] + dx[c]));
+      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    }
+    if (ch) stW<W>(vel.x, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
   }
   if (my) {
     ldW<W>(v, vel.y, idx);
+    bool ch = false;
 #pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fy[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sy) * (double)(d0[c] + dy[c]));
-    stW<W>(vel.y, idx, v);
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fy[c])) {
+      const float o = v[c];
+      v[c] = (float)((double)o + (0.5 * (double)sy) * (double)(d0[c] + dy[c]));
+      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    }
+    if (ch) stW<W>(vel.y, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
   }
   if (mz) {
     ldW<W>(v, vel.z, idx);
+    bool ch = false;
 #pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fz[c])) v[c] = (float)((double)v[c] + (0.5 * (double)sz) * (double)(d0[c] + dz[c]));
-    stW<W>(vel.z, idx, v);
+    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fz[c])) {
+      const float o = v[c];
+      v[c] = (float)((double)o + (0.5 * (double)sz) * (double)(d0[c] + dz[c]));
+      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    }
+    if (ch) stW<W>(vel.z, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
   }
 }
 // KnApplyForce (extforces.cpp:46-59), additive flag as in addGravity
@@ -198,6 +213,13 @@ __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restri
   if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
   if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
   if (!on) return;
+  if (g.is3D) {
+    // every rule below needs an obstacle or a stick bit in the cell or one of its six neighbours: the bulk of the domain leaves here
+    int any = 0;
+#pragma unroll
+    for (int c = 0; c < W; c++) any |= f[c] | fxm[c] | fxp[c] | fym[c] | fyp[c] | fzm[c] | fzp[c];
+    if (!(any & (MF_OBSTACLE | MF_STICK))) return;
+  }
   // what happens to each component of each cell: 0 keep, 1 set to the obstacle velocity, 2 set to zero (applied in this order)
   int ax[W], ay[W], az[W];
   bool anyx = false, anyy = false, anyz = false;

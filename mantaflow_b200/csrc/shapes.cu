@@ -18,17 +18,26 @@ namespace mf {
   const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
 
 // ApplyShapeToGrid<T>: NC components of a cell-centred grid (int / Real / Vec3)
+// The apply kernels visit only a conservative bounding box of the shape (shapeBounds below): Geo carries the box's z range,
+// i0 / j0 shift the launch in x / y.  Every cell the reference's full-grid loop would change lies inside the box.
+#define IJK_BOX \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + i0; \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + j0; \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0; \
+  if (i >= g.nx || j >= g.ny || k >= g.k1) return; \
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+
 template <class T, int NC>
-__global__ void __launch_bounds__(256) k_shape_apply(Geo g, ShapeD s, T* __restrict__ d, long long np, T v0, T v1, T v2, const int* __restrict__ respect) {
-  IJK_ALL
+__global__ void __launch_bounds__(256) k_shape_apply(Geo g, int i0, int j0, ShapeD s, T* __restrict__ d, long long np, T v0, T v1, T v2, const int* __restrict__ respect) {
+  IJK_BOX
   if (respect && fIsObstacle(respect[idx])) return;
   if (!shapeInside(s, i + 0.5f, j + 0.5f, k + 0.5f)) return;
   d[idx] = v0;
   if (NC == 3) { d[idx + np] = v1; d[idx + 2 * np] = v2; }
 }
 // ApplyShapeToMACGrid: each face tested at its own position
-__global__ void __launch_bounds__(256) k_shape_apply_mac(Geo g, ShapeD s, V3 d, float vx, float vy, float vz, const int* __restrict__ respect) {
-  IJK_ALL
+__global__ void __launch_bounds__(256) k_shape_apply_mac(Geo g, int i0, int j0, ShapeD s, V3 d, float vx, float vy, float vz, const int* __restrict__ respect) {
+  IJK_BOX
   if (respect && fIsObstacle(respect[idx])) return;
   if (shapeInside(s, (float)i, j + 0.5f, k + 0.5f)) d.x[idx] = vx;
   if (shapeInside(s, i + 0.5f, (float)j, k + 0.5f)) d.y[idx] = vy;
@@ -129,6 +138,36 @@ __global__ void __launch_bounds__(256) k_set_obstacle_flags(Geo g, int* __restri
 
 using namespace mf;
 
+// Cell index box [lo, hi) that contains every cell / face position p with shapeInside(p) (positions are i, i + 0.5): the box
+// itself, the sphere's scaled radius, the cylinder's bounding sphere -- each widened by two cells.  Non-finite or huge
+// parameters fall back to the whole grid.
+struct ShapeBox { int lo[3], hi[3]; };
+static ShapeBox shapeBounds(const Solver* s, const ShapeD& d) {
+  const int n[3] = {s->nx, s->ny, s->nz};
+  ShapeBox b;
+  for (int c = 0; c < 3; c++) {
+    double lo, hi;
+    if (d.type == MF_SHAPE_BOX) { lo = d.a[c]; hi = d.b[c]; }
+    else if (d.type == MF_SHAPE_SPHERE) { const double e = std::fabs((double)d.r * d.b[c]); lo = d.a[c] - e; hi = d.a[c] + e; }
+    else { const double e = std::sqrt((double)d.zlen * d.zlen + (double)d.r * d.r); lo = d.a[c] - e; hi = d.a[c] + e; }
+    b.lo[c] = 0; b.hi[c] = n[c];
+    if (std::isfinite(lo) && std::isfinite(hi) && std::fabs(lo) < 1e9 && std::fabs(hi) < 1e9) {
+      b.lo[c] = std::max(0, (int)std::floor(lo) - 2);
+      b.hi[c] = std::min(n[c], (int)std::ceil(hi) + 3);
+    }
+  }
+  if (!s->is3D) { b.lo[2] = 0; b.hi[2] = 1; }
+  b.lo[0] &= ~31;                                   // whole 128-byte lines in x
+  return b;
+}
+// launch an apply kernel (Geo, i0, j0, ...) over the part of the box that lies in each local rank's slab
+#define MF_LAUNCH_BOX(s, box, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { mf::Geo _g = mf::geo((s), _r); \
+  _g.k0 = std::max(_g.k0, (box).lo[2]); _g.k1 = std::min(_g.k1, (box).hi[2]); \
+  if (_g.k1 > _g.k0 && (box).hi[0] > (box).lo[0] && (box).hi[1] > (box).lo[1]) { \
+    const dim3 _gr(cdiv((box).hi[0] - (box).lo[0], _b.x), cdiv((box).hi[1] - (box).lo[1], _b.y), cdiv(_g.k1 - _g.k0, _b.z)); \
+    mf::Geo _gg = _g; _gg.nx = (s)->nx; _gg.ny = (s)->ny; \
+    MF_LAUNCH(s, kern, _gr, _b, _gg, (box).lo[0], (box).lo[1], __VA_ARGS__); } } (s)->rankSync(); } while (0)
+
 extern "C" {
 
 int mf_shape_apply(const mf_shape* sh, mf_grid* gp, float vx, float vy, float vz, int ivalue, const mf_grid* respectFlags) {
@@ -138,10 +177,11 @@ int mf_shape_apply(const mf_shape* sh, mf_grid* gp, float vx, float vy, float vz
   Grid* gr = G(gp); Solver* s = gr->s; s->use();
   const ShapeD d = shapeOf(sh);
   const int* rf = respectFlags ? G(respectFlags)->di() : nullptr;
-  if (gr->isInt()) { markFlagsChanged(gr); MF_LAUNCH_IJK(s, (k_shape_apply<int, 1>), d, gr->di(), 0LL, ivalue, 0, 0, rf); }
-  else if (gr->isReal()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 1>), d, gr->d, 0LL, vx, 0.f, 0.f, rf);
-  else if (gr->isMAC()) MF_LAUNCH_IJK(s, k_shape_apply_mac, d, v3(gr), vx, vy, vz, rf);
-  else if (gr->isVec()) MF_LAUNCH_IJK(s, (k_shape_apply<float, 3>), d, gr->d, s->Np, vx, vy, vz, rf);
+  const ShapeBox box = shapeBounds(s, d);
+  if (gr->isInt()) { markFlagsChanged(gr); MF_LAUNCH_BOX(s, box, (k_shape_apply<int, 1>), d, gr->di(), 0LL, ivalue, 0, 0, rf); }
+  else if (gr->isReal()) MF_LAUNCH_BOX(s, box, (k_shape_apply<float, 1>), d, gr->d, 0LL, vx, 0.f, 0.f, rf);
+  else if (gr->isMAC()) MF_LAUNCH_BOX(s, box, k_shape_apply_mac, d, v3(gr), vx, vy, vz, rf);
+  else if (gr->isVec()) MF_LAUNCH_BOX(s, box, (k_shape_apply<float, 3>), d, gr->d, s->Np, vx, vy, vz, rf);
   else mfErr("Shape::applyToGrid(): unknown grid type");
   MF_LAUNCH_CHECK();
   MF_API_END
