@@ -75,53 +75,66 @@ static void flushGroups(MgHierarchy* mg) { if (mg->pendingSolo) { mg->s->rankSyn
 
 // ---- coarsest level: Jacobi-preconditioned CG in double, one CTA (solveCG, multigrid.cpp:796-902) ---------
 // One thread per vertex (n <= 1024).  The 27 (7) coefficients of the thread's row are loaded once into registers, the
-// search vector lives in shared memory; 3 block barriers per iteration.
-// block-wide sums of (a, b): warp tree, one partial per warp in shared memory, then warp 0 alone combines the partials (the same
-// xor tree every warp used to run redundantly, so the sums are bit-identical) and runs `fin(a, b)` -- the scalar double
-// divisions / square root of the iteration, which would otherwise occupy the FP64 pipe once per warp -- before the results
-// are published through shared memory.  Two block barriers per call.
-template <class Fin>
-__device__ __forceinline__ void cgBlockSum2(double a, double b, double (*sh)[32], double* out, Fin fin) {
-  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+// search vector lives in shared memory; 3 block barriers per iteration.  An iteration is a chain of dependent double
+// instructions on one SM (measured per phase with clock64, 736 threads, 9^3 level of a 256^3 grid, cycles: row 2100 -> 1500,
+// p.Ap sum 1060 -> 870, update 340 -> 120, r.r / r.z sums 1850 -> 1490):
+//  * the row: 27 LDS.64 of the search vector per thread are 157 KB per iteration = 1230 cycles of the SM's shared-memory
+//    port, the floor of this phase.  The coefficients stay 27 floats in registers and are converted where they are used: as
+//    54 registers of doubles ptxas has no room left to batch the loads and serialises LDS -> DFMA -> LDS on one register
+//    pair.  No mask test per term: a term that does not exist has coefficient 0 and reads a zeroed margin of the vector;
+//  * a term is one DFMA (explicit __fma_rn in this -fmad=false translation unit; the reference's own sums are sequential
+//    doubles whose order the block-wide trees below do not keep either -- the level is solved to 1e-4 of the outer accuracy,
+//    the difference is ~1e-16 relative), the Jacobi step multiplies by a reciprocal computed once;
+//  * block-wide sums of one or two values: warp tree, one partial per warp in shared memory, then warp 0 alone combines the
+//    partials and runs `fin` -- the scalar double divisions / square root of the iteration (130 / 105 cycles each), which
+//    would otherwise occupy the FP64 pipe once per warp -- before the results are published through shared memory.  Two
+//    block barriers per call.
+template <int NV, class Fin>
+__device__ __forceinline__ void cgBlockSum(double a, double b, double (*sh)[32], double* out, Fin fin) {
+  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); if (NV > 1) b += __shfl_xor_sync(0xffffffffu, b, o); }
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  if (l == 0) { sh[0][w] = a; sh[1][w] = b; }
+  if (l == 0) { sh[0][w] = a; if (NV > 1) sh[1][w] = b; }
   __syncthreads();
   if (w == 0) {
     const int nw = (blockDim.x + 31) >> 5;
     a = (l < nw) ? sh[0][l] : 0.0;
-    b = (l < nw) ? sh[1][l] : 0.0;
-    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (NV > 1) b = (l < nw) ? sh[1][l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); if (NV > 1) b += __shfl_xor_sync(0xffffffffu, b, o); }
     if (l == 0) fin(a, b, out);
   }
   __syncthreads();
 }
 
 template <bool LEVEL0>
-__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[32], double* out, double* vec) {
+__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[32], double* out, double* vecBase) {
   constexpr int NS = LEVEL0 ? 7 : 27;
   const int v = threadIdx.x;
   const bool in = v < L.n;
   const int vx = in ? v % L.sx : 0, vy = in ? (v % (L.sx * L.sy)) / L.sx : 0, vz = in ? v / (L.sx * L.sy) : 0;
   const int p = in ? mgIdx(L, vx, vy, vz) : 0;
   const bool active = in && L.type[p] != vtInactive;
-  // row of A in the order the reference applies it; nbr[] = natural index of the neighbour, mask bit = term present
-  float coef[NS]; unsigned mask = 0;
+  // row of A in the order the reference applies it; a term that does not exist (neighbour outside the grid or inactive, or an
+  // inactive row) has coefficient 0 and reads a finite value: vec has a zeroed margin of Z + Y + 1 entries on both sides
+  float coef[NS];
 #pragma unroll
   for (int s = 0; s < NS; s++) coef[s] = 0.f;
   const int Y = L.sx, Z = L.sx * L.sy;
+  const int M = Z + Y + 1;
+  double* vec = vecBase + M;
+  for (int t = threadIdx.x; t < M; t += blockDim.x) { vecBase[t] = 0.0; vec[blockDim.x + t] = 0.0; }
   if (active) {
     if (LEVEL0) {
       // order -x,+x,-y,+y,-z,+z, centre (multigrid.cpp:840-850 for l == 0)
       const long long n = L.as;
-      if (vx > 0)        { coef[0] = L.A[n + v - 1]; mask |= 1u; }
-      if (vx < L.sx - 1) { coef[1] = L.A[n + v]; mask |= 2u; }
-      if (vy > 0)        { coef[2] = L.A[2 * n + v - Y]; mask |= 4u; }
-      if (vy < L.sy - 1) { coef[3] = L.A[2 * n + v]; mask |= 8u; }
+      if (vx > 0)        coef[0] = L.A[n + v - 1];
+      if (vx < L.sx - 1) coef[1] = L.A[n + v];
+      if (vy > 0)        coef[2] = L.A[2 * n + v - Y];
+      if (vy < L.sy - 1) coef[3] = L.A[2 * n + v];
       if (D.is3D) {
-        if (vz > 0)        { coef[4] = L.A[3 * n + v - Z]; mask |= 16u; }
-        if (vz < L.sz - 1) { coef[5] = L.A[3 * n + v]; mask |= 32u; }
+        if (vz > 0)        coef[4] = L.A[3 * n + v - Z];
+        if (vz < L.sz - 1) coef[5] = L.A[3 * n + v];
       }
-      coef[6] = L.A[v]; mask |= 64u;
+      coef[6] = L.A[v];
     } else {
       const int SS = D.SS;
       int s = 0;
@@ -138,63 +151,91 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
               const int pn = mgIdx(L, Nx, Ny, Nz);
               if (L.type[pn] != vtInactive) {
                 coef[slot] = (s < SS) ? L.A[(SS - 1 - s) * L.as + pn] : L.A[(s - SS + 1) * L.as + p];
-                mask |= 1u << slot;
               }
             }
             s++;
           }
     }
   }
+  // the loads of a row are issued in batches of 9 (one z plane of the stencil), the sum keeps the reference's term order
   auto applyA = [&]() {
     double sum = 0;
+    constexpr int NB = LEVEL0 ? 7 : 9;
 #pragma unroll
-    for (int s = 0; s < NS; s++) {
-      int off;
-      if (LEVEL0) off = (s == 0) ? -1 : (s == 1) ? 1 : (s == 2) ? -Y : (s == 3) ? Y : (s == 4) ? -Z : (s == 5) ? Z : 0;
-      else off = (s % 3 - 1) + Y * ((s / 3) % 3 - 1) + Z * (s / 9 - 1);
-      if (mask & (1u << s)) sum += (double)coef[s] * vec[v + off];
+    for (int g = 0; g < NS; g += NB) {
+      double xv[NB];
+#pragma unroll
+      for (int i = 0; i < NB; i++) {
+        const int s = g + i;
+        int off;
+        if (LEVEL0) off = (s == 0) ? -1 : (s == 1) ? 1 : (s == 2) ? -Y : (s == 3) ? Y : (s == 4) ? -Z : (s == 5) ? Z : 0;
+        else off = (s % 3 - 1) + Y * ((s / 3) % 3 - 1) + Z * (s / 9 - 1);
+        xv[i] = vec[v + off];
+      }
+#pragma unroll
+      for (int i = 0; i < NB; i++) {
+        float c = coef[g + i];
+        asm volatile("" : "+f"(c));          // keep the row as 27 floats: converted copies would not fit the register budget
+        sum = __fma_rn((double)c, xv[i], sum);
+      }
     }
     return sum;
   };
-  const double diag = active ? (double)L.A[p] : 1.0;
+  const double invDiag = active ? 1.0 / (double)L.A[p] : 0.0;
   double x = in ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
   vec[v] = x;
   __syncthreads();
   if (active) {
     r = (double)L.b[p] - applyA();
-    z = r / diag;
+    z = r * invDiag;
     pp = z;
   }
-  // out[0] = sqrt(sum r.r), out[1] = sum r.z
-  cgBlockSum2(active ? r * r : 0.0, active ? r * z : 0.0, sh, out, [](double rr, double rz, double* o) { o[0] = sqrt(rr); o[1] = rz; });
+  // out[0] = sqrt(sum r.r), out[1] = sum r.z   (inactive rows: r = z = pp = 0 throughout, their coefficients are all zero)
+  cgBlockSum<2>(r * r, r * z, sh, out, [](double rr, double rz, double* o) { o[0] = sqrt(rr); o[1] = rz; });
   const double initialResidual = out[0];
   double alphaTop = out[1];
   const double acc = (double)accuracy;
+#ifdef MF_CG_DBG
+  long long tc[6] = {0, 0, 0, 0, 0, 0}; int nit = 0; const long long tstart = clock64();
+#define TCK(i) { const long long _t = clock64(); tc[i] += _t - tl; tl = _t; }
+#else
+#define TCK(i)
+#endif
   for (int iter = 0; iter < 10000 && initialResidual > 1E-12; iter++) {
+#ifdef MF_CG_DBG
+    long long tl = clock64(); nit++;
+#endif
     vec[v] = pp;              // the previous contents were last read before the barriers of the reduction above
     __syncthreads();
-    if (active) z = applyA();
-    cgBlockSum2(active ? pp * z : 0.0, 0.0, sh, out, [alphaTop](double pz, double, double* o) { o[0] = alphaTop / pz; });
+    TCK(0)
+    z = applyA();
+    TCK(1)
+    cgBlockSum<1>(pp * z, 0.0, sh, out, [alphaTop](double pz, double, double* o) { o[0] = alphaTop / pz; });
+    TCK(2)
     const double alpha = out[0];
-    if (active) { x += alpha * pp; r -= alpha * z; z = r / diag; }
+    x = __fma_rn(alpha, pp, x); r = __fma_rn(-alpha, z, r); z = r * invDiag;
+    TCK(3)
     // out[0] = beta, out[1] = new alphaTop, out[2] = converged
-    cgBlockSum2(active ? r * r : 0.0, active ? r * z : 0.0, sh, out, [alphaTop, initialResidual, acc](double rr, double rz, double* o) {
+    cgBlockSum<2>(r * r, r * z, sh, out, [alphaTop, initialResidual, acc](double rr, double rz, double* o) {
       o[0] = rz / alphaTop; o[1] = rz; o[2] = (sqrt(rr) / initialResidual < acc) ? 1.0 : 0.0; });
+    TCK(4)
     if (out[2] != 0.0) break;
     const double beta = out[0];
     alphaTop = out[1];
-    pp = z + beta * pp;
+    pp = __fma_rn(beta, pp, z);
   }
+#ifdef MF_CG_DBG
+  if (threadIdx.x == 0) printf("cgdbg it %d publish %lld row %lld sum1 %lld upd %lld sum2 %lld total %lld\n", nit, tc[0] / nit, tc[1] / nit, tc[2] / nit, tc[3] / nit, tc[4] / nit, clock64() - tstart);
+#endif
   if (in) L.x[p] = (float)x;
 }
-// MAXT = 768: up to 85 registers per thread -- with 1024 threads (64 registers) the 27 coefficients and the double state of the
-// iteration spill to local memory inside the loop
+// MAXT = 768: up to 85 registers per thread; with 1024 threads (64 registers) part of the state spills to local memory
 template <bool LEVEL0, int MAXT>
 __global__ void __launch_bounds__(MAXT) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
   MF_PDL_PROLOGUE
   __shared__ double sh[2][32];
   __shared__ double out[4];
-  __shared__ double vec[1024];
+  __shared__ double vec[1024 + 2 * (1024 + 1024 + 1)];      // n + two margins of Z + Y + 1 <= 2049
   mgCoarseCg<LEVEL0>(L, D, accuracy, sh, out, vec);
 }
 
