@@ -24,6 +24,7 @@ struct TailArgs {
   int nl;                                // lv[0 .. nl-2]: swept levels (fine to coarse); lv[nl-1]: the coarsest level (CG)
   int prefetch;                          // pull the operators into L2 before the first phase
   int fold;                              // mgFoldFirst in use: colour 0 of the pre-smoothing is done by the restriction
+  int cluster;                           // the grid is ONE thread-block cluster: phases are separated by the hardware cluster barrier
   unsigned base;                         // value of *bar when the kernel starts (host-tracked; all arithmetic wraps)
   unsigned* bar;                         // monotonic arrival counter
   int* err;                              // mapped host flag: a barrier timed out
@@ -39,6 +40,18 @@ __host__ __device__ inline int mgTailBarriers(int nl, bool down, bool fold) {
 }
 
 __device__ __forceinline__ void tailBarrier(const TailArgs& T, unsigned& target, bool& dead) {
+  if (T.cluster) {
+    // release / acquire at cluster scope: the global stores of every CTA of the cluster before the barrier are visible to the
+    // (L2) loads of every CTA behind it
+    // (SASS: MEMBAR.ALL.GPU + UCGABAR_ARV / UCGABAR_WAIT + CCTL.IVALL.  Measured on 16 CTAs: the bare barrier 0.24 us, with
+    // release / acquire 0.75 us; a smoothing phase of <= 1 vertex per thread is 1.8 us of dependent instructions on top)
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (T.dbg && blockIdx.x == 0 && threadIdx.x == 0) {
+      target += gridDim.x;
+      unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); T.dbg[(target - T.base) / gridDim.x] = t;
+    }
+    return;
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     target += gridDim.x;

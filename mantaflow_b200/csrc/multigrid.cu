@@ -31,7 +31,7 @@ struct MgHierarchy {
   std::vector<MgOff8> offs;                  // blocked level l: stencil offset tables of the sweeps (buildOffsets)
   __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when exact)
   // persistent kernels for the small levels (mg_tail.cuh): grid-barrier counter, its host-tracked value, time-out flag
-  unsigned* tailBar; unsigned tailBase; int* tailErrHost; int* tailErrDev; MgOff8* tailOffs;
+  int tailCluster; unsigned* tailBar; unsigned tailBase; int* tailErrHost; int* tailErrDev; MgOff8* tailOffs;
   int tailFirst;            // first level swept by the tail kernels, or -1
 };
 
@@ -341,7 +341,7 @@ MgHierarchy* mg_create(Solver* s) {
   mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
   mg->half1 = nullptr; mg->ash1 = 0;
-  mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
+  mg->tailCluster = 0; mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
   mg->D.zmin = is3D ? -1 : 0; mg->D.zmax = is3D ? 1 : 0;
@@ -800,9 +800,38 @@ static void planTail(MgHierarchy* mg) {
   const int maxLevel = (int)mg->lv.size() - 1;
   // opt-in (MF_MG_TAIL=1): measured at 256^3 the persistent kernels need ~2.7-3.2 us per phase (1.25 us of it the grid barrier,
   // the rest one L2 round trip and the 52-operation dependent chain of a vertex) against ~3.4 us per programmatic dependent
-  // launch -- 6.83 vs 6.78 ms per step, no gain; kept for the parity test and as the starting point of a shared-memory variant
+  // launch -- 6.83 vs 6.78 ms per step, no gain; kept for the parity test and as the starting point of a shared-memory variant.
+  // MF_MG_TAIL=cluster (r1l): the same kernels as one 16-CTA cluster with the hardware barrier: 2.5 us per phase (barrier 0.24 us,
+  // release / acquire 0.5 us, the vertex' ~300 dependent instructions 1.8 us), 5.20 vs 5.04 ms per step -- the phases are bound
+  // by the instruction chain of one vertex, not by the barrier or the launch
   if (!mg->D.is3D || maxLevel < 2 || !getenv("MF_MG_TAIL") || getenv("MF_MG_NOTAIL")) return;
-  const long long cap = (long long)s->numSMs * MG_TAIL_THREADS;
+  // MF_MG_TAIL=cluster: the kernels run as ONE cluster of 16 (8) CTAs with the hardware cluster barrier between the phases;
+  // the tail then starts where a colour has at most one vertex per thread of the cluster
+  mg->tailCluster = 0;
+  if (!strcmp(getenv("MF_MG_TAIL"), "cluster")) {
+    int cl = getenv("MF_MG_TAILCL") ? atoi(getenv("MF_MG_TAILCL")) : 16;
+    for (; cl >= 2; cl /= 2) {
+      cudaError_t e = cudaSuccess;
+      if (cl > 8) {
+        e = cudaFuncSetAttribute(k_mg_tail<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_mg_tail<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      }
+      int nc = 0;
+      if (e == cudaSuccess) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(cl); cfg.blockDim = dim3(MG_TAIL_THREADS);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        e = cudaOccupancyMaxActiveClusters(&nc, k_mg_tail<true>, &cfg);
+      }
+      if (e == cudaSuccess && nc >= 1) break;
+      (void)cudaGetLastError();
+    }
+    if (cl < 2) return;
+    mg->tailCluster = cl;
+  }
+  const long long cap = (long long)(mg->tailCluster ? mg->tailCluster : s->numSMs) * MG_TAIL_THREADS;
   int tf = -1;
   for (int l = 1; l < maxLevel; l++) {
     const LvlD& L = mg->lv[l];
@@ -844,9 +873,22 @@ static void tailLeg(MgHierarchy* mg, bool down, bool fold) {
     if (getenv("MF_MG_TAILDBG") && !dbgBuf) CUDA_CHECK(cudaMalloc(&dbgBuf, 64 * sizeof(unsigned long long)));
     T.dbg = getenv("MF_MG_TAILDBG") ? dbgBuf : nullptr;
     for (int l = tf; l <= maxLevel; l++) T.lv[l - tf] = mg->lv[l];
-    const int G = s->numSMs;
-    if (down) { MF_LAUNCH_PDL(s, k_mg_tail<true>, G, MG_TAIL_THREADS, T); }
-    else      { MF_LAUNCH_PDL(s, k_mg_tail<false>, G, MG_TAIL_THREADS, T); }
+    const int G = mg->tailCluster ? mg->tailCluster : s->numSMs;
+    T.cluster = mg->tailCluster ? 1 : 0;
+    if (!mg->tailCluster) {
+      if (down) { MF_LAUNCH_PDL(s, k_mg_tail<true>, G, MG_TAIL_THREADS, T); }
+      else      { MF_LAUNCH_PDL(s, k_mg_tail<false>, G, MG_TAIL_THREADS, T); }
+    } else {
+      mf::ProfScope _ps(s, "k_mg_tail");
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(G); cfg.blockDim = dim3(MG_TAIL_THREADS); cfg.stream = s->stream;
+      cudaLaunchAttribute at[2];
+      at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = G; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[1].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at; cfg.numAttrs = s->profiling ? 1 : 2;
+      CUDA_CHECK(cudaLaunchKernelEx(&cfg, down ? k_mg_tail<true> : k_mg_tail<false>, T));
+      s->launches++;
+    }
     mg->tailBase += (unsigned)G * (unsigned)mgTailBarriers(T.nl, down, fold);
     if (T.dbg) {     // MF_MG_TAILDBG: per-phase times of this launch (development)
       unsigned long long h[64];

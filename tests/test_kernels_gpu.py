@@ -151,7 +151,7 @@ VC_SIZES = [(64, 50, 37), (8, 8, 8), (60, 29, 33), (120, 31, 18), (56, 26, 64), 
 def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     """one V(1,1)-cycle: the z-marching wavefront legs (mg_wave0.cuh), the tiled fused legs (mg_fused0.cuh) and the plain
     per-colour sweeps give bit-identical results; so does the binary16 copy of the level-1 operator (exact by construction)
-    and so do the opt-in persistent small-level kernels (mg_tail.cuh, MF_MG_TAIL=1)"""
+    and so do the persistent small-level kernels (mg_tail.cuh, MF_MG_TAIL=1: grid barrier, MF_MG_TAIL=cluster: one cluster)"""
     from mantaflow_b200 import manta
     from mantaflow_b200._lib import lib, check
     rs = np.random.RandomState(21)
@@ -162,7 +162,7 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
     outs = []
     fmt = []
-    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}, {"MF_MG_NOFOLD": "1"}, {"MF_MG_TAIL": "1"}):
+    for env in ({}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}, {"MF_MG_NOHALF": "1"}, {"MF_MG_NOFOLD": "1"}, {"MF_MG_TAIL": "1"}, {"MF_MG_TAIL": "cluster"}):
         for k in ("MF_MG_NOWAVE", "MF_MG_UNFUSED", "MF_MG_NOHALF", "MF_MG_NOFOLD", "MF_MG_TAIL"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
@@ -180,10 +180,11 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
             check(lib().mf_mg_level_format(s._h, 1, Ct.byref(b)))
         fmt.append(b.value)
         manta.releaseMG(s)
-    assert fmt in ([2, 2, 2, 4, 2, 2], [0, 0, 0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
+    assert fmt in ([2, 2, 2, 4, 2, 2, 2], [0, 0, 0, 0, 0, 0, 0]), "level-1 operator of a flags-only Laplacian must be stored in binary16"
     assert np.array_equal(outs[3].view(np.int32), outs[2].view(np.int32)), "binary16 level-1 operator changes the V-cycle"
     assert np.array_equal(outs[4].view(np.int32), outs[0].view(np.int32)), "folding the first colour-0 sweep into the restriction changes the V-cycle"
     assert np.array_equal(outs[5].view(np.int32), outs[0].view(np.int32)), "persistent small-level kernels change the V-cycle"
+    assert np.array_equal(outs[6].view(np.int32), outs[0].view(np.int32)), "small-level kernels as one thread-block cluster change the V-cycle"
     assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
     assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
     assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
