@@ -217,14 +217,15 @@ __global__ void __launch_bounds__(256) k_cg_dot_beta(long long n, const float* _
   gridReduceK<1>(acc, ops, ctx, sh, FinBeta{ st });
 }
 
-// init: sigma = tmp . residual                                           (conjugategrad.cpp:234)
+// init: search = tmp (when given), sigma = tmp . residual                 (conjugategrad.cpp:229-234)
 __global__ void __launch_bounds__(256) k_cg_dot_sigma(long long n, const float* __restrict__ tmp, const float* __restrict__ residual,
-                                                      CgState* st, RedCtx ctx) {
+                                                      float* __restrict__ search, CgState* st, RedCtx ctx) {
   __shared__ double sh[32];
   double acc[1] = { 0.0 };
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long stp = (long long)gridDim.x * blockDim.x;
-  for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]);
+  if (search) { for (; i < n; i += stp) { const float t = tmp[i]; search[i] = t; acc[0] += (double)(t * residual[i]); } }
+  else { for (; i < n; i += stp) acc[0] += (double)(tmp[i] * residual[i]); }
   const int ops[1] = { 0 };
   gridReduceK<1>(acc, ops, ctx, sh, FinSigma{ st });
 }

@@ -95,12 +95,13 @@ struct CgDriver {
     s->writeSmall(st, &h, (int)sizeof(h));
     (void)N;
     slabZero(s, v.dst);
-    slabCopy(s, v.residual, v.rhs);
+    if (v.residual != v.rhs) slabCopy(s, v.residual, v.rhs);          // (solvePressure hands its own rhs temporary over as the residual)
     const float* z = v.residual;
     if (pcMethod != 0) { applyPrecond(true); z = v.tmp; }
-    slabCopy(s, v.search, z);
-    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, sp.n), 256, sp.n, z + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+    // search = z in the pass that computes sigma
+    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH(s, k_cg_dot_sigma, redBlocks(s, sp.n), 256, sp.n, z + sp.off, v.residual + sp.off, v.search + sp.off, st, redCtx(s, r)); }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinSigma{ st });
+    s->rankSync();
   }
   // tmp = A search, alpha (conjugategrad.cpp:246-252)
   void spmv() {
@@ -177,7 +178,8 @@ static CgState* cgStateBuf(Solver* s) {
 }
 
 // solvePressureSystem (pressure.cpp:312-454)
-static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, const Grid* flags, const mf_pressure_params* p, mf_solve_info* info) {
+static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, const Grid* flags, const mf_pressure_params* p, mf_solve_info* info,
+                        bool rhsScratch = false) {
   int preconditioner = p->preconditioner;
   if (!p->precondition) preconditioner = MF_PC_NONE;
   mfAssert(preconditioner >= 0 && preconditioner <= 3, "solvePressureSystem: unknown preconditioner " << preconditioner);
@@ -217,7 +219,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   }
   CgDriver cg;
   cg.s = s; cg.st = cgStateBuf(s); cg.P = nullptr; cg.mg = nullptr;
-  cg.v.flags = flags->di(); cg.v.dst = pressure->d; cg.v.residual = t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
+  cg.v.flags = flags->di(); cg.v.dst = pressure->d; cg.v.residual = rhsScratch ? rhs : t.residual; cg.v.search = t.search; cg.v.tmp = t.tmp;
   cg.v.rhs = rhs; cg.v.A0 = t.A0; cg.v.Ai = t.Ai; cg.v.Aj = t.Aj; cg.v.Ak = t.Ak;
   cg.v.code = useCode ? s->cgCode : nullptr;
   cg.v4 = (s->nx % 4 == 0);
@@ -354,7 +356,7 @@ int mf_solve_pressure(mf_grid* vel, mf_grid* pressure, const mf_grid* flags, con
   checkParams(s, p, "solvePressure");
   TmpReal rhs(s);                                    // Grid<Real> rhs(vel.getParent())  (pressure.cpp:499)
   computeRhs(s, rhs.p, G(vel), G(flags), p, true);
-  solveSystem(s, rhs.p, G(vel), G(pressure), G(flags), p, info);
+  solveSystem(s, rhs.p, G(vel), G(pressure), G(flags), p, info, /* rhs is not needed afterwards */ !p->retRhs);
   correctVel(s, G(vel), G(pressure), G(flags), p);
   if (p->retRhs) slabCopy(s, G(p->retRhs)->d, rhs.p);
   MF_LAUNCH_CHECK();
