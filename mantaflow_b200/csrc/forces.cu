@@ -116,6 +116,13 @@ __global__ void k_apply_cylinder(Geo g, float* __restrict__ d, float cx, float c
 }
 
 // ---- forces ---------------------------------------------------------------------------------------
+// vel + (0.5 * strength) * factorSum as the reference evaluates it: a double product and sum, rounded once.  For a zero strength
+// component the float expression gives the same bits (the product is a zero of the same sign or NaN, the sum is exact), and
+// two of three components of a gravity vector are zero: they stay off the FP64 pipe and its conversions.
+__device__ __forceinline__ float buoy(float v, float strength, float factorSum) {
+  if (strength == 0.f) return v + (0.5f * strength) * factorSum;
+  return (float)((double)v + (0.5 * (double)strength) * (double)factorSum);
+}
 // KnAddBuoyancy (extforces.cpp:73-81): (0.5*strength) is a double product, the update is done in double.
 // W x-consecutive cells per thread (quad.cuh); a component's cells are only stored when one of them changed.
 template <int W>
@@ -124,55 +131,49 @@ __global__ void __launch_bounds__(256) k_add_buoyancy(Geo g, const int* __restri
   MF_CELLS_W(g, W)
   if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
   const long long Y = g.nx, Z = g.Z;
+  // all loads first (flags, factor, velocity: one round trip to memory), the shuffles of the x - 1 neighbours behind them
+  // (quad.cuh); rows j = 0 / k = 0 never reach this point, so idx - Y / idx - Z exist
   int f[W], fx[W], fy[W], fz[W];
-  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
-  if (g.is3D) ldW<W>(fz, flags, idx - Z); else { for (int c = 0; c < W; c++) fz[c] = 0; }
-  xMinusW<W, int>(fx, f, flags, idx, i, 0);
   float d0[W], dx[W], dy[W], dz[W];
+  float vx[W], vy[W], vz[W];
+  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
+  if (g.is3D) ldW<W>(fz, flags, idx - Z);
   ldW<W>(d0, factor, idx); ldW<W>(dy, factor, idx - Y);
-  if (g.is3D) ldW<W>(dz, factor, idx - Z); else { for (int c = 0; c < W; c++) dz[c] = 0.f; }
-  xMinusW<W, float>(dx, d0, factor, idx, i, 0.f);
+  if (g.is3D) ldW<W>(dz, factor, idx - Z);
+  ldW<W>(vx, vel.x, idx); ldW<W>(vy, vel.y, idx);
+  if (g.is3D) ldW<W>(vz, vel.z, idx);
+  if constexpr (W > 1) {
+    const int fe = xEdgeMinus<W, int>(flags, idx, i, 0);
+    const float de = xEdgeMinus<W, float>(factor, idx, i, 0.f);
+    xMinusWS<W, int>(fx, f, fe); xMinusWS<W, float>(dx, d0, de);
+  } else { xMinusW<W, int>(fx, f, flags, idx, i, 0); xMinusW<W, float>(dx, d0, factor, idx, i, 0.f); }
+  if (!g.is3D) { for (int c = 0; c < W; c++) { fz[c] = 0; dz[c] = 0.f; vz[c] = 0.f; } }
   if (!on) return;
-  bool mx = false, my = false, mz = false, cell[W];
+  bool chx = false, chy = false, chz = false;
 #pragma unroll
   for (int c = 0; c < W; c++) {
-    cell[c] = (i + c >= 1) && (i + c < g.nx - 1) && fIsFluid(f[c]);
-    mx |= cell[c] && fIsFluid(fx[c]); my |= cell[c] && fIsFluid(fy[c]); mz |= cell[c] && g.is3D && fIsFluid(fz[c]);
-  }
-  float v[W];
-  if (mx) {
-    ldW<W>(v, vel.x, idx);
-    bool ch = false;
-#pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fx[c])) {
-      const float o = v[c];
-      v[c] = (float)((double)o + (0.5 * (double)sx) * (double)(d0[c] + dx[c]));
-      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    const bool cell = (i + c >= 1) && (i + c < g.nx - 1) && fIsFluid(f[c]);
+    if (cell && fIsFluid(fx[c])) {
+      const float o = vx[c];
+      vx[c] = buoy(o, sx, d0[c] + dx[c]);
+      chx |= __float_as_uint(vx[c]) != __float_as_uint(o);
     }
-    if (ch) stW<W>(vel.x, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
-  }
-  if (my) {
-    ldW<W>(v, vel.y, idx);
-    bool ch = false;
-#pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fy[c])) {
-      const float o = v[c];
-      v[c] = (float)((double)o + (0.5 * (double)sy) * (double)(d0[c] + dy[c]));
-      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    if (cell && fIsFluid(fy[c])) {
+      const float o = vy[c];
+      vy[c] = buoy(o, sy, d0[c] + dy[c]);
+      chy |= __float_as_uint(vy[c]) != __float_as_uint(o);
     }
-    if (ch) stW<W>(vel.y, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
-  }
-  if (mz) {
-    ldW<W>(v, vel.z, idx);
-    bool ch = false;
-#pragma unroll
-    for (int c = 0; c < W; c++) if (cell[c] && fIsFluid(fz[c])) {
-      const float o = v[c];
-      v[c] = (float)((double)o + (0.5 * (double)sz) * (double)(d0[c] + dz[c]));
-      ch |= __float_as_uint(v[c]) != __float_as_uint(o);
+    if (cell && g.is3D && fIsFluid(fz[c])) {
+      const float o = vz[c];
+      vz[c] = buoy(o, sz, d0[c] + dz[c]);
+      chz |= __float_as_uint(vz[c]) != __float_as_uint(o);
     }
-    if (ch) stW<W>(vel.z, idx, v);          // a zero strength component leaves the bits as they are (except -0 -> +0, NaN factors)
   }
+  // a component is stored only where its bits changed: a zero strength component leaves them as they are (except -0 -> +0
+  // and non-finite factors)
+  if (chx) stW<W>(vel.x, idx, vx);
+  if (chy) stW<W>(vel.y, idx, vy);
+  if (chz) stW<W>(vel.z, idx, vz);
 }
 // KnApplyForce (extforces.cpp:46-59), additive flag as in addGravity
 __global__ void __launch_bounds__(256) k_apply_force(Geo g, const int* __restrict__ flags, V3 vel, float fx, float fy, float fz,
@@ -205,13 +206,16 @@ __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restri
   MF_CELLS_W(g, W)
   const long long Y = g.nx, Z = g.Z;
   int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  // all loads first, the shuffles of the x neighbours behind them (quad.cuh)
   ldW<W>(f, flags, idx);
-  xMinusW<W, int>(fxm, f, flags, idx, i, 0);
-  xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0);
   if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
   if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
   if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
   if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  if constexpr (W > 1) {
+    const int le = xEdgeMinus<W, int>(flags, idx, i, 0), re = xEdgePlus<W, int>(flags, idx, i, g.nx, 0);
+    xMinusWS<W, int>(fxm, f, le); xPlusWS<W, int>(fxp, f, re, i, g.nx);
+  } else { xMinusW<W, int>(fxm, f, flags, idx, i, 0); xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0); }
   if (!on) return;
   if (g.is3D) {
     // every rule below needs an obstacle or a stick bit in the cell or one of its six neighbours: the bulk of the domain leaves here
@@ -226,6 +230,9 @@ __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restri
 #pragma unroll
   for (int c = 0; c < W; c++) {
     ax[c] = ay[c] = az[c] = 0;
+    // (a row of 4-cell groups is a whole number of warps whose first / last lane sits at a wall: the branch is uniform for the
+    // one active lane of such a warp, so its cells without an obstacle / stick neighbour cost a test, not the rules)
+    if (g.is3D && !((f[c] | fxm[c] | fxp[c] | fym[c] | fyp[c] | fzm[c] | fzp[c]) & (MF_OBSTACLE | MF_STICK))) continue;
     const bool curFluid = fIsFluid(f[c]), curObs = fIsObstacle(f[c]);
     if (!curFluid && !curObs) continue;
     // (neighbours outside the grid were loaded as 0: no obstacle, no fluid, no stick bit -- the same as the index guards)

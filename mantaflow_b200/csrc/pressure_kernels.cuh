@@ -98,9 +98,12 @@ __global__ void __launch_bounds__(256) k_make_rhs_plain(Geo g, const int* __rest
     }
     int f[W]; float vx[W], vxp[W], vy[W], vyp[W], vz[W], vzp[W];
     ldW<W>(f, flags, idx);
-    ldW<W>(vx, vel.x, idx); xPlusW<W, float>(vxp, vx, vel.x, idx, i, g.nx, 0.f);
+    ldW<W>(vx, vel.x, idx);
     ldW<W>(vy, vel.y, idx); ldW<W>(vyp, vel.y, idx + Y);
     if (g.is3D) { ldW<W>(vz, vel.z, idx); ldW<W>(vzp, vel.z, idx + Z); }
+    // (the shuffle of the x + 1 neighbour behind all loads, see quad.cuh)
+    if constexpr (W > 1) { const float re = xEdgePlus<W, float>(vel.x, idx, i, g.nx, 0.f); xPlusWS<W, float>(vxp, vx, re, i, g.nx); }
+    else xPlusW<W, float>(vxp, vx, vel.x, idx, i, g.nx, 0.f);
     if (!on) continue;
     const bool edgeQuad = (i == 0) || (i + W >= g.nx);
     if (edgeQuad && !writeBorder) ldW<W>(r, rhs, idx);
@@ -208,12 +211,15 @@ __global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __r
   const long long Y = g.nx, Z = g.Z;
   int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
   ldW<W>(f, flags, idx);
-  xMinusW<W, int>(fxm, f, flags, idx, i, 0);
-  xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0);
   if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
   if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
   if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
   if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  // (the shuffles of the x neighbours behind all loads, see quad.cuh)
+  if constexpr (W > 1) {
+    const int le = xEdgeMinus<W, int>(flags, idx, i, 0), re = xEdgePlus<W, int>(flags, idx, i, g.nx, 0);
+    xMinusWS<W, int>(fxm, f, le); xPlusWS<W, int>(fxp, f, re, i, g.nx);
+  } else { xMinusW<W, int>(fxm, f, flags, idx, i, 0); xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0); }
   if (!on) return;
   const bool rowJK = j >= 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
   int out[W];
@@ -340,17 +346,22 @@ __global__ void __launch_bounds__(256) k_correct_velocity(Geo g, const int* __re
   MF_CELLS_W(g, W)
   if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
   const long long Y = g.nx, Z = g.Z;
+  // all loads first, the shuffles of the x - 1 neighbours behind them (see quad.cuh)
   int f[W], fx[W], fy[W], fz[W];
-  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
-  if (g.is3D) ldW<W>(fz, flags, idx - Z); else { for (int c = 0; c < W; c++) fz[c] = 0; }
-  xMinusW<W, int>(fx, f, flags, idx, i, 0);
   float pc[W], px[W], py[W], pz[W];
-  ldW<W>(pc, p, idx); ldW<W>(py, p, idx - Y);
-  if (g.is3D) ldW<W>(pz, p, idx - Z); else { for (int c = 0; c < W; c++) pz[c] = 0.f; }
-  xMinusW<W, float>(px, pc, p, idx, i, 0.f);
   float vx[W], vy[W], vz[W];
+  ldW<W>(f, flags, idx); ldW<W>(fy, flags, idx - Y);
+  if (g.is3D) ldW<W>(fz, flags, idx - Z);
+  ldW<W>(pc, p, idx); ldW<W>(py, p, idx - Y);
+  if (g.is3D) ldW<W>(pz, p, idx - Z);
   ldW<W>(vx, vel.x, idx); ldW<W>(vy, vel.y, idx);
   if (g.is3D) ldW<W>(vz, vel.z, idx);
+  if constexpr (W > 1) {
+    const int fe = xEdgeMinus<W, int>(flags, idx, i, 0);
+    const float pe = xEdgeMinus<W, float>(p, idx, i, 0.f);
+    xMinusWS<W, int>(fx, f, fe); xMinusWS<W, float>(px, pc, pe);
+  } else { xMinusW<W, int>(fx, f, flags, idx, i, 0); xMinusW<W, float>(px, pc, p, idx, i, 0.f); }
+  if (!g.is3D) { for (int c = 0; c < W; c++) { fz[c] = 0; pz[c] = 0.f; } }
 #pragma unroll
   for (int c = 0; c < W; c++) {
     if (i + c < 1 || i + c >= g.nx - 1) continue;

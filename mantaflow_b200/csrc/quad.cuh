@@ -58,6 +58,38 @@ __device__ __forceinline__ void xPlusW(T (&o)[W], const T (&c)[W], const T* __re
   o[W - 1] = right;
 }
 
+// The same in two steps, for kernels that issue ALL their loads before the first use: warps issue in order, so a shuffle placed
+// between the loads would wait for its operand and hold the loads behind it back (one round trip to memory per group of loads
+// instead of one per thread -- k_add_buoyancy / k_correct_velocity / k_set_wall_bcs were latency-bound that way).
+// xEdgeMinus / xEdgePlus: the one value per warp that no lane holds (lane 0's left cell, lane 31's right cell), loaded with
+// the other loads; xMinusWS / xPlusWS: the shuffle, after the loads.
+template <int W, class T>
+__device__ __forceinline__ T xEdgeMinus(const T* __restrict__ p, long long idx, int i, T edge) {
+  return ((threadIdx.x & 31) == 0 && i > 0) ? p[idx - 1] : edge;
+}
+template <int W, class T>
+__device__ __forceinline__ T xEdgePlus(const T* __restrict__ p, long long idx, int i, int nx, T edge) {
+  return (((threadIdx.x & 31) == 31 || i + 2 * W > nx) && i + W < nx) ? p[idx + W] : edge;
+}
+template <int W, class T>
+__device__ __forceinline__ void xMinusWS(T (&o)[W], const T (&c)[W], T le) {
+  static_assert(W > 1, "one cell per thread: use xMinusW");
+  T left = __shfl_up_sync(0xffffffffu, c[W - 1], 1);
+  if ((threadIdx.x & 31) == 0) left = le;
+  o[0] = left;
+#pragma unroll
+  for (int q = 1; q < W; q++) o[q] = c[q - 1];
+}
+template <int W, class T>
+__device__ __forceinline__ void xPlusWS(T (&o)[W], const T (&c)[W], T re, int i, int nx) {
+  static_assert(W > 1, "one cell per thread: use xPlusW");
+  T right = __shfl_down_sync(0xffffffffu, c[0], 1);
+  if ((threadIdx.x & 31) == 31 || i + 2 * W > nx) right = re;
+#pragma unroll
+  for (int q = 0; q + 1 < W; q++) o[q] = c[q + 1];
+  o[W - 1] = right;
+}
+
 inline dim3 quadGridOf(dim3 b, const Geo& g, int W) { return dim3(cdiv(cdiv(g.nx, W), b.x), cdiv(g.ny, b.y), cdiv(g.k1 - g.k0, b.z)); }
 // ijk kernel template kern<W> over every local rank's z range (first parameter Geo), then the cross-rank barrier
 #define MF_LAUNCH_IJK_W(s, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { const mf::Geo _g = mf::geo((s), _r); \

@@ -364,3 +364,42 @@ def test_rowcode_cache_follows_flag_changes(monkeypatch):
     for (pa, va, ia), (pb, vb, ib) in zip(a, b):
         assert ia == ib and np.array_equal(pa.view(np.int32), pb.view(np.int32)) and np.array_equal(va.view(np.int32), vb.view(np.int32))
     assert not np.array_equal(a[1][0], a[2][0]) and not np.array_equal(a[3][0], a[4][0]) and not np.array_equal(a[4][0], a[5][0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gravity", [(0.0, -6e-3, 0.0), (0.0, 0.0, 0.0), (-0.0, 2e-3, 0.0), (1e-3, -2e-3, 3e-3)])
+def test_add_buoyancy_bits(gravity):
+    """KnAddBuoyancy (extforces.cpp:73-81) bit for bit against the reference's expression evaluated in numpy (double product and
+    sum, rounded once), with the inputs that tell the kernel's shortcuts apart: negative zeros in the velocity, an infinite and a
+    NaN factor, zero strength components of either sign (float path) and non-zero ones (double path)"""
+    from mantaflow_b200 import manta
+    rs = np.random.RandomState(5)
+    size = (24, 10, 12)
+    f = _flags(rs, size, 3)
+    nz, ny, nx = f.shape
+    dens = rs.rand(nz, ny, nx).astype(np.float32)
+    dens[3, 4, 5] = np.inf; dens[6, 5, 9] = np.nan; dens[7, 3, 11] = -dens[7, 3, 11]
+    vel0 = (rs.rand(nz, ny, nx, 3).astype(np.float32) - np.float32(0.5))
+    vel0[rs.rand(nz, ny, nx, 3) < 0.3] = np.float32(-0.0)
+    s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+    flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+    density = s.create(manta.RealGrid); density.from_numpy(dens)
+    vel = s.create(manta.MACGrid); vel.from_numpy(vel0)
+    manta.addBuoyancy(flags=flags, density=density, vel=vel, gravity=manta.vec3(*gravity))
+    got = vel.to_numpy()
+    dt, dx = np.float32(s.timestep), np.float32(1.0 / max(size))
+    want = vel0.copy()
+    fluid = (f & FLUID) != 0
+    for c, sh in ((0, (0, 0, 1)), (1, (0, 1, 0)), (2, (1, 0, 0))):
+        strength = np.float32(np.float32(np.float32(-np.float32(gravity[c])) * dt) / dx) * np.float32(1.0)   # -gravity * (dt / dx) * coefficient, extforces.cpp:86-88
+        lo = tuple(slice(1 - d, (n - 1) - d) for d, n in zip(sh, (nz, ny, nx)))
+        hi = (slice(1, nz - 1), slice(1, ny - 1), slice(1, nx - 1))
+        m = fluid[hi] & fluid[lo]
+        with np.errstate(invalid="ignore", over="ignore"):
+            fs = (dens[hi] + dens[lo]).astype(np.float32)
+            upd = (want[hi + (c,)].astype(np.float64) + (0.5 * np.float64(strength)) * fs.astype(np.float64)).astype(np.float32)
+        w = want[hi + (c,)]
+        w[m] = upd[m]
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan)
+    assert np.array_equal(got.view(np.int32)[~nan], want.view(np.int32)[~nan])
