@@ -130,9 +130,13 @@ __global__ void __launch_bounds__(256) k_cg_spmv_dot_code(Geo g, Span sp, CgVecs
       if (idx - Z >= 0) zm = *reinterpret_cast<const float4*>(v.search + idx - Z);
       if (idx + Z < N) zp = *reinterpret_cast<const float4*>(v.search + idx + Z);
     }
+    // the two x neighbours no lane of the warp holds are loaded with the other loads, before the shuffles wait for `s`
+    const bool edgeM = lane == 0, edgeP = lane == 31 || q + 1 >= q1;
+    const float xmE = (edgeM && idx - 1 >= 0) ? v.search[idx - 1] : 0.f;
+    const float xpE = (edgeP && idx + 4 < N) ? v.search[idx + 4] : 0.f;
     float xm = __shfl_up_sync(0xffffffffu, s.w, 1), xp = __shfl_down_sync(0xffffffffu, s.x, 1);
-    if (lane == 0) xm = (idx - 1 >= 0) ? v.search[idx - 1] : 0.f;
-    if (lane == 31 || q + 1 >= q1) xp = (idx + 4 < N) ? v.search[idx + 4] : 0.f;
+    if (edgeM) xm = xmE;
+    if (edgeP) xp = xpE;
     float4 t;
     t.x = rowFromCode((int)(cw.x & 0xffffu), s.x, xm, s.y, ym.x, yp.x, zm.x, zp.x, g.is3D);
     t.y = rowFromCode((int)(cw.x >> 16), s.y, s.x, s.z, ym.y, yp.y, zm.y, zp.y, g.is3D);
