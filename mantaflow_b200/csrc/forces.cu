@@ -201,37 +201,17 @@ __global__ void k_set_inflow(Geo g, V3 vel, int dim, int p0, float vx, float vy,
 
 // KnSetWallBcs (extforces.cpp:187-237): all cells, in place.  W x-consecutive cells per thread (quad.cuh); the kernel streams
 // the flags and touches a velocity component only where a wall condition applies (a thin shell of the domain).
+// wallBcsApply: the rules for one group of W cells whose flags and the flags of the six neighbours are in registers.
 template <int W>
-__global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel) {
-  MF_CELLS_W(g, W)
-  const long long Y = g.nx, Z = g.Z;
-  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
-  // all loads first, the shuffles of the x neighbours behind them (quad.cuh)
-  ldW<W>(f, flags, idx);
-  if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
-  if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
-  if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
-  if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
-  if constexpr (W > 1) {
-    const int le = xEdgeMinus<W, int>(flags, idx, i, 0), re = xEdgePlus<W, int>(flags, idx, i, g.nx, 0);
-    xMinusWS<W, int>(fxm, f, le); xPlusWS<W, int>(fxp, f, re, i, g.nx);
-  } else { xMinusW<W, int>(fxm, f, flags, idx, i, 0); xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0); }
-  if (!on) return;
-  if (g.is3D) {
-    // every rule below needs an obstacle or a stick bit in the cell or one of its six neighbours: the bulk of the domain leaves here
-    int any = 0;
-#pragma unroll
-    for (int c = 0; c < W; c++) any |= f[c] | fxm[c] | fxp[c] | fym[c] | fyp[c] | fzm[c] | fzp[c];
-    if (!(any & (MF_OBSTACLE | MF_STICK))) return;
-  }
+__device__ __forceinline__ void wallBcsApply(const Geo& g, int i, int j, int k, long long idx, const int (&f)[W], const int (&fxm)[W], const int (&fxp)[W],
+                                             const int (&fym)[W], const int (&fyp)[W], const int (&fzm)[W], const int (&fzp)[W],
+                                             V3 vel, CV3 obvel, int haveObvel) {
   // what happens to each component of each cell: 0 keep, 1 set to the obstacle velocity, 2 set to zero (applied in this order)
   int ax[W], ay[W], az[W];
   bool anyx = false, anyy = false, anyz = false;
 #pragma unroll
   for (int c = 0; c < W; c++) {
     ax[c] = ay[c] = az[c] = 0;
-    // (a row of 4-cell groups is a whole number of warps whose first / last lane sits at a wall: the branch is uniform for the
-    // one active lane of such a warp, so its cells without an obstacle / stick neighbour cost a test, not the rules)
     if (g.is3D && !((f[c] | fxm[c] | fxp[c] | fym[c] | fyp[c] | fzm[c] | fzp[c]) & (MF_OBSTACLE | MF_STICK))) continue;
     const bool curFluid = fIsFluid(f[c]), curObs = fIsObstacle(f[c]);
     if (!curFluid && !curObs) continue;
@@ -269,6 +249,57 @@ __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restri
     for (int c = 0; c < W; c++) v[c] = az[c] == 0 ? v[c] : (az[c] == 1 ? o[c] : 0.f);
     stW<W>(vel.z, idx, v);
   }
+}
+// split != 0 (3-D, W = 4): the groups at the two x walls are left to k_set_wall_bcs_edge.  A row of 4-cell groups is a whole
+// number of warps whose first / last lane sits at a wall, so with those groups in the same launch NO warp could take the early
+// exit below and the kernel was bound by the rules' instructions (380 per warp) instead of the flag stream.
+template <int W>
+__global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel, int split) {
+  MF_CELLS_W(g, W)
+  const long long Y = g.nx, Z = g.Z;
+  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  // all loads first, the shuffles of the x neighbours behind them (quad.cuh)
+  ldW<W>(f, flags, idx);
+  if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
+  if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
+  if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
+  if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  if constexpr (W > 1) {
+    const int le = xEdgeMinus<W, int>(flags, idx, i, 0), re = xEdgePlus<W, int>(flags, idx, i, g.nx, 0);
+    xMinusWS<W, int>(fxm, f, le); xPlusWS<W, int>(fxp, f, re, i, g.nx);
+  } else { xMinusW<W, int>(fxm, f, flags, idx, i, 0); xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0); }
+  if (!on) return;
+  if (split && (i == 0 || i + W >= g.nx)) return;                      // k_set_wall_bcs_edge
+  if (g.is3D) {
+    // every rule needs an obstacle or a stick bit in the cell or one of its six neighbours: the bulk of the domain leaves here
+    int any = 0;
+#pragma unroll
+    for (int c = 0; c < W; c++) any |= f[c] | fxm[c] | fxp[c] | fym[c] | fyp[c] | fzm[c] | fzp[c];
+    if (!(any & (MF_OBSTACLE | MF_STICK))) return;
+  }
+  wallBcsApply<W>(g, i, j, k, idx, f, fxm, fxp, fym, fyp, fzm, fzp, vel, obvel, haveObvel);
+}
+// the first and the last group of every row (blockDim.x == 2: side), see above
+template <int W>
+__global__ void __launch_bounds__(256) k_set_wall_bcs_edge(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel) {
+  const int side = threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + g.k0;
+  if (j >= g.ny || k >= g.k1) return;
+  if (side == 1 && g.nx <= W) return;                                   // one group per row: side 0 has it
+  const int i = side == 0 ? 0 : g.nx - W;
+  const long long Y = g.nx, Z = g.Z;
+  const long long idx = (long long)i + (long long)g.nx * j + (long long)g.nx * g.ny * k;
+  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  ldW<W>(f, flags, idx);
+  if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
+  if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
+  if (g.is3D && k > 0) ldW<W>(fzm, flags, idx - Z); else { for (int c = 0; c < W; c++) fzm[c] = 0; }
+  if (g.is3D && k < g.nz - 1) ldW<W>(fzp, flags, idx + Z); else { for (int c = 0; c < W; c++) fzp[c] = 0; }
+  const int le = (i > 0) ? flags[idx - 1] : 0, re = (i + W < g.nx) ? flags[idx + W] : 0;
+#pragma unroll
+  for (int c = 0; c < W; c++) { fxm[c] = c > 0 ? f[c - 1] : le; fxp[c] = c + 1 < W ? f[c + 1] : re; }
+  wallBcsApply<W>(g, i, j, k, idx, f, fxm, fxp, fym, fyp, fzm, fzp, vel, obvel, haveObvel);
 }
 
 // KnSetWallBcsFrac (extforces.cpp:240-323): writes velTarget for every cell
@@ -524,7 +555,13 @@ int mf_set_wall_bcs(const mf_grid* fp, mf_grid* vp, const mf_grid* obvel, const 
   if (!phiObs || !fractions) {
     CV3 ov; ov.x = ov.y = ov.z = nullptr;
     if (obvel) ov = cv3(G(obvel));
-    MF_LAUNCH_IJK_W(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0);
+    const int split = (s->is3D && s->nx % 4 == 0 && !getenv("MF_WALLBCS_NOSPLIT")) ? 1 : 0;
+    if (split) {
+      const dim3 eb(2, 64, 2);
+      MF_RANKS(s, r) { const Geo g = geo(s, r);
+        if (g.k1 > g.k0) { MF_LAUNCH(s, k_set_wall_bcs_edge<4>, dim3(1, cdiv(g.ny, 64), cdiv(g.k1 - g.k0, 2)), eb, g, flags->di(), v3(vel), ov, obvel ? 1 : 0); } }
+    }
+    MF_LAUNCH_IJK_W(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0, split);
   } else {
     mfAssert(s->nx >= 3 && s->ny >= 3, "setWallBcs: grid too small");
     float* tmp = s->getVec();

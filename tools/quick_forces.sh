@@ -6,6 +6,6 @@ python - <<'PY'
 import json
 d = json.load(open("gpurun_out/bench_quick.json")); print(d["ms_per_step"], d["pcg_iterations"])
 for k in json.load(open("gpurun_out/kq.json"))["kernels"]:
-    if k["kernel"] in ("k_set_wall_bcs", "k_add_buoyancy", "k_cg_dot_sigma", "k_correct_velocity", "k_make_rhs_plain", "k_make_laplace_code", "k_cg_update", "k_cg_search", "k_cg_dot_beta", "k_cg_spmv_dot_code"):
+    if k["kernel"] in ("k_set_wall_bcs", "k_set_wall_bcs_edge<4>", "k_set_wall_bcs_edge", "k_add_buoyancy", "k_cg_dot_sigma", "k_correct_velocity", "k_make_rhs_plain", "k_make_laplace_code", "k_cg_update", "k_cg_search", "k_cg_dot_beta", "k_cg_spmv_dot_code"):
         print("%-22s %7.1f us x %.1f" % (k["kernel"], k["avg_us"], k["launches_per_step"]))
 PY
