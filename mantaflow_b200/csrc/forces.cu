@@ -456,6 +456,7 @@ int mf_reset_outflow(mf_grid* fp, mf_grid* phi, mf_grid* real) {
   Grid* flags = G(fp); Solver* s = flags->s; s->use();
   if (phi) REQ_GRID(phi, G(phi)->isReal(), "phi", "resetOutflow");
   if (real) REQ_GRID(real, G(real)->isReal(), "real", "resetOutflow");
+  { const int o = flags->outflowState; markFlagsChanged(flags); flags->outflowState = o; }   // fluid / empty bits change, the outflow bit does not
   MF_RANKS(s, r) { const Span sp = span(s, r);
     MF_LAUNCH(s, k_reset_outflow, s->numSMs * 8, 256, flags->di() + sp.off, phi ? G(phi)->d + sp.off : nullptr, real ? G(real)->d + sp.off : nullptr, sp.n); }
   s->rankSync();

@@ -29,6 +29,22 @@ CUDA = True
 
 _TYPE_REAL, _TYPE_INT, _TYPE_VEC3, _TYPE_MAC, _TYPE_LEVELSET, _TYPE_FLAGS = 1, 2, 4, 8, 16, 32
 
+_UNI_HEADER_BYTES = 288
+
+
+def _unifyGridType(t):
+    """unifyGridType (fileio/iogrids.cpp:213-221): real <> levelset, vec3 <> MAC"""
+    if t & _TYPE_REAL:
+        t |= _TYPE_LEVELSET
+    if t & _TYPE_LEVELSET:
+        t |= _TYPE_REAL
+    if t & _TYPE_VEC3:
+        t |= _TYPE_MAC
+    if t & _TYPE_MAC:
+        t |= _TYPE_VEC3
+    return t
+
+
 _debugLevel = 1
 # the reference's solvePressure(preconditioner=PcNone) throws in setICPreconditioner (conjugategrad.cpp:312);
 # set allowPcNone = True to run plain CG instead
@@ -413,11 +429,13 @@ class GridBase(object):
             with gzip.open(name, "wb", compresslevel=1) as f:
                 f.write(a.tobytes())
         elif name.endswith(".uni"):
+            # "MNT3" + UniHeader v4 (fileio/iogrids.cpp:38-44): 6 ints, info[252], int dimT, 8-byte timestamp = 288 bytes
             nx, ny, nz = self.parent._size
             et = 0 if self._dtype == np.int32 else (2 if self._ncomp == 3 else 1)
             info = lib().mf_build_info()[:251]
-            head = struct.pack("<iiiiii252sQ", nx, ny, nz, self._type, et, a.itemsize * self._ncomp,
-                               info, int(_time.time()))
+            head = struct.pack("<iiiiii252siQ", nx, ny, nz, self._type, et, a.itemsize * self._ncomp,
+                               info, 0, int(_time.time()))
+            assert len(head) == _UNI_HEADER_BYTES
             with gzip.open(name, "wb", compresslevel=1) as f:
                 f.write(b"MNT3")
                 f.write(head)
@@ -435,12 +453,18 @@ class GridBase(object):
         elif name.endswith(".uni"):
             with gzip.open(name, "rb") as f:
                 ident = f.read(4)
-                if ident != b"MNT3":
+                if ident not in (b"MNT3", b"MNT2"):     # MNT2 (UniLegacyHeader3: info[256], no dimT) has the same 288 bytes
                     raise MantaError("readGridUni: Unknown header '%s' " % ident.decode("ascii", "replace"))
-                nx, ny, nz, gt, et, bpe = struct.unpack("<iiiiii", f.read(24))
-                f.read(252 + 8)
+                head = f.read(_UNI_HEADER_BYTES)
+                if len(head) != _UNI_HEADER_BYTES:
+                    raise MantaError("can't read file, no header present")
+                nx, ny, nz, gt, et, bpe = struct.unpack("<iiiiii", head[:24])
                 if (nx, ny, nz) != self.parent._size:
                     raise MantaError("grid dim doesn't match, [%d,%d,%d] vs %s" % (nx, ny, nz, self.getSize()))
+                if _unifyGridType(gt) != _unifyGridType(self._type):
+                    raise MantaError("grid type doesn't match %d vs %d" % (gt, self._type))
+                if bpe != np.dtype(self._dtype).itemsize * self._ncomp:
+                    raise MantaError("grid element size doesn't match %d vs %d" % (bpe, np.dtype(self._dtype).itemsize * self._ncomp))
                 a = np.frombuffer(f.read(), dtype=self._dtype)
         elif name.endswith(".npy"):
             a = np.load(name)

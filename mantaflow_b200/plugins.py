@@ -18,7 +18,11 @@ __all__ = ["advectSemiLagrange", "setWallBcs", "addBuoyancy", "addGravity", "add
            "solvePressure", "releaseMG", "cgSolveDiffusion", "gridMaxDiff", "gridMaxDiffInt", "gridMaxDiffVec3",
            "getSolveInfo", "extrapolateMACSimple", "extrapolateMACFromWeight", "extrapolateLsSimple", "extrapolateVec3Simple",
            "updateFractions", "setObstacleFlags", "densityInflow", "addNoise", "getComponent", "setComponent",
-           "sampleFlagsWithParticles", "mapPartsToMAC", "markFluidCells", "mapMACToParts", "flipVelocityUpdate", "GridCg"]
+           "sampleFlagsWithParticles", "mapPartsToMAC", "markFluidCells", "mapMACToParts", "flipVelocityUpdate", "GridCg",
+           "copyArrayToGridReal", "copyGridToArrayReal", "copyArrayToGridFlag", "copyGridToArrayFlag", "copyArrayToGridLevelset",
+           "copyGridToArrayLevelset", "copyArrayToGridVec3", "copyGridToArrayVec3", "copyArrayToGridMAC", "copyGridToArrayMAC",
+           "copyArrayToPdataInt", "copyPdataToArrayInt", "copyArrayToPdataReal", "copyPdataToArrayReal", "copyArrayToPdataVec3",
+           "copyPdataToArrayVec3"]
 
 
 def _h(g):
@@ -412,3 +416,93 @@ def flipVelocityUpdate(flags=None, vel=None, velOld=None, parts=None, partVel=No
     _req(velOld, M.MACGrid, "velOld", "flipVelocityUpdate")
     _parts(parts, "parts", "flipVelocityUpdate")
     check(lib().mf_flip_velocity_update(_h(flags), vel._h, velOld._h, parts._h, _pvec(partVel, parts, "partVel", "flipVelocityUpdate"), float(flipRatio)))
+
+
+# ---- numpy bridge (source/plugin/numpyconvert.cpp:145-222): C-order arrays, z slowest; the grid side is device memory -------------
+def _np_to_grid(fn, cls, ncomp, int_grid=False):
+    import numpy as np
+
+    def plugin(source=None, target=None, **kwargs):
+        M._checkArgs(fn, kwargs, ())
+        if source is None:
+            raise MantaError("Argument 'source' is not defined.")
+        _req(target, cls, "target", fn)
+        a = np.asarray(source)
+        nx, ny, nz = target.parent._size
+        if a.size != nx * ny * nz * ncomp:
+            raise MantaError("The size of the numpy array doesn't match the size of the grid!")
+        if a.ndim >= 3 and tuple(a.shape[:3]) != (nz, ny, nx):
+            raise MantaError("The dimensions of source grid (%d, %d, %d) and target numpy array (%d, %d, %d) do not match!"
+                             % (nx, ny, nz, a.shape[2], a.shape[1], a.shape[0]))
+        ok = ("i", "u") if int_grid else ("f",)
+        if a.dtype.kind not in ok or a.dtype.itemsize not in (4, 8):
+            raise MantaError("unknown/unsupported type of Numpy array")
+        target.from_numpy(a)           # converts to the grid's element type like the N_DOUBLE / N_INT branches
+    plugin.__name__ = fn
+    return M._plugin(plugin)
+
+
+def _grid_to_np(fn, cls, ncomp):
+    import numpy as np
+
+    def plugin(source=None, target=None, **kwargs):
+        M._checkArgs(fn, kwargs, ())
+        _req(source, cls, "source", fn)
+        if not isinstance(target, np.ndarray):
+            raise MantaError("Argument 'target' is not defined.")
+        nx, ny, nz = source.parent._size
+        if target.size != nx * ny * nz * ncomp:
+            raise MantaError("The size of the numpy array doesn't match the size of the grid!")
+        if target.ndim >= 3 and tuple(target.shape[:3]) != (nz, ny, nx):
+            raise MantaError("The dimensions of source grid (%d, %d, %d) and target numpy array (%d, %d, %d) do not match!"
+                             % (nx, ny, nz, target.shape[2], target.shape[1], target.shape[0]))
+        if not target.flags["C_CONTIGUOUS"] or not target.flags["WRITEABLE"]:
+            raise MantaError("numpy array must be C-contiguous and writeable")
+        target.reshape(source._shape())[...] = source.to_numpy()
+    plugin.__name__ = fn
+    return M._plugin(plugin)
+
+
+copyArrayToGridReal = _np_to_grid("copyArrayToGridReal", M.RealGrid, 1)
+copyGridToArrayReal = _grid_to_np("copyGridToArrayReal", M.RealGrid, 1)
+copyArrayToGridLevelset = _np_to_grid("copyArrayToGridLevelset", M.LevelsetGrid, 1)
+copyGridToArrayLevelset = _grid_to_np("copyGridToArrayLevelset", M.LevelsetGrid, 1)
+copyArrayToGridFlag = _np_to_grid("copyArrayToGridFlag", M.FlagGrid, 1, int_grid=True)
+copyGridToArrayFlag = _grid_to_np("copyGridToArrayFlag", M.FlagGrid, 1)
+copyArrayToGridVec3 = _np_to_grid("copyArrayToGridVec3", M.VecGrid, 3)
+copyGridToArrayVec3 = _grid_to_np("copyGridToArrayVec3", M.VecGrid, 3)
+copyArrayToGridMAC = _np_to_grid("copyArrayToGridMAC", M.MACGrid, 3)
+copyGridToArrayMAC = _grid_to_np("copyGridToArrayMAC", M.MACGrid, 3)
+
+
+def _np_to_pdata(fn, cls):
+    import numpy as np
+
+    def plugin(source=None, target=None, **kwargs):
+        M._checkArgs(fn, kwargs, ())
+        _req(target, cls, "target", fn)
+        a = np.asarray(source)
+        if a.size != target.parts.size() * (3 if cls._ncomp == 3 else 1):
+            raise MantaError("The size of the numpy array doesn't match the size of the pdata field!")
+        target.from_numpy(a)
+    plugin.__name__ = fn
+    return M._plugin(plugin)
+
+
+def _pdata_to_np(fn, cls):
+    def plugin(source=None, target=None, **kwargs):
+        M._checkArgs(fn, kwargs, ())
+        _req(source, cls, "source", fn)
+        if target is None or target.size != source.parts.size() * (3 if cls._ncomp == 3 else 1):
+            raise MantaError("The size of the numpy array doesn't match the size of the pdata field!")
+        target.reshape(-1)[...] = source.to_numpy().reshape(-1)
+    plugin.__name__ = fn
+    return M._plugin(plugin)
+
+
+copyArrayToPdataInt = _np_to_pdata("copyArrayToPdataInt", M.PdataInt)
+copyPdataToArrayInt = _pdata_to_np("copyPdataToArrayInt", M.PdataInt)
+copyArrayToPdataReal = _np_to_pdata("copyArrayToPdataReal", M.PdataReal)
+copyPdataToArrayReal = _pdata_to_np("copyPdataToArrayReal", M.PdataReal)
+copyArrayToPdataVec3 = _np_to_pdata("copyArrayToPdataVec3", M.PdataVec3)
+copyPdataToArrayVec3 = _pdata_to_np("copyPdataToArrayVec3", M.PdataVec3)

@@ -247,6 +247,34 @@ def test_live_oracle_plume_step_256():
     assert [i["iterations"] for i in infos] == ref["ref_iterations"].tolist()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("pc", ["PcMGStatic", "PcMIC"])
+def test_live_oracle_simpleplume_shipped_size(pc, parity_report):
+    """BASELINE.json configs[0] at the size scenes/simpleplume.py ships (64 x 96 x 64, wavelet-noise source, MacCormack, buoyancy),
+    8 steps against the unmodified reference run single-threaded (its reductions are then order-stable): with PcMGStatic the state
+    must be BIT-IDENTICAL with the reference's iteration counts; with the scene's default PcMIC the reference's own regression
+    thresholds apply (tools/tests/test_2010_plume3d.py:72-73).  The unmodified scene FILE is run by tests/test_scenes_gpu.py."""
+    _need_oracle()
+    V = C.V
+    extra = {"preconditioner": "$PcMGStatic", "zeroPressureFixing": True} if pc == "PcMGStatic" else {}
+    step = [op if op[1] != "solvePressure" else ["call", "solvePressure", dict(op[2], **extra)] for op in C._SIMPLEPLUME_STEP]
+    setup = [["object", "nz", "NoiseField", {"loadFromFile": True}, C._NZ_PLUME],
+             ["object", "src", "Cylinder", {"center": V(32, 9.6, 32), "radius": 8.96, "z": V(0, 1.92, 0)}]] + C.DOMAIN
+    case = {"size": [64, 96, 64], "dim": 3, "dt": 1.0, "grids": dict(C.BASEGRIDS), "load": [], "inputs": {},
+            "ops": setup + [["repeat", 8, step]], "save": ["density", "vel", "pressure"], "exact": pc == "PcMGStatic",
+            "abs_tol": {"density": 1e-3, "vel": 5e-3, "pressure": 5e-3}}
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as MG
+    ref = MG.run_reference("simpleplume_shipped", case, threads="1")
+    ins, out, infos = T.run_ours(case)
+    rep = parity_report.setdefault("simpleplume_64x96x64_" + pc, {})
+    rep["ref_iterations"] = ref["ref_iterations"].tolist()
+    rep["our_iterations"] = [i["iterations"] for i in infos]
+    for g in case["save"]:
+        T.compare("simpleplume_shipped", case, g, out[g], ref["out_" + g], rep)
+    assert rep["our_iterations"] == rep["ref_iterations"], (rep["our_iterations"], rep["ref_iterations"])
+
+
 def _flip01(res, steps):
     """scenes/flip01_simple.py with dim=3, res as asked (BASELINE.json configs[3]: res=128)"""
     from mantaflow_b200 import manta as M
