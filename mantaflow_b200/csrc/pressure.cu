@@ -246,8 +246,12 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     mgLevels = mg_num_levels(cg.mg);
   }
   cg.init(p->cgAccuracy, p->useL2Norm != 0);
+  // MF_TIME_PCG: user event slots 14 / 15 bracket the iteration loop alone (bench.py: PCG time per iteration)
+  const bool timeLoop = std::getenv("MF_TIME_PCG") != nullptr;
+  if (timeLoop) { for (int e = 14; e < 16; e++) if (!s->userEvents[e]) CUDA_CHECK(cudaEventCreate(&s->userEvents[e])); CUDA_CHECK(cudaEventRecord(s->userEvents[14], s->stream)); }
   if (cg.pcMethod == 2 && !std::getenv("MF_CG_WHOLE_ITERATIONS")) cg.solveSplit(maxIter);
   else cg.solve(maxIter, batch);
+  if (timeLoop) CUDA_CHECK(cudaEventRecord(s->userEvents[15], s->stream));
   if (info) {
     info->iterations = cg.host.iterations; info->resNorm = cg.host.resNorm; info->maxIter = maxIter;
     info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
