@@ -37,6 +37,7 @@ void set_last_error(const std::string& s);
 
 struct Solver;
 struct MgHierarchy;
+struct MicPlan;
 struct Comm;
 struct CommShared;
 
@@ -81,6 +82,7 @@ struct Solver {
   int* hostInts;        // pinned
   float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)
+  MicPlan* mic;         // tile order / flags of the MIC(0) wavefront sweeps (mic.cuh), lazily created
   float* noiseTile;         // 3 x 128^3 wavelet-noise tile (noise.cu), uploaded on first use
   unsigned short* cgCode;   // 16-bit Laplace row codes for the CG's ApplyMatrix (pressure_kernels.cuh CGC_*), lazily allocated
   // the row codes (and the pinned cell of zeroPressureFixing) depend on the flags only: kept while the same flag storage holds
@@ -160,6 +162,7 @@ inline const Solver* S(const mf_solver* s) { return reinterpret_cast<const Solve
 
 void check_same_solver(const Grid* a, const Grid* b, const char* what);
 void release_mg(Solver* s);   // drop the cached multigrid hierarchy (pressure.cu)
+void release_mic(Solver* s);  // drop the MIC(0) sweep plan (pressure.cu)
 #define REQ_GRID(g, cond, name, fn) mfAssert((g) != nullptr && (cond), fn ": argument '" name "' has the wrong grid type or is missing")
 
 // launch helpers -----------------------------------------------------------------------

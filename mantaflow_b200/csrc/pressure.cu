@@ -4,6 +4,7 @@
 #include "reduce.cuh"
 #include "pressure_kernels.cuh"
 #include "cg.cuh"
+#include "mic.cuh"
 #include "multigrid.h"
 #include <cmath>
 #include <cstdlib>
@@ -64,7 +65,7 @@ struct SolveTemps {   // the 7 (+4) temp grids of solvePressureSystem (pressure.
 };
 
 struct CgDriver {
-  Solver* s; CgVecs v; CgState* st; int pcMethod;   // 0 none, 1 red-black MIC, 2 multigrid
+  Solver* s; CgVecs v; CgState* st; int pcMethod;   // 0 none, 1 red-black MIC (partitioned solvers), 2 multigrid, 3 the reference's MIC(0) (mic.cuh)
   float* P; MgHierarchy* mg;
   bool v4 = false;      // nx % 4 == 0: every slab starts and ends on a 16-byte boundary -> vectorised kernels
   CgState host;
@@ -79,6 +80,9 @@ struct CgDriver {
       s->rankSync();
     } else if (pcMethod == 2) {
       mg_apply(mg, v.tmp, v.residual);
+    } else if (pcMethod == 3) {
+      micSweep(s, 1, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, v.residual, v.tmp, st);
+      micSweep(s, 2, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, nullptr, v.tmp, st);
     }
     (void)init;
   }
@@ -230,9 +234,17 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     maxIter = (int)(p->cgMaxIterFac * maxDim) * (s->is3D ? 1 : 4);
     // 2-D: ICP/mICP silently disabled (conjugategrad.cpp:315-321)
     if (preconditioner == MF_PC_MIC && s->is3D) {
-      cg.pcMethod = 1;
       t.pc = s->getReal(); cg.P = t.pc;
-      MF_LAUNCH_IJK(s, k_rbic_init, flags->di(), cg.P, t.A0, t.Ai, t.Aj, t.Ak);
+      // single-GPU solvers run the reference's own sequential MIC(0) as a tile wavefront (bit-identical iterates); z-slab
+      // partitioned solvers keep the red-black variant (a lexicographic sweep would serialise the ranks)
+      if (!s->multi() && !std::getenv("MF_MIC_REDBLACK")) {
+        cg.pcMethod = 3;
+        micSweep(s, 0, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, cg.P, nullptr, nullptr, nullptr);
+      } else {
+        cg.pcMethod = 1;
+        maxIter *= 3;      // the red-black ordering needs about 2.5x the iterations of the sequential one (73 vs 29 on the 18x22x14 case)
+        MF_LAUNCH_IJK(s, k_rbic_init, flags->di(), cg.P, t.A0, t.Ai, t.Aj, t.Ak);
+      }
     } else cg.pcMethod = 0;
   } else {
     maxIter = 100; batch = 1;
@@ -297,7 +309,8 @@ __global__ void __launch_bounds__(256) k_diffusion_matrix(Geo g, const int* __re
 
 using namespace mf;
 
-namespace mf { void release_mg(Solver* s) { if (s->mg) { mg_destroy(s->mg); s->mg = nullptr; } } }
+namespace mf { void release_mg(Solver* s) { if (s->mg) { mg_destroy(s->mg); s->mg = nullptr; } }
+               void release_mic(Solver* s) { if (s->mic) { micDestroy(s->mic); s->mic = nullptr; } } }
 
 extern "C" {
 
@@ -467,8 +480,14 @@ static void cgObjInit(CgObject* c) {
   d.pcMethod = 0; d.P = nullptr; d.mg = nullptr;
   if ((c->method == 1 || c->method == 2) && s->is3D) {
     if (!c->pc) c->pc = s->getReal();
-    d.pcMethod = 1; d.P = c->pc;
-    MF_LAUNCH_IJK(s, k_rbic_init, c->flags->di(), d.P, c->A0->d, c->Ai->d, c->Aj->d, c->Ak->d);
+    d.P = c->pc;
+    if (c->method == 2 && !s->multi() && !std::getenv("MF_MIC_REDBLACK")) {    // PC_mICP: the reference's MIC(0), bit for bit (mic.cuh)
+      d.pcMethod = 3;
+      micSweep(s, 0, c->flags->di(), c->A0->d, c->Ai->d, c->Aj->d, c->Ak->d, d.P, nullptr, nullptr, nullptr);
+    } else {
+      d.pcMethod = 1;
+      MF_LAUNCH_IJK(s, k_rbic_init, c->flags->di(), d.P, c->A0->d, c->Ai->d, c->Aj->d, c->Ak->d);
+    }
   } else if (c->method == 3) {
     if (c->rebuildMg && s->mg) { mg_destroy(s->mg); s->mg = nullptr; }
     c->rebuildMg = false;

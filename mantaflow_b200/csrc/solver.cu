@@ -229,7 +229,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   s->dx = (float)(1.0 / mx);       // grid.cpp:57
   s->device = device;
   s->profTag = -1; s->profLevels = getenv("MF_PROFILE_LEVELS") != nullptr;
-  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->cgCode = nullptr; s->codeFlags = nullptr; s->codeVersion = 0; s->codeFixing = 0; s->codeFixedCell = -1; s->noiseTile = nullptr; s->profiling = false; s->copyIn = nullptr; s->copyOut = nullptr;
+  s->launches = 0; s->poolBytes = 0; s->aosStage = nullptr; s->mg = nullptr; s->mic = nullptr; s->cgCode = nullptr; s->codeFlags = nullptr; s->codeVersion = 0; s->codeFixing = 0; s->codeFixedCell = -1; s->noiseTile = nullptr; s->profiling = false; s->copyIn = nullptr; s->copyOut = nullptr;
   for (int q = 0; q < 16; q++) s->userEvents[q] = nullptr;
   CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
@@ -279,6 +279,7 @@ void mf_solver_destroy(mf_solver* sp) {
   s->use();
   cudaStreamSynchronize(s->stream);
   release_mg(s);
+  release_mic(s);
   for (float* p : s->poolReal) s->gfree(p);
   for (float* p : s->poolVec) s->gfree(p);
   if (s->cgCode) s->gfree(s->cgCode);

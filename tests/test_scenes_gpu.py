@@ -23,7 +23,7 @@ SCENES = os.path.join(HERE, "golden", "scenes")
 # scene file, steps, {object: type}, {object: threshold}, grid size
 RUNS = {
     "simpleplume": ("simpleplume.py", 8, {"density": "RealGrid", "vel": "MACGrid", "pressure": "RealGrid", "flags": "FlagGrid"},
-                    {"density": 1e-3, "vel": 5e-3, "flags": 0}, (64, 96, 64)),
+                    {"density": 1e-3, "vel": 5e-3, "pressure": 5e-3, "flags": 0}, (64, 96, 64)),
     "karman": ("karman.py", 30, {"density": "RealGrid", "vel": "MACGrid", "flags": "FlagGrid", "fractions": "MACGrid", "phiObs": "RealGrid"},
                {"density": 5e-3, "vel": 5e-3, "flags": 0, "fractions": 0, "phiObs": 0}, (128, 64, 1)),
     "flip01_simple": ("flip01_simple.py", 25, {"vel": "MACGrid", "flags": "FlagGrid", "pp": "BasicParticleSystem", "pVel": "PdataVec3"},
