@@ -122,6 +122,18 @@ int          mf_grid_sum_sqr(const mf_grid* g, double* out);             /* Grid
 int          mf_grid_dot(const mf_grid* a, const mf_grid* b, double* out);/* GridDotProduct conjugategrad.cpp:175 */
 int          mf_grid_max_diff(const mf_grid* a, const mf_grid* b, double* out); /* gridMaxDiff* grid.cpp:437-467 */
 
+/* ---- allocation-free reduction ---------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).
+ * GridDotProduct's arithmetic (float products summed in double) on caller-owned DEVICE arrays a_dev[n], b_dev[n]; the result is
+ * written to *out_dev (device memory) asynchronously on `stream` (a cudaStream_t, NULL = the default stream) of the CURRENT
+ * device.  Allocates nothing: the reduction's scratch is a file-scope static __device__ array of MF_NOALLOC_SCRATCH_BYTES that
+ * every GPU loading the library holds until exit.  n > MF_NOALLOC_MAX_ELEMS is rejected (status != 0, mf_last_error()).
+ * All calls on a device share that scratch: calls that overlap on the GPU race -- serialise them (one stream, or graph edges). */
+#define MF_NOALLOC_MAX_ELEMS      33554432LL      /* 4096 blocks x 8192 elements = 2 x 256^3 floats per input */
+#define MF_NOALLOC_SCRATCH_BYTES  33024           /* 4096 partial sums (double) + the ticket counter's 256-byte line */
+int          mf_dot_product_noalloc(const float* a_dev, const float* b_dev, long long n, double* out_dev, void* stream);
+
 /* FlagGrid setup (source/grid.cpp:798-927, plugin/extforces.cpp:106-131) */
 int          mf_flags_init_domain(mf_grid* flags, int boundaryWidth, const char* wall, const char* open,
                                   const char* inflow, const char* outflow, mf_grid* phiWalls /* or NULL */);

@@ -95,6 +95,7 @@ SIGNATURES = {
     "mf_grid_sum_sqr": (_i, [_P, C.POINTER(C.c_double)]),
     "mf_grid_dot": (_i, [_P, _P, C.POINTER(C.c_double)]),
     "mf_grid_max_diff": (_i, [_P, _P, C.POINTER(C.c_double)]),
+    "mf_dot_product_noalloc": (_i, [_P, _P, C.c_longlong, _P, _P]),
     "mf_flags_init_domain": (_i, [_P, _i, _s, _s, _s, _s, _P]),
     "mf_flags_fill_grid": (_i, [_P, _i]),
     "mf_flags_count_cells": (_i, [_P, _i, _i, C.POINTER(_i)]),
