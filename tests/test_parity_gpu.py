@@ -96,6 +96,13 @@ def test_case_matches_reference(name, parity_report):
         except AssertionError as e:
             errors.append(str(e))
     assert not errors, "; ".join(errors)
-    # multigrid-preconditioned solves must take the reference's iteration count (same V-cycle, same stopping rule)
-    if "mg" in name and len(infos) == len(gold["ref_iterations"]) and name.startswith("solve"):
+    # Single-GPU solvers run the reference's own preconditioners operation for operation (GridMg V-cycle, sequential MIC(0) as a
+    # tile wavefront, plain CG): every solve must take the reference's iteration count, and the iterates may differ from the
+    # reference's only through the summation order of the dot products (double sums rounded to float) -- measured on B200 every
+    # case is bit-identical (gpurun_out/parity_report.json); the bar asserted here is 1e-5 relative L-inf, 100x inside the case
+    # tolerances that the z-slab partitioned path (red-black IC, per-rank partial sums) is held to in test_multi_gpu.py.
+    if len(infos) == len(gold["ref_iterations"]):
         assert rep["our_iterations"] == rep["ref_iterations"], (rep["our_iterations"], rep["ref_iterations"])
+    for g in case["save"]:
+        if rep[g]["ref_max_abs"] > 0:
+            assert rep[g]["rel"] <= 1e-5, "%s/%s: rel L-inf %.3g vs the reference on a single GPU" % (name, g, rep[g]["rel"])
