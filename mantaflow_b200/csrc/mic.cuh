@@ -23,6 +23,7 @@ struct MicPlan {
   int* ctl;       // device: [0] ticket counter, [1] finished CTAs (the last one resets both)
   int epoch;
   int ctas;
+  MicPlan* code16;  // the 16^3-tile plan of the row-code fast path (k_mic_code), lazily created
 };
 
 struct MicArgs {
@@ -162,19 +163,228 @@ __global__ void __launch_bounds__(16 * TZ) k_mic_wave(Geo g, MicArgs a) {
   if (tid == 0) { if (atomicAdd(&a.ctl[1], 1) == (int)gridDim.x - 1) { a.ctl[0] = 0; a.ctl[1] = 0; __threadfence(); } }
 }
 
+// ---- fast path for the plain Laplace matrix (16-bit row codes, pressure_kernels.cuh CGC_*) ---------------------------------
+// Couplings are 0 or -1, so (dst(n) * A) * P == dst(n) * (A * P) bit for bit (a multiplication by -1 or +0 is exact), and
+// A * P is -P(n) where the code has the coupling bit and +0 elsewhere: a tile needs P, the right-hand side and 2 bytes of code per
+// cell (14 B/cell of DRAM traffic per sweep instead of 28).  One thread per x-line as above, but the value of the line's
+// previous cell stays in a register, the coefficients of the next cell are fetched while the thread waits at the barrier, the
+// results leave for global memory as they are produced (only the fence is left at the end of the tile), the ticket of the next
+// tile is drawn while this one is swept, and the three upstream faces are fetched by three warps that each wait for their own flag.
+// MODE 1 forward, 2 backward.  Tile 16 x 16 x 16, 256 threads.
+struct MicCodeArgs {
+  const unsigned short* code; const float* P; const float* src; float* dst;
+  const int* order; int* done; int* ctl; int ntiles, tx, ty, tz, epoch; const CgState* st;
+  unsigned char lines[256];   // thread -> x-line (jl | kl << 4), sorted by jl + kl
+  unsigned long long* dbg;    // MF_MIC_DBG: 8 globaltimer stamps per tile (ticket, static data, flags seen, faces, sweep, published, SM id)
+};
+__device__ __forceinline__ unsigned long long micNow() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define MIC_STAMP(slot) do { if (a.dbg && tid == 0) a.dbg[(size_t)t * 8 + (slot)] = micNow(); } while (0)
+template <int MODE>
+__global__ void __launch_bounds__(256, 3) k_mic_code(Geo g, MicCodeArgs a) {
+  constexpr int TX = 16, TY = 16, TZ = 16, S = TX + 3, R = TY + 2, PL = S * R, SZ = PL * (TZ + 1);
+  extern __shared__ float sm[];
+  float* sP = sm; float* sD = sm + SZ;
+  unsigned short* sC = reinterpret_cast<unsigned short*>(sm + 2 * SZ);
+  __shared__ int sQ[2];
+  const int tid = threadIdx.x;
+  if (a.st->done) return;
+  // lines in the order of their diagonal jl + kl: the lines that are active on a hyperplane sit in neighbouring warps, the
+  // other warps only pass the barrier
+  const int jl = a.lines[tid] & 15, kl = a.lines[tid] >> 4;
+  constexpr int dir = (MODE == 2) ? -1 : 1;
+  constexpr int BI = (MODE == 2) ? CGC_XP : CGC_XM, BJ = (MODE == 2) ? CGC_YP : CGC_YM, BK = (MODE == 2) ? CGC_ZP : CGC_ZM;
+  const long long Y = g.nx, Z = g.Z;
+  const float* gsrc = (MODE == 1) ? a.src : a.dst;
+  if (tid == 0) sQ[0] = atomicAdd(&a.ctl[0], 1);
+  __syncthreads();
+  for (int round = 0;; round++) {
+    const int q = sQ[round & 1];
+    if (q >= a.ntiles) break;
+    int nextTicket = 0;
+    if (tid == 0) nextTicket = atomicAdd(&a.ctl[0], 1);     // consumed at the end of this tile
+    int t = a.order[q];
+    int bi = t % a.tx, bj = (t / a.tx) % a.ty, bk = t / (a.tx * a.ty);
+    if (MODE == 2) { bi = a.tx - 1 - bi; bj = a.ty - 1 - bj; bk = a.tz - 1 - bk; t = bi + a.tx * (bj + a.ty * bk); }
+    const int i0 = (MODE == 2) ? bi * TX + TX - 1 : bi * TX;      // local (il, jl, kl) -> global (i0 + dir * il, ...)
+    const int j0 = (MODE == 2) ? bj * TY + TY - 1 : bj * TY;
+    const int k0 = (MODE == 2) ? bk * TZ + TZ - 1 : bk * TZ;
+    MIC_STAMP(0);
+    if (a.dbg && tid == 0) { unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid)); a.dbg[(size_t)t * 8 + 6] = smid; a.dbg[(size_t)t * 8 + 7] = q; }
+    // ---- static data, all loads of a thread in one batch: the tile's rows are 16 floats = 4 x 16 bytes (nx % 4 == 0)
+    {
+      const int xb = bi * TX;
+      float4 vp[4], vs[4]; uint2 vc[4]; float hp[3];
+      int rowOk[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {           // (row, quarter): 1024 items
+        const int item = tid + 256 * u, qx = item & 3, row = item >> 2, rj = row & 15, rk = row >> 4;     // row in GLOBAL orientation
+        const int gj = bj * TY + rj, gk = bk * TZ + rk, gx = xb + 4 * qx;
+        rowOk[u] = (gj < g.ny && gk < g.nz && gx < g.nx);
+        const long long idx = gx + Y * gj + Z * gk;
+        vp[u] = make_float4(0.f, 0.f, 0.f, 0.f); vs[u] = vp[u]; vc[u] = make_uint2(0u, 0u);
+        if (rowOk[u]) {
+          vp[u] = *reinterpret_cast<const float4*>(a.P + idx);
+          vs[u] = *reinterpret_cast<const float4*>(gsrc + idx);
+          vc[u] = *reinterpret_cast<const uint2*>(a.code + idx);
+        }
+      }
+      if (MODE == 1) {                         // P on the three lower faces (768 values)
+#pragma unroll
+        for (int u = 0; u < 3; u++) {
+          const int c = tid;
+          int li, lj, lk;
+          if (u == 0) { li = -1; lj = c % TY; lk = c / TY; }
+          else if (u == 1) { li = c % TX; lj = -1; lk = c / TX; }
+          else { li = c % TX; lj = c / TX; lk = -1; }
+          const int gi = i0 + li, gj = j0 + lj, gk = k0 + lk;
+          const bool in = gi >= 0 && gi < g.nx && gj >= 0 && gj < g.ny && gk >= 0 && gk < g.nz;
+          hp[u] = in ? a.P[gi + Y * gj + Z * gk] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int item = tid + 256 * u, qx = item & 3, row = item >> 2, rj = row & 15, rk = row >> 4;
+        const int lj = (MODE == 2) ? TY - 1 - rj : rj, lk = (MODE == 2) ? TZ - 1 - rk : rk;
+        const float pv[4] = { vp[u].x, vp[u].y, vp[u].z, vp[u].w };
+        const float sv[4] = { vs[u].x, vs[u].y, vs[u].z, vs[u].w };
+        const unsigned cv[4] = { vc[u].x & 0xffffu, vc[u].x >> 16, vc[u].y & 0xffffu, vc[u].y >> 16 };
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          const int xi = 4 * qx + e, li = (MODE == 2) ? TX - 1 - xi : xi;
+          const int sc = (li + 1) + S * ((lj + 1) + R * (lk + 1));
+          sP[sc] = pv[e];
+          sD[sc] = (cv[e] & CGC_FLUID) ? sv[e] : 0.f;       // non-fluid cells: the cleared temp grid's 0
+          sC[li + TX * (lj + TY * lk)] = (unsigned short)cv[e];
+        }
+      }
+      // halo slots: P of the lower faces (forward), zero for the dynamic values until the upstream faces arrive
+#pragma unroll
+      for (int u = 0; u < 3; u++) {
+        const int c = tid;
+        int li, lj, lk;
+        if (u == 0) { li = -1; lj = c % TY; lk = c / TY; }
+        else if (u == 1) { li = c % TX; lj = -1; lk = c / TX; }
+        else { li = c % TX; lj = c / TX; lk = -1; }
+        const int sc = (li + 1) + S * ((lj + 1) + R * (lk + 1));
+        if (MODE == 1) sP[sc] = hp[u];
+        sD[sc] = 0.f;
+      }
+    }
+    __syncthreads();
+    MIC_STAMP(1);
+    // ---- the three upstream faces, each fetched by the warp that waited for its tile (8 values per lane, one batch)
+    {
+      const int w = tid >> 5, lane = tid & 31;
+      if (w < 3) {
+        const int pb = (w == 0) ? bi - dir : (w == 1) ? bj - dir : bk - dir;
+        const int lim = (w == 0) ? a.tx : (w == 1) ? a.ty : a.tz;
+        if (pb >= 0 && pb < lim) {
+          const int pt = (w == 0) ? t - dir : (w == 1) ? t - dir * a.tx : t - dir * a.tx * a.ty;
+          if (lane == 0) { while (micLdAcquire(&a.done[pt]) != a.epoch) { } }
+          __syncwarp();
+          if (a.dbg && lane == 0) atomicMax(&a.dbg[(size_t)t * 8 + 2], micNow());
+          float fv[8]; int fs[8];
+#pragma unroll
+          for (int u = 0; u < 8; u++) {
+            const int c = lane + 32 * u;
+            int li, lj, lk;
+            if (w == 0) { li = -1; lj = c % TY; lk = c / TY; }
+            else if (w == 1) { li = c % TX; lj = -1; lk = c / TX; }
+            else { li = c % TX; lj = c / TX; lk = -1; }
+            const int gi = i0 + dir * li, gj = j0 + dir * lj, gk = k0 + dir * lk;
+            const bool in = gi >= 0 && gi < g.nx && gj >= 0 && gj < g.ny && gk >= 0 && gk < g.nz;
+            fs[u] = (li + 1) + S * ((lj + 1) + R * (lk + 1));
+            fv[u] = in ? __ldcg(a.dst + gi + Y * gj + Z * gk) : 0.f;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; u++) sD[fs[u]] = fv[u];
+        }
+      }
+    }
+    __syncthreads();
+    MIC_STAMP(3);
+    // ---- hyperplane sweep: this thread's line is (jl, kl), its cell on hyperplane h is il = h - jl - kl
+    {
+      const int cb = 1 + S * ((jl + 1) + R * (kl + 1));          // smem index of il = 0
+      const unsigned short* cl = sC + TX * (jl + TY * kl);
+      const int hs = jl + kl;
+      // warp-uniform range of hyperplanes on which some lane of this warp has a cell
+      const int wlo = __reduce_min_sync(0xffffffffu, hs), whi = __reduce_max_sync(0xffffffffu, hs) + TX - 1;
+      float dprev = sD[cb - 1];
+      int cd = cl[0];
+      float p = sP[cb], v0 = sD[cb];
+      float ci = (cd & BI) ? -((MODE == 1) ? sP[cb - 1] : p) : 0.f;
+      float cj = (cd & BJ) ? -((MODE == 1) ? sP[cb - S] : p) : 0.f;
+      float ck = (cd & BK) ? -((MODE == 1) ? sP[cb - PL] : p) : 0.f;
+#pragma unroll 2
+      for (int h = 0; h < TX + TY + TZ - 2; h++) {
+        if (h >= wlo && h <= whi) {
+          const int il = h - hs;
+          if (il >= 0 && il < TX) {
+            const int c = cb + il;
+            const int cn = (il + 1 < TX) ? c + 1 : c;            // next cell of the line (clamped: the values are then unused)
+            // all loads first: the two neighbours this step depends on, then the next cell's static data
+            const float dj = sD[c - S], dk = sD[c - PL];
+            const int cdn = cl[(il + 1 < TX) ? il + 1 : il];
+            const float pn = sP[cn], v0n = sD[cn];
+            const float pjn = (MODE == 1) ? sP[cn - S] : 0.f, pkn = (MODE == 1) ? sP[cn - PL] : 0.f;
+            float v = v0 - dprev * ci;
+            v = v - dj * cj;
+            v = v - dk * ck;
+            const float d = (cd & CGC_FLUID) ? p * v : 0.f;
+            sD[c] = d; dprev = d;
+            ci = (cdn & BI) ? -((MODE == 1) ? p : pn) : 0.f;
+            cj = (cdn & BJ) ? -((MODE == 1) ? pjn : pn) : 0.f;
+            ck = (cdn & BK) ? -((MODE == 1) ? pkn : pn) : 0.f;
+            p = pn; v0 = v0n; cd = cdn;
+          }
+        }
+        __syncthreads();
+      }
+    }
+    MIC_STAMP(4);
+    // ---- results to global memory in whole 16-byte pieces (scattered 4-byte stores from inside the sweep would queue in front of
+    // its shared-memory loads), then publish the tile
+    {
+      const int xb = bi * TX;
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int item = tid + 256 * u, qx = item & 3, row = item >> 2, rj = row & 15, rk = row >> 4;
+        const int gj = bj * TY + rj, gk = bk * TZ + rk, gx = xb + 4 * qx;
+        if (gj < g.ny && gk < g.nz && gx < g.nx) {
+          const int lj = (MODE == 2) ? TY - 1 - rj : rj, lk = (MODE == 2) ? TZ - 1 - rk : rk;
+          const int rb = 1 + S * ((lj + 1) + R * (lk + 1));
+          float4 o;
+          if (MODE == 2) { const int l0 = TX - 1 - 4 * qx; o = make_float4(sD[rb + l0], sD[rb + l0 - 1], sD[rb + l0 - 2], sD[rb + l0 - 3]); }
+          else { const int l0 = 4 * qx; o = make_float4(sD[rb + l0], sD[rb + l0 + 1], sD[rb + l0 + 2], sD[rb + l0 + 3]); }
+          *reinterpret_cast<float4*>(a.dst + gx + Y * gj + Z * gk) = o;
+        }
+      }
+    }
+    // the block barrier orders every thread's stores before thread 0's release at gpu scope (release is cumulative), so the
+    // 256 per-thread MEMBAR.SC.GPU of a __threadfence() are not needed
+    if (tid == 0) sQ[(round + 1) & 1] = nextTicket;
+    __syncthreads();
+    if (tid == 0) micStRelease(&a.done[t], a.epoch);
+    MIC_STAMP(5);
+  }
+  if (tid == 0) { if (atomicAdd(&a.ctl[1], 1) == (int)gridDim.x - 1) { a.ctl[0] = 0; a.ctl[1] = 0; __threadfence(); } }
+}
+inline size_t micCodeSmemBytes() { return sizeof(float) * 2 * (size_t)(19 * 18 * 17) + sizeof(unsigned short) * 16 * 16 * 16; }
+
 template <int TZ> inline size_t micSmemBytes() { return sizeof(float) * 5 * (size_t)(19 * 18 * (TZ + 1)); }
 
 inline void micDestroy(MicPlan* m) {
   if (!m) return;
+  if (m->code16) micDestroy(m->code16);
   cudaFree(m->order); cudaFree(m->done); cudaFree(m->ctl);
   delete m;
 }
 
-inline MicPlan* micPlan(Solver* s) {
-  if (s->mic) return s->mic;
+inline MicPlan* micBuild(Solver* s, int tzEdge) {
   MicPlan* m = new MicPlan();
-  m->tzEdge = getenv("MF_MIC_TZ") ? atoi(getenv("MF_MIC_TZ")) : 8;
-  mfAssert(m->tzEdge == 8 || m->tzEdge == 16, "MF_MIC_TZ must be 8 or 16");
+  m->code16 = nullptr;
+  m->tzEdge = tzEdge;
   m->tx = (s->nx + 15) / 16; m->ty = (s->ny + 15) / 16; m->tz = (s->nz + m->tzEdge - 1) / m->tzEdge;
   m->ntiles = m->tx * m->ty * m->tz;
   std::vector<int> order(m->ntiles);
@@ -193,22 +403,70 @@ inline MicPlan* micPlan(Solver* s) {
   CUDA_CHECK(cudaMemsetAsync(m->done, 0, sizeof(int) * m->ntiles, s->stream));
   CUDA_CHECK(cudaMemsetAsync(m->ctl, 0, sizeof(int) * 2, s->stream));
   m->epoch = 0;
+  m->ctas = 1;
+  return m;
+}
+
+inline MicPlan* micPlan(Solver* s) {
+  if (s->mic) return s->mic;
+  MicPlan* m = micBuild(s, 8);
   int occ = 1;
-  if (m->tzEdge == 8) {
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
-    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_mic_wave<1, 8>, 128, micSmemBytes<8>()));
-  } else {
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<0, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<16>()));
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<1, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<16>()));
-    CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<16>()));
-    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_mic_wave<1, 16>, 256, micSmemBytes<16>()));
-  }
+  CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
+  CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
+  CUDA_CHECK(cudaFuncSetAttribute(k_mic_wave<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micSmemBytes<8>()));
+  CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_mic_wave<1, 8>, 128, micSmemBytes<8>()));
   if (occ < 1) occ = 1;
   m->ctas = s->numSMs * occ; if (m->ctas > m->ntiles) m->ctas = m->ntiles;
   s->mic = m;
   return m;
+}
+
+inline MicPlan* micPlanCode(Solver* s) {
+  MicPlan* base = micPlan(s);
+  if (base->code16) return base->code16;
+  MicPlan* m = micBuild(s, 16);
+  int occ = 1;
+  CUDA_CHECK(cudaFuncSetAttribute(k_mic_code<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micCodeSmemBytes()));
+  CUDA_CHECK(cudaFuncSetAttribute(k_mic_code<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)micCodeSmemBytes()));
+  CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_mic_code<1>, 256, micCodeSmemBytes()));
+  if (occ < 1) occ = 1;
+  if (getenv("MF_MIC_OCC")) { const int o = atoi(getenv("MF_MIC_OCC")); if (o >= 1 && o < occ) occ = o; }
+  m->ctas = s->numSMs * occ; if (m->ctas > m->ntiles) m->ctas = m->ntiles;
+  base->code16 = m;
+  return m;
+}
+
+// forward (mode 1: dst = L^-1 src) / backward (mode 2, in place) sweep from the 16-bit row codes
+inline void micSweepCode(Solver* s, int mode, const unsigned short* code, const float* P, const float* src, float* dst, const CgState* st) {
+  MicPlan* m = micPlanCode(s);
+  MicCodeArgs a; a.code = code; a.P = P; a.src = src; a.dst = dst;
+  a.order = m->order; a.done = m->done; a.ctl = m->ctl; a.ntiles = m->ntiles; a.tx = m->tx; a.ty = m->ty; a.tz = m->tz; a.st = st;
+  a.epoch = ++m->epoch;
+  { int n = 0; for (int d = 0; d < 31; d++) for (int jl = 0; jl < 16; jl++) { const int kl = d - jl; if (kl >= 0 && kl < 16) a.lines[n++] = (unsigned char)(jl | (kl << 4)); } }
+  a.dbg = nullptr;
+  if (getenv("MF_MIC_DBG")) {     // development aid: dump the stamps of sweep number MF_MIC_DBG to mic_dbg.bin
+    static unsigned long long* dbgBuf = nullptr; static int calls = 0;
+    if (!dbgBuf) CUDA_CHECK(cudaMalloc(&dbgBuf, sizeof(unsigned long long) * 8 * (size_t)m->ntiles));
+    if (++calls == atoi(getenv("MF_MIC_DBG"))) {
+      CUDA_CHECK(cudaMemsetAsync(dbgBuf, 0, sizeof(unsigned long long) * 8 * (size_t)m->ntiles, s->stream));
+      a.dbg = dbgBuf;
+      const Geo g2 = geo(s);
+      if (mode == 1) k_mic_code<1><<<m->ctas, 256, micCodeSmemBytes(), s->stream>>>(g2, a);
+      else k_mic_code<2><<<m->ctas, 256, micCodeSmemBytes(), s->stream>>>(g2, a);
+      std::vector<unsigned long long> h(8 * (size_t)m->ntiles);
+      CUDA_CHECK(cudaMemcpyAsync(h.data(), dbgBuf, h.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+      CUDA_CHECK(cudaStreamSynchronize(s->stream));
+      FILE* f = fopen("mic_dbg.bin", "wb");
+      if (f) { int hdr[4] = { m->tx, m->ty, m->tz, mode }; fwrite(hdr, sizeof(int), 4, f); fwrite(h.data(), 8, h.size(), f); fclose(f); }
+      s->launches++;
+      return;
+    }
+  }
+  const Geo g = geo(s);
+  ProfScope ps(s, mode == 1 ? "k_mic_code_forward" : "k_mic_code_backward");
+  if (mode == 1) k_mic_code<1><<<m->ctas, 256, micCodeSmemBytes(), s->stream>>>(g, a);
+  else k_mic_code<2><<<m->ctas, 256, micCodeSmemBytes(), s->stream>>>(g, a);
+  s->launches++;
 }
 
 // one sweep: mode 0 set-up, 1 forward (dst = L^-1 src), 2 backward (in place)
@@ -220,17 +478,10 @@ inline void micSweep(Solver* s, int mode, const int* flags, const float* A0, con
   a.epoch = ++m->epoch;
   const Geo g = geo(s);
   ProfScope ps(s, mode == 0 ? "k_mic_setup" : mode == 1 ? "k_mic_forward" : "k_mic_backward");
-  if (m->tzEdge == 8) {
-    const size_t sm = micSmemBytes<8>();
-    if (mode == 0) k_mic_wave<0, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
-    else if (mode == 1) k_mic_wave<1, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
-    else k_mic_wave<2, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
-  } else {
-    const size_t sm = micSmemBytes<16>();
-    if (mode == 0) k_mic_wave<0, 16><<<m->ctas, 256, sm, s->stream>>>(g, a);
-    else if (mode == 1) k_mic_wave<1, 16><<<m->ctas, 256, sm, s->stream>>>(g, a);
-    else k_mic_wave<2, 16><<<m->ctas, 256, sm, s->stream>>>(g, a);
-  }
+  const size_t sm = micSmemBytes<8>();
+  if (mode == 0) k_mic_wave<0, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
+  else if (mode == 1) k_mic_wave<1, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
+  else k_mic_wave<2, 8><<<m->ctas, 128, sm, s->stream>>>(g, a);
   s->launches++;
 }
 

@@ -81,8 +81,13 @@ struct CgDriver {
     } else if (pcMethod == 2) {
       mg_apply(mg, v.tmp, v.residual);
     } else if (pcMethod == 3) {
-      micSweep(s, 1, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, v.residual, v.tmp, st);
-      micSweep(s, 2, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, nullptr, v.tmp, st);
+      if (v.code && s->is3D && !std::getenv("MF_MIC_GENERIC")) {
+        micSweepCode(s, 1, v.code, P, v.residual, v.tmp, st);
+        micSweepCode(s, 2, v.code, P, nullptr, v.tmp, st);
+      } else {
+        micSweep(s, 1, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, v.residual, v.tmp, st);
+        micSweep(s, 2, v.flags, v.A0, v.Ai, v.Aj, v.Ak, P, nullptr, v.tmp, st);
+      }
     }
     (void)init;
   }

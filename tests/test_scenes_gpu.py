@@ -37,10 +37,12 @@ def _env(scene, steps, save, out):
                 OMP_NUM_THREADS=str(os.cpu_count() or 1), PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
 
 
-def run_reference(scene, steps, save, size, cwd=None):
-    """cwd: where waveletNoiseTile.bin is looked up / written (noisefield.cpp:97-122), shared by both sides of a comparison"""
+def run_reference(scene, steps, save, size, cwd=None, binary=None, extra_env=None):
+    """cwd: where waveletNoiseTile.bin is looked up / written (noisefield.cpp:97-122), shared by both sides of a comparison.
+    binary: the reference executable (oracle/_ref/manta), or integration/_build/manta_b200 -- the same executable with the
+    hot-path plugin bodies bound to libmantacuda.so"""
     with tempfile.TemporaryDirectory(dir=cwd) as d:
-        p = subprocess.run([MANTA_REF, DRIVER], env=_env(scene, steps, save, d), cwd=cwd or d, capture_output=True, text=True, timeout=1800)
+        p = subprocess.run([binary or MANTA_REF, DRIVER], env=dict(_env(scene, steps, save, d), **(extra_env or {})), cwd=cwd or d, capture_output=True, text=True, timeout=1800)
         assert p.returncode == 0 and "Error" not in p.stdout and "Traceback" not in p.stderr, p.stdout[-3000:] + p.stderr[-3000:]
         out = {}
         case = {"size": list(size)}
@@ -49,6 +51,7 @@ def run_reference(scene, steps, save, size, cwd=None):
                 out[g] = sr.read_pdata_uni(os.path.join(d, "out_%s.uni" % g), 3)
             else:
                 out[g] = sr.read_raw(os.path.join(d, "out_%s.raw" % g), np.int32 if gt == "FlagGrid" else np.float32, sr.grid_shape(case, gt))
+        out["_stdout"] = p.stdout
         return out
 
 
