@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "sample.cuh"
 #include "advect_fast.cuh"
+#include "advect_tma.cuh"
 #include <cfloat>
 
 namespace mf {
@@ -397,6 +398,20 @@ static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* 
   if (NC == 1) s->putReal(fwd); else s->putVec(fwd);
 }
 
+static bool tmaEnabled() { const char* e = getenv("MF_ADVECT_TMA"); return e && atoi(e) != 0; }
+static void launchSlMacTma(Solver* s, const Grid* vel, Grid* fw, float dt) {
+  static bool attr = false;
+  if (!attr) { CUDA_CHECK(cudaFuncSetAttribute(k_sl_mac_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tmaSmemBytes())); attr = true; }
+  TmaMaps3 maps;
+  for (int c = 0; c < 3; c++) maps.m[c] = tmaPlaneMap(s, vel->comp(c));
+  const int zc = getenv("MF_TMA_ZC") ? atoi(getenv("MF_TMA_ZC")) : 32;
+  const Geo g = geo(s);
+  const int tiles = ((s->nx + TMA_TX - 1) / TMA_TX) * ((s->ny + TMA_TY - 1) / TMA_TY), chunks = (s->nz + zc - 1) / zc;
+  ProfScope ps(s, "k_sl_mac_tma");
+  k_sl_mac_tma<<<tiles * chunks, 256, tmaSmemBytes(), s->stream>>>(g, maps, cv3(vel), v3(fw), dt, zc);
+  s->launches++;
+}
+
 template <int OS, int OT>
 static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid, int order, float strength, int clampMode) {
   const float dt = s->dt;
@@ -404,7 +419,9 @@ static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid,
   float* fwd = s->getVec();
   Grid fw = *grid; fw.d = fwd;
   const bool fast = fastPath(s, OS, OT);
-  if (fast) MF_LAUNCH_IJK(s, k_sl_mac_f, cv3(vel), cv3(grid), v3(&fw), dt);
+  // MF_ADVECT_TMA=1: the TMA-staged variant (advect_tma.cuh) for self-advection on a single GPU
+  if (fast && self && tmaUsable(s) && tmaEnabled()) launchSlMacTma(s, vel, &fw, dt);
+  else if (fast) MF_LAUNCH_IJK(s, k_sl_mac_f, cv3(vel), cv3(grid), v3(&fw), dt);
   else MF_LAUNCH_IJK(s, (k_sl_mac<OS, OT>), cv3(vel), cv3(grid), v3(&fw), dt);
   if (order == 1) {
     applyOutflowBC(s, flags, v3(&fw), cv3(grid), dt);

@@ -258,7 +258,8 @@ __global__ void k_comm_barrier(char* shared, size_t stride, int rank, int nranks
   MF_PDL_PROLOGUE
   const int t = threadIdx.x;
   if (t >= nranks || t == rank) return;
-  __threadfence_system();
+  // no separate __threadfence_system(): griddepcontrol.wait above made the preceding kernels' writes visible to this thread, and
+  // the release store below is cumulative over them at system scope
   CommShared* theirs = reinterpret_cast<CommShared*>(shared + (size_t)t * stride);
   CommShared* mine = reinterpret_cast<CommShared*>(shared + (size_t)rank * stride);
   stReleaseSys(&theirs->flag[rank], epoch);

@@ -260,6 +260,33 @@ def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("size,amp,zc", [((64, 48, 40), 1.5, 32), ((72, 45, 38), 3.0, 16), ((36, 20, 9), 12.0, 4), ((128, 96, 70), 2.0, 32)])
+@pytest.mark.parametrize("order,clampMode", [(1, 2), (2, 2), (2, 1)])
+def test_advect_tma_matches_ldg(size, amp, zc, order, clampMode, monkeypatch):
+    """the TMA-staged MAC advection (advect_tma.cuh: cp.async.bulk.tensor.3d boxes with halos in a shared-memory ring, stencils and
+    in-window gathers from shared memory, global fallback for traces that leave the window) against the per-thread-LDG kernels of
+    advect_fast.cuh: bit-identical, on ragged grids (tiles and z chunks that hang over the grid), with obstacles and empty cells,
+    with velocities inside the window (|v| dt < 2) and far outside it (fallback gathers, traces that leave the grid)"""
+    from mantaflow_b200 import manta
+    rs = np.random.RandomState(47)
+    f = _flags(rs, size, 3)
+    vel0 = ((rs.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5)) * np.float32(2.0 * amp))
+    vel0[rs.rand(size[2], size[1], size[0]) < 0.3] *= np.float32(0.05)
+    outs = []
+    for tma in (False, True):
+        monkeypatch.setenv("MF_ADVECT_TMA", "1" if tma else "0")
+        monkeypatch.setenv("MF_TMA_ZC", str(zc))
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        vel = s.create(manta.MACGrid); vel.from_numpy(vel0)
+        l0 = s.launchCount()
+        manta.advectSemiLagrange(flags=flags, vel=vel, grid=vel, order=order, clampMode=clampMode)
+        outs.append(vel.to_numpy())
+    assert np.isfinite(outs[0]).all()
+    assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32))
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("pc", ["none", "mic", "mg"])
 @pytest.mark.parametrize("dim", [3, 2])
 def test_gridcg_object_matches_solve_pressure(pc, dim, monkeypatch):
