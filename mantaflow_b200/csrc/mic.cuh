@@ -361,8 +361,9 @@ __global__ void __launch_bounds__(256, 3) k_mic_code(Geo g, MicCodeArgs a) {
         }
       }
     }
-    // the block barrier orders every thread's stores before thread 0's release at gpu scope (release is cumulative), so the
-    // 256 per-thread MEMBAR.SC.GPU of a __threadfence() are not needed
+    // every thread fences its own stores: measured on B200, leaving the flush to thread 0's cumulative release alone costs 23 us
+    // per tile instead of 1.7 us (gpurun_out/mic_dbg.bin, tools/mic_dbg.py)
+    __threadfence();
     if (tid == 0) sQ[(round + 1) & 1] = nextTicket;
     __syncthreads();
     if (tid == 0) micStRelease(&a.done[t], a.epoch);
