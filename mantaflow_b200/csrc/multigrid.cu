@@ -438,94 +438,86 @@ int mg_level_size(const MgHierarchy* mg, int l, int* sx, int* sy, int* sz) {
   *sx = mg->lv[l].sx; *sy = mg->lv[l].sy; *sz = mg->lv[l].sz; return mg->lv[l].n;
 }
 
-// serial genCoarseGrid (multigrid.cpp:520-578) on the host: only taken when the order-independent device sweeps leave
-// vertices with >= 2 free interpolation vertices.  Bucket min-heap with the reference's LIFO order inside a bucket
-// (NKMinHeap, multigrid.cpp:59-186).
+// The order-dependent branch of coarse-vertex selection (GridMg::genCoarseGrid, multigrid.cpp:520-578), on the host; only taken
+// when the order-independent device sweeps leave fine vertices with >= 2 free interpolation vertices (tests: solve_thin_mg).
+// The result must be the reference's, so the visiting order is the specification: always the fine vertex with the fewest free
+// interpolation vertices, and among equals the one whose count changed (or was set) most recently.
+//
+// StampedStacks gives that order without the reference's linked lists: one stack per count; (re)filing a vertex pushes a fresh
+// (vertex, stamp) entry and bumps the vertex' stamp, which turns every older entry of it into a tombstone that pop() skips.
 namespace {
-struct BucketHeap {
-  int N, K, size, minKey;
-  std::vector<int> key, prev, next;   // K bucket heads followed by N entries
-  BucketHeap(int n, int k) : N(n), K(k), size(0), minKey(-1), key(n + k, -1), prev(n + k, -1), next(n + k, -1) {}
-  int getKey(int id) const { return key[K + id]; }
-  void setKey(int id, int k) {
-    const int kid = K + id;
-    if (key[kid] == k) return;
-    if (key[kid] != -1) {
-      const int pred = prev[kid], succ = next[kid];
-      next[pred] = succ;
-      if (succ != -1) prev[succ] = pred;
-      if (key[kid] == minKey) {
-        if (size == 1) minKey = -1;
-        else for (; minKey < K; minKey++) if (next[minKey] != -1) break;
+class StampedStacks {
+ public:
+  StampedStacks(int vertices, int counts) : stacks_(counts), count_(vertices, 0), stamp_(vertices, 0), live_(0) {}
+  int countOf(int v) const { return count_[v]; }            // 0 = not filed
+  bool empty() const { return live_ == 0; }
+  void file(int v, int count) {                             // count >= 1: (re)file; count == 0: withdraw
+    if (count_[v] == 0 && count > 0) live_++;
+    if (count_[v] > 0 && count == 0) live_--;
+    count_[v] = count; stamp_[v]++;
+    if (count > 0) stacks_[count].push_back({ v, stamp_[v] });
+  }
+  int pop() {                                               // the vertex to visit next; it is withdrawn
+    for (size_t c = 1; c < stacks_.size(); c++) {
+      std::vector<Item>& st = stacks_[c];
+      while (!st.empty()) {
+        const Item it = st.back(); st.pop_back();
+        if (stamp_[it.v] == it.stamp && count_[it.v] == (int)c) { count_[it.v] = 0; stamp_[it.v]++; live_--; return it.v; }
       }
-      size--;
     }
-    key[kid] = k;
-    if (k == -1) { next[kid] = prev[kid] = -1; return; }
-    size++;
-    minKey = (minKey == -1) ? k : std::min(minKey, k);
-    const int tmp = next[k];
-    next[k] = kid; prev[kid] = k; next[kid] = tmp;
-    if (tmp != -1) prev[tmp] = kid;
+    return -1;
   }
-  int popMin() {
-    if (size == 0) return -1;
-    const int kid = next[minKey], id = kid - K;
-    const int pred = prev[kid], succ = next[kid];
-    next[pred] = succ;
-    if (succ != -1) prev[succ] = pred;
-    key[kid] = prev[kid] = next[kid] = -1;
-    size--;
-    if (size == 0) minKey = -1;
-    else for (; minKey < K; minKey++) if (next[minKey] != -1) break;
-    return id;
-  }
+ private:
+  struct Item { int v; unsigned stamp; };
+  std::vector<std::vector<Item>> stacks_;
+  std::vector<int> count_; std::vector<unsigned> stamp_;
+  int live_;
 };
+struct Box3 { int lo[3], hi[3]; };      // inclusive index box
+template <class F> void forBox(const Box3& b, F f) {
+  for (int z = b.lo[2]; z <= b.hi[2]; z++) for (int y = b.lo[1]; y <= b.hi[1]; y++) for (int x = b.lo[0]; x <= b.hi[0]; x++) f(x, y, z);
+}
 }
 
 static void coarsenOnHost(MgHierarchy* mg, int l) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[l - 1]; LvlD& C = mg->lv[l];
-  std::vector<unsigned char> fts(F.na), ft(F.n), ct(C.n, vtFree), cts(C.na, vtInactive);
-  CUDA_CHECK(cudaMemcpyAsync(fts.data(), F.type, F.na, cudaMemcpyDeviceToHost, s->stream));
+  const int fdim[3] = { F.sx, F.sy, F.sz }, cdim[3] = { C.sx, C.sy, C.sz };
+  std::vector<unsigned char> fineStored(F.na), coarseStored(C.na, vtInactive);
+  CUDA_CHECK(cudaMemcpyAsync(fineStored.data(), F.type, F.na, cudaMemcpyDeviceToHost, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
-  const int fxy = F.sx * F.sy, cxy = C.sx * C.sy;
-  for (int v = 0; v < F.n; v++) ft[v] = fts[mgIdx(F, v % F.sx, (v % fxy) / F.sx, v / fxy)];   // natural order, as the reference walks it
-  BucketHeap heap(F.n, mg->D.is3D ? 9 : 5);
-  for (int v = 0; v < F.n; v++) {
-    if (ft[v] != vtInactive) {
-      const int x = v % F.sx, y = (v % fxy) / F.sx, z = v / fxy;
-      heap.setKey(v, 1 << ((x % 2) + (y % 2) + (z % 2)));
-    }
+  auto fineId = [&](int x, int y, int z) { return x + fdim[0] * (y + fdim[1] * z); };           // natural order = the reference's vertex ids
+  auto coarseId = [&](int x, int y, int z) { return x + cdim[0] * (y + cdim[1] * z); };
+  enum Pick : unsigned char { Open, Chosen, Dropped };
+  std::vector<unsigned char> pick(C.n, Open);
+  // file every active fine vertex under the number of coarse vertices it interpolates from (1, 2, 4 or 8), in id order
+  StampedStacks queue(F.n, mg->D.is3D ? 9 : 5);
+  forBox(Box3{ { 0, 0, 0 }, { fdim[0] - 1, fdim[1] - 1, fdim[2] - 1 } }, [&](int x, int y, int z) {
+    if (fineStored[mgIdx(F, x, y, z)] != vtInactive) queue.file(fineId(x, y, z), 1 << ((x & 1) + (y & 1) + (z & 1)));
+  });
+  while (!queue.empty()) {
+    const int v = queue.pop();
+    const int vx = v % fdim[0], vy = (v / fdim[0]) % fdim[1], vz = v / (fdim[0] * fdim[1]);
+    bool haveOne = false;
+    // the coarse vertices v interpolates from: the first open one is chosen, further open ones are dropped
+    forBox(Box3{ { vx / 2, vy / 2, vz / 2 }, { (vx + 1) / 2, (vy + 1) / 2, (vz + 1) / 2 } }, [&](int ix, int iy, int iz) {
+      unsigned char& state = pick[coarseId(ix, iy, iz)];
+      if (state != Open) return;
+      state = haveOne ? Dropped : Chosen;
+      haveOne = true;
+      // either way it is no longer open for the fine vertices it restricts from: each loses one free interpolation vertex
+      Box3 fineNbrs;
+      const int ci[3] = { ix, iy, iz };
+      for (int d = 0; d < 3; d++) { fineNbrs.lo[d] = std::max(0, 2 * ci[d] - 1); fineNbrs.hi[d] = std::min(fdim[d] - 1, 2 * ci[d] + 1); }
+      forBox(fineNbrs, [&](int rx, int ry, int rz) {
+        const int r = fineId(rx, ry, rz), left = queue.countOf(r);
+        if (left > 0) queue.file(r, left - 1);
+      });
+    });
   }
-  while (heap.size > 0) {
-    const int v = heap.popMin();
-    const int x = v % F.sx, y = (v % fxy) / F.sx, z = v / fxy;
-    bool vdone = false;
-    for (int iz = z / 2; iz <= (z + 1) / 2; iz++)
-    for (int iy = y / 2; iy <= (y + 1) / 2; iy++)
-    for (int ix = x / 2; ix <= (x + 1) / 2; ix++) {
-      const int i = ix + iy * C.sx + iz * cxy;
-      if (ct[i] == vtFree) {
-        if (vdone) ct[i] = vtRemoved; else { ct[i] = vtZero; vdone = true; }
-        for (int rz = std::max(0, iz * 2 - 1); rz <= std::min(F.sz - 1, iz * 2 + 1); rz++)
-        for (int ry = std::max(0, iy * 2 - 1); ry <= std::min(F.sy - 1, iy * 2 + 1); ry++)
-        for (int rx = std::max(0, ix * 2 - 1); rx <= std::min(F.sx - 1, ix * 2 + 1); rx++) {
-          const int r = rx + ry * F.sx + rz * fxy;
-          const int key = heap.getKey(r);
-          if (key > 1) heap.setKey(r, key - 1);
-          else if (key > -1) heap.setKey(r, -1);
-        }
-      }
-    }
-  }
-  for (int i = 0; i < C.n; i++) {
-    unsigned char c = ct[i];
-    if (c == vtFree) c = vtRemoved;
-    if (c == vtZero) c = vtActive;
-    if (c == vtRemoved) c = vtInactive;
-    cts[mgIdx(C, i % C.sx, (i % cxy) / C.sx, i / cxy)] = c;
-  }
+  for (int z = 0; z < cdim[2]; z++) for (int y = 0; y < cdim[1]; y++) for (int x = 0; x < cdim[0]; x++)
+    coarseStored[mgIdx(C, x, y, z)] = (pick[coarseId(x, y, z)] == Chosen) ? vtActive : vtInactive;     // knActivateCoarseVertices
+  const std::vector<unsigned char>& cts = coarseStored;
   // every process computes the same classification; one writes it
   if (s->rankBegin == 0) CUDA_CHECK(cudaMemcpyAsync(C.type, cts.data(), C.na, cudaMemcpyHostToDevice, s->stream));
   CUDA_CHECK(cudaStreamSynchronize(s->stream));

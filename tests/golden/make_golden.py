@@ -26,14 +26,16 @@ import scene_runner as sr  # noqa: E402
 MANTA = os.path.join(ROOT, "oracle", "_ref", "manta")
 
 
-def run_reference(name, case, threads="1"):
+def run_reference(name, case, threads="1", binary=None, real_bytes=4):
+    """binary: oracle/_ref/manta (default) or oracle/_ref/mantad, the double-precision build (-DFLOATINGPOINT_PRECISION=2, real_bytes=8:
+    its .raw files hold doubles; inputs are written as doubles too)"""
     ins = C.inputs_for(case)
     with tempfile.TemporaryDirectory() as d:
         json.dump(case, open(os.path.join(d, "case.json"), "w"))
         for k, a in ins.items():
-            sr.write_raw(os.path.join(d, "in_%s.raw" % k), a)
+            sr.write_raw(os.path.join(d, "in_%s.raw" % k), a.astype(np.float64) if (real_bytes == 8 and a.dtype == np.float32) else a)
         env = dict(os.environ, MF_CASE_DIR=d, MF_TESTS_DIR=TESTS, OMP_NUM_THREADS=threads, MANTA_DISABLE_UI="1")
-        p = subprocess.run([MANTA, os.path.join(HERE, "ref_driver.py")], env=env, cwd=d, capture_output=True, text=True, timeout=1800)
+        p = subprocess.run([binary or MANTA, os.path.join(HERE, "ref_driver.py")], env=env, cwd=d, capture_output=True, text=True, timeout=1800)
         if p.returncode != 0 or "Error" in p.stdout or not os.path.exists(os.path.join(d, "log.json")):
             print(p.stdout[-3000:], p.stderr[-3000:])
             raise RuntimeError("reference failed on case %s" % name)
@@ -43,7 +45,7 @@ def run_reference(name, case, threads="1"):
             if sr.is_particle_type(gt):
                 out["out_" + g] = sr.read_pdata_uni(os.path.join(d, "out_%s.uni" % g), 1 if gt.startswith("PdataReal") else 3)
                 continue
-            dt = np.int32 if gt in ("FlagGrid", "IntGrid") else np.float32
+            dt = np.int32 if gt in ("FlagGrid", "IntGrid") else (np.float64 if real_bytes == 8 else np.float32)
             out["out_" + g] = sr.read_raw(os.path.join(d, "out_%s.raw" % g), dt, sr.grid_shape(case, gt))
         its = [int(m) for m in re.findall(r"solvePressure done\. Iterations:(\d+)", p.stdout)]
         res = [float(m) for m in re.findall(r"solvePressure done\. Iterations:\d+, residual:([-+0-9.eE]+|nan|inf)", p.stdout)]
