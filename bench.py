@@ -343,12 +343,23 @@ def strong_leg(M, L, check, comm, world, rank, local, precond, barrier, max_over
     size = (1024, 1024, 1024)
     cells = size[0] * size[1] * size[2]
     out = {"grid": list(size), "steps": steps, "warmup": warm}
+    def state_sums(P):      # size-independent check of the state after the warm-up steps: sum of squares of density and pressure
+        out = {}
+        for name, g in (("density", P.density), ("pressure", P.pressure)):
+            v = C.c_double()
+            check(L.mf_grid_sum_sqr(g._h, C.byref(v)))
+            out[name + "_sumsqr"] = v.value
+        out["pcg_iterations"] = list(P.iterations)
+        return out
+
     one = None
+    sums1 = None
     if rank == 0:     # the single-GPU time of the same grid, measured in this very run (needs ~110 GB of the 180 GB)
         try:
             P1 = Plume(size, local, precond, None)
             for _ in range(warm):
                 P1.step()
+            sums1 = state_sums(P1)
             n1 = 3 if world > 1 else steps
             t1, _ = time_steps(P1, L, check, n1, lambda: None, lambda x: x, ev=(8, 9))
             one = {"ms_per_step": 1e3 * t1 / n1, "value": cells * n1 / t1, "steps": n1, "pcg_iterations": P1.iterations[-n1:]}
@@ -365,6 +376,13 @@ def strong_leg(M, L, check, comm, world, rank, local, precond, barrier, max_over
     P = Plume(size, local, precond, comm)
     for _ in range(warm):
         P.step()
+    sumsN = state_sums(P)       # collective: every rank calls it
+    if sums1 is not None:
+        rel = {k: abs(sumsN[k] - sums1[k]) / max(abs(sums1[k]), 1e-300) for k in ("density_sumsqr", "pressure_sumsqr")}
+        out["check"] = {"after_steps": warm, "one_gpu": sums1, "n_gpus": sumsN, "rel_diff": rel,
+                        "ok": bool(max(rel.values()) < 1e-4 and sums1["pcg_iterations"] == sumsN["pcg_iterations"]),
+                        "what": "sum of squares of density / pressure after the warm-up steps: 1024^3 on one GPU vs z-slab partitioned over the N GPUs "
+                                "(the partitioned PCG sums its dot products per rank first: equal to rounding, not bit for bit)"}
     t, _ = time_steps(P, L, check, steps, barrier, max_over_ranks, ev=(8, 9))
     out.update({"n_gpus": world, "ms_per_step": 1e3 * t / steps, "value": cells * steps / t, "pcg_iterations": P.iterations[-steps:], "one_gpu": one,
                 "speedup_vs_1gpu": (one["ms_per_step"] / (1e3 * t / steps)) if one and "ms_per_step" in one else None})
