@@ -89,3 +89,30 @@ def test_unmodified_scene_matches_reference(name, parity_report):
         if d > thr[g]:
             errors.append("%s: gridMaxDiff %.3g > %.3g" % (g, d, thr[g]))
     assert not errors, "%s: %s" % (name, "; ".join(errors))
+
+
+@pytest.mark.gpu
+def test_simpleplume_as_shipped_all_250_frames(parity_report):
+    """BASELINE configs[0] exactly as the reference ships it: scenes/simpleplume.py, 64 x 96 x 64, its own 250 frames (noise inflow for
+    the first 100, default PcMIC solve), nothing cut -- through the reference, through `python -m mantaflow_b200` and, where built,
+    through integration/_build/manta_b200.  Required: the reference's regression thresholds; measured on B200: bit-identical."""
+    if not os.path.exists(MANTA_REF):
+        pytest.skip("oracle/_ref/manta not built")
+    import time
+    save = {"density": "RealGrid", "vel": "MACGrid", "pressure": "RealGrid", "flags": "FlagGrid"}
+    thr = {"density": 1e-3, "vel": 5e-3, "pressure": 5e-3, "flags": 0}
+    binding = os.path.join(ROOT, "integration", "_build", "manta_b200")
+    with tempfile.TemporaryDirectory() as cwd:
+        t0 = time.time(); ref = run_reference("simpleplume.py", 250, save, (64, 96, 64), cwd=cwd)
+        t1 = time.time(); ours, _ = run_ours("simpleplume.py", 250, save, cwd=cwd)
+        t2 = time.time(); bnd = run_reference("simpleplume.py", 250, save, (64, 96, 64), cwd=cwd, binary=binding) if os.path.exists(binding) else None
+        t3 = time.time()
+    rep = parity_report.setdefault("scene_simpleplume_250_frames", {"wall_s": {"reference": t1 - t0, "python -m mantaflow_b200": t2 - t1,
+                                                                               "manta_b200": (t3 - t2) if bnd else None}})
+    for g in save:
+        d = grid_max_diff(ours[g], ref[g])
+        rep[g] = {"gridMaxDiff": d, "bit_identical": bool(np.array_equal(ours[g], ref[g])),
+                  "binding_bit_identical": bool(np.array_equal(bnd[g], ref[g])) if bnd else None}
+        assert d <= thr[g], "%s: gridMaxDiff %.3g > %.3g after 250 frames" % (g, d, thr[g])
+        if bnd:
+            assert grid_max_diff(bnd[g], ref[g]) <= thr[g], g
