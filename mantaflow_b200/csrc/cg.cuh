@@ -151,6 +151,58 @@ __global__ void __launch_bounds__(256) k_cg_spmv_dot_code(Geo g, Span sp, CgVecs
   gridReduceK<1>(acc, ops, ctx, sh, FinAlpha{ st });
 }
 
+// The same product as a z-marching register pipeline (3-D): a warp owns 32 x-consecutive quads of one row and
+// walks a chunk of z planes; the quads of planes k - 1, k, k + 1 of its column stay in registers, so every value of `search` is
+// loaded once as a centre (plus the two row neighbours, which the neighbouring warps of the CTA have just pulled into L1) instead of
+// five times.  Identical products in identical order per cell: tmp is bit-identical to k_cg_spmv_dot_code's.
+// Work item = (row j, 32-quad segment of the row); a CTA takes 8 consecutive items, blockIdx.y the z chunk.
+__global__ void __launch_bounds__(256) k_cg_spmv_dot_zm(Geo g, CgVecs v, CgState* st, RedCtx ctx, int zc, int ntiles, int units) {
+  MF_PDL_PROLOGUE
+  __shared__ double sh[32];
+  if (st->done) return;
+  double acc[1] = { 0.0 };
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nqx = g.nx >> 2, segs = (nqx + 31) >> 5;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {       // unit = (8 work items, z chunk); consecutive CTAs take consecutive tiles of a chunk
+  const int item = (u % ntiles) * 8 + warp;
+  const int j = item / segs, q = (item - j * segs) * 32 + lane;
+  const int ka = g.k0 + (u / ntiles) * zc, kb = min(ka + zc, g.k1);
+  if (j < g.ny && ka < kb) {                      // warp-uniform
+    const bool on = q < nqx;
+    const long long Y = g.nx, Z = g.Z, N = g.N;
+    const long long col = (long long)4 * (on ? q : nqx - 1) + Y * j;
+    const bool edgeM = lane == 0, edgeP = lane == 31 || q + 1 >= nqx;
+    long long idx = col + Z * ka;
+    float4 sm = (idx - Z >= 0) ? *reinterpret_cast<const float4*>(v.search + idx - Z) : zero4;
+    float4 s0 = *reinterpret_cast<const float4*>(v.search + idx);
+    for (int k = ka; k < kb; k++, idx += Z) {
+      const float4 sp = (idx + Z < N) ? *reinterpret_cast<const float4*>(v.search + idx + Z) : zero4;
+      const uint2 cw = *reinterpret_cast<const uint2*>(v.code + idx);
+      const float4 ym = (idx - Y >= 0) ? *reinterpret_cast<const float4*>(v.search + idx - Y) : zero4;
+      const float4 yp = (idx + Y < N) ? *reinterpret_cast<const float4*>(v.search + idx + Y) : zero4;
+      const float xmE = (edgeM && idx - 1 >= 0) ? v.search[idx - 1] : 0.f;
+      const float xpE = (edgeP && idx + 4 < N) ? v.search[idx + 4] : 0.f;
+      float xm = __shfl_up_sync(0xffffffffu, s0.w, 1), xp = __shfl_down_sync(0xffffffffu, s0.x, 1);
+      if (edgeM) xm = xmE;
+      if (edgeP) xp = xpE;
+      float4 t;
+      t.x = rowFromCode((int)(cw.x & 0xffffu), s0.x, xm, s0.y, ym.x, yp.x, sm.x, sp.x, true);
+      t.y = rowFromCode((int)(cw.x >> 16), s0.y, s0.x, s0.z, ym.y, yp.y, sm.y, sp.y, true);
+      t.z = rowFromCode((int)(cw.y & 0xffffu), s0.z, s0.y, s0.w, ym.z, yp.z, sm.z, sp.z, true);
+      t.w = rowFromCode((int)(cw.y >> 16), s0.w, s0.z, xp, ym.w, yp.w, sm.w, sp.w, true);
+      if (on) {
+        *reinterpret_cast<float4*>(v.tmp + idx) = t;
+        acc[0] += (double)(t.x * s0.x); acc[0] += (double)(t.y * s0.y); acc[0] += (double)(t.z * s0.z); acc[0] += (double)(t.w * s0.w);
+      }
+      sm = s0; s0 = sp;
+    }
+  }
+  }
+  const int ops[1] = { 0 };
+  gridReduceK<1>(acc, ops, ctx, sh, FinAlpha{ st });
+}
+
 // dst += alpha*search ; residual += -alpha*tmp ; norm(residual)     (conjugategrad.cpp:254-277)
 // PCNONE: also tmp := residual (implicitly) and sigmaNew = residual . residual, beta        (:279-286)
 template <bool PCNONE>

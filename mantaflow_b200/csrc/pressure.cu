@@ -64,6 +64,27 @@ struct SolveTemps {   // the 7 (+4) temp grids of solvePressureSystem (pressure.
   ~SolveTemps() { if (pc) s->putReal(pc); s->putReal(tmp); s->putReal(Ak); s->putReal(Aj); s->putReal(Ai); s->putReal(A0); s->putReal(search); s->putReal(residual); }
 };
 
+// tmp = A search from the 16-bit row codes (+ the partial dot products): the 1-D kernel; MF_SPMV_ZM=1 selects the z-marching
+// register pipeline in 3-D (bit-identical, tests compare the two; measured 50.2 us against 50.9 us at 256^3 -- the kernel is bound
+// by its 229 instructions per 4-cell group, not by the re-fetches of `search` through L1, so the simpler kernel stays the default)
+static void launchSpmvCode(Solver* s, const CgVecs& v, CgState* st, bool pdl) {
+  if (s->is3D && std::getenv("MF_SPMV_ZM")) {
+    const int zc = std::getenv("MF_SPMV_ZC") ? atoi(std::getenv("MF_SPMV_ZC")) : 32;
+    MF_RANKS(s, r) { const Geo g = geo(s, r);
+      const int items = s->ny * (((s->nx >> 2) + 31) >> 5), ntiles = (items + 7) / 8, chunks = (g.k1 - g.k0 + zc - 1) / zc;
+      if (chunks <= 0) continue;
+      const long long units = (long long)ntiles * chunks;
+      const int cap = std::min(RED_MAX_BLOCKS, s->numSMs * 6);
+      const int grid = (int)std::min<long long>(units, cap);
+      if (pdl) { MF_LAUNCH_PDL(s, k_cg_spmv_dot_zm, grid, 256, g, v, st, redCtx(s, r), zc, ntiles, (int)units); }
+      else { MF_LAUNCH(s, k_cg_spmv_dot_zm, grid, 256, g, v, st, redCtx(s, r), zc, ntiles, (int)units); } }
+    return;
+  }
+  MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r);
+    if (pdl) { MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n, 5), 256, g, sp, v, st, redCtx(s, r)); }
+    else { MF_LAUNCH(s, k_cg_spmv_dot_code, redBlocks(s, sp.n), 256, g, sp, v, st, redCtx(s, r)); } }
+}
+
 struct CgDriver {
   Solver* s; CgVecs v; CgState* st; int pcMethod;   // 0 none, 1 red-black MIC (partitioned solvers), 2 multigrid, 3 the reference's MIC(0) (mic.cuh)
   float* P; MgHierarchy* mg;
@@ -114,7 +135,7 @@ struct CgDriver {
   }
   // tmp = A search, alpha (conjugategrad.cpp:246-252)
   void spmv() {
-    if (v.code) { MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot_code, redBlocks(s, sp.n, 5), 256, g, sp, v, st, redCtx(s, r)); } }
+    if (v.code) launchSpmvCode(s, v, st, true);
     else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_PDL(s, k_cg_spmv_dot, tileBlocks(s, g), 256, g, v, st, redCtx(s, r)); } }
     redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
   }
@@ -435,7 +456,7 @@ int mf_apply_laplace_rowcode(const mf_grid* flags, mf_grid* dst, const mf_grid* 
   CUDA_CHECK(cudaMemsetAsync(st, 0, sizeof(CgState), s->stream));
   CgVecs v; memset(&v, 0, sizeof(v));
   v.search = G(src)->d; v.tmp = G(dst)->d; v.code = s->cgCode;
-  MF_RANKS(s, r) { const Geo g = geo(s, r); const Span sp = span(s, r); MF_LAUNCH(s, k_cg_spmv_dot_code, redBlocks(s, sp.n), 256, g, sp, v, st, redCtx(s, r)); }
+  launchSpmvCode(s, v, st, false);
   redFinish<1>(s, RedOps<1>{ { 0 } }, FinAlpha{ st });
   MF_LAUNCH_CHECK();
   MF_API_END

@@ -99,6 +99,34 @@ def test_laplace_matrix_and_apply(size, dim, border_fluid):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("size", [(64, 48, 40), (8, 8, 8), (132, 21, 70), (256, 9, 33), (4, 3, 3)])
+@pytest.mark.parametrize("zc", [32, 5])
+def test_rowcode_spmv_zmarch_matches_flat(size, zc, monkeypatch):
+    """the z-marching register-pipeline SpMV (k_cg_spmv_dot_zm, MF_SPMV_ZM=1) against the default 1-D kernel and numpy:
+    bit-identical products, on rows shorter / longer than one warp segment and z chunks that do not divide the grid"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    rs = np.random.RandomState(13)
+    f = _flags(rs, size, 3, True)
+    src = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
+    outs = []
+    for flat in (False, True):
+        monkeypatch.setenv("MF_SPMV_ZC", str(zc))
+        if flat:
+            monkeypatch.delenv("MF_SPMV_ZM", raising=False)
+        else:
+            monkeypatch.setenv("MF_SPMV_ZM", "1")
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        S = s.create(manta.RealGrid); D = s.create(manta.RealGrid); S.from_numpy(src)
+        check(lib().mf_apply_laplace_rowcode(flags._h, D._h, S._h))
+        outs.append(D.to_numpy())
+    want = _np_apply(f, src, *_np_laplace(f, 3), 3)
+    assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32))
+    assert np.array_equal(outs[0], want)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("nranks", [2, 3])
 def test_rowcode_spmv_partitioned(nranks):
     """z-slab partition (emulated ranks): the row-code SpMV reads the neighbour planes of other slabs"""
