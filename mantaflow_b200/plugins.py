@@ -144,10 +144,13 @@ def _params(fn, kw, allowObvel=True, allowRetRhs=False):
     return p, keep
 
 
-def _publish(info):
+def _publish(info, accuracy=None):
+    converged = accuracy is None or info.resNorm < accuracy
     M.lastSolveInfo = dict(iterations=info.iterations, resNorm=info.resNorm, maxIter=info.maxIter,
-                           fixedCell=info.fixedCell, mgLevels=info.mgLevels, mgRebuilt=info.mgRebuilt)
+                           fixedCell=info.fixedCell, mgLevels=info.mgLevels, mgRebuilt=info.mgRebuilt, converged=converged)
     M.mantaMsg("FluidSolver::solvePressure done. Iterations:%d, residual:%g" % (info.iterations, info.resNorm), 2)
+    if not converged:     # the reference stops silently at maxIter (pressure.cpp:430-436); say so at its debug level
+        M.mantaMsg("FluidSolver::solvePressure stopped at maxIter=%d with residual %g >= cgAccuracy %g" % (info.maxIter, info.resNorm, accuracy), 2)
 
 
 def getSolveInfo():
@@ -170,7 +173,7 @@ def solvePressureSystem(rhs=None, vel=None, pressure=None, flags=None, **kwargs)
     p, keep = _params("solvePressureSystem", kwargs, allowObvel=False)
     info = SolveInfo()
     check(lib().mf_solve_pressure_system(rhs._h, vel._h, pressure._h, flags._h, C.byref(p), C.byref(info)))
-    _publish(info)
+    _publish(info, p.cgAccuracy)
 
 
 @M._plugin
@@ -188,7 +191,7 @@ def solvePressure(vel=None, pressure=None, flags=None, **kwargs):
     p, keep = _params("solvePressure", kwargs, allowRetRhs=True)
     info = SolveInfo()
     check(lib().mf_solve_pressure(vel._h, pressure._h, flags._h, C.byref(p), C.byref(info)))
-    _publish(info)
+    _publish(info, p.cgAccuracy)
 
 
 def releaseMG(solver=None, **kwargs):
