@@ -280,7 +280,10 @@ __device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int
   const int BX = L.PX - 2, BY = L.PY - 2;
   if (t >= BX * BY) return false;
   q.ly = (BX == 1) ? t : (int)__umulhi((unsigned)t, L.bxMagic);
-  q.lx = t - q.ly * BX; q.lz = lz0 + blockIdx.y;
+  // z pairs in the order first, last, second, ...: on a z-slab partitioned level the two boundary pairs read their neighbours'
+  // values over NVLink; scheduled first, that latency hides behind the interior pairs instead of forming the kernel's tail
+  const int ypairs = gridDim.y, yb = blockIdx.y;
+  q.lx = t - q.ly * BX; q.lz = lz0 + (yb == 0 ? 0 : (yb == 1 ? ypairs - 1 : yb - 1));
   q.p = (((q.lz + L.zoff) * L.NC + c) * L.PY + q.ly + 1) * L.PX + q.lx + 1;
   return true;
 }
