@@ -75,10 +75,10 @@ ALGO_BYTES_PER_CELL = {
 
 
 def mg_level_sizes(size):
-    """vertex counts of the GridMg levels (multigrid.cpp:283-301: size/2 + 1 per axis, down to <= 5 ... the library's own
-    hierarchy is authoritative; this is only used to turn per-level times into bytes)"""
+    """sizes of the GridMg levels (multigrid.cpp:256-261: (size + 2) / 2 per axis until every axis is <= 5 or the level has <= 1000
+    vertices); only used to turn per-level kernel times into bytes"""
     out = [tuple(size)]
-    while max(out[-1]) > 5 and len(out) < 12:
+    while max(out[-1]) > 5 and out[-1][0] * out[-1][1] * out[-1][2] > 1000 and len(out) < 101:     # multigrid.cpp:256-261
         out.append(tuple((n + 2) // 2 for n in out[-1]))
     return out
 
