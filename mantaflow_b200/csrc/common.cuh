@@ -79,6 +79,7 @@ struct Solver {
   double* redHost;      // pinned
   int* devFlagsScratch; // small int scratch (16 ints), job-wide when partitioned over GPUs: any rank's kernels raise flags here
   int* localInts;       // small int scratch (16 ints), private to this process
+  volatile unsigned* seqHost; unsigned seqTicket;   // pinned ticket readSmall spins on (solver.cu)
   int* hostInts;        // pinned
   float* aosStage;      // staging buffer for AoS<->SoA (3*N floats), lazily allocated
   MgHierarchy* mg;      // static multigrid cache (gMapMG, pressure.cpp:250)

@@ -409,6 +409,40 @@ __global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, i
   mgInterpAddItem(F, C, z0, z1, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
+// The same for a colour-blocked fine level, without divisions: a work item is a storage position of colour CF (blockIdx.z) in z
+// pair blockIdx.y, so the vertex is (2 lx + cx, 2 ly + cy, 2 lz + cz) and the coarse vertices it interpolates from are
+// (lx .. lx + cx, ly .. ly + cy, lz .. lz + cz): compile-time loop bounds, same summation order (z, y, x ascending).
+template <int CF>
+__device__ __forceinline__ void mgInterpAddBlockedItem(const LvlD& F, const LvlD& C, int lz0) {
+  BlkPos q;
+  if (!mgBlockThread(F, CF, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
+  constexpr int cx = CF & 1, cy = (CF >> 1) & 1, cz = (CF >> 2) & 1;
+  const bool off = mgRowZero(F, q.p);
+  const float xo = F.x[q.p];
+  float sum = 0.f;
+#pragma unroll
+  for (int dz = 0; dz <= cz; dz++)
+#pragma unroll
+    for (int dy = 0; dy <= cy; dy++)
+#pragma unroll
+      for (int dx = 0; dx <= cx; dx++) sum += C.x[mgIdx(C, q.lx + dx, q.ly + dy, q.lz + dz)];
+  const float iw = 1.0f / (float)(1 << (cx + cy + cz));
+  if (!off) F.x[q.p] = xo + iw * sum;
+}
+__global__ void __launch_bounds__(128) k_mg_interp_add_b(LvlD F, LvlD C, int lz0) {
+  MF_PDL_PROLOGUE
+  switch (blockIdx.z) {
+    case 0: mgInterpAddBlockedItem<0>(F, C, lz0); break;
+    case 1: mgInterpAddBlockedItem<1>(F, C, lz0); break;
+    case 2: mgInterpAddBlockedItem<2>(F, C, lz0); break;
+    case 3: mgInterpAddBlockedItem<3>(F, C, lz0); break;
+    case 4: mgInterpAddBlockedItem<4>(F, C, lz0); break;
+    case 5: mgInterpAddBlockedItem<5>(F, C, lz0); break;
+    case 6: mgInterpAddBlockedItem<6>(F, C, lz0); break;
+    default: mgInterpAddBlockedItem<7>(F, C, lz0); break;
+  }
+}
+
 // ---- Galerkin coarse operators (setup) ---------------------------------------------------------------------
 // precomputed coarsening paths for level 1 (multigrid.cpp:286-318)
 struct MgPath { signed char Nx, Ny, Nz, Ux, Uy, Uz, Wx, Wy, Wz; signed char sc, sf, inU; float rw, iw; };

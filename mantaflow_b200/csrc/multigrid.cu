@@ -702,7 +702,14 @@ static void interpAdd(MgHierarchy* mg, int l) {
   LvlD& F = mg->lv[l]; LvlD& C = mg->lv[l + 1];
   const bool solo = lvlSolo(mg, l);
   beginGroup(mg, solo);
+  const bool blocked = F.perm && mg->D.is3D && F.NC == 8 && !getenv("MF_MG_INTERP_GENERIC");
   MF_RANKS(s, r) {
+    if (blocked) {
+      int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
+      if (lz1 <= lz0) continue;
+      MF_LAUNCH_PDL(s, k_mg_interp_add_b, dim3(cdiv((long long)(F.PX - 2) * (F.PY - 2), 128), lz1 - lz0, 8), 128, F, C, lz0);
+      continue;
+    }
     int z0, z1; lvlPlanes(mg, l, r, z0, z1);
     if (z1 <= z0) continue;
     const long long nt = (long long)F.sx * F.sy * (z1 - z0);

@@ -1,6 +1,7 @@
 // solver.cu -- FluidSolver / Grid<T> data model on the device, elementwise ops and reductions.
 // Reference: source/fluidsolver.{h,cpp} (temp-grid pool :25-50, ctor :107), source/grid.{h,cpp}.
 #include "common.cuh"
+#include <atomic>
 #include "reduce.cuh"
 #include "comm.h"
 #include <cstring>
@@ -79,8 +80,12 @@ cudaEvent_t Solver::profEvent() {
 }
 
 struct SmallPayload { unsigned w[16]; };
-__global__ void k_read_small(unsigned* dst, const unsigned* __restrict__ src, int nwords) {
+// payload into mapped pinned memory, then (after a system-scope fence) the ticket the host is spinning on
+__global__ void k_read_small(unsigned* dst, const unsigned* __restrict__ src, int nwords, volatile unsigned* seq, unsigned ticket) {
   if ((int)threadIdx.x < nwords) dst[threadIdx.x] = src[threadIdx.x];
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) *seq = ticket;
 }
 __global__ void k_write_small(unsigned* dst, SmallPayload p, int nwords) {
   if ((int)threadIdx.x < nwords) dst[threadIdx.x] = p.w[threadIdx.x];
@@ -88,9 +93,26 @@ __global__ void k_write_small(unsigned* dst, SmallPayload p, int nwords) {
 void Solver::readSmall(void* pinnedDst, const void* dev, int bytes) {
   void* mapped = nullptr;
   CUDA_CHECK(cudaHostGetDevicePointer(&mapped, pinnedDst, 0));
-  k_read_small<<<1, 64, 0, stream>>>((unsigned*)mapped, (const unsigned*)dev, bytes / 4);
+  // The host waits on a ticket in pinned memory instead of cudaStreamSynchronize (the PCG reads its stop flag once per iteration:
+  // the wake-up latency of a stream synchronisation is paid 4-5 times per step); every 64 Ki polls the stream is queried so that a
+  // faulted kernel surfaces as an error instead of a hang.  MF_SYNC_READS=1 restores the plain synchronisation.
+  static const bool plain = getenv("MF_SYNC_READS") != nullptr;
+  void* seqDev = nullptr;
+  CUDA_CHECK(cudaHostGetDevicePointer(&seqDev, (void*)seqHost, 0));
+  const unsigned ticket = ++seqTicket;
+  k_read_small<<<1, 64, 0, stream>>>((unsigned*)mapped, (const unsigned*)dev, bytes / 4, (volatile unsigned*)seqDev, ticket);
   launches++;
-  CUDA_CHECK(cudaStreamSynchronize(stream));
+  if (plain) { CUDA_CHECK(cudaStreamSynchronize(stream)); return; }
+  CUDA_CHECK(cudaGetLastError());
+  volatile unsigned* seq = seqHost;
+  for (unsigned spins = 1; *seq != ticket; spins++) {
+    if ((spins & 0xffffu) == 0) {
+      const cudaError_t e = cudaStreamQuery(stream);
+      if (e == cudaSuccess) break;                                   // everything queued has finished: the ticket is written
+      if (e != cudaErrorNotReady) CUDA_CHECK(e);
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
 }
 void Solver::writeSmall(void* dev, const void* hostSrc, int bytes) {
   SmallPayload p; memset(&p, 0, sizeof(p)); memcpy(&p, hostSrc, (size_t)bytes);
@@ -244,6 +266,7 @@ static Solver* createSolver(int nx, int ny, int nz, int dim, int device, Comm* c
   CUDA_CHECK(cudaMemset(s->localInts, 0, sizeof(int) * 16));
   s->devFlagsScratch = (int*)s->galloc(sizeof(int) * 16);      // job-wide: kernels on any rank raise flags here
   CUDA_CHECK(cudaHostAlloc(&s->hostInts, sizeof(int) * 16, cudaHostAllocMapped));
+  CUDA_CHECK(cudaHostAlloc((void**)&s->seqHost, 64, cudaHostAllocMapped)); *s->seqHost = 0; s->seqTicket = 0;
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   return s;
 }
@@ -285,7 +308,7 @@ void mf_solver_destroy(mf_solver* sp) {
   if (s->cgCode) s->gfree(s->cgCode);
   if (s->noiseTile) cudaFree(s->noiseTile);
   cudaFree(s->redScratch); cudaFree(s->redCounter); cudaFree(s->redOut); cudaFreeHost(s->redHost);
-  cudaFree(s->localInts); s->gfree(s->devFlagsScratch); cudaFreeHost(s->hostInts);
+  cudaFree(s->localInts); s->gfree(s->devFlagsScratch); cudaFreeHost(s->hostInts); cudaFreeHost((void*)s->seqHost);
   if (s->aosStage) cudaFree(s->aosStage);
   for (auto& r : s->profRecs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (cudaEvent_t e : s->evPool) cudaEventDestroy(e);

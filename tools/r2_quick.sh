@@ -1,0 +1,19 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_kernels_gpu.py tests/test_parity_gpu.py tests/test_multi_gpu.py -q -m gpu -p no:cacheprovider -x > gpurun_out/quick_tests.log 2>&1; tail -4 gpurun_out/quick_tests.log
+for v in new sync; do
+if [ $v = sync ]; then export MF_SYNC_READS=1 MF_MG_INTERP_GENERIC=1; fi
+timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-strong1024 > gpurun_out/bench_quick_$v.json 2> gpurun_out/bench_quick.err; tail -c 300 gpurun_out/bench_quick.err
+python - <<PY
+import json
+d = json.load(open("gpurun_out/bench_quick_$v.json"))
+ks = {k["kernel"]: k for k in d["kernels"]}
+print("$v step %.3f ms" % d["ms_per_step"], {n: round(ks[n]["avg_us"], 1) for n in ks if "interp" in n}, d["pcg_ms_per_iteration"]["ms_per_iteration"])
+PY
+done
+python - <<'PY'
+import json
+r = json.load(open("gpurun_out/parity_report.json"))
+bad = [k for k, v in r.items() if any(isinstance(x, dict) and x.get("mismatching") for x in v.values())]
+print("cases", len(r), "not bit-identical:", bad)
+PY
