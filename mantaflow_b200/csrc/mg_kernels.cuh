@@ -66,7 +66,13 @@ __device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, 
 __device__ __forceinline__ bool mgRowZero(const LvlD& L, int p) {
   return L.Ah ? (__half_as_ushort(L.Ah[p]) & 0x7fffu) == 0 : L.A[p] == 0.f;
 }
-__device__ __forceinline__ float mgDiag(const LvlD& L, int p) { return L.Ah ? __half2float(L.Ah[p]) : L.A[p]; }
+// (binary16 levels mark a vertex whose row -- or a row it reads -- is not exactly representable with a NaN diagonal: such a
+//  vertex takes its coefficients from the float planes, see k_mg_mark_special)
+__device__ __forceinline__ float mgDiag(const LvlD& L, int p) {
+  if (!L.Ah) return L.A[p];
+  const float d = __half2float(L.Ah[p]);
+  return d == d ? d : L.A[p];
+}
 // setup kernels walk the storage range [p0, p1) (a rank's share of the level)
 #define MG_P_FROM_THREAD(L) \
   const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x; \
@@ -300,6 +306,19 @@ __device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const
   }
   return sum;
 }
+// a marked vertex of a binary16 level: the same sum from the float planes.  Stored entry e of a row is stencil term 13 + e; the
+// lower half of the stencil (s < 13) is entry 13 - s of the neighbour's row, whose position is p + xo[s] / 4.
+template <bool WITH_CENTER>
+__device__ __noinline__ float mgStencilSubFloat(const LvlD& L, int p, const MgOff1& o, float sum) {
+  const char* xp = reinterpret_cast<const char*>(L.x + p);
+  for (int s = 0; s < 27; s++) {
+    if (s == 13 && !WITH_CENTER) continue;
+    const int e = s >= 13 ? s - 13 : 13 - s;
+    const long long pos = s >= 13 ? (long long)p : (long long)p + (o.xo[s] >> 2);
+    sum -= L.A[e * L.as + pos] * *reinterpret_cast<const float*>(xp + o.xo[s]);
+  }
+  return sum;
+}
 template <bool HALF> __device__ __forceinline__ const char* mgRowPtr(const LvlD& L, int p) {
   return HALF ? reinterpret_cast<const char*>(L.Ah + p) : reinterpret_cast<const char*>(L.A + p);
 }
@@ -315,8 +334,9 @@ __global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_const
   // to L2 / DRAM instead of two) -- the sweeps of the small levels are pure latency.  (128, 6): up to 80 registers, enough for
   // the compiler to issue all 54 loads before the first use (with 32 registers it interleaved them in three dependent rounds).
   const char* ap = mgRowPtr<HALF>(L, q.p);
-  const float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
-  const float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
+  float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
+  float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
+  if (HALF && IS3D && diag != diag) { diag = L.A[q.p]; sum = mgStencilSubFloat<false>(L, q.p, o, L.b[q.p]); }      // marked vertex (rare)
   if (diag != 0.f) L.x[q.p] = sum / diag;
 }
 // knCalcResidual, l > 0; blockIdx.z = colour
@@ -325,7 +345,10 @@ __device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, i
   BlkPos q;
   if (!mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
   // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
-  L.r[q.p] = mgStencilSub<IS3D, true, HALF>(mgRowPtr<HALF>(L, q.p), reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
+  const char* ap = mgRowPtr<HALF>(L, q.p);
+  float r = mgStencilSub<IS3D, true, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
+  if (HALF && IS3D) { const float dg = __half2float(*reinterpret_cast<const __half*>(ap)); if (dg != dg) r = mgStencilSubFloat<true>(L, q.p, O.t[C], L.b[q.p]); }
+  L.r[q.p] = r;
 }
 template <bool IS3D, bool HALF>
 __global__ void __launch_bounds__(128, 6) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0) {
@@ -533,7 +556,7 @@ __global__ void __launch_bounds__(128) k_mg_galerkin(LvlD F, LvlD C, MgDims D, i
 
 // binary16 copy of a blocked level's operator; *inexact is set when an entry does not survive the round trip.  The level-1
 // Galerkin operator of a 0 / -1 / small-integer Laplacian consists of multiples of 1/64 below 32 and converts exactly.
-__global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* __restrict__ Ah, int* __restrict__ inexact, int p0, int p1) {
+__global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* __restrict__ Ah, float* __restrict__ rowBad, int p0, int p1) {
   const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= p1) return;
   bool bad = false;
@@ -543,7 +566,26 @@ __global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* 
     bad |= !(__half2float(h) == a);
     Ah[e * L.ash + p] = h;
   }
-  if (bad) *inexact = 1;
+  rowBad[p] = bad ? 1.f : 0.f;
+}
+// A vertex is "special" when its own row or the row of any of its 26 neighbours (a superset of the 13 rows its sweep reads) has an
+// entry that binary16 cannot hold -- in practice the rows around the pinned cell of zeroPressureFixing, whose level-0 equation is
+// scaled by 1e-6.  Its binary16 diagonal becomes NaN: the sweeps then take that vertex' coefficients from the float planes
+// (mgStencilSubFloat), everybody else streams the binary16 copy.  *count = number of special vertices.
+__global__ void __launch_bounds__(256) k_mg_mark_special(LvlD L, __half* __restrict__ Ah, const float* __restrict__ rowBad, int* __restrict__ count, int p0, int p1) {
+  const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= p1) return;
+  int x, y, z;
+  if (!mgDecode(L, p, x, y, z)) return;
+  bool special = false;
+  for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) special |= rowBad[mgIdx(L, x + dx, y + dy, z + dz)] != 0.f;
+  // (inactive vertices keep their exact all-zero row: the entries that couple a neighbour to them are zero as well, and a NaN
+  //  diagonal would make mgRowZero() take them for active)
+  if (special && L.A[p] != 0.f) { Ah[p] = __ushort_as_half((unsigned short)0x7e00); atomicAdd(count, 1); }
+}
+__global__ void __launch_bounds__(256) k_mg_zero_range(float* __restrict__ a, int p0, int p1) {
+  const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < p1) a[p] = 0.f;
 }
 
 } // namespace mf

@@ -29,7 +29,8 @@ struct MgHierarchy {
   bool pendingSolo;         // a group of rank-0-only launches has not been followed by a cross-rank barrier yet
   std::vector<std::vector<int>> pairSplit;   // blocked level l: rank r sweeps z pairs [pairSplit[l][r], pairSplit[l][r+1])
   std::vector<MgOff8> offs;                  // blocked level l: stencil offset tables of the sweeps (buildOffsets)
-  __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when exact)
+  __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when used)
+  int nspecial1;                             // level-1 vertices that keep the float planes (k_mg_mark_special)
   // persistent kernels for the small levels (mg_tail.cuh): grid-barrier counter, its host-tracked value, time-out flag
   int tailCluster; unsigned* tailBar; unsigned tailBase; int* tailErrHost; int* tailErrDev; MgOff8* tailOffs;
   int tailFirst;            // first level swept by the tail kernels, or -1
@@ -340,7 +341,7 @@ MgHierarchy* mg_create(Solver* s) {
   MgHierarchy* mg = new MgHierarchy();
   mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
-  mg->half1 = nullptr; mg->ash1 = 0;
+  mg->half1 = nullptr; mg->ash1 = 0; mg->nspecial1 = 0;
   mg->tailCluster = 0; mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
@@ -588,14 +589,26 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
     if (l == 1 && mg->half1) {
       // level 1 carries most of the coarse-level traffic (14 planes, every entry read twice per sweep): keep it in binary16
       // when that is exact, so that the whole level stays resident in L2 between the sweeps of a V-cycle
-      int* inexact = mg->dFlags + 6;
-      s->clearShared(inexact, sizeof(int));
+      // Rows that binary16 cannot hold exactly (the rows around the pinned cell of zeroPressureFixing) stay in float: their
+      // vertices are marked with a NaN binary16 diagonal (k_mg_mark_special) and take the float planes in the sweeps.  The level's x
+      // vector serves as scratch for the per-row flags and is zeroed again afterwards (it must be 0 at padding / inactive entries).
+      int* nspecial = mg->dFlags + 6;
+      s->clearShared(nspecial, sizeof(int));
       C.Ah = nullptr; C.ash = mg->ash1;
-      MG_SETUP(mg, l, k_mg_pack_half, 256, C, mg->D, mg->half1, inexact);
+      MG_SETUP(mg, l, k_mg_pack_half, 256, C, mg->D, mg->half1, C.x);
       flushGroups(mg);
-      CUDA_CHECK(cudaMemcpyAsync(s->hostInts + 6, inexact, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+      MG_SETUP(mg, l, k_mg_mark_special, 256, C, mg->half1, (const float*)C.x, nspecial);
+      flushGroups(mg);
+      MG_SETUP(mg, l, k_mg_zero_range, 256, C.x);
+      flushGroups(mg);
+      CUDA_CHECK(cudaMemcpyAsync(s->hostInts + 6, nspecial, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
       CUDA_CHECK(cudaStreamSynchronize(s->stream));
-      if (s->hostInts[6] == 0) C.Ah = mg->half1;
+      mg->nspecial1 = s->hostInts[6];
+      // Default: binary16 only when the whole level converts exactly.  MF_MG_HALF_SPECIAL=1 also takes it with marked float rows
+      // (bit-identical, tests/test_kernels_gpu.py) -- measured on B200 at 256^3 it does not pay: the level-1 sweep takes 15.0 us
+      // instead of 12.7 us and the residual 64 us instead of 51 us (27 two-byte loads and 27 conversions per vertex cost more
+      // than the halved operator traffic saves), 5.15 against 5.00 ms per step.
+      if (mg->nspecial1 == 0 || (mg->nspecial1 <= 65536 && getenv("MF_MG_HALF_SPECIAL"))) C.Ah = mg->half1;
     }
     buildOffsets(mg, l);
   }

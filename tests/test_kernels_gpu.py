@@ -127,6 +127,32 @@ def test_rowcode_spmv_zmarch_matches_flat(size, zc, monkeypatch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("size", [(32, 24, 16), (64, 48, 40)])
+def test_half_level1_with_float_rows_matches_float(size, monkeypatch):
+    """MF_MG_HALF_SPECIAL=1: the level-1 operator in binary16 with the rows binary16 cannot hold (around the pinned cell of
+    zeroPressureFixing) kept in float through a NaN-diagonal marker -- same pressure bit for bit, same iteration count, as the
+    all-float level, with the wavefront legs and with the per-colour sweeps"""
+    from mantaflow_b200 import manta
+    res = []
+    for env in ({}, {"MF_MG_HALF_SPECIAL": "1"}, {"MF_MG_HALF_SPECIAL": "1", "MF_MG_NOWAVE": "1"}):
+        for k in ("MF_MG_HALF_SPECIAL", "MF_MG_NOWAVE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.initDomain(); flags.fillGrid()
+        vel = s.create(manta.MACGrid); p = s.create(manta.RealGrid)
+        rs2 = np.random.RandomState(9)
+        vel.from_numpy(rs2.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5))
+        manta.solvePressure(flags=flags, vel=vel, pressure=p, cgAccuracy=1e-6, preconditioner=manta.PcMGStatic, zeroPressureFixing=True)
+        res.append((p.to_numpy(), manta.getSolveInfo()["iterations"]))
+        manta.releaseMG(s)
+    for r in res[1:]:
+        assert r[1] == res[0][1]
+        assert np.array_equal(r[0].view(np.int32), res[0][0].view(np.int32))
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("nranks", [2, 3])
 def test_rowcode_spmv_partitioned(nranks):
     """z-slab partition (emulated ranks): the row-code SpMV reads the neighbour planes of other slabs"""

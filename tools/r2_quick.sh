@@ -1,14 +1,14 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_kernels_gpu.py tests/test_parity_gpu.py tests/test_multi_gpu.py -q -m gpu -p no:cacheprovider -x > gpurun_out/quick_tests.log 2>&1; tail -4 gpurun_out/quick_tests.log
-for v in new sync; do
-if [ $v = sync ]; then export MF_SYNC_READS=1 MF_MG_INTERP_GENERIC=1; fi
+timeout 1200 python -m pytest tests/test_kernels_gpu.py tests/test_parity_gpu.py tests/test_multi_gpu.py tests/test_fullsize_gpu.py -q -m gpu -p no:cacheprovider -x > gpurun_out/quick_tests.log 2>&1; tail -4 gpurun_out/quick_tests.log
+for v in new old; do
+if [ $v = old ]; then export MF_MG_HALF_EXACT_ONLY=1; fi
 timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-strong1024 > gpurun_out/bench_quick_$v.json 2> gpurun_out/bench_quick.err; tail -c 300 gpurun_out/bench_quick.err
 python - <<PY
 import json
 d = json.load(open("gpurun_out/bench_quick_$v.json"))
 ks = {k["kernel"]: k for k in d["kernels"]}
-print("$v step %.3f ms" % d["ms_per_step"], {n: round(ks[n]["avg_us"], 1) for n in ks if "interp" in n}, d["pcg_ms_per_iteration"]["ms_per_iteration"])
+print("$v step %.3f ms" % d["ms_per_step"], {n: round(ks[n]["avg_us"], 1) for n in ks if "@L1" in n}, d["pcg_ms_per_iteration"]["ms_per_iteration"], d["pcg_iterations"][:5])
 PY
 done
 python - <<'PY'
