@@ -153,6 +153,17 @@ __global__ void k_part_delete_in_obstacle(Geo g, long long n, const float* __res
 }
 
 // markFluidCells (flip.cpp:143-147, :166-180)
+// whole-array fills / copies as kernels: on a partitioned solver the arrays span the memory of several GPUs
+__global__ void k_zero_words(long long n, unsigned* __restrict__ d) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) d[i] = 0u;
+}
+__global__ void k_copy_words(long long n, unsigned* __restrict__ d, const unsigned* __restrict__ src) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long st = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += st) d[i] = src[i];
+}
 __global__ void k_clear_fluid_flags(long long n, int* __restrict__ flags) {
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (t >= n) return;
@@ -293,7 +304,11 @@ mf_parts* mf_parts_create(mf_solver* sp) {
   try {
     mfAssert(sp, "BasicParticleSystem: null solver");
     Solver* s = S(sp);
-    mfAssert(!s->multi(), "BasicParticleSystem: particle systems are not supported on z-slab partitioned solvers yet");
+    // z-slab partitioned solvers: the particle system is REPLICATED -- every rank holds all particles and runs the particle-side
+    // kernels (advection, grid -> particle transfers read the grids through the one address space), which are deterministic, so the
+    // replicas stay bit-identical without any exchange; the particle -> grid writers (mapPartsToMAC, markFluidCells) run on rank 0
+    // alone, whose stores reach the other ranks' slabs over NVLink, followed by the device barrier (flip.cpp:619-670 has no
+    // counterpart: the reference is a shared-memory program).
     mfAssert(s->N < (1LL << 32) - 1, "BasicParticleSystem: grid too large for 32-bit face keys");
     Parts* p = new Parts();
     p->s = s; p->n = 0; p->cap = 0; p->pos = nullptr; p->flag = nullptr; p->scratch = nullptr; p->scratchBytes = 0;
@@ -401,8 +416,7 @@ int mf_sample_flags_with_particles(const mf_grid* flagsG, mf_parts* pp, int disc
   Parts* p = P(pp); Solver* s = p->s; s->use();
   mfAssert(G(flagsG)->s == s, "sampleFlagsWithParticles: flags and parts belong to different solvers");
   std::vector<int> fl((size_t)s->N);
-  CUDA_CHECK(cudaStreamSynchronize(s->stream));
-  CUDA_CHECK(cudaMemcpy(fl.data(), G(flagsG)->di(), sizeof(int) * (size_t)s->N, cudaMemcpyDeviceToHost));
+  check_api(mf_grid_download(flagsG, fl.data()));          // (every rank of a partitioned solver reads the whole grid and samples identically)
   const bool is3D = s->is3D;
   const float jlen = randomness / (float)discretization;
   const float disp = (float)(1.0 / (double)discretization);
@@ -456,7 +470,7 @@ int mf_parts_advect_in_grid(mf_parts* pp, const mf_grid* flagsG, const mf_grid* 
   mfAssert(integrationMode >= 0 && integrationMode <= 2, "unknown integration type");
   const long long n = p->n;
   if (!n) return 0;
-  const Geo g = geo(s, 0);
+  const Geo g = geo(s);
   // scratch: x0 (3n), u (3n), total (3n)
   float* sc = (float*)scratchOf(p, sizeof(float) * 9 * (size_t)n);
   float* x0 = sc; float* u = sc + 3 * n; float* tot = sc + 6 * n;
@@ -497,15 +511,20 @@ int mf_mark_fluid_cells(const mf_parts* pp, mf_grid* flagsG, const mf_grid* phiO
   Grid* fg = G(flagsG);
   mfAssert(fg->s == s, "markFluidCells: flags and parts belong to different solvers");
   markFlagsChanged(fg);
-  const Geo g = geo(s, 0);
-  MF_LAUNCH(s, k_clear_fluid_flags, pblocks(s->N), 256, s->N, fg->di());
-  if (p->n) MF_LAUNCH(s, k_mark_fluid, pblocks(p->n), 256, g, p->n, (const float*)p->px(), (const float*)p->py(), (const float*)p->pz(), (const int*)p->flag, fg->di());
+  const Geo g = geo(s);                       // particle kernels address the whole grid
+  if (s->rankBegin == 0) {                    // the writer (see mf_parts_create)
+    MF_LAUNCH(s, k_clear_fluid_flags, pblocks(s->N), 256, s->N, fg->di());
+    if (p->n) MF_LAUNCH(s, k_mark_fluid, pblocks(p->n), 256, g, p->n, (const float*)p->px(), (const float*)p->py(), (const float*)p->pz(), (const int*)p->flag, fg->di());
+  }
+  s->rankSync();
   if (phiObs) {
     TmpReal tmp(s);
     int* nf = reinterpret_cast<int*>(tmp.p);
-    CUDA_CHECK(cudaMemcpyAsync(nf, fg->di(), sizeof(int) * (size_t)s->N, cudaMemcpyDeviceToDevice, s->stream));
+    MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) MF_LAUNCH(s, k_copy_words, pblocks(sp.n), 256, sp.n, (unsigned*)(nf + sp.off), (const unsigned*)(fg->di() + sp.off)); }
+    s->rankSync();
     MF_LAUNCH_IJK(s, k_set_nb_obstacle, nf, (const int*)fg->di(), (const float*)G(phiObs)->d);
-    CUDA_CHECK(cudaMemcpyAsync(fg->di(), nf, sizeof(int) * (size_t)s->N, cudaMemcpyDeviceToDevice, s->stream));
+    MF_RANKS(s, r) { const Span sp = span(s, r); if (sp.n) MF_LAUNCH(s, k_copy_words, pblocks(sp.n), 256, sp.n, (unsigned*)(fg->di() + sp.off), (const unsigned*)(nf + sp.off)); }
+    s->rankSync();
   }
   MF_LAUNCH_CHECK();
   MF_API_END
@@ -519,7 +538,7 @@ static void gridToParts(const mf_grid* flagsG, const mf_grid* velG, const mf_gri
   (void)flagsG;
   const PData& d = pdataOf(p, pdVel, 3, fn);
   if (!p->n) return;
-  const Geo g = geo(s, 0);
+  const Geo g = geo(s);
   const CV3 v = cv3(G(velG)); const CV3 vo = flip ? cv3(G(velOldG)) : v;
   MF_LAUNCH(s, k_grid_to_parts, pblocks(p->n), 256, g, p->n, (const float*)p->px(), (const float*)p->py(), (const float*)p->pz(), (const int*)p->flag, v, vo, flip, flipRatio,
             d.d, d.d + p->cap, d.d + 2 * p->cap);
@@ -550,11 +569,14 @@ int mf_map_parts_to_mac(const mf_grid* flagsG, mf_grid* velG, mf_grid* velOldG, 
   TmpVec tmpW(s);
   float* weight = weightG ? G(weightG)->d : tmpW.p;
   float* vel = G(velG)->d;
-  CUDA_CHECK(cudaMemsetAsync(weight, 0, sizeof(float) * 3 * (size_t)s->Np, s->stream));
-  CUDA_CHECK(cudaMemsetAsync(vel, 0, sizeof(float) * 3 * (size_t)s->Np, s->stream));
+  const bool writer = s->rankBegin == 0;      // see mf_parts_create: rank 0 scatters, its stores reach every slab; then the device barrier
   const long long n = p->n, m = 8 * n;
-  if (n) {
-    const Geo g = geo(s, 0);
+  if (writer) {
+    MF_LAUNCH(s, k_zero_words, pblocks(3 * s->Np), 256, 3 * s->Np, (unsigned*)weight);
+    MF_LAUNCH(s, k_zero_words, pblocks(3 * s->Np), 256, 3 * s->Np, (unsigned*)vel);
+  }
+  if (n && writer) {
+    const Geo g = geo(s);
     size_t sortBytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sortBytes, (const unsigned*)nullptr, (unsigned*)nullptr, (const unsigned*)nullptr, (unsigned*)nullptr, (int)m, 0, 32, s->stream);
     const size_t arr = ((size_t)m * 4 + 255) / 256 * 256;
@@ -571,8 +593,11 @@ int mf_map_parts_to_mac(const mf_grid* flagsG, mf_grid* velG, mf_grid* velOldG, 
       MF_LAUNCH(s, k_part_accumulate, pblocks(m), 256, m, (const unsigned*)keys2, (const unsigned*)ids2, (const float*)w, (const float*)wv, weight + c * s->Np, vel + c * s->Np);
     }
   }
-  MF_LAUNCH(s, k_stomp_divide, pblocks(3 * s->Np), 256, 3 * s->Np, vel, weight);
-  CUDA_CHECK(cudaMemcpyAsync(G(velOldG)->d, vel, sizeof(float) * 3 * (size_t)s->Np, cudaMemcpyDeviceToDevice, s->stream));
+  if (writer) {
+    MF_LAUNCH(s, k_stomp_divide, pblocks(3 * s->Np), 256, 3 * s->Np, vel, weight);
+    MF_LAUNCH(s, k_copy_words, pblocks(3 * s->Np), 256, 3 * s->Np, (unsigned*)G(velOldG)->d, (const unsigned*)vel);
+  }
+  s->rankSync();
   MF_LAUNCH_CHECK();
   MF_API_END
 }

@@ -24,9 +24,8 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
 def _cases_for(nranks):
-    # particle systems are not z-slab partitioned yet (mf_parts_create refuses a partitioned solver)
-    return [n for n, c in C.CASES.items() if c.get("dim", 3) == 3 and c["size"][2] >= 2 * nranks
-            and "BasicParticleSystem" not in c["grids"].values()]
+    # particle systems are replicated on every rank, rank 0 writes the particle -> grid transfers (csrc/particles.cu)
+    return [n for n, c in C.CASES.items() if c.get("dim", 3) == 3 and c["size"][2] >= 2 * nranks]
 
 
 def _run_partitioned(name, comm):
@@ -96,7 +95,8 @@ def test_two_processes_two_gpus(tmp_path):
         pytest.skip("needs 2 GPUs")
     out = tmp_path / "dist.json"
     names = ["adv_real_o2_c2", "adv_mac_o2_c2", "adv_mac_o2_outflow", "wallbcs", "buoyancy", "rhs_plain", "correct_vel",
-             "solve_mic_tight", "solve_mgstatic_tight", "solve_mg_default", "solve_l2norm", "plume3d_mg", "flags_domain"]
+             "solve_mic_tight", "solve_mgstatic_tight", "solve_mg_default", "solve_l2norm", "plume3d_mg", "flags_domain",
+             "flip_transfer", "flip_advect_rk4", "flip01_3d"]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", os.path.join(ROOT, "tools", "dist_cases.py"), "--out", str(out)] + names
     p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
