@@ -9,7 +9,8 @@
 // in particle order (KERNEL(pts, single)), so every face value is a float sum in particle order.  Here each particle emits its 8
 // (weight, weight * value) contributions per component in the reference's order, the contributions are stably sorted by target
 // face (cub radix sort) and one thread per face adds its run front to back -- the same sums, bit for bit, at any thread count.
-// Particle systems are not z-slab partitioned yet: single-rank solvers only.
+// On z-slab partitioned solvers the particle arrays are replicated on every rank; the rank that owns slab 0 writes the
+// particle -> grid transfers for the whole grid and every rank then passes rankSync().
 #include "common.cuh"
 #include "sample.cuh"
 #include <cub/device/device_radix_sort.cuh>
