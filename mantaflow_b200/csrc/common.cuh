@@ -177,7 +177,15 @@ struct ProfScope {   // brackets one launch with events on the solver stream whe
   }
   ~ProfScope() { if (b) cudaEventRecord(b, s->stream); }
 };
-#define MF_LAUNCH(s, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } while (0)
+// MF_DEBUG_SYNC=1 (development): synchronise after every launch and name the kernel an error comes from
+inline void dbgSync(Solver* s, const char* name) {
+  static const bool on = getenv("MF_DEBUG_SYNC") != nullptr;
+  if (!on) return;
+  cudaError_t e = cudaStreamSynchronize(s->stream);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) fprintf(stderr, "MF_DEBUG_SYNC: %s after %s\n", cudaGetErrorString(e), name);
+}
+#define MF_LAUNCH(s, kern, grid, block, ...) do { { mf::ProfScope _ps((s), #kern); kern<<<(grid), (block), 0, (s)->stream>>>(__VA_ARGS__); (s)->launches++; } mf::dbgSync((s), #kern); } while (0)
 // Programmatic dependent launch (sm_90+): a kernel launched with MF_LAUNCH_PDL may be scheduled while its predecessor on the
 // stream is still draining; it must call pdlWait() before it touches global memory (waits for the predecessor's completion and
 // memory flush) and calls pdlTrigger() so that ITS successor can be scheduled early.  Hides the ~4 us launch gap between the
@@ -194,10 +202,10 @@ inline void launchPdlS(cudaStream_t st, size_t smem, void (*kern)(KArgs...), dim
 template <class... KArgs, class... Args>
 inline void launchPdl(cudaStream_t st, void (*kern)(KArgs...), dim3 grid, dim3 block, Args... args) { launchPdlS(st, 0, kern, grid, block, args...); }
 // with dynamic shared memory (profiling mode brackets the launch with events like MF_LAUNCH)
-#define MF_LAUNCH_PDL_SMEM(s, smem, kern, grid, block, ...) do { mf::ProfScope _ps((s), #kern); \
-  mf::launchPdlS((s)->stream, smem, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } while (0)
+#define MF_LAUNCH_PDL_SMEM(s, smem, kern, grid, block, ...) do { { mf::ProfScope _ps((s), #kern); \
+  mf::launchPdlS((s)->stream, smem, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } mf::dbgSync((s), #kern); } while (0)
 #define MF_LAUNCH_PDL(s, kern, grid, block, ...) do { if ((s)->profiling) { MF_LAUNCH(s, kern, grid, block, __VA_ARGS__); } \
-  else { mf::launchPdl((s)->stream, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; } } while (0)
+  else { mf::launchPdl((s)->stream, kern, dim3(grid), dim3(block), __VA_ARGS__); (s)->launches++; mf::dbgSync((s), #kern); } } while (0)
 #define MF_LAUNCH_CHECK() CUDA_CHECK(cudaGetLastError())
 // SPMD launch helpers: MF_RANKS iterates over the ranks this process executes; every group of per-rank launches is followed
 // by rankSync (dependent launches on other GPUs read/write the same global arrays).

@@ -282,13 +282,12 @@ struct MgOff8 { MgOff1 t[8]; };
 struct BlkPos { int p; int lx, ly, lz; };
 // work item -> storage position among the vertices of colour c: blockIdx.y = z pair (from lz0), t = position in the pair's
 // BX x BY block of the colour (t / BX by multiplication: t * BX < 2^32)
-__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int t, BlkPos& q) {
+__device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int t, BlkPos& q, int ypairs, int yb) {
   const int BX = L.PX - 2, BY = L.PY - 2;
   if (t >= BX * BY) return false;
   q.ly = (BX == 1) ? t : (int)__umulhi((unsigned)t, L.bxMagic);
   // z pairs in the order first, last, second, ...: on a z-slab partitioned level the two boundary pairs read their neighbours'
   // values over NVLink; scheduled first, that latency hides behind the interior pairs instead of forming the kernel's tail
-  const int ypairs = gridDim.y, yb = blockIdx.y;
   q.lx = t - q.ly * BX; q.lz = lz0 + (yb == 0 ? 0 : (yb == 1 ? ypairs - 1 : yb - 1));
   q.p = (((q.lz + L.zoff) * L.NC + c) * L.PY + q.ly + 1) * L.PX + q.lx + 1;
   return true;
@@ -309,8 +308,9 @@ __device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const
 // a marked vertex of a binary16 level: the same sum from the float planes.  Stored entry e of a row is stencil term 13 + e; the
 // lower half of the stencil (s < 13) is entry 13 - s of the neighbour's row, whose position is p + xo[s] / 4.
 template <bool WITH_CENTER>
-__device__ __noinline__ float mgStencilSubFloat(const LvlD& L, int p, const MgOff1& o, float sum) {
+__device__ __forceinline__ float mgStencilSubFloat(const LvlD& L, int p, const MgOff1& o, float sum) {
   const char* xp = reinterpret_cast<const char*>(L.x + p);
+#pragma unroll
   for (int s = 0; s < 27; s++) {
     if (s == 13 && !WITH_CENTER) continue;
     const int e = s >= 13 ? s - 13 : 13 - s;
@@ -322,46 +322,85 @@ __device__ __noinline__ float mgStencilSubFloat(const LvlD& L, int p, const MgOf
 template <bool HALF> __device__ __forceinline__ const char* mgRowPtr(const LvlD& L, int p) {
   return HALF ? reinterpret_cast<const char*>(L.Ah + p) : reinterpret_cast<const char*>(L.A + p);
 }
+// Operator format of a blocked level (template parameter HM of the sweeps): float planes, binary16 planes (every entry converts
+// exactly), or binary16 planes + per-colour lists of the vertices that keep the float planes (k_mg_mark_special): those are swept by
+// ONE extra CTA row of the same launch (blockIdx.y == 0: scheduled first, its chain of dependent loads -- count, position, row --
+// hides behind the streaming CTAs instead of forming the tail), the streaming CTAs only skip them (NaN diagonal).
+enum { MG_FMT_FLOAT = 0, MG_FMT_HALF = 1, MG_FMT_HALF_LISTS = 2 };
+constexpr int MG_SPECIAL_CAP = 1024;        // vertices per colour list
+struct MgSpecial { const int* count; const int* list; };     // count[8], list[8][MG_SPECIAL_CAP]: storage positions
+// z pair of storage position p
+__device__ __forceinline__ int mgPairOf(const LvlD& L, int p) { return p / (L.PX * L.PY) / L.NC - L.zoff; }
+
 // knSmoothColor, l > 0: one vertex of one of the 8 (4) colours (multigrid.cpp:668-711)
-template <bool IS3D, bool HALF>
-__global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0) {
+template <bool IS3D, int HM>
+__global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0, MgSpecial sp) {
   MF_PDL_PROLOGUE
+  constexpr bool HALF = HM != MG_FMT_FLOAT;
+  const int ypairs = gridDim.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0);
+  if (HM == MG_FMT_HALF_LISTS && blockIdx.y == 0) {
+    // the listed vertices of this colour in the z pairs [lz0, lz0 + ypairs) of this launch, from the float planes
+    if (blockIdx.x != 0) return;
+    const int n = min(sp.count[c], MG_SPECIAL_CAP);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const int p = sp.list[c * MG_SPECIAL_CAP + i];
+      const int lz = mgPairOf(L, p);
+      if (lz < lz0 || lz >= lz0 + ypairs) continue;
+      const float diag = L.A[p];
+      const float sum = mgStencilSubFloat<false>(L, p, o, L.b[p]);
+      if (diag != 0.f) L.x[p] = sum / diag;
+    }
+    return;
+  }
   BlkPos q;
-  if (!mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
+  if (!mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0))) return;
   // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
   // reference's own division below would not be finite
   // The diagonal is loaded with the rest of the row and only the store is predicated: a vertex is one batch of loads (one trip
   // to L2 / DRAM instead of two) -- the sweeps of the small levels are pure latency.  (128, 6): up to 80 registers, enough for
   // the compiler to issue all 54 loads before the first use (with 32 registers it interleaved them in three dependent rounds).
   const char* ap = mgRowPtr<HALF>(L, q.p);
-  float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
-  float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
-  if (HALF && IS3D && diag != diag) { diag = L.A[q.p]; sum = mgStencilSubFloat<false>(L, q.p, o, L.b[q.p]); }      // marked vertex (rare)
-  if (diag != 0.f) L.x[q.p] = sum / diag;
+  const float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
+  const float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
+  if (HM == MG_FMT_HALF_LISTS) { if (diag != 0.f && diag == diag) L.x[q.p] = sum / diag; }      // NaN: a listed vertex
+  else if (diag != 0.f) L.x[q.p] = sum / diag;
 }
 // knCalcResidual, l > 0; blockIdx.z = colour
-template <bool IS3D, bool HALF, int C>
-__device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, int lz0) {
+template <bool IS3D, int HM, int C>
+__device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, int lz0, const MgSpecial& sp) {
+  constexpr bool HALF = HM != MG_FMT_FLOAT;
+  const int ypairs = gridDim.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0);
+  if (HM == MG_FMT_HALF_LISTS && blockIdx.y == 0) {
+    if (blockIdx.x != 0) return;
+    const int n = min(sp.count[C], MG_SPECIAL_CAP);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const int p = sp.list[C * MG_SPECIAL_CAP + i];
+      const int lz = mgPairOf(L, p);
+      if (lz < lz0 || lz >= lz0 + ypairs) continue;
+      L.r[p] = mgStencilSubFloat<true>(L, p, O.t[C], L.b[p]);
+    }
+    return;
+  }
   BlkPos q;
-  if (!mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
+  if (!mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0))) return;
   // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
   const char* ap = mgRowPtr<HALF>(L, q.p);
-  float r = mgStencilSub<IS3D, true, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
-  if (HALF && IS3D) { const float dg = __half2float(*reinterpret_cast<const __half*>(ap)); if (dg != dg) r = mgStencilSubFloat<true>(L, q.p, O.t[C], L.b[q.p]); }
-  L.r[q.p] = r;
+  const float r = mgStencilSub<IS3D, true, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
+  if (HM == MG_FMT_HALF_LISTS) { const float dg = __half2float(*reinterpret_cast<const __half*>(ap)); if (dg == dg) L.r[q.p] = r; }
+  else L.r[q.p] = r;
 }
-template <bool IS3D, bool HALF>
-__global__ void __launch_bounds__(128, 6) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0) {
+template <bool IS3D, int HM>
+__global__ void __launch_bounds__(128, 6) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0, MgSpecial sp) {
   MF_PDL_PROLOGUE
   switch (blockIdx.z) {       // the colour selects compile-time positions in the offset table
-    case 0: mgResidualItem<IS3D, HALF, 0>(L, O, lz0); break;
-    case 1: mgResidualItem<IS3D, HALF, 1>(L, O, lz0); break;
-    case 2: mgResidualItem<IS3D, HALF, 2>(L, O, lz0); break;
-    case 3: mgResidualItem<IS3D, HALF, 3>(L, O, lz0); break;
-    case 4: if (IS3D) mgResidualItem<IS3D, HALF, 4>(L, O, lz0); break;
-    case 5: if (IS3D) mgResidualItem<IS3D, HALF, 5>(L, O, lz0); break;
-    case 6: if (IS3D) mgResidualItem<IS3D, HALF, 6>(L, O, lz0); break;
-    default: if (IS3D) mgResidualItem<IS3D, HALF, 7>(L, O, lz0); break;
+    case 0: mgResidualItem<IS3D, HM, 0>(L, O, lz0, sp); break;
+    case 1: mgResidualItem<IS3D, HM, 1>(L, O, lz0, sp); break;
+    case 2: mgResidualItem<IS3D, HM, 2>(L, O, lz0, sp); break;
+    case 3: mgResidualItem<IS3D, HM, 3>(L, O, lz0, sp); break;
+    case 4: if (IS3D) mgResidualItem<IS3D, HM, 4>(L, O, lz0, sp); break;
+    case 5: if (IS3D) mgResidualItem<IS3D, HM, 5>(L, O, lz0, sp); break;
+    case 6: if (IS3D) mgResidualItem<IS3D, HM, 6>(L, O, lz0, sp); break;
+    default: if (IS3D) mgResidualItem<IS3D, HM, 7>(L, O, lz0, sp); break;
   }
 }
 
@@ -438,7 +477,7 @@ __global__ void __launch_bounds__(256) k_mg_interp_add(LvlD F, LvlD C, int z0, i
 template <int CF>
 __device__ __forceinline__ void mgInterpAddBlockedItem(const LvlD& F, const LvlD& C, int lz0) {
   BlkPos q;
-  if (!mgBlockThread(F, CF, lz0, blockIdx.x * blockDim.x + threadIdx.x, q)) return;
+  if (!mgBlockThread(F, CF, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, gridDim.y, blockIdx.y)) return;
   constexpr int cx = CF & 1, cy = (CF >> 1) & 1, cz = (CF >> 2) & 1;
   const bool off = mgRowZero(F, q.p);
   const float xo = F.x[q.p];
@@ -572,7 +611,8 @@ __global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* 
 // entry that binary16 cannot hold -- in practice the rows around the pinned cell of zeroPressureFixing, whose level-0 equation is
 // scaled by 1e-6.  Its binary16 diagonal becomes NaN: the sweeps then take that vertex' coefficients from the float planes
 // (mgStencilSubFloat), everybody else streams the binary16 copy.  *count = number of special vertices.
-__global__ void __launch_bounds__(256) k_mg_mark_special(LvlD L, __half* __restrict__ Ah, const float* __restrict__ rowBad, int* __restrict__ count, int p0, int p1) {
+__global__ void __launch_bounds__(256) k_mg_mark_special(LvlD L, __half* __restrict__ Ah, const float* __restrict__ rowBad, int* __restrict__ count,
+                                                         int* __restrict__ colourCount, int* __restrict__ colourList, int p0, int p1) {
   const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= p1) return;
   int x, y, z;
@@ -581,7 +621,13 @@ __global__ void __launch_bounds__(256) k_mg_mark_special(LvlD L, __half* __restr
   for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) special |= rowBad[mgIdx(L, x + dx, y + dy, z + dz)] != 0.f;
   // (inactive vertices keep their exact all-zero row: the entries that couple a neighbour to them are zero as well, and a NaN
   //  diagonal would make mgRowZero() take them for active)
-  if (special && L.A[p] != 0.f) { Ah[p] = __ushort_as_half((unsigned short)0x7e00); atomicAdd(count, 1); }
+  if (special && L.A[p] != 0.f) {
+    Ah[p] = __ushort_as_half((unsigned short)0x7e00); atomicAdd(count, 1);
+    // per-colour list for the sweeps (vertices of one colour are independent of each other: the order in the list is free)
+    const int c = (x & 1) | ((y & 1) << 1) | ((z & 1) << 2);
+    const int i = atomicAdd(colourCount + c, 1);
+    if (i < MG_SPECIAL_CAP) colourList[c * MG_SPECIAL_CAP + i] = p;
+  }
 }
 __global__ void __launch_bounds__(256) k_mg_zero_range(float* __restrict__ a, int p0, int p1) {
   const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;

@@ -17,6 +17,7 @@
 // rows with x = +0, which leaves the guarded sums of the reference bit-unchanged.
 #pragma once
 #include "mg_kernels.cuh"
+#include "multigrid.h"
 
 namespace mf {
 
@@ -95,8 +96,8 @@ __device__ __forceinline__ float wvOffdiagAt(const L0Code& op, const L0Code::Row
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float trivialScale, int firstColor, int U0, int U1, WvSched S,
                                                   int z0, int z1, int cz0, int cz1, int foldFirst) {
   MF_PDL_PROLOGUE
-  __shared__ float xs[4][WV_RY][WV_RX];
-  __shared__ float rs[WV_RY][WV_RX];
+  __shared__ __align__(16) float xs[4][WV_RY][WV_RX];     // read and written as float2
+  __shared__ __align__(16) float rs[WV_RY][WV_RX];
   const L0Code op(F, trivialScale);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int tileX, tileY, c0, c1;
@@ -241,11 +242,26 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float tri
 // xin is the down leg's x (another array than xout: the halo planes of a neighbour chunk must keep their old values).
 constexpr int WU_CX = WV_RX / 2 + 1, WU_CY = WV_RY / 2 + 1;        // coarse vertices under the region: 33 x 17
 
+// sigmaNew = xout . b, beta = sigmaNew / sigma (FinBeta of cg.cuh on the caller's scalars)
+struct WvFinBeta {
+  MgDotBeta d;
+  __device__ void operator()(double* r) const {
+    if (*d.done) return;
+    const float sigmaNew = (float)r[0];
+    *d.beta = sigmaNew / *d.sigma;
+    *d.sigma = sigmaNew;
+    if (!(*d.resNorm < 1e35f)) { *d.diverged = 1; *d.done = 1; }
+  }
+};
+// DOT: the kernel also reduces sum (double)(xout * b) over the cells it stores -- the CG's next dot product (GridDotProduct,
+// conjugategrad.cpp:175: float products accumulated in double) -- while both factors are in registers
+template <bool DOT>
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_up0w(LvlD F, LvlD C, float trivialScale, int firstColor, const float* __restrict__ xin,
-                                                 float* __restrict__ xout, int U0, int U1, WvSched S, int z0, int z1) {
+                                                 float* __restrict__ xout, int U0, int U1, WvSched S, int z0, int z1, WvFinBeta fin, RedCtx ctx) {
   MF_PDL_PROLOGUE
-  __shared__ float xs[4][WV_RY][WV_RX];
-  __shared__ float cs[2][WU_CY][WU_CX];
+  double dotAcc[1] = { 0.0 };
+  __shared__ __align__(16) float xs[4][WV_RY][WV_RX];     // read and written as float2
+  __shared__ __align__(16) float cs[2][WU_CY][WU_CX];
   const L0Code op(F, trivialScale);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int tileX, tileY, c0, c1;
@@ -355,13 +371,21 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_up0w(LvlD F, LvlD C, float triv
           const float v = wvOffdiagAt(op, r, wvRhs(rowC[i], w), &xs[q & 3][ry][col], &xs[(q - 1) & 3][ry][col], &xs[(q + 1) & 3][ry][col]) / op.diag(r, 0);
           if (w) out.y = v; else out.x = v;
         }
-        if (storeQ && inX && gy < F.sy) *reinterpret_cast<float2*>(xout + gx0 + F.sx * (gy + F.sy * q)) = out;
+        if (storeQ && inX && gy < F.sy) {
+          *reinterpret_cast<float2*>(xout + gx0 + F.sx * (gy + F.sy * q)) = out;
+          if (DOT) { dotAcc[0] += (double)(out.x * rowC[i].b0); dotAcc[0] += (double)(out.y * rowC[i].b1); }
+        }
       }
       if (p < pEnd && ((p + 1) & 1)) loadCoarse((p + 2) >> 1);     // plane p+1 odd: it also needs coarse plane (p+2)/2
     }
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < WV_RPW; i++) { rowC[i] = rowB[i]; rowB[i] = rowA[i]; rowA[i] = rowN[i]; xinA[i] = xinN[i]; }
+  }
+  if (DOT) {
+    __shared__ double sh[32];
+    const int ops[1] = { 0 };
+    gridReduceK<1>(dotAcc, ops, ctx, sh, fin);
   }
 }
 

@@ -31,9 +31,13 @@ struct MgHierarchy {
   std::vector<MgOff8> offs;                  // blocked level l: stencil offset tables of the sweeps (buildOffsets)
   __half* half1; long long ash1;             // level 1 (3-D): storage for the binary16 operator (LvlD::Ah points here when used)
   int nspecial1;                             // level-1 vertices that keep the float planes (k_mg_mark_special)
+  int* special1;                             // job-wide: count[8], list[8][MG_SPECIAL_CAP] of those vertices by colour
+  int* special1Local;                        // this process' copy (the sweeps read it in every launch)
   // persistent kernels for the small levels (mg_tail.cuh): grid-barrier counter, its host-tracked value, time-out flag
   int tailCluster; unsigned* tailBar; unsigned tailBase; int* tailErrHost; int* tailErrDev; MgOff8* tailOffs;
   int tailFirst;            // first level swept by the tail kernels, or -1
+  // the last swept level + the coarsest level in one CTA (mg_bottom.cuh)
+  bool bottomOn; MgOff8* bottomOff; size_t bottomSmem; int bottomVec;
 };
 
 // ---- partition of a level over the ranks ----------------------------------------------------------------------
@@ -107,7 +111,10 @@ __device__ __forceinline__ void cgBlockSum(double a, double b, double (*sh)[32],
 }
 
 template <bool LEVEL0>
-__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[32], double* out, double* vecBase) {
+__device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float accuracy, double (*sh)[32], double* out, double* vecBase,
+                                           bool fromReg = false, float bReg = 0.f, float* xShared = nullptr) {
+  // fromReg (mg_bottom.cuh): the right-hand side arrives in a register, the initial guess is 0, and the solution also goes to
+  // xShared (the level's x in shared memory) -- what the restriction kernel would have left in L.b / L.x
   constexpr int NS = LEVEL0 ? 7 : 27;
   const int v = threadIdx.x;
   const bool in = v < L.n;
@@ -183,11 +190,11 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
     return sum;
   };
   const double invDiag = active ? 1.0 / (double)L.A[p] : 0.0;
-  double x = in ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
+  double x = (in && !fromReg) ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
   vec[v] = x;
   __syncthreads();
   if (active) {
-    r = (double)L.b[p] - applyA();
+    r = (double)(fromReg ? bReg : L.b[p]) - applyA();
     z = r * invDiag;
     pp = z;
   }
@@ -228,8 +235,11 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
 #ifdef MF_CG_DBG
   if (threadIdx.x == 0) printf("cgdbg it %d publish %lld row %lld sum1 %lld upd %lld sum2 %lld total %lld\n", nit, tc[0] / nit, tc[1] / nit, tc[2] / nit, tc[3] / nit, tc[4] / nit, clock64() - tstart);
 #endif
-  if (in) L.x[p] = (float)x;
+  if (in) { L.x[p] = (float)x; if (xShared) xShared[p] = (float)x; }
 }
+} // namespace mf
+#include "mg_bottom.cuh"
+namespace mf {
 // MAXT = 768: up to 85 registers per thread; with 1024 threads (64 registers) part of the state spills to local memory
 template <bool LEVEL0, int MAXT>
 __global__ void __launch_bounds__(MAXT) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
@@ -242,6 +252,7 @@ __global__ void __launch_bounds__(MAXT) k_mg_coarse_cg(LvlD L, MgDims D, float a
 
 // ---- host side ----------------------------------------------------------------------------------------------
 static void planTail(MgHierarchy* mg);
+static void planBottom(MgHierarchy* mg);
 static void buildPaths(MgHierarchy* mg) {
   // restatement of the path enumeration in GridMg::GridMg (multigrid.cpp:286-318)
   struct P { int N[3], U[3], W[3]; int sc, sf; float rw, iw; bool inU; };
@@ -341,8 +352,9 @@ MgHierarchy* mg_create(Solver* s) {
   MgHierarchy* mg = new MgHierarchy();
   mg->s = s; mg->code0 = nullptr; mg->useCode = false; mg->pendingSolo = false; mg->aSet = false; mg->hasTrivial = false; mg->nonZeroStencilSum = false;
   mg->coarsestAcc = 1E-8f; mg->trivialScale = 1E-6f; mg->pre = 1; mg->post = 1; mg->dPaths = nullptr; mg->npaths = 0; mg->usedFallback = 0;
-  mg->half1 = nullptr; mg->ash1 = 0; mg->nspecial1 = 0;
+  mg->half1 = nullptr; mg->ash1 = 0; mg->nspecial1 = 0; mg->special1 = nullptr; mg->special1Local = nullptr;
   mg->tailCluster = 0; mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
+  mg->bottomOn = false; mg->bottomOff = nullptr; mg->bottomSmem = 0; mg->bottomVec = 0;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
   mg->D.zmin = is3D ? -1 : 0; mg->D.zmax = is3D ? 1 : 0;
@@ -391,6 +403,8 @@ MgHierarchy* mg_create(Solver* s) {
       if (l == 1 && is3D && !getenv("MF_MG_NOHALF")) {
         mg->ash1 = planeStride(s, L.na, sizeof(__half));
         mg->half1 = (__half*)s->galloc(sizeof(__half) * (size_t)L.na, mg->D.SS, sizeof(__half) * (size_t)mg->ash1, es.data(), 2);
+        mg->special1 = (int*)s->galloc(sizeof(int) * (8 + 8 * MG_SPECIAL_CAP));
+        CUDA_CHECK(cudaMalloc(&mg->special1Local, sizeof(int) * (8 + 8 * MG_SPECIAL_CAP)));
       }
     }                                                      // level 0: A (float planes) or code0 are allocated by mg_set_a
     mg->lv.push_back(L);
@@ -421,9 +435,12 @@ void mg_destroy(MgHierarchy* mg) {
   }
   if (mg->code0) mg->s->gfree(mg->code0);
   if (mg->half1) mg->s->gfree(mg->half1);
+  if (mg->special1) mg->s->gfree(mg->special1);
+  if (mg->special1Local) cudaFree(mg->special1Local);
   mg->s->gfree(mg->dFlags); cudaFree(mg->dPaths);
   if (mg->tailBar) cudaFree(mg->tailBar);
   if (mg->tailOffs) cudaFree(mg->tailOffs);
+  if (mg->bottomOff) cudaFree(mg->bottomOff);
   if (mg->tailErrHost) cudaFreeHost(mg->tailErrHost);
   delete mg;
 }
@@ -594,27 +611,31 @@ void mg_set_a(MgHierarchy* mg, const float* A0, const float* Ai, const float* Aj
       // vector serves as scratch for the per-row flags and is zeroed again afterwards (it must be 0 at padding / inactive entries).
       int* nspecial = mg->dFlags + 6;
       s->clearShared(nspecial, sizeof(int));
+      s->clearShared(mg->special1, sizeof(int) * 8);
       C.Ah = nullptr; C.ash = mg->ash1;
       MG_SETUP(mg, l, k_mg_pack_half, 256, C, mg->D, mg->half1, C.x);
       flushGroups(mg);
-      MG_SETUP(mg, l, k_mg_mark_special, 256, C, mg->half1, (const float*)C.x, nspecial);
+      MG_SETUP(mg, l, k_mg_mark_special, 256, C, mg->half1, (const float*)C.x, nspecial, mg->special1, mg->special1 + 8);
       flushGroups(mg);
       MG_SETUP(mg, l, k_mg_zero_range, 256, C.x);
       flushGroups(mg);
       CUDA_CHECK(cudaMemcpyAsync(s->hostInts + 6, nspecial, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+      CUDA_CHECK(cudaMemcpyAsync(s->hostInts + 7, mg->special1, sizeof(int) * 8, cudaMemcpyDeviceToHost, s->stream));
+      CUDA_CHECK(cudaMemcpyAsync(mg->special1Local, mg->special1, sizeof(int) * (8 + 8 * MG_SPECIAL_CAP), cudaMemcpyDeviceToDevice, s->stream));
       CUDA_CHECK(cudaStreamSynchronize(s->stream));
       mg->nspecial1 = s->hostInts[6];
-      // Default: binary16 only when the whole level converts exactly.  MF_MG_HALF_SPECIAL=1 also takes it with marked float rows
-      // (bit-identical, tests/test_kernels_gpu.py) -- measured on B200 at 256^3 it does not pay: the level-1 sweep takes 15.0 us
-      // instead of 12.7 us and the residual 64 us instead of 51 us (27 two-byte loads and 27 conversions per vertex cost more
-      // than the halved operator traffic saves), 5.15 against 5.00 ms per step.
-      if (mg->nspecial1 == 0 || (mg->nspecial1 <= 65536 && getenv("MF_MG_HALF_SPECIAL"))) C.Ah = mg->half1;
+      bool fits = true;
+      for (int c = 0; c < 8; c++) fits = fits && s->hostInts[7 + c] <= MG_SPECIAL_CAP;
+      // binary16 when the whole level converts exactly, or when the rows that do not (around the pinned cell of zeroPressureFixing)
+      // fit the per-colour lists the sweeps take from the float planes (MF_MG_HALF_EXACT_ONLY=1: only the former)
+      if (mg->nspecial1 == 0 || (fits && !getenv("MF_MG_HALF_EXACT_ONLY"))) C.Ah = mg->half1;
     }
     buildOffsets(mg, l);
   }
   MF_LAUNCH_CHECK();
   mg->aSet = true;
   planTail(mg);
+  planBottom(mg);
 }
 
 // ---- V-cycle launches: every group = the same kernel on every local rank's z range of the level, then the barrier ----
@@ -653,9 +674,11 @@ static void smoothGS(MgHierarchy* mg, int l, bool reversed, bool xzero, bool fir
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
       const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2), 128), lz1 - lz0);
-      if (L.Ah)            { MF_LAUNCH_PDL(s, (k_mg_smooth<true, true>), gr, 128, L, o, color, lz0); }
-      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_smooth<true, false>), gr, 128, L, o, color, lz0); }
-      else                 { MF_LAUNCH_PDL(s, (k_mg_smooth<false, false>), gr, 128, L, o, color, lz0); }
+      const MgSpecial sp = { mg->special1Local, mg->special1Local + 8 };
+      if (L.Ah && mg->nspecial1) { MF_LAUNCH_PDL(s, (k_mg_smooth<true, MG_FMT_HALF_LISTS>), dim3(gr.x, gr.y + 1), 128, L, o, color, lz0, sp); }
+      else if (L.Ah)       { MF_LAUNCH_PDL(s, (k_mg_smooth<true, MG_FMT_HALF>), gr, 128, L, o, color, lz0, sp); }
+      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_smooth<true, MG_FMT_FLOAT>), gr, 128, L, o, color, lz0, sp); }
+      else                 { MF_LAUNCH_PDL(s, (k_mg_smooth<false, MG_FMT_FLOAT>), gr, 128, L, o, color, lz0, sp); }
     }
     endGroup(mg, solo);
   }
@@ -677,9 +700,11 @@ static void residual(MgHierarchy* mg, int l) {
       if (lz1 <= lz0) continue;
       const dim3 gr(cdiv((long long)(L.PX - 2) * (L.PY - 2), 128), lz1 - lz0, L.NC);
       const MgOff8& O = mg->offs[l];
-      if (L.Ah)            { MF_LAUNCH_PDL(s, (k_mg_residual<true, true>), gr, 128, L, O, lz0); }
-      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_residual<true, false>), gr, 128, L, O, lz0); }
-      else                 { MF_LAUNCH_PDL(s, (k_mg_residual<false, false>), gr, 128, L, O, lz0); }
+      const MgSpecial sp = { mg->special1Local, mg->special1Local + 8 };
+      if (L.Ah && mg->nspecial1) { MF_LAUNCH_PDL(s, (k_mg_residual<true, MG_FMT_HALF_LISTS>), dim3(gr.x, gr.y + 1, gr.z), 128, L, O, lz0, sp); }
+      else if (L.Ah)       { MF_LAUNCH_PDL(s, (k_mg_residual<true, MG_FMT_HALF>), gr, 128, L, O, lz0, sp); }
+      else if (mg->D.is3D) { MF_LAUNCH_PDL(s, (k_mg_residual<true, MG_FMT_FLOAT>), gr, 128, L, O, lz0, sp); }
+      else                 { MF_LAUNCH_PDL(s, (k_mg_residual<false, MG_FMT_FLOAT>), gr, 128, L, O, lz0, sp); }
     }
   }
   endGroup(mg, solo);
@@ -797,20 +822,35 @@ static void waveDown0(MgHierarchy* mg, bool fold) {
   }
   endGroup(mg, false);
 }
-static void waveUp0(MgHierarchy* mg, float* dst) {
+// dot: also reduce dst . rhs and update the CG scalars (MgDotBeta); false when that is not possible here (a rank without
+// planes, more CTAs than the reduction holds partials for)
+static bool waveUp0(MgHierarchy* mg, float* dst, const MgDotBeta* dot) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[0]; LvlD& C = mg->lv[1];
   s->profTag = 0;
+  const int tx = (int)cdiv(F.sx, WV_TX), ty = (int)cdiv(F.sy, WU_TY);
+  bool withDot = dot != nullptr && !getenv("MF_MG_NODOT");
+  for (int r = 0; r < s->nranks && withDot; r++) {
+    int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
+    int total = 0;
+    if (z1 > z0) waveSched(s, tx, ty, z1 - (z0 & ~1), total);
+    if (z1 <= z0 || total > RED_MAX_BLOCKS) withDot = false;
+  }
   beginGroup(mg, false);
+  WvFinBeta fin; memset(&fin, 0, sizeof(fin));
+  if (withDot) fin.d = *dot;
   MF_RANKS(s, r) {
     int z0, z1; lvlPlanes(mg, 0, r, z0, z1);
     if (z1 <= z0) continue;
     const int U0 = z0 & ~1, U1 = z1;
-    const int tx = (int)cdiv(F.sx, WV_TX), ty = (int)cdiv(F.sy, WU_TY);
     int total; const WvSched S = waveSched(s, tx, ty, U1 - U0, total);
-    MF_LAUNCH_PDL(s, k_mg_up0w, total, WV_NT, F, C, mg->trivialScale, 1, (const float*)F.r, dst, U0, U1, S, z0, z1);
+    if (withDot) { MF_LAUNCH_PDL(s, k_mg_up0w<true>, total, WV_NT, F, C, mg->trivialScale, 1, (const float*)F.r, dst, U0, U1, S, z0, z1, fin, redCtx(s, r)); }
+    else         { MF_LAUNCH_PDL(s, k_mg_up0w<false>, total, WV_NT, F, C, mg->trivialScale, 1, (const float*)F.r, dst, U0, U1, S, z0, z1, fin, redCtx(s, r)); }
   }
-  endGroup(mg, false);
+  // several ranks: the cross-rank barrier that ends the group is the one in front of the combining kernel
+  if (withDot && s->multi()) { redFinish<1>(s, RedOps<1>{ { 0 } }, fin); mg->pendingSolo = false; }
+  else endGroup(mg, false);
+  return withDot;
 }
 
 // ---- small levels in two persistent kernels (mg_tail.cuh) ---------------------------------------------------------------------
@@ -878,6 +918,44 @@ static void planTail(MgHierarchy* mg) {
   CUDA_CHECK(cudaStreamSynchronize(s->stream));
   mg->tailFirst = tf;
 }
+// ---- the last swept level and the coarsest level in one CTA (mg_bottom.cuh) ----------------------------------------------------
+static void planBottom(MgHierarchy* mg) {
+  Solver* s = mg->s;
+  mg->bottomOn = false;
+  const int maxLevel = (int)mg->lv.size() - 1;
+  // opt-in (MF_MG_BOTTOM=1): measured at 256^3 (17^3 + 9^3) the one launch takes 156 us against 124 us for the 18 programmatic
+  // dependent launches (~2.2 us each) + the CG kernel (85 us) it replaces, 5.13 vs 5.00 ms per step: 24 warps x ~300 instructions
+  // per colour phase are ~1 us of ONE SM's issue slots, the residual eight times that -- the level is too much work for one SM and
+  // too little for the launches to matter.  Kept for the parity test.
+  if (!mg->D.is3D || maxLevel < 2 || !getenv("MF_MG_BOTTOM") || getenv("MF_MG_NOBOTTOM") || mg->tailFirst >= 0) return;
+  const LvlD& L = mg->lv[maxLevel - 1]; const LvlD& B = mg->lv[maxLevel];
+  const long long nt = (long long)(L.PX - 2) * (L.PY - 2) * (L.PZ - 2);
+  if (!L.perm || !B.perm || L.Ah || L.NC != 8 || nt > MG_BOTTOM_THREADS || B.n > MG_BOTTOM_THREADS) return;
+  if (s->multi() && !lvlSolo(mg, maxLevel - 1)) return;
+  const int vecDoubles = MG_BOTTOM_THREADS + 2 * (B.sx * B.sy + B.sx + 1);
+  const size_t smem = mgBottomSmem(L.na, B.na, vecDoubles);
+  if (smem > 200 * 1024) return;
+  CUDA_CHECK(cudaFuncSetAttribute(k_mg_bottom, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (!mg->bottomOff) CUDA_CHECK(cudaMalloc(&mg->bottomOff, sizeof(MgOff8)));
+  // (stream-ordered behind the kernels of an earlier hierarchy that may still read the table)
+  CUDA_CHECK(cudaMemcpyAsync(mg->bottomOff, &mg->offs[maxLevel - 1], sizeof(MgOff8), cudaMemcpyHostToDevice, s->stream));
+  CUDA_CHECK(cudaStreamSynchronize(s->stream));
+  mg->bottomSmem = smem; mg->bottomVec = vecDoubles; mg->bottomOn = true;
+}
+static void bottomLeg(MgHierarchy* mg, bool fold) {
+  Solver* s = mg->s;
+  const int maxLevel = (int)mg->lv.size() - 1;
+  const bool solo = s->multi();
+  s->profTag = maxLevel - 1;
+  beginGroup(mg, solo);
+  if (s->rankBegin == 0) {
+    BottomArgs T;
+    T.L = mg->lv[maxLevel - 1]; T.B = mg->lv[maxLevel]; T.D = mg->D; T.off = mg->bottomOff; T.accuracy = mg->coarsestAcc; T.fold = fold ? 1 : 0;
+    T.nt = (T.L.PX - 2) * (T.L.PY - 2) * (T.L.PZ - 2); T.vecDoubles = mg->bottomVec;
+    MF_LAUNCH_PDL_SMEM(s, mg->bottomSmem, k_mg_bottom, 1, MG_BOTTOM_THREADS, T);
+  }
+  endGroup(mg, solo);
+}
 void mg_check_errors(const MgHierarchy* mg) {
   mfAssert(!(mg && mg->tailErrHost && *mg->tailErrHost), "GridMg: a grid barrier of the small-level kernel timed out");
 }
@@ -926,7 +1004,8 @@ static void tailLeg(MgHierarchy* mg, bool down, bool fold) {
 }
 
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
-void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
+bool mg_apply(MgHierarchy* mg, float* dst, const float* rhs, const MgDotBeta* dot) {
+  bool dotDone = false;
   Solver* s = mg->s;
   mfAssert(mg->aSet, "GridMg::setRhs Error: A has not been set.");
   mg_check_errors(mg);
@@ -960,16 +1039,23 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   // ~256 us for the separate PDL launches at 256^3; a thread-block cluster of 8 x 512 threads walking all phases of a 33^3 or
   // 17^3 level with cluster barriers, 5-9 us per phase against ~4.4 us per dependent launch -- too few threads in flight for
   // the latency of a 41-load stencil item)
-  const int lb = maxLevel;
+  // the last swept level and the coarsest one: one CTA with the level in shared memory (mg_bottom.cuh)
+  const bool bottom = mg->bottomOn && mg->pre == 1 && mg->post == 1 && maxLevel - 1 >= (fused0 ? 1 : 0) && !getenv("MF_MG_UNFUSED");
+  const int lb = bottom ? maxLevel - 1 : maxLevel;
   // levels tail .. maxLevel-1: both legs as one persistent kernel each (mg_tail.cuh)
   const int tail = (mg->tailFirst >= 1 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_NOTAIL") && !getenv("MF_MG_UNFUSED")) ? mg->tailFirst : -1;
+  // development (tools/vcycle_time.py --levels): MF_MG_DEVSKIP=l leaves out every level >= l -- WRONG results, per-level timing only
+  const int devSkip = getenv("MF_MG_DEVSKIP") ? atoi(getenv("MF_MG_DEVSKIP")) : 1000;
   for (int l = fused0 ? 1 : 0; l < lb; l++) {
+    if (l >= devSkip) break;
     if (l == tail) { tailLeg(mg, true, foldTo(l)); break; }
     for (int i = 0; i < mg->pre; i++) smoothGS(mg, l, false, l == 0 && i == 0, i == 0 && foldTo(l));
     residual(mg, l);
     restrictTo(mg, l, foldTo(l + 1));
   }
-  {
+  if (devSkip <= maxLevel) {}
+  else if (bottom) bottomLeg(mg, foldTo(lb));
+  else {
     const bool solo = s->multi();        // the bottom levels are always handled by rank 0
     beginGroup(mg, solo);
     s->profTag = lb;
@@ -985,18 +1071,20 @@ void mg_apply(MgHierarchy* mg, float* dst, const float* rhs) {
   }
   if (tail >= 0) tailLeg(mg, false, false);
   for (int l = (tail >= 0 ? tail : lb) - 1; l >= (fused0 ? 1 : 0); l--) {
+    if (l >= devSkip) continue;
     interpAdd(mg, l);
     for (int i = 0; i < mg->post; i++) smoothGS(mg, l, true, false);
   }
   if (fused0) {
     L0.r = r0keep; L0.x = dst;
-    if (wave) waveUp0(mg, dst);
+    if (wave) dotDone = waveUp0(mg, dst, dot);
     else if (mg->useCode) fusedUp0<L0Code>(mg, dst); else fusedUp0<L0Float>(mg, dst);
   }
   flushGroups(mg);
   s->profTag = -1;
   // the trailing calcResidual(0)/calcResidualNorm(0) of doVCycle only feed its return value, which the CG driver
   // ignores (conjugategrad.cpp:162-167) -- skipped.
+  return dotDone;
 }
 
 void mg_download_level(MgHierarchy* mg, int l, unsigned char* type, float* A) {

@@ -90,7 +90,9 @@ struct CgDriver {
   float* P; MgHierarchy* mg;
   bool v4 = false;      // nx % 4 == 0: every slab starts and ends on a 16-byte boundary -> vectorised kernels
   CgState host;
-  void applyPrecond(bool init) {
+  // returns true when the preconditioner's last kernel also reduced tmp . residual and set sigma / beta (mg_apply with MgDotBeta)
+  bool applyPrecond(bool init, bool wantBeta = false) {
+    bool betaDone = false;
     if (pcMethod == 1) {
       const dim3 b = ijkBlockOf(s);
       MF_RANKS(s, r) { const Geo g = geo(s, r); dim3 gr(cdiv((s->nx + 1) / 2, b.x), cdiv(s->ny, b.y), cdiv(g.k1 - g.k0, b.z));
@@ -100,7 +102,8 @@ struct CgDriver {
                        MF_LAUNCH(s, k_rbic_red, gr, b, g, P, v.residual, v.tmp, v.Ai, v.Aj, v.Ak, st); }
       s->rankSync();
     } else if (pcMethod == 2) {
-      mg_apply(mg, v.tmp, v.residual);
+      const MgDotBeta d = { &st->sigma, &st->beta, &st->resNorm, &st->done, &st->diverged };
+      betaDone = mg_apply(mg, v.tmp, v.residual, wantBeta ? &d : nullptr);
     } else if (pcMethod == 3) {
       if (v.code && s->is3D && !std::getenv("MF_MIC_GENERIC")) {
         micSweepCode(s, 1, v.code, P, v.residual, v.tmp, st);
@@ -111,6 +114,7 @@ struct CgDriver {
       }
     }
     (void)init;
+    return betaDone;
   }
   void fetch() {
     s->readSmall(s->hostInts, st, (int)sizeof(CgState));
@@ -148,9 +152,10 @@ struct CgDriver {
   }
   // second half: tmp = M^-1 residual, sigmaNew, beta, new search direction (:262-295)
   template <bool V4> void tailT() {
-    applyPrecond(false);
-    MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta<V4>, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
-    redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
+    if (!applyPrecond(false, true)) {
+      MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_dot_beta<V4>, redBlocks(s, sp.n), 256, sp.n, v.tmp + sp.off, v.residual + sp.off, st, redCtx(s, r)); }
+      redFinish<1>(s, RedOps<1>{ { 0 } }, FinBeta{ st });
+    }
     MF_RANKS(s, r) { const Span sp = span(s, r); MF_LAUNCH_PDL(s, k_cg_search<V4>, ewBlocks(s, sp.n / (V4 ? 4 : 1)), 256, sp.n, v.search + sp.off, v.tmp + sp.off, st); }
     s->rankSync();
   }

@@ -129,13 +129,14 @@ def test_rowcode_spmv_zmarch_matches_flat(size, zc, monkeypatch):
 @pytest.mark.gpu
 @pytest.mark.parametrize("size", [(32, 24, 16), (64, 48, 40)])
 def test_half_level1_with_float_rows_matches_float(size, monkeypatch):
-    """MF_MG_HALF_SPECIAL=1: the level-1 operator in binary16 with the rows binary16 cannot hold (around the pinned cell of
-    zeroPressureFixing) kept in float through a NaN-diagonal marker -- same pressure bit for bit, same iteration count, as the
-    all-float level, with the wavefront legs and with the per-colour sweeps"""
+    """the level-1 operator in binary16 with the rows binary16 cannot hold (around the pinned cell of zeroPressureFixing) kept in
+    float -- NaN-diagonal marker + per-colour vertex lists swept by one extra CTA row of each launch -- against the all-float
+    level (MF_MG_HALF_EXACT_ONLY=1): same pressure bit for bit, same iteration count, with the wavefront legs and with the
+    per-colour sweeps, on one rank and on emulated z-slab ranks"""
     from mantaflow_b200 import manta
     res = []
-    for env in ({}, {"MF_MG_HALF_SPECIAL": "1"}, {"MF_MG_HALF_SPECIAL": "1", "MF_MG_NOWAVE": "1"}):
-        for k in ("MF_MG_HALF_SPECIAL", "MF_MG_NOWAVE"):
+    for env in ({"MF_MG_HALF_EXACT_ONLY": "1"}, {}, {"MF_MG_NOWAVE": "1"}, {"MF_MG_UNFUSED": "1"}):
+        for k in ("MF_MG_HALF_EXACT_ONLY", "MF_MG_NOWAVE", "MF_MG_UNFUSED"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -146,10 +147,80 @@ def test_half_level1_with_float_rows_matches_float(size, monkeypatch):
         vel.from_numpy(rs2.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5))
         manta.solvePressure(flags=flags, vel=vel, pressure=p, cgAccuracy=1e-6, preconditioner=manta.PcMGStatic, zeroPressureFixing=True)
         res.append((p.to_numpy(), manta.getSolveInfo()["iterations"]))
+        fmt = Ct.c_int(0)
+        from mantaflow_b200._lib import lib, check
+        check(lib().mf_mg_level_format(s._h, 1, Ct.byref(fmt)))
+        assert fmt.value == (4 if "MF_MG_HALF_EXACT_ONLY" in env else 2)
         manta.releaseMG(s)
     for r in res[1:]:
         assert r[1] == res[0][1]
         assert np.array_equal(r[0].view(np.int32), res[0][0].view(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nranks", [2, 3])
+def test_half_level1_lists_partitioned(nranks, monkeypatch):
+    """the same on a z-slab partitioned level 1 (>= 2^20 vertices, emulated ranks): every rank sweeps the listed float-row
+    vertices of its own z pairs; against the all-float level on one rank"""
+    from mantaflow_b200 import manta
+    size = (256, 128, 256)
+    rs2 = np.random.RandomState(9)
+    v0 = rs2.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5)
+
+    def run(comm):
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3, comm=comm)
+        flags = s.create(manta.FlagGrid); flags.initDomain(); flags.fillGrid()
+        vel = s.create(manta.MACGrid); p = s.create(manta.RealGrid)
+        vel.from_numpy(v0)
+        manta.solvePressure(flags=flags, vel=vel, pressure=p, cgAccuracy=1e-4, preconditioner=manta.PcMGStatic, zeroPressureFixing=True)
+        out = (p.to_numpy(), manta.getSolveInfo()["iterations"])
+        manta.releaseMG(s)
+        return out
+
+    monkeypatch.setenv("MF_MG_HALF_EXACT_ONLY", "1")
+    ref = run(None)
+    monkeypatch.delenv("MF_MG_HALF_EXACT_ONLY")
+    comm = manta.Comm.emulated(nranks)
+    try:
+        got = run(comm)
+    finally:
+        comm.destroy()
+    assert got[1] == ref[1]
+    assert np.array_equal(got[0].view(np.int32), ref[0].view(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size,nranks", [((64, 48, 40), 1), ((128, 96, 80), 1), ((256, 128, 256), 1), ((256, 128, 256), 2)])
+def test_fused_dot_beta_matches_separate(size, nranks, monkeypatch):
+    """sigmaNew = z . r reduced by the level-0 up leg of the V-cycle while it stores z (k_mg_up0w<true>) against the separate
+    k_cg_dot_beta pass (MF_MG_NODOT=1): same iteration count and pressure, one launch less per PCG iteration"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib
+    rs2 = np.random.RandomState(11)
+    v0 = rs2.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5)
+    lib().mf_solver_launch_count.restype = Ct.c_longlong
+    res = []
+    for env in ({"MF_MG_NODOT": "1"}, {}):
+        monkeypatch.delenv("MF_MG_NODOT", raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        comm = manta.Comm.emulated(nranks) if nranks > 1 else None
+        try:
+            s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3, comm=comm)
+            flags = s.create(manta.FlagGrid); flags.initDomain(); flags.fillGrid()
+            vel = s.create(manta.MACGrid); p = s.create(manta.RealGrid)
+            vel.from_numpy(v0)
+            n0 = lib().mf_solver_launch_count(s._h)
+            manta.solvePressure(flags=flags, vel=vel, pressure=p, cgAccuracy=1e-5, preconditioner=manta.PcMGStatic, zeroPressureFixing=True)
+            res.append((p.to_numpy(), manta.getSolveInfo()["iterations"], lib().mf_solver_launch_count(s._h) - n0))
+            manta.releaseMG(s)
+            del flags, vel, p, s
+        finally:
+            if comm is not None:
+                comm.destroy()
+    assert res[0][1] == res[1][1] and res[0][1] >= 3
+    assert np.array_equal(res[0][0].view(np.int32), res[1][0].view(np.int32))
+    assert res[1][2] < res[0][2], "the fused reduction must save launches"
 
 
 @pytest.mark.gpu
@@ -242,6 +313,41 @@ def test_vcycle_wavefront_matches_unfused(size, monkeypatch):
     assert np.isfinite(outs[0]).all() and np.abs(outs[2]).max() > 0
     assert np.array_equal(outs[1].view(np.int32), outs[2].view(np.int32)), "tiled fused legs differ from the plain sweeps"
     assert np.array_equal(outs[0].view(np.int32), outs[2].view(np.int32)), "wavefront legs differ from the plain sweeps"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size", [(64, 50, 37), (128, 96, 80), (120, 31, 18), (256, 256, 256)])
+def test_vcycle_bottom_matches_unfused(size, monkeypatch):
+    """the last swept level + the coarsest-level CG in one CTA out of shared memory (mg_bottom.cuh, opt-in MF_MG_BOTTOM=1) against
+    the per-phase launches: bit-identical V-cycle, 18 launches fewer (7 + 8 colour sweeps, residual, restriction, interpolation, CG -> 1)"""
+    from mantaflow_b200 import manta
+    from mantaflow_b200._lib import lib, check
+    rs = np.random.RandomState(5)
+    f = _flags(rs, size, 3)
+    f[f == EMPTY] = FLUID
+    nz, ny, nx = f.shape
+    f[nz // 2, ny // 2, nx // 2] = EMPTY
+    rhs = (rs.rand(*f.shape).astype(np.float32) - np.float32(0.5))
+    outs, launches = [], []
+    lib().mf_solver_launch_count.restype = Ct.c_longlong
+    for env in ({"MF_MG_BOTTOM": "1"}, {}):
+        monkeypatch.delenv("MF_MG_BOTTOM", raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        s = manta.Solver(name="s", gridSize=manta.vec3(*size), dim=3)
+        flags = s.create(manta.FlagGrid); flags.from_numpy(f)
+        A0, Ai, Aj, Ak, R, D = [s.create(manta.RealGrid) for _ in range(6)]
+        R.from_numpy(rhs)
+        check(lib().mf_make_laplace_matrix(flags._h, A0._h, Ai._h, Aj._h, Ak._h, None))
+        check(lib().mf_mg_vcycle(s._h, A0._h, Ai._h, Aj._h, Ak._h, R._h, D._h, 1e-7))     # builds the hierarchy
+        n0 = lib().mf_solver_launch_count(s._h)
+        check(lib().mf_mg_vcycle(s._h, None, None, None, None, R._h, D._h, 1e-7))          # re-applies it: launches of one V-cycle
+        launches.append(lib().mf_solver_launch_count(s._h) - n0)
+        outs.append(D.to_numpy())
+        manta.releaseMG(s)
+    assert np.isfinite(outs[0]).all() and np.abs(outs[0]).max() > 0
+    assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32)), "one-CTA bottom of the V-cycle differs from the per-phase launches"
+    assert launches[1] - launches[0] == 18, launches
 
 
 @pytest.mark.gpu

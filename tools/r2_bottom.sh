@@ -1,0 +1,14 @@
+#!/bin/bash
+# one-CTA bottom of the V-cycle (mg_bottom.cuh): parity tests, then the bench line with and without it
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_kernels_gpu.py -q -m gpu -p no:cacheprovider -x -k "vcycle or pressure_solve or gridcg" > gpurun_out/bottom_tests.log 2>&1; tail -4 gpurun_out/bottom_tests.log
+for v in new old; do
+if [ $v = old ]; then export MF_MG_NOBOTTOM=1; fi
+timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-strong1024 > gpurun_out/bench_bottom_$v.json 2> gpurun_out/bench_bottom.err; tail -c 300 gpurun_out/bench_bottom.err
+python - <<PY
+import json
+d = json.load(open("gpurun_out/bench_bottom_$v.json"))
+ks = {k["kernel"]: k for k in d["kernels"]}
+print("$v step %.3f ms" % d["ms_per_step"], {n: round(ks[n]["avg_us"], 1) for n in ks if "@L4" in n or "@L5" in n or "bottom" in n}, d["pcg_ms_per_iteration"]["ms_per_iteration"], d["pcg_iterations"][:5], d["gpu_launches"])
+PY
+done

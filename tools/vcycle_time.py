@@ -17,6 +17,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--size", type=int, default=256)
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--levels", action="store_true", help="per-level cost with programmatic dependent launches on: V-cycles that leave out every level >= l (MF_MG_DEVSKIP)")
     a = ap.parse_args()
     import torch
     from mantaflow_b200 import manta
@@ -41,6 +42,22 @@ def main():
     for _ in range(a.reps):
         cyc()
     s.sync(); torch.cuda.synchronize(); t1 = time.perf_counter()
+    if a.levels:
+        nl = Ct.c_int(0); fb = Ct.c_int(0)
+        check(lib().mf_mg_info(s._h, Ct.byref(nl), Ct.byref(fb)))
+        prev = None
+        for skip in list(range(1, nl.value + 1)) + [1000]:
+            os.environ["MF_MG_DEVSKIP"] = str(skip)
+            for _ in range(3):
+                cyc()
+            s.sync(); torch.cuda.synchronize(); t2 = time.perf_counter()
+            for _ in range(a.reps):
+                cyc()
+            s.sync(); torch.cuda.synchronize(); t3 = time.perf_counter()
+            us = (t3 - t2) / a.reps * 1e6
+            print("levels < %d: %.1f us%s" % (skip, us, "" if prev is None else "  (+%.1f)" % (us - prev)))
+            prev = us
+        os.environ.pop("MF_MG_DEVSKIP")
     b = Ct.c_int(0)
     check(lib().mf_mg_level_format(s._h, 1, Ct.byref(b)))
     print("size %d: %.1f us per V-cycle (incl. setRhs), level-1 operator %d bytes/entry" % (n, (t1 - t0) / a.reps * 1e6, b.value))
