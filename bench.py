@@ -53,6 +53,7 @@ ALGO_BYTES_PER_CELL = {
     "k_make_rhs_plain": 20.0,
     "k_flag_stats": 4.0,
     "k_make_laplace_code": 6.0,  # flags 4 + row code 2
+    "k_make_laplace_code_stats": 6.0,  # the same pass also counts the empty cells / finds the first fluid cell (zeroPressureFixing)
     "k_make_laplace": 22.0,    # flags 4 + 4 coefficient planes 16 + row code 2 (only when a preconditioner is (re)built)
     "k_cg_spmv_dot": 28.0,     # stored-A: flags 4 + src 4 + dst 4 + A 16
     "k_cg_spmv_dot_code": 10.0,  # 16-bit row code 2 + src 4 + dst 4
@@ -86,11 +87,13 @@ def mg_level_sizes(size):
 L2_BYTES = 126e6
 
 
-def algo_bytes(kernel, size_gpu, cells_gpu):
+def algo_bytes(kernel, size_gpu, cells_gpu, entry_bytes=None):
     """algorithmic bytes ONE launch of `kernel` moves and the roofline that bounds it.
     Multigrid kernels on the 27-point levels are tagged with their level ("k_mg_smooth@L2"): a colour sweep reads, per vertex of
     its colour, the 27 coefficients of the row, x of the 27 stencil points (perfect reuse: one x per vertex), b, and writes x;
-    a level whose operator + vectors fit the L2 never reaches HBM in steady state: bound "latency"."""
+    a level whose operator + vectors fit the L2 never reaches HBM in steady state: bound "latency".
+    entry_bytes: {level: bytes per stored operator entry} as the library reports them (mf_mg_level_format: 4 = float planes,
+    2 = binary16 planes, the format level 1 takes when its entries convert exactly or the exceptions fit the float-row lists)."""
     base, _, lv = kernel.partition("@L")
     if base in ALGO_BYTES_PER_CELL and (lv in ("", "0")):
         return ALGO_BYTES_PER_CELL[base] * cells_gpu, "hbm"
@@ -101,12 +104,13 @@ def algo_bytes(kernel, size_gpu, cells_gpu):
     if lv >= len(sizes):
         return None, None
     nv = sizes[lv][0] * sizes[lv][1] * sizes[lv][2]
-    level_bytes = nv * (14 * 4 + 3 * 4)
+    eb = (entry_bytes or {}).get(lv, 4)
+    level_bytes = nv * (14 * eb + 3 * 4)
     bound = "hbm" if level_bytes > L2_BYTES else "latency"
-    per_vertex = {"k_mg_smooth": (27 * 4 + 12) / 8.0,        # one of 8 colours per launch
-                  "k_mg_smooth_ml": (27 * 4 + 12) / 8.0,
-                  "k_mg_residual": 27 * 4 + 12, "k_mg_restrict": 4 + 0.5, "k_mg_interp_add": 8 + 0.5, "k_mg_interp_add_b": 8 + 0.5,
-                  "k_mg_level_sweep": 14 * 4 + 12}.get(base)
+    per_vertex = {"k_mg_smooth": (27 * eb + 12) / 8.0,        # one of 8 colours per launch
+                  "k_mg_smooth_ml": (27 * eb + 12) / 8.0,
+                  "k_mg_residual": 27 * eb + 12, "k_mg_restrict": 4 + 0.5, "k_mg_interp_add": 8 + 0.5, "k_mg_interp_add_b": 8 + 0.5,
+                  "k_mg_level_sweep": 14 * eb + 12}.get(base)
     if per_vertex is None:
         return None, None
     return per_vertex * nv, bound
@@ -522,12 +526,19 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md 6.65 TB/s)"
+        entry_bytes = {}
+        if a.precond == "mg":
+            nl, fb, fmt = C.c_int(0), C.c_int(0), C.c_int(0)
+            if L.mf_mg_info(s._h, C.byref(nl), C.byref(fb)) == 0:
+                for lv in range(1, nl.value):
+                    if L.mf_mg_level_format(s._h, lv, C.byref(fmt)) == 0:
+                        entry_bytes[lv] = fmt.value
         for line in buf.value.decode().splitlines():
             name, n, tot = line.split()
             n, tot = int(n), float(tot)
             e = {"kernel": name, "launches_per_step": n / a.profile_steps, "ms_per_step": tot / a.profile_steps,
                  "share_of_step": tot / prof_ms, "avg_us": 1e3 * tot / n}
-            nbytes, bound = algo_bytes(name, size_gpu, cells_gpu)
+            nbytes, bound = algo_bytes(name, size_gpu, cells_gpu, entry_bytes)
             if nbytes is not None:
                 e["algo_bytes_per_launch"] = nbytes
                 e["achieved_gbs"] = nbytes / (tot / n * 1e-3) / 1e9
@@ -551,6 +562,7 @@ def main():
             roofline = {"bound": top.get("bound", "latency"), "kernel": top["kernel"], "achieved": top.get("achieved_gbs"), "peak": peak, "unit": "GB/s",
                         "frac": top.get("frac_of_peak"), "traffic": traffic, "peak_source": peak_src,
                         "algo_bytes_per_launch": top.get("algo_bytes_per_launch"), "avg_launch_us": top["avg_us"],
+                        "operator_entry_bytes": entry_bytes.get(int(top["kernel"].partition("@L")[2])) if "@L" in top["kernel"] and top["kernel"].partition("@L")[2] != "0" else None,
                         "launches_per_step": top["launches_per_step"],
                         "share_of_step": top["share_of_step"], "timed": "CUDA events around every launch, %d extra steps after the timed region" % a.profile_steps,
                         "note": "the kernel with the largest share of the step; bound 'latency' = the level's operator and vectors are L2-resident, "

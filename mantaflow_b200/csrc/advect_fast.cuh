@@ -63,6 +63,23 @@ __global__ void __launch_bounds__(256) k_sl_f(Geo gg, CV3 vel, const float* __re
   dst[idx] = interpolF(src, g, (i + 0.5f) - cx * dt, (j + 0.5f) - cy * dt, (k + 0.5f) - cz * dt);
 }
 
+// MacCormackCorrect (advection.cpp:91,113): dst = fwd + strength * 0.5 * (old - bwd) -- `strength * 0.5` is a double, so the
+// reference evaluates float(double(fw) + s2 * double(old - bwd)).  When s2 is a power of two (strength 1: s2 = 0.5) the float
+// expression fw + s2f * t gives the same bits: s2f * t is exact, and the double sum is either exact (exponents at most 29 apart:
+// 24 + 29 bits fit 53) or its smaller term is below 2^-29 of the larger one, far inside half a float ulp, so both roundings end at
+// fw's neighbour-free value.  The only exception is a t so small that s2f * t underflows; that case keeps the double expression.
+// 2 float operations instead of 3 conversions + 2 double operations per component (the FP64 / conversion pipes are quarter rate).
+__device__ __forceinline__ float mcCorrect(float fw, float t, double s2, float s2f) {
+  if (s2f != 0.f && !(fabsf(t) < 1.0e-30f && t != 0.f)) return fw + s2f * t;
+  return (float)((double)fw + s2 * (double)t);
+}
+// s2 as a float when it is a power of two (exact scaling), else 0
+__device__ __forceinline__ float mcPow2Scale(double s2) {
+  const float f = (float)s2;
+  const int bits = __float_as_int(f);
+  return ((double)f == s2 && (bits & 0x007fffff) == 0 && (bits & 0x7f800000) != 0 && (bits & 0x7f800000) != 0x7f800000 && fabsf(f) > 1.0e-6f && fabsf(f) < 1.0e6f) ? f : 0.f;
+}
+
 // backward SL + MacCormackCorrect + MacCormackClamp fused (see k_mc_centered in advect.cu)
 template <int CM>
 __global__ void __launch_bounds__(256) k_mc_centered_f(Geo gg, const int* __restrict__ flags, CV3 vel, const float* __restrict__ orig,
@@ -70,6 +87,7 @@ __global__ void __launch_bounds__(256) k_mc_centered_f(Geo gg, const int* __rest
   IJK_FROM_BLOCK_F
   const bool fluid = (flags[idx] & MF_FLUID) != 0;
   const double s2 = (double)strength * 0.5;
+  const float s2f = mcPow2Scale(s2);
   if (border) {
     float d = 0.0f;
     if (fluid) d = (float)((double)0.0f + s2 * (double)(orig[idx] - 0.0f));
@@ -83,7 +101,7 @@ __global__ void __launch_bounds__(256) k_mc_centered_f(Geo gg, const int* __rest
   float dv = fw;
   if (fluid) {
     const float bw = interpolF(fwd, g, (i + 0.5f) + vx, (j + 0.5f) + vy, (k + 0.5f) + vz);     // p0 - c * (-dt)
-    dv = (float)((double)fw + s2 * (double)(orig[idx] - bw));
+    dv = mcCorrect(fw, orig[idx] - bw, s2, s2f);
   }
   // doClampComponent (advection.cpp:146-187)
   float minv = FLT_MAX, maxv = -FLT_MAX;
@@ -166,7 +184,7 @@ __global__ void __launch_bounds__(256) k_sl_mac_f(Geo gg, CV3 vel, CV3 src, V3 d
 // lower neighbour along the component's axis
 template <int C, int CM>
 __device__ __forceinline__ float mcMacCompF(const GeoF& g, const int* __restrict__ flags, const CV3& vel, const CV3& orig, const CV3& fwd,
-                                            int i, int j, int k, int idx, float dt, double s2, bool skip, int fc, int fn) {
+                                            int i, int j, int k, int idx, float dt, double s2, float s2f, bool skip, int fc, int fn) {
   const float* fwdc = compPtrF(fwd, C);
   const float* origc = compPtrF(orig, C);
   const float fw = fwdc[idx];
@@ -175,7 +193,7 @@ __device__ __forceinline__ float mcMacCompF(const GeoF& g, const int* __restrict
   float d = fw;
   if (!skip) {
     const float bw = interpolF(fwdc, g, (i + 0.5f) + vx, (j + 0.5f) + vy, (k + 0.5f) + vz);     // p0 - v * (-dt)
-    d = (float)((double)fw + s2 * (double)(origc[idx] - bw));                                  // advection.cpp:113
+    d = mcCorrect(fw, origc[idx] - bw, s2, s2f);                                               // advection.cpp:113
   }
   // doClampComponentMAC<C> (advection.cpp:193-236)
   if (CM == 2 && !(FCHECKFLAG(fc) && FCHECKFLAG(fn))) return fw;
@@ -212,6 +230,7 @@ __global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restri
   // skip[] of MacCormackCorrectMAC (advection.cpp:99-106)
   const bool sx = nf || (fxm & MF_FLUID) == 0, sy = nf || (fym & MF_FLUID) == 0, sz = nf || (fzm & MF_FLUID) == 0;
   const double s2 = (double)strength * 0.5;
+  const float s2f = mcPow2Scale(s2);
   if (border) {
     // fwd == bwd == 0 on the border; MacCormackCorrectMAC still runs there (KERNEL() without bnd), the clamp does not
     dst.x[idx] = sx ? 0.0f : (float)((double)0.0f + s2 * (double)(orig.x[idx] - 0.0f));
@@ -219,9 +238,9 @@ __global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restri
     dst.z[idx] = sz ? 0.0f : (float)((double)0.0f + s2 * (double)(orig.z[idx] - 0.0f));
     return;
   }
-  dst.x[idx] = mcMacCompF<0, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, sx, f, fxm);
-  dst.y[idx] = mcMacCompF<1, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, sy, f, fym);
-  dst.z[idx] = mcMacCompF<2, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, sz, f, fzm);
+  dst.x[idx] = mcMacCompF<0, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, s2f, sx, f, fxm);
+  dst.y[idx] = mcMacCompF<1, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, s2f, sy, f, fym);
+  dst.z[idx] = mcMacCompF<2, CM>(g, flags, vel, orig, fwd, i, j, k, idx, dt, s2, s2f, sz, f, fzm);
 }
 
 } // namespace mf

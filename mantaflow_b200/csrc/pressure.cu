@@ -236,14 +236,23 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   const bool codeCached = useCode && !needPlanes && !s->multi() && s->codeFlags == (const void*)flags->d && s->codeVersion == flags->version &&
                           s->codeFixing == (fixing ? 1 : 0) && !std::getenv("MF_CG_NOCODECACHE");
   s->codeFlags = nullptr;
+  bool statsDone = false;
   if (codeCached) {
     if (fixing && s->codeFixedCell >= 0) CUDA_CHECK(cudaMemsetAsync(rhs + s->codeFixedCell, 0, sizeof(float), s->stream));   // fixPressure: rhs(cell) = 0
   } else
   if (useCode && needPlanes) MF_LAUNCH_IJK(s, k_make_laplace<true>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, 0, phiD, p->gfClamp, s->cgCode);
+  else if (useCode && fixing && !std::getenv("MF_CODE_STATS_SEPARATE")) {
+    // row codes and the statistics of zeroPressureFixing in one pass over the flags
+    statsDone = true;
+    MF_RANKS(s, r) { const Geo g = geo(s, r);
+      if (s->nx % 4 == 0) { MF_LAUNCH(s, k_make_laplace_code_stats<4>, quadTileBlocks(s, g, 4), 256, g, flags->di(), s->cgCode, redCtx(s, r), s->redOut); }
+      else { MF_LAUNCH(s, k_make_laplace_code_stats<1>, quadTileBlocks(s, g, 1), 256, g, flags->di(), s->cgCode, redCtx(s, r), s->redOut); } }
+  }
   else if (useCode) MF_LAUNCH_IJK_W(s, k_make_laplace_code, flags->di(), s->cgCode);
   else MF_LAUNCH_IJK(s, k_make_laplace<false>, flags->di(), t.A0, t.Ai, t.Aj, t.Ak, fr, p->fractions ? 1 : 0, phiD, p->gfClamp, (unsigned short*)nullptr);
   if (fixing && !codeCached) {
-    if (s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<4>, quadTileBlocks(s, g, 4), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
+    if (statsDone) {}
+    else if (s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<4>, quadTileBlocks(s, g, 4), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
     else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_flag_stats<1>, quadTileBlocks(s, g, 1), 256, g, flags->di(), redCtx(s, r), s->redOut); } }
     redFinish<2>(s, RedOps<2>{ { 0, 1 } }, FinStore<2>{ s->redOut });
     // every process applies the same single-cell fix (identical inputs, value 0: redundant peer writes are benign)

@@ -205,11 +205,12 @@ __global__ void __launch_bounds__(256) k_make_laplace(Geo g, const int* __restri
 
 // Row codes only (no coefficient planes), W x-consecutive cells per thread: the matrix setup of a plain projection step whose
 // preconditioner is already built.  Same bits as k_make_laplace<false, true>.
+// the row codes of W x-consecutive cells; f = their flags (also returned for the caller's own use).  All lanes of a warp take part
+// (shuffles), `on` = the quad lies inside the row
 template <int W>
-__global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __restrict__ flags, unsigned short* __restrict__ code) {
-  MF_CELLS_W(g, W)
+__device__ __forceinline__ void laplaceCodeQuad(const Geo& g, const int* __restrict__ flags, long long idx, int i, int j, int k, int (&f)[W], int (&out)[W]) {
   const long long Y = g.nx, Z = g.Z;
-  int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
+  int fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
   ldW<W>(f, flags, idx);
   if (j > 0) ldW<W>(fym, flags, idx - Y); else { for (int c = 0; c < W; c++) fym[c] = 0; }
   if (j < g.ny - 1) ldW<W>(fyp, flags, idx + Y); else { for (int c = 0; c < W; c++) fyp[c] = 0; }
@@ -220,9 +221,7 @@ __global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __r
     const int le = xEdgeMinus<W, int>(flags, idx, i, 0), re = xEdgePlus<W, int>(flags, idx, i, g.nx, 0);
     xMinusWS<W, int>(fxm, f, le); xPlusWS<W, int>(fxp, f, re, i, g.nx);
   } else { xMinusW<W, int>(fxm, f, flags, idx, i, 0); xPlusW<W, int>(fxp, f, flags, idx, i, g.nx, 0); }
-  if (!on) return;
   const bool rowJK = j >= 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
-  int out[W];
 #pragma unroll
   for (int c = 0; c < W; c++) {
     int cd = 0;
@@ -245,7 +244,36 @@ __global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __r
     }
     out[c] = cd;
   }
+}
+template <int W>
+__global__ void __launch_bounds__(256) k_make_laplace_code(Geo g, const int* __restrict__ flags, unsigned short* __restrict__ code) {
+  MF_CELLS_W(g, W)
+  int f[W], out[W];
+  laplaceCodeQuad<W>(g, flags, idx, i, j, k, f, out);
+  if (!on) return;
   stW<W>(code, idx, out);
+}
+// The same in the pass that gathers the statistics zeroPressureFixing needs (k_flag_stats below: CountEmptyCells + the first
+// interior fluid cell): one read of the flag grid instead of two.  1-D grid-stride tile loop (the reduction's partials are bounded).
+template <int W>
+__global__ void __launch_bounds__(256) k_make_laplace_code_stats(Geo g, const int* __restrict__ flags, unsigned short* __restrict__ code, RedCtx ctx, double* outStats) {
+  __shared__ double sh[32];
+  double numEmpty = 0.0, minFluid = 1e300;
+  MF_QTILE_LOOP_BEGIN(g, W)
+    int f[W], out[W];
+    laplaceCodeQuad<W>(g, flags, idx, i, j, k, f, out);
+    if (!on) continue;
+    stW<W>(code, idx, out);
+    const bool rowJK = j >= 1 && j < g.ny - 1 && (!g.is3D || (k >= 1 && k < g.nz - 1));
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+      if (fIsEmpty(f[c])) numEmpty += 1.0;
+      if (fIsFluid(f[c]) && rowJK && i + c >= 1 && i + c < g.nx - 1) { const double v = (double)(idx + c); if (v < minFluid) minFluid = v; }
+    }
+  MF_QTILE_LOOP_END
+  double acc[2] = { numEmpty, minFluid };
+  const int ops[2] = { 0, 1 };
+  gridReduceK<2>(acc, ops, ctx, sh, FinStore<2>{ outStats });
 }
 
 // CountEmptyCells (pressure.cpp:217) + "first interior fluid cell in FOR_IJK_BND order" (:371-381)

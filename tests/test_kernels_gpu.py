@@ -389,11 +389,13 @@ def test_vcycle_wavefront_partitioned(nranks, monkeypatch):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("gridtype", ["RealGrid", "MACGrid"])
-@pytest.mark.parametrize("order,clampMode", [(1, 2), (2, 2), (2, 1)])
-def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
+@pytest.mark.parametrize("order,clampMode,strength", [(1, 2, 1.0), (2, 2, 1.0), (2, 1, 1.0), (2, 2, 0.8), (2, 1, 2.0), (2, 2, 0.25)])
+def test_advect_fast_matches_generic(gridtype, order, clampMode, strength, monkeypatch):
     """the 32-bit-index advection kernels (advect_fast.cuh: 3-D, linear interpolation, first-order trace) against the generic
     ones (MF_ADVECT_GENERIC=1) on a grid with obstacles, empty cells and velocities of up to ~6 cells per step (so that traces
-    leave the grid and hit every edge case of BUILD_INDEX and of the clamp lookups): bit-identical"""
+    leave the grid and hit every edge case of BUILD_INDEX and of the clamp lookups): bit-identical.  strength 1 / 2 / 0.25 take the
+    float form of the MacCormack correction (mcCorrect: strength * 0.5 is a power of two), 0.8 the reference's double expression;
+    the data carries zeros, denormals and values 2^-30 .. 2^-120 apart in magnitude to hit the roundings that could tell them apart"""
     from mantaflow_b200 import manta
     size = (70, 45, 38)
     rs = np.random.RandomState(31)
@@ -401,6 +403,12 @@ def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
     vel0 = ((rs.rand(size[2], size[1], size[0], 3).astype(np.float32) - np.float32(0.5)) * np.float32(12.0))
     vel0[rs.rand(size[2], size[1], size[0]) < 0.5] *= np.float32(0.05)
     d0 = rs.rand(size[2], size[1], size[0]).astype(np.float32)
+    # magnitudes spread over the float range, exact zeros and denormals
+    sel = rs.rand(size[2], size[1], size[0])
+    scale = np.where(sel < 0.1, 0.0, np.where(sel < 0.2, 1e-40, np.where(sel < 0.3, 1e-33, np.where(sel < 0.4, 1e-12, np.where(sel < 0.45, 3e-38, 1.0))))).astype(np.float32)
+    d0 = d0 * scale
+    vsel = rs.rand(size[2], size[1], size[0], 3)
+    vel0 = vel0 * np.where(vsel < 0.05, 0.0, np.where(vsel < 0.1, 1e-40, np.where(vsel < 0.15, 1e-20, 1.0))).astype(np.float32)
     outs = []
     for generic in (False, True):
         monkeypatch.delenv("MF_ADVECT_GENERIC", raising=False)
@@ -413,7 +421,7 @@ def test_advect_fast_matches_generic(gridtype, order, clampMode, monkeypatch):
             g = s.create(manta.RealGrid); g.from_numpy(d0)
         else:
             g = vel
-        manta.advectSemiLagrange(flags=flags, vel=vel, grid=g, order=order, clampMode=clampMode)
+        manta.advectSemiLagrange(flags=flags, vel=vel, grid=g, order=order, clampMode=clampMode, strength=strength)
         outs.append(g.to_numpy())
     assert np.isfinite(outs[0]).all()
     assert np.array_equal(outs[0].view(np.int32), outs[1].view(np.int32))
