@@ -389,8 +389,8 @@ static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* 
     float* old = grid->d; grid->d = fwd; fwd = old;       // orig.swap(fwd)
   } else {
     float* nw = (NC == 1) ? s->getReal() : s->getVec();
-    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_centered_f<1>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength);
-    else if (fast) MF_LAUNCH_IJK(s, k_mc_centered_f<2>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength);
+    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_centered_f<1>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
+    else if (fast) MF_LAUNCH_IJK(s, k_mc_centered_f<2>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
     else MF_LAUNCH_IJK(s, (k_mc_centered<NC, OS, OT>), flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
     float* old = grid->d; grid->d = nw;                   // orig.swap(newGrid)
     if (NC == 1) s->putReal(old); else s->putVec(old);
@@ -429,8 +429,8 @@ static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid,
   } else {
     float* nw = s->getVec();
     Grid ng = *grid; ng.d = nw;
-    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_mac_f<1>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength);
-    else if (fast) MF_LAUNCH_IJK(s, k_mc_mac_f<2>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength);
+    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_mac_f<1>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
+    else if (fast) MF_LAUNCH_IJK(s, k_mc_mac_f<2>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
     else MF_LAUNCH_IJK(s, (k_mc_mac<OS, OT>), flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
     applyOutflowBC(s, flags, v3(&ng), cv3(grid), dt);
     float* old = grid->d; grid->d = nw;

@@ -73,21 +73,22 @@ __device__ __forceinline__ float mcCorrect(float fw, float t, double s2, float s
   if (s2f != 0.f && !(fabsf(t) < 1.0e-30f && t != 0.f)) return fw + s2f * t;
   return (float)((double)fw + s2 * (double)t);
 }
-// s2 as a float when it is a power of two (exact scaling), else 0
-__device__ __forceinline__ float mcPow2Scale(double s2) {
+// strength * 0.5 as a float when it is a power of two (exact scaling), else 0 (host side; MF_ADVECT_MC_DOUBLE=1 keeps the double form)
+inline float mcPow2Scale(float strength) {
+  const double s2 = (double)strength * 0.5;
   const float f = (float)s2;
-  const int bits = __float_as_int(f);
-  return ((double)f == s2 && (bits & 0x007fffff) == 0 && (bits & 0x7f800000) != 0 && (bits & 0x7f800000) != 0x7f800000 && fabsf(f) > 1.0e-6f && fabsf(f) < 1.0e6f) ? f : 0.f;
+  int e = 0;
+  const double m = frexp(s2, &e);
+  return ((double)f == s2 && (m == 0.5 || m == -0.5) && e > -20 && e < 20 && !getenv("MF_ADVECT_MC_DOUBLE")) ? f : 0.f;
 }
 
 // backward SL + MacCormackCorrect + MacCormackClamp fused (see k_mc_centered in advect.cu)
 template <int CM>
 __global__ void __launch_bounds__(256) k_mc_centered_f(Geo gg, const int* __restrict__ flags, CV3 vel, const float* __restrict__ orig,
-                                                       const float* __restrict__ fwd, float* __restrict__ dst, float dt, float strength) {
+                                                       const float* __restrict__ fwd, float* __restrict__ dst, float dt, float strength, float s2f) {
   IJK_FROM_BLOCK_F
   const bool fluid = (flags[idx] & MF_FLUID) != 0;
   const double s2 = (double)strength * 0.5;
-  const float s2f = mcPow2Scale(s2);
   if (border) {
     float d = 0.0f;
     if (fluid) d = (float)((double)0.0f + s2 * (double)(orig[idx] - 0.0f));
@@ -222,7 +223,7 @@ __device__ __forceinline__ float mcMacCompF(const GeoF& g, const int* __restrict
 }
 
 template <int CM>
-__global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restrict__ flags, CV3 vel, CV3 orig, CV3 fwd, V3 dst, float dt, float strength) {
+__global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restrict__ flags, CV3 vel, CV3 orig, CV3 fwd, V3 dst, float dt, float strength, float s2f) {
   IJK_FROM_BLOCK_F
   const int f = flags[idx];
   const int fxm = (i > 0) ? flags[idx - 1] : MF_FLUID, fym = (j > 0) ? flags[idx - g.nx] : MF_FLUID, fzm = (k > 0) ? flags[idx - g.Z] : MF_FLUID;
@@ -230,7 +231,6 @@ __global__ void __launch_bounds__(256, 8) k_mc_mac_f(Geo gg, const int* __restri
   // skip[] of MacCormackCorrectMAC (advection.cpp:99-106)
   const bool sx = nf || (fxm & MF_FLUID) == 0, sy = nf || (fym & MF_FLUID) == 0, sz = nf || (fzm & MF_FLUID) == 0;
   const double s2 = (double)strength * 0.5;
-  const float s2f = mcPow2Scale(s2);
   if (border) {
     // fwd == bwd == 0 on the border; MacCormackCorrectMAC still runs there (KERNEL() without bnd), the clamp does not
     dst.x[idx] = sx ? 0.0f : (float)((double)0.0f + s2 * (double)(orig.x[idx] - 0.0f));
