@@ -36,7 +36,11 @@ struct LvlD {
   unsigned char* type;
   const unsigned short* code;   // level 0 only: compact operator (or nullptr)
   unsigned bxMagic;    // blocked: ceil(2^32 / (PX-2)), see mgBlockThread
-  const __half* Ah; long long ash;   // blocked levels: the operator in binary16 when every entry converts exactly (else nullptr)
+  // blocked levels: the operator in binary16 (else nullptr).  Planes are interleaved in pairs: entry e of the row stored at position
+  // p is the half Ah[2 * ((e >> 1) * ash + p) + (e & 1)], i.e. seven planes of 4-byte (half2) elements with plane stride ash -- the
+  // element size of every other array of the level, so that a z-slab partition of the level cuts the binary16 planes at the same
+  // allocation granules as the vectors (2-byte planes put half of a rank's boundary granule on its neighbour: +0.6 ms per step at N = 8)
+  const __half* Ah; long long ash;
 };
 
 struct MgDims { int is3D; int dim; int SS; int SS0; int zmin; int zmax; };   // mStencilSize, mStencilSize0, mStencilMin/Max.z
@@ -64,13 +68,13 @@ __device__ __host__ __forceinline__ bool mgDecode(const LvlD& L, int p, int& x, 
 }
 // all-zero row (inactive vertex or padding) of a blocked level: the diagonal is 0
 __device__ __forceinline__ bool mgRowZero(const LvlD& L, int p) {
-  return L.Ah ? (__half_as_ushort(L.Ah[p]) & 0x7fffu) == 0 : L.A[p] == 0.f;
+  return L.Ah ? (__half_as_ushort(L.Ah[2 * (long long)p]) & 0x7fffu) == 0 : L.A[p] == 0.f;
 }
 // (binary16 levels mark a vertex whose row -- or a row it reads -- is not exactly representable with a NaN diagonal: such a
 //  vertex takes its coefficients from the float planes, see k_mg_mark_special)
 __device__ __forceinline__ float mgDiag(const LvlD& L, int p) {
   if (!L.Ah) return L.A[p];
-  const float d = __half2float(L.Ah[p]);
+  const float d = __half2float(L.Ah[2 * (long long)p]);
   return d == d ? d : L.A[p];
 }
 // setup kernels walk the storage range [p0, p1) (a rank's share of the level)
@@ -320,7 +324,7 @@ __device__ __forceinline__ float mgStencilSubFloat(const LvlD& L, int p, const M
   return sum;
 }
 template <bool HALF> __device__ __forceinline__ const char* mgRowPtr(const LvlD& L, int p) {
-  return HALF ? reinterpret_cast<const char*>(L.Ah + p) : reinterpret_cast<const char*>(L.A + p);
+  return HALF ? reinterpret_cast<const char*>(L.Ah + 2 * (long long)p) : reinterpret_cast<const char*>(L.A + p);
 }
 // Operator format of a blocked level (template parameter HM of the sweeps): float planes, binary16 planes (every entry converts
 // exactly), or binary16 planes + per-colour lists of the vertices that keep the float planes (k_mg_mark_special): those are swept by
@@ -603,7 +607,7 @@ __global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* 
     const float a = L.A[e * L.as + p];
     const __half h = __float2half_rn(a);
     bad |= !(__half2float(h) == a);
-    Ah[e * L.ash + p] = h;
+    Ah[2 * ((e >> 1) * L.ash + p) + (e & 1)] = h;
   }
   rowBad[p] = bad ? 1.f : 0.f;
 }
@@ -622,7 +626,7 @@ __global__ void __launch_bounds__(256) k_mg_mark_special(LvlD L, __half* __restr
   // (inactive vertices keep their exact all-zero row: the entries that couple a neighbour to them are zero as well, and a NaN
   //  diagonal would make mgRowZero() take them for active)
   if (special && L.A[p] != 0.f) {
-    Ah[p] = __ushort_as_half((unsigned short)0x7e00); atomicAdd(count, 1);
+    Ah[2 * (long long)p] = __ushort_as_half((unsigned short)0x7e00); atomicAdd(count, 1);
     // per-colour list for the sweeps (vertices of one colour are independent of each other: the order in the list is free)
     const int c = (x & 1) | ((y & 1) << 1) | ((z & 1) << 2);
     const int i = atomicAdd(colourCount + c, 1);

@@ -330,7 +330,8 @@ static void buildOffsets(MgHierarchy* mg, int l) {
   const bool is3D = mg->D.is3D != 0;
   const int SS = mg->D.SS;
   const long long PXY = (long long)L.PX * L.PY;
-  const long long elem = L.Ah ? 2 : 4, as = L.Ah ? L.ash : L.as;
+  const bool half = L.Ah != nullptr;
+  const long long as = half ? L.ash : L.as;
   for (int c = 0; c < L.NC; c++) {
     const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
     int s = 0;
@@ -342,7 +343,9 @@ static void buildOffsets(MgHierarchy* mg, int l) {
           const long long dp = (long long)((cz + dz + 2) / 2 - 1) * L.NC * PXY + (long long)(nc - c) * PXY
                              + (long long)((cy + dy + 2) / 2 - 1) * L.PX + ((cx + dx + 2) / 2 - 1);
           O.t[c].xo[s] = 4 * dp;
-          O.t[c].ao[s] = elem * ((s < SS) ? (SS - 1 - s) * as + dp : (long long)(s - SS + 1) * as);
+          // stored entry e of the row at shift d: float planes 4 * (e * as + d); binary16 plane pairs 4 * ((e >> 1) * as + d) + 2 * (e & 1)
+          const long long e = (s < SS) ? (SS - 1 - s) : (s - SS + 1), d = (s < SS) ? dp : 0;
+          O.t[c].ao[s] = half ? 4 * ((e >> 1) * as + d) + 2 * (e & 1) : 4 * (e * as + d);
         }
   }
 }
@@ -401,8 +404,9 @@ MgHierarchy* mg_create(Solver* s) {
       L.x = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
       L.b = (float*)s->galloc(sizeof(float) * (size_t)L.na, 1, 0, es.data(), 4);
       if (l == 1 && is3D && !getenv("MF_MG_NOHALF")) {
-        mg->ash1 = planeStride(s, L.na, sizeof(__half));
-        mg->half1 = (__half*)s->galloc(sizeof(__half) * (size_t)L.na, mg->D.SS, sizeof(__half) * (size_t)mg->ash1, es.data(), 2);
+        // seven planes of half2 elements (LvlD::Ah): partitioned like the float planes
+        mg->ash1 = L.as;
+        mg->half1 = (__half*)s->galloc(sizeof(float) * (size_t)L.na, (mg->D.SS + 1) / 2, sizeof(float) * (size_t)mg->ash1, es.data(), 4);
         mg->special1 = (int*)s->galloc(sizeof(int) * (8 + 8 * MG_SPECIAL_CAP));
         CUDA_CHECK(cudaMalloc(&mg->special1Local, sizeof(int) * (8 + 8 * MG_SPECIAL_CAP)));
       }
