@@ -301,10 +301,19 @@ __device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int
 template <bool IS3D, bool WITH_CENTER, bool HALF>
 __device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const char* xp, const MgOff1& o, float sum) {
   constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
+  // binary16: the vertex' own row (terms SS-1 .. NS-1 = stored entries 0 .. SS-1) lies in plane PAIRS at its own position: one
+  // 4-byte load per two entries (LvlD::Ah); the lower half of the stencil comes from 13 different neighbours' rows, entry by entry
+  __half2 own[(SS + 1) / 2];
+  if (HALF) {
+#pragma unroll
+    for (int q = 0; q < (SS + 1) / 2; q++) own[q] = *reinterpret_cast<const __half2*>(ap + o.ao[SS - 1 + 2 * q]);
+  }
 #pragma unroll
   for (int s = 0; s < NS; s++) {
     if (s == SS - 1 && !WITH_CENTER) continue;
-    const float a = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
+    float a;
+    if (HALF && s >= SS - 1) { const int e = s - (SS - 1); a = (e & 1) ? __high2float(own[e >> 1]) : __low2float(own[e >> 1]); }
+    else a = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
     sum -= a * *reinterpret_cast<const float*>(xp + o.xo[s]);
   }
   return sum;
