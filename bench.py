@@ -109,7 +109,7 @@ def algo_bytes(kernel, size_gpu, cells_gpu, entry_bytes=None):
     bound = "hbm" if level_bytes > L2_BYTES else "latency"
     per_vertex = {"k_mg_smooth": (27 * eb + 12) / 8.0,        # one of 8 colours per launch
                   "k_mg_smooth_ml": (27 * eb + 12) / 8.0,
-                  "k_mg_residual": 27 * eb + 12, "k_mg_restrict": 4 + 0.5, "k_mg_interp_add": 8 + 0.5, "k_mg_interp_add_b": 8 + 0.5,
+                  "k_mg_residual": 27 * eb + 12, "k_mg_restrict": 4 + 0.5, "k_mg_interp_add": 8 + 0.5, "k_mg_interp_add_b": 8 + 0.5, "k_mg_interp_add_c": 8 + 0.5,
                   "k_mg_level_sweep": 14 * eb + 12}.get(base)
     if per_vertex is None:
         return None, None

@@ -518,6 +518,39 @@ __global__ void __launch_bounds__(128) k_mg_interp_add_b(LvlD F, LvlD C, int lz0
   }
 }
 
+// The same with one work item per 2 x 2 x 2 CELL of fine vertices: the eight vertices (2 lx + cx, 2 ly + cy, 2 lz + cz) sit at the
+// SAME position of the eight colour blocks and interpolate from the eight coarse vertices (lx .. lx + 1, ly .. ly + 1, lz .. lz + 1),
+// which are loaded once (8 loads instead of 27 for the eight vertices; the per-vertex sums keep the order z, y, x ascending).
+__global__ void __launch_bounds__(128) k_mg_interp_add_c(LvlD F, LvlD C, int lz0) {
+  MF_PDL_PROLOGUE
+  BlkPos q;
+  if (!mgBlockThread(F, 0, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, gridDim.y, blockIdx.y)) return;
+  const int PXY = F.PX * F.PY;
+  float cv[2][2][2];
+#pragma unroll
+  for (int dz = 0; dz < 2; dz++)
+#pragma unroll
+    for (int dy = 0; dy < 2; dy++)
+#pragma unroll
+      for (int dx = 0; dx < 2; dx++) cv[dz][dy][dx] = C.x[mgIdx(C, q.lx + dx, q.ly + dy, q.lz + dz)];
+  float xo[8]; bool off[8];
+#pragma unroll
+  for (int c = 0; c < 8; c++) { const int p = q.p + c * PXY; xo[c] = F.x[p]; off[c] = mgRowZero(F, p); }
+#pragma unroll
+  for (int c = 0; c < 8; c++) {
+    const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
+    float sum = 0.f;
+#pragma unroll
+    for (int dz = 0; dz <= cz; dz++)
+#pragma unroll
+      for (int dy = 0; dy <= cy; dy++)
+#pragma unroll
+        for (int dx = 0; dx <= cx; dx++) sum += cv[dz][dy][dx];
+    const float iw = 1.0f / (float)(1 << (cx + cy + cz));
+    if (!off[c]) F.x[q.p + c * PXY] = xo[c] + iw * sum;
+  }
+}
+
 // ---- Galerkin coarse operators (setup) ---------------------------------------------------------------------
 // precomputed coarsening paths for level 1 (multigrid.cpp:286-318)
 struct MgPath { signed char Nx, Ny, Nz, Ux, Uy, Uz, Wx, Wy, Wz; signed char sc, sf, inU; float rw, iw; };

@@ -749,7 +749,8 @@ static void interpAdd(MgHierarchy* mg, int l) {
     if (blocked) {
       int lz0, lz1; lvlPairs(mg, l, r, lz0, lz1);
       if (lz1 <= lz0) continue;
-      MF_LAUNCH_PDL(s, k_mg_interp_add_b, dim3(cdiv((long long)(F.PX - 2) * (F.PY - 2), 128), lz1 - lz0, 8), 128, F, C, lz0);
+      if (getenv("MF_MG_INTERP_PERVERTEX")) { MF_LAUNCH_PDL(s, k_mg_interp_add_b, dim3(cdiv((long long)(F.PX - 2) * (F.PY - 2), 128), lz1 - lz0, 8), 128, F, C, lz0); }
+      else { MF_LAUNCH_PDL(s, k_mg_interp_add_c, dim3(cdiv((long long)(F.PX - 2) * (F.PY - 2), 128), lz1 - lz0), 128, F, C, lz0); }
       continue;
     }
     int z0, z1; lvlPlanes(mg, l, r, z0, z1);

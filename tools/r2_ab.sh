@@ -12,7 +12,7 @@ python - <<PY
 import json
 d = json.load(open("gpurun_out/bench_ab_$v.json"))
 ks = {k["kernel"]: k for k in d["kernels"]}
-print({n: round(ks[n]["avg_us"], 1) for n in ks if n in ("k_mc_mac_f", "k_mc_centered_f", "k_sl_mac_f", "k_sl_f", "k_mg_down0@L0", "k_mg_up0w@L0", "k_mg_smooth@L1")})
+print({n: round(ks[n]["avg_us"], 1) for n in ks if n in ("k_mc_mac_f", "k_mc_centered_f", "k_sl_mac_f", "k_sl_f", "k_mg_down0@L0", "k_mg_up0w@L0", "k_mg_smooth@L1", "k_mg_interp_add_b@L1", "k_mg_interp_add_c@L1", "k_mg_residual@L1")})
 print("$v step %.3f ms" % d["ms_per_step"], "pcg/it %.4f" % d["pcg_ms_per_iteration"]["ms_per_iteration"], "solve %.3f" % d["pcg_ms_per_iteration"]["solve_ms_per_step"], d["pcg_iterations"][:5], d["gpu_launches"], d["roofline"]["kernel"], round(d["roofline"]["frac"] or 0, 3), d["roofline"]["bound"])
 PY
 done
