@@ -434,17 +434,22 @@ __device__ __forceinline__ void mgRestrictItem(const LvlD& F, const LvlD& C, int
   float sum = 0.f;
   const float* fr = F.r;
   if (F.perm) {
+    // fine vertex (2 vx + dx, 2 vy + dy, 2 vz + dz): colour = parity of (dx, dy, dz), position (vx, vy, vz) of its colour block, one
+    // entry / row / z pair back for an offset of -1 -- a constant shift from the position of (2 vx, 2 vy, 2 vz) in colour block 0
+    const int PXY = F.PX * F.PY;
+    const float* f0 = fr + ((((vz + F.zoff) * F.NC) * F.PY + vy + 1) * F.PX + vx + 1);
 #pragma unroll
     for (int dz = IS3D ? -1 : 0; dz <= (IS3D ? 1 : 0); dz++)
 #pragma unroll
       for (int dy = -1; dy <= 1; dy++)
 #pragma unroll
         for (int dx = -1; dx <= 1; dx++) {
-          const int x = vx * 2 + dx, y = vy * 2 + dy, z = vz * 2 + dz;
           // the reference clamps the loops to the grid: skipped terms, not zero terms -- identical sums because the
           // first in-range term is added to +0 either way
           const float rw = 1.0f / (float)(1 << ((dx & 1) + (dy & 1) + (dz & 1)));
-          sum += rw * fr[mgIdx(F, x, y, z)];
+          const int c = (dx & 1) | ((dy & 1) << 1) | ((dz & 1) << 2);
+          const int off = (dz < 0 ? -F.NC * PXY : 0) + c * PXY + (dy < 0 ? -F.PX : 0) + (dx < 0 ? -1 : 0);
+          sum += rw * f0[off];
         }
   } else {
     for (int z = max(0, vz * 2 - 1); z <= min(F.sz - 1, vz * 2 + 1); z++)
