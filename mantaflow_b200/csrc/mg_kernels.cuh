@@ -318,6 +318,32 @@ __device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const
   }
   return sum;
 }
+// The same in two steps: the row's coefficients (the operator is constant between hierarchy builds, so a kernel launched with
+// programmatic dependent launch may load them BEFORE griddepcontrol.wait, while its predecessor drains), then the sum.
+template <bool IS3D, bool HALF>
+__device__ __forceinline__ void mgLoadRow(const char* __restrict__ ap, const MgOff1& o, float (&a)[IS3D ? 27 : 9]) {
+  constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
+  __half2 own[(SS + 1) / 2];
+  if (HALF) {
+#pragma unroll
+    for (int q = 0; q < (SS + 1) / 2; q++) own[q] = *reinterpret_cast<const __half2*>(ap + o.ao[SS - 1 + 2 * q]);
+  }
+#pragma unroll
+  for (int s = 0; s < NS; s++) {
+    if (HALF && s >= SS - 1) { const int e = s - (SS - 1); a[s] = (e & 1) ? __high2float(own[e >> 1]) : __low2float(own[e >> 1]); }
+    else a[s] = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
+  }
+}
+template <bool IS3D, bool WITH_CENTER>
+__device__ __forceinline__ float mgRowSub(const float (&a)[IS3D ? 27 : 9], const char* xp, const MgOff1& o, float sum) {
+  constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
+#pragma unroll
+  for (int s = 0; s < NS; s++) {
+    if (s == SS - 1 && !WITH_CENTER) continue;
+    sum -= a[s] * *reinterpret_cast<const float*>(xp + o.xo[s]);
+  }
+  return sum;
+}
 // a marked vertex of a binary16 level: the same sum from the float planes.  Stored entry e of a row is stencil term 13 + e; the
 // lower half of the stencil (s < 13) is entry 13 - s of the neighbour's row, whose position is p + xo[s] / 4.
 template <bool WITH_CENTER>
@@ -348,10 +374,18 @@ __device__ __forceinline__ int mgPairOf(const LvlD& L, int p) { return p / (L.PX
 // knSmoothColor, l > 0: one vertex of one of the 8 (4) colours (multigrid.cpp:668-711)
 template <bool IS3D, int HM>
 __global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_constant__ MgOff1 o, int c, int lz0, MgSpecial sp) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();
   constexpr bool HALF = HM != MG_FMT_FLOAT;
   const int ypairs = gridDim.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0);
-  if (HM == MG_FMT_HALF_LISTS && blockIdx.y == 0) {
+  BlkPos q;
+  const bool listRow = HM == MG_FMT_HALF_LISTS && blockIdx.y == 0;
+  const bool mine = !listRow && mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0));
+  // the operator row before the wait (constant data), x and b behind it
+  float a[IS3D ? 27 : 9];
+  const char* ap = nullptr;
+  if (mine) { ap = mgRowPtr<HALF>(L, q.p); mgLoadRow<IS3D, HALF>(ap, o, a); }
+  pdlWait();
+  if (listRow) {
     // the listed vertices of this colour in the z pairs [lz0, lz0 + ypairs) of this launch, from the float planes
     if (blockIdx.x != 0) return;
     const int n = min(sp.count[c], MG_SPECIAL_CAP);
@@ -365,16 +399,14 @@ __global__ void __launch_bounds__(128, 6) k_mg_smooth(LvlD L, const __grid_const
     }
     return;
   }
-  BlkPos q;
-  if (!mgBlockThread(L, c, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0))) return;
+  if (!mine) return;
   // inactive vertices and padding have an all-zero row (k_mg_galerkin*); an active row has a non-zero diagonal, or the
   // reference's own division below would not be finite
   // The diagonal is loaded with the rest of the row and only the store is predicated: a vertex is one batch of loads (one trip
   // to L2 / DRAM instead of two) -- the sweeps of the small levels are pure latency.  (128, 6): up to 80 registers, enough for
   // the compiler to issue all 54 loads before the first use (with 32 registers it interleaved them in three dependent rounds).
-  const char* ap = mgRowPtr<HALF>(L, q.p);
-  const float diag = HALF ? __half2float(*reinterpret_cast<const __half*>(ap)) : *reinterpret_cast<const float*>(ap);
-  const float sum = mgStencilSub<IS3D, false, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
+  const float diag = a[IS3D ? 13 : 4];
+  const float sum = mgRowSub<IS3D, false>(a, reinterpret_cast<const char*>(L.x + q.p), o, L.b[q.p]);
   if (HM == MG_FMT_HALF_LISTS) { if (diag != 0.f && diag == diag) L.x[q.p] = sum / diag; }      // NaN: a listed vertex
   else if (diag != 0.f) L.x[q.p] = sum / diag;
 }
