@@ -415,7 +415,14 @@ template <bool IS3D, int HM, int C>
 __device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, int lz0, const MgSpecial& sp) {
   constexpr bool HALF = HM != MG_FMT_FLOAT;
   const int ypairs = gridDim.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0);
-  if (HM == MG_FMT_HALF_LISTS && blockIdx.y == 0) {
+  const bool listRow = HM == MG_FMT_HALF_LISTS && blockIdx.y == 0;
+  BlkPos q;
+  const bool mine = !listRow && mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0));
+  // the operator row before the wait (constant data, see k_mg_smooth)
+  float a[IS3D ? 27 : 9];
+  if (mine) mgLoadRow<IS3D, HALF>(mgRowPtr<HALF>(L, q.p), O.t[C], a);
+  pdlWait();
+  if (listRow) {
     if (blockIdx.x != 0) return;
     const int n = min(sp.count[C], MG_SPECIAL_CAP);
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -426,17 +433,15 @@ __device__ __forceinline__ void mgResidualItem(const LvlD& L, const MgOff8& O, i
     }
     return;
   }
-  BlkPos q;
-  if (!mgBlockThread(L, C, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, ypairs, (int)blockIdx.y - (HM == MG_FMT_HALF_LISTS ? 1 : 0))) return;
+  if (!mine) return;
   // inactive / padding entries: b = 0 and an all-zero row give r = 0, what they hold anyway -- no type test needed
-  const char* ap = mgRowPtr<HALF>(L, q.p);
-  const float r = mgStencilSub<IS3D, true, HALF>(ap, reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
-  if (HM == MG_FMT_HALF_LISTS) { const float dg = __half2float(*reinterpret_cast<const __half*>(ap)); if (dg == dg) L.r[q.p] = r; }
+  const float r = mgRowSub<IS3D, true>(a, reinterpret_cast<const char*>(L.x + q.p), O.t[C], L.b[q.p]);
+  if (HM == MG_FMT_HALF_LISTS) { const float dg = a[IS3D ? 13 : 4]; if (dg == dg) L.r[q.p] = r; }
   else L.r[q.p] = r;
 }
 template <bool IS3D, int HM>
 __global__ void __launch_bounds__(128, 6) k_mg_residual(LvlD L, const __grid_constant__ MgOff8 O, int lz0, MgSpecial sp) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();                 // (griddepcontrol.wait inside the item, behind the loads of the operator row)
   switch (blockIdx.z) {       // the colour selects compile-time positions in the offset table
     case 0: mgResidualItem<IS3D, HM, 0>(L, O, lz0, sp); break;
     case 1: mgResidualItem<IS3D, HM, 1>(L, O, lz0, sp); break;
@@ -559,10 +564,17 @@ __global__ void __launch_bounds__(128) k_mg_interp_add_b(LvlD F, LvlD C, int lz0
 // SAME position of the eight colour blocks and interpolate from the eight coarse vertices (lx .. lx + 1, ly .. ly + 1, lz .. lz + 1),
 // which are loaded once (8 loads instead of 27 for the eight vertices; the per-vertex sums keep the order z, y, x ascending).
 __global__ void __launch_bounds__(128) k_mg_interp_add_c(LvlD F, LvlD C, int lz0) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();
   BlkPos q;
-  if (!mgBlockThread(F, 0, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, gridDim.y, blockIdx.y)) return;
+  const bool mine = mgBlockThread(F, 0, lz0, blockIdx.x * blockDim.x + threadIdx.x, q, gridDim.y, blockIdx.y);
   const int PXY = F.PX * F.PY;
+  bool off[8];                          // all-zero rows: read from the (constant) operator before the wait
+  if (mine) {
+#pragma unroll
+    for (int c = 0; c < 8; c++) off[c] = mgRowZero(F, q.p + c * PXY);
+  }
+  pdlWait();
+  if (!mine) return;
   float cv[2][2][2];
 #pragma unroll
   for (int dz = 0; dz < 2; dz++)
@@ -570,9 +582,9 @@ __global__ void __launch_bounds__(128) k_mg_interp_add_c(LvlD F, LvlD C, int lz0
     for (int dy = 0; dy < 2; dy++)
 #pragma unroll
       for (int dx = 0; dx < 2; dx++) cv[dz][dy][dx] = C.x[mgIdx(C, q.lx + dx, q.ly + dy, q.lz + dz)];
-  float xo[8]; bool off[8];
+  float xo[8];
 #pragma unroll
-  for (int c = 0; c < 8; c++) { const int p = q.p + c * PXY; xo[c] = F.x[p]; off[c] = mgRowZero(F, p); }
+  for (int c = 0; c < 8; c++) xo[c] = F.x[q.p + c * PXY];
 #pragma unroll
   for (int c = 0; c < 8; c++) {
     const int cx = c & 1, cy = (c >> 1) & 1, cz = (c >> 2) & 1;
