@@ -106,7 +106,7 @@ __device__ __forceinline__ float wvOffdiagAt(const L0Code& op, const L0Code::Row
 // plane needs it, so the coarse vertices at 2X == sx (even sizes) have an owner too.
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float trivialScale, int firstColor, int U0, int U1, WvSched S,
                                                   int z0, int z1, int cz0, int cz1, int foldFirst) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();              // griddepcontrol.wait follows the set-up (ring clears, tile geometry): it overlaps the predecessor's drain
   __shared__ __align__(16) float xs[4][WV_RY][WV_RX];     // read and written as float2
   __shared__ __align__(16) float rs[WV_RY][WV_RX];
   const L0Code op(F, trivialScale);
@@ -136,6 +136,7 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float tri
     rowOff[i] = gx0 + F.sx * gy;
     if (inX && gy >= 0 && gy < F.sy) rowOk |= 1u << i;
   }
+  pdlWait();
   {
     const int gz = c0 - 3; const bool zok = gz >= 0 && gz < F.sz;
 #pragma unroll
@@ -277,7 +278,7 @@ struct WvFinBeta {
 template <bool DOT>
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_up0w(LvlD F, LvlD C, float trivialScale, int firstColor, const float* __restrict__ xin,
                                                  float* __restrict__ xout, int U0, int U1, WvSched S, int z0, int z1, WvFinBeta fin, RedCtx ctx) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();              // griddepcontrol.wait follows the set-up, in front of the first load of data a predecessor wrote
   double dotAcc[1] = { 0.0 };
   __shared__ __align__(16) float xs[4][WV_RY][WV_RX];     // read and written as float2
   __shared__ __align__(16) float cs[2][WU_CY][WU_CX];
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_up0w(LvlD F, LvlD C, float triv
     }
   };
   const int pBeg = c0 - 2, pEnd = c1 + 1;
+  pdlWait();
   loadCoarse(pBeg >> 1);
   if (pBeg & 1) loadCoarse((pBeg + 1) >> 1);
   WvPair rowA[WV_RPW], rowB[WV_RPW], rowC[WV_RPW], rowN[WV_RPW];

@@ -190,6 +190,8 @@ __device__ __forceinline__ void mgCoarseCg(const LvlD& L, const MgDims& D, float
     return sum;
   };
   const double invDiag = active ? 1.0 / (double)L.A[p] : 0.0;
+  // everything above reads the operator only (constant between hierarchy builds): the wait for the predecessor comes here
+  pdlWait();
   double x = (in && !fromReg) ? (double)L.x[p] : 0.0, r = 0.0, z = 0.0, pp = 0.0;
   vec[v] = x;
   __syncthreads();
@@ -243,7 +245,7 @@ namespace mf {
 // MAXT = 768: up to 85 registers per thread; with 1024 threads (64 registers) part of the state spills to local memory
 template <bool LEVEL0, int MAXT>
 __global__ void __launch_bounds__(MAXT) k_mg_coarse_cg(LvlD L, MgDims D, float accuracy) {
-  MF_PDL_PROLOGUE
+  pdlTrigger();                 // (griddepcontrol.wait inside mgCoarseCg, behind the loads of the row)
   __shared__ double sh[2][32];
   __shared__ double out[4];
   __shared__ double vec[1024 + 2 * (1024 + 1024 + 1)];      // n + two margins of Z + Y + 1 <= 2049
