@@ -106,6 +106,8 @@ struct Solver {
   // small control transfers on the solver stream WITHOUT the copy engines (a 40-byte readback must not queue behind a bulk
   // host copy of the streaming transfers): a one-warp kernel stores into mapped pinned memory / carries the payload as argument
   void  readSmall(void* pinnedDst, const void* dev, int bytes);     // then synchronises the stream; bytes % 4 == 0, <= 256
+  unsigned readSmallLaunch(void* pinnedDst, const void* dev, int bytes);   // the copy alone; the data is valid after readSmallWait(ticket)
+  void  readSmallWait(unsigned ticket);
   void  writeSmall(void* dev, const void* hostSrc, int bytes);      // asynchronous; bytes % 4 == 0, <= 64
   // per-kernel CUDA-event timing (mf_solver_profile_*): one event pair per launch while enabled
   bool profiling;

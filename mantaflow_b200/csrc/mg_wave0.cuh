@@ -105,7 +105,7 @@ __device__ __forceinline__ float wvOffdiagAt(const L0Code& op, const L0Code::Row
 // the rank's coarse range [cz0, cz1).  Tiles cover [0, sx] x [0, sy] and the chunks [U0, U1) reach plane sz when the last coarse
 // plane needs it, so the coarse vertices at 2X == sx (even sizes) have an owner too.
 __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float trivialScale, int firstColor, int U0, int U1, WvSched S,
-                                                  int z0, int z1, int cz0, int cz1, int foldFirst) {
+                                                  int z0, int z1, int cz0, int cz1, int foldFirst, const int* __restrict__ skip) {
   pdlTrigger();              // griddepcontrol.wait follows the set-up (ring clears, tile geometry): it overlaps the predecessor's drain
   __shared__ __align__(16) float xs[4][WV_RY][WV_RX];     // read and written as float2
   __shared__ __align__(16) float rs[WV_RY][WV_RX];
@@ -137,6 +137,8 @@ __global__ void __launch_bounds__(WV_NT, 2) k_mg_down0(LvlD F, LvlD C, float tri
     if (inX && gy >= 0 && gy < F.sy) rowOk |= 1u << i;
   }
   pdlWait();
+  // launched ahead of the caller's decision (mg_apply_begin): the PCG has converged, this V-cycle is not wanted
+  if (skip && *reinterpret_cast<const volatile int*>(skip)) return;
   {
     const int gz = c0 - 3; const bool zok = gz >= 0 && gz < F.sz;
 #pragma unroll

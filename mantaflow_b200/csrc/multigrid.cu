@@ -38,6 +38,8 @@ struct MgHierarchy {
   int tailFirst;            // first level swept by the tail kernels, or -1
   // the last swept level + the coarsest level in one CTA (mg_bottom.cuh)
   bool bottomOn; MgOff8* bottomOff; size_t bottomSmem; int bottomVec;
+  // mg_apply_begin: the level-0 down leg of the next mg_apply is already queued
+  bool begun; float* begunDst; const float* begunRhs; float* begunR0;
 };
 
 // ---- partition of a level over the ranks ----------------------------------------------------------------------
@@ -360,6 +362,7 @@ MgHierarchy* mg_create(Solver* s) {
   mg->half1 = nullptr; mg->ash1 = 0; mg->nspecial1 = 0; mg->special1 = nullptr; mg->special1Local = nullptr;
   mg->tailCluster = 0; mg->tailBar = nullptr; mg->tailBase = 0; mg->tailErrHost = nullptr; mg->tailErrDev = nullptr; mg->tailFirst = -1; mg->tailOffs = nullptr;
   mg->bottomOn = false; mg->bottomOff = nullptr; mg->bottomSmem = 0; mg->bottomVec = 0;
+  mg->begun = false; mg->begunDst = nullptr; mg->begunRhs = nullptr; mg->begunR0 = nullptr;
   const bool is3D = s->nz > 1;
   mg->D.is3D = is3D; mg->D.dim = is3D ? 3 : 2; mg->D.SS = is3D ? 14 : 5; mg->D.SS0 = is3D ? 4 : 3;
   mg->D.zmin = is3D ? -1 : 0; mg->D.zmax = is3D ? 1 : 0;
@@ -811,7 +814,7 @@ static WvSched waveSched(const Solver* s, int tx, int ty, int planes, int& total
   S.nq = tiles - (total - S.q * tiles);           // the remaining total - q*tiles tiles get q+1 chunks
   return S;
 }
-static void waveDown0(MgHierarchy* mg, bool fold) {
+static void waveDown0(MgHierarchy* mg, bool fold, const int* skip = nullptr) {
   Solver* s = mg->s;
   LvlD& F = mg->lv[0]; LvlD& C = mg->lv[1];
   s->profTag = 0;
@@ -825,7 +828,7 @@ static void waveDown0(MgHierarchy* mg, bool fold) {
     U0 &= ~1;
     const int tx = (int)cdiv(F.sx + 1, WV_TX), ty = (int)cdiv(F.sy + 1, WD_TY);
     int total; const WvSched S = waveSched(s, tx, ty, U1 - U0, total);
-    MF_LAUNCH_PDL(s, k_mg_down0, total, WV_NT, F, C, mg->trivialScale, 0, U0, U1, S, z0, z1, cz0, cz1, (int)fold);
+    MF_LAUNCH_PDL(s, k_mg_down0, total, WV_NT, F, C, mg->trivialScale, 0, U0, U1, S, z0, z1, cz0, cz1, (int)fold, skip);
   }
   endGroup(mg, false);
 }
@@ -1011,6 +1014,31 @@ static void tailLeg(MgHierarchy* mg, bool down, bool fold) {
 }
 
 // setRhs + doVCycle(dst) with src == nullptr (multigrid.cpp:426-433, :448-504)
+// the V-cycle starts with the level-0 wavefront down leg
+static bool startsWithWave(const MgHierarchy* mg) {
+  const int maxLevel = (int)mg->lv.size() - 1;
+  return mg->aSet && mg->D.is3D && maxLevel > 0 && mg->pre == 1 && mg->post == 1 && !getenv("MF_MG_UNFUSED") && waveOk(mg) && !getenv("MF_MG_DEVSKIP");
+}
+bool mg_apply_begin(MgHierarchy* mg, float* dst, const float* rhs, const int* skip) {
+  // (not under the per-kernel event profile: a skipped launch would enter the kernel's average)
+  if (mg->begun || !startsWithWave(mg) || mg->s->profiling || getenv("MF_MG_NOSPECULATE")) return false;
+  mg_check_errors(mg);
+  const int maxLevel = (int)mg->lv.size() - 1;
+  LvlD& L0 = mg->lv[0];
+  L0.b = const_cast<float*>(rhs);
+  mg->begunR0 = L0.r; mg->begunDst = dst; mg->begunRhs = rhs;
+  L0.x = L0.r; L0.r = dst;
+  waveDown0(mg, 1 < maxLevel && !getenv("MF_MG_NOFOLD"), skip);
+  mg->begun = true;
+  return true;
+}
+void mg_apply_abort(MgHierarchy* mg) {
+  if (!mg->begun) return;
+  LvlD& L0 = mg->lv[0];
+  L0.r = mg->begunR0; L0.x = mg->begunDst;
+  flushGroups(mg);
+  mg->begun = false;
+}
 bool mg_apply(MgHierarchy* mg, float* dst, const float* rhs, const MgDotBeta* dot) {
   bool dotDone = false;
   Solver* s = mg->s;
@@ -1018,6 +1046,9 @@ bool mg_apply(MgHierarchy* mg, float* dst, const float* rhs, const MgDotBeta* do
   mg_check_errors(mg);
   const int maxLevel = (int)mg->lv.size() - 1;
   LvlD& L0 = mg->lv[0];
+  const bool begun = mg->begun;        // mg_apply_begin has queued the level-0 down leg of this very cycle
+  mg->begun = false;
+  if (begun) { mfAssert(dst == mg->begunDst && rhs == mg->begunRhs, "mg_apply: arguments differ from mg_apply_begin's"); L0.r = mg->begunR0; }
   L0.b = const_cast<float*>(rhs);      // knSetRhs' trivial-row scaling is applied on the fly (OP::rhs)
   L0.x = dst;
   if (maxLevel == 0 || mg->pre == 0) {
@@ -1035,7 +1066,7 @@ bool mg_apply(MgHierarchy* mg, float* dst, const float* rhs, const MgDotBeta* do
   const bool wave = fused0 && waveOk(mg);
   if (fused0) {
     L0.x = r0keep; L0.r = dst;
-    if (wave) waveDown0(mg, foldTo(1));   // both colours, residual and restriction in one pass; the residual stays on chip
+    if (wave) { if (!begun) waveDown0(mg, foldTo(1)); }   // both colours, residual and restriction in one pass; the residual stays on chip
     else {
       if (mg->useCode) fusedPresmooth0<L0Code>(mg); else fusedPresmooth0<L0Float>(mg);
       residual(mg, 0);

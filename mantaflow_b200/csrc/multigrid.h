@@ -19,6 +19,12 @@ int  mg_num_levels(const MgHierarchy* mg);
 // runs the update of the CG scalars) and mg_apply returns true; otherwise false and the caller launches its own reduction.
 struct MgDotBeta { float* sigma; float* beta; const float* resNorm; int* done; int* diverged; };
 bool mg_apply(MgHierarchy* mg, float* dst, const float* rhs, const MgDotBeta* dot = nullptr);
+// The PCG driver reads its stop flag on the host between the two halves of an iteration.  mg_apply_begin queues the first kernel of
+// the V-cycle mg_apply(mg, dst, rhs) would run (the level-0 down leg; it returns at once when *skip != 0 on the device) BEFORE the host
+// waits for the flag, so the device is busy while the host decides; then either mg_apply(mg, dst, rhs, ...) continues the cycle or
+// mg_apply_abort drops it.  Returns false (nothing queued) when the cycle does not start with that kernel.
+bool mg_apply_begin(MgHierarchy* mg, float* dst, const float* rhs, const int* skip);
+void mg_apply_abort(MgHierarchy* mg);
 void mg_check_errors(const MgHierarchy* mg);               // raises if a device-side barrier of the V-cycle timed out (call after a stream sync)
 // test hooks
 int  mg_level_size(const MgHierarchy* mg, int l, int* sx, int* sy, int* sz);

@@ -116,8 +116,10 @@ struct CgDriver {
     (void)init;
     return betaDone;
   }
-  void fetch() {
-    s->readSmall(s->hostInts, st, (int)sizeof(CgState));
+  void fetch() { fetchWait(fetchLaunch()); }
+  unsigned fetchLaunch() { return s->readSmallLaunch(s->hostInts, st, (int)sizeof(CgState)); }
+  void fetchWait(unsigned ticket) {
+    s->readSmallWait(ticket);
     memcpy(&host, s->hostInts, sizeof(CgState));
     if (pcMethod == 2) mg_check_errors(mg);
   }
@@ -183,8 +185,12 @@ struct CgDriver {
     for (int it = 0; it < maxIter; it++) {
       if (v4) headT<true>(); else headT<false>();
       MF_LAUNCH_CHECK();
-      fetch(); fresh = true;
-      if (host.done) break;
+      // the copy of the state is queued, then -- ahead of the decision -- the first kernel of the V-cycle the next half needs (it
+      // returns at once on the device when the stop flag is set): the device works while the host waits for the flag
+      const unsigned ticket = fetchLaunch();
+      const bool begun = mg_apply_begin(mg, v.tmp, v.residual, &st->done);
+      fetchWait(ticket); fresh = true;
+      if (host.done) { if (begun) mg_apply_abort(mg); break; }
       if (v4) tailT<true>(); else tailT<false>();
       fresh = false;
     }

@@ -90,20 +90,26 @@ __global__ void k_read_small(unsigned* dst, const unsigned* __restrict__ src, in
 __global__ void k_write_small(unsigned* dst, SmallPayload p, int nwords) {
   if ((int)threadIdx.x < nwords) dst[threadIdx.x] = p.w[threadIdx.x];
 }
-void Solver::readSmall(void* pinnedDst, const void* dev, int bytes) {
+void Solver::readSmall(void* pinnedDst, const void* dev, int bytes) { readSmallWait(readSmallLaunch(pinnedDst, dev, bytes)); }
+// The two halves of readSmall: the copy kernel is queued now, the host waits for its ticket later -- kernels launched in between
+// run behind the copy, so the host can decide about the work that follows while the device is already busy with its first part.
+unsigned Solver::readSmallLaunch(void* pinnedDst, const void* dev, int bytes) {
   void* mapped = nullptr;
   CUDA_CHECK(cudaHostGetDevicePointer(&mapped, pinnedDst, 0));
   // The host waits on a ticket in pinned memory instead of cudaStreamSynchronize (the PCG reads its stop flag once per iteration:
   // the wake-up latency of a stream synchronisation is paid 4-5 times per step); every 64 Ki polls the stream is queried so that a
   // faulted kernel surfaces as an error instead of a hang.  MF_SYNC_READS=1 restores the plain synchronisation.
-  static const bool plain = getenv("MF_SYNC_READS") != nullptr;
   void* seqDev = nullptr;
   CUDA_CHECK(cudaHostGetDevicePointer(&seqDev, (void*)seqHost, 0));
   const unsigned ticket = ++seqTicket;
   k_read_small<<<1, 64, 0, stream>>>((unsigned*)mapped, (const unsigned*)dev, bytes / 4, (volatile unsigned*)seqDev, ticket);
   launches++;
-  if (plain) { CUDA_CHECK(cudaStreamSynchronize(stream)); return; }
   CUDA_CHECK(cudaGetLastError());
+  return ticket;
+}
+void Solver::readSmallWait(unsigned ticket) {
+  static const bool plain = getenv("MF_SYNC_READS") != nullptr;
+  if (plain) { CUDA_CHECK(cudaStreamSynchronize(stream)); return; }
   volatile unsigned* seq = seqHost;
   for (unsigned spins = 1; *seq != ticket; spins++) {
     if ((spins & 0xffffu) == 0) {
