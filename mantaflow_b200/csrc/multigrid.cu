@@ -1029,6 +1029,7 @@ bool mg_apply_begin(MgHierarchy* mg, float* dst, const float* rhs, const int* sk
   mg->begunR0 = L0.r; mg->begunDst = dst; mg->begunRhs = rhs;
   L0.x = L0.r; L0.r = dst;
   waveDown0(mg, 1 < maxLevel && !getenv("MF_MG_NOFOLD"), skip);
+  mg->s->profTag = -1;
   mg->begun = true;
   return true;
 }

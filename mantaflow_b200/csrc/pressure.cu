@@ -117,7 +117,7 @@ struct CgDriver {
     return betaDone;
   }
   void fetch() { fetchWait(fetchLaunch()); }
-  unsigned fetchLaunch() { return s->readSmallLaunch(s->hostInts, st, (int)sizeof(CgState)); }
+  unsigned fetchLaunch() { return s->readSmallLaunch(s->hostInts, st, (int)sizeof(CgState) + 8); }   // + the word behind it (solveSystem: fixedDev)
   void fetchWait(unsigned ticket) {
     s->readSmallWait(ticket);
     memcpy(&host, s->hostInts, sizeof(CgState));
@@ -236,7 +236,9 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
   const bool needPlanes = !useCode || (preconditioner == MF_PC_MIC && s->is3D) || (mgPc && !(s->mg && mg_is_a_set(s->mg)));
   if (useCode && !s->cgCode) s->cgCode = (unsigned short*)s->galloc(sizeof(unsigned short) * (size_t)(s->N + 64), 1, 0, nullptr, 2);
   const float* phiD = p->phi ? G(p->phi)->d : nullptr;
-  int* fixedDev = s->localInts + 2;
+  // the pinned cell's index sits right behind the CG state (redOut doubles 8..12), so that the solver's last read of the state brings
+  // it to the host as well: no separate synchronisation for mf_solve_info::fixedCell
+  int* fixedDev = reinterpret_cast<int*>(s->redOut + 13);
   bool fixing = (p->zeroPressureFixing || p->cgAccuracy < 1e-07f);
   // the row codes and the choice of the pinned cell depend on the flags only: reuse them while the flag grid is unchanged
   const bool codeCached = useCode && !needPlanes && !s->multi() && s->codeFlags == (const void*)flags->d && s->codeVersion == flags->version &&
@@ -315,8 +317,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
     info->mgLevels = mgLevels; info->mgRebuilt = mgRebuilt; info->fixedCell = -1;
     if (fixing && codeCached) info->fixedCell = s->codeFixedCell;
     else if (fixing) {
-      s->readSmall(s->hostInts, fixedDev, (int)sizeof(int));
-      info->fixedCell = s->hostInts[0];
+      info->fixedCell = s->hostInts[sizeof(CgState) / sizeof(int)];
     }
   }
   // remember what the row codes were built from (a solve that also wrote the planes rebuilt them, which is just as valid)
@@ -565,8 +566,8 @@ mf_cg* mf_cg_create(mf_grid* dst, mf_grid* rhs, mf_grid* residual, mf_grid* sear
     CgObject* c = new CgObject();
     c->s = s; c->A0 = G(A0); c->Ai = G(Ai); c->Aj = G(Aj); c->Ak = G(Ak); c->flags = G(flags);
     c->accuracy = 1e-6f; c->useL2 = true; c->inited = false; c->method = 0; c->rebuildMg = false; c->pc = nullptr;
-    CUDA_CHECK(cudaMalloc(&c->state, sizeof(CgState)));
-    CUDA_CHECK(cudaMemset(c->state, 0, sizeof(CgState)));
+    CUDA_CHECK(cudaMalloc(&c->state, sizeof(CgState) + 8));      // (+ the word CgDriver::fetchLaunch copies with the state)
+    CUDA_CHECK(cudaMemset(c->state, 0, sizeof(CgState) + 8));
     CgDriver& d = c->drv;
     d.s = s; d.st = c->state; d.P = nullptr; d.mg = nullptr; d.pcMethod = 0;
     d.v.flags = G(flags)->di(); d.v.dst = G(dst)->d; d.v.residual = G(residual)->d; d.v.search = G(search)->d; d.v.tmp = G(tmp)->d;
