@@ -383,14 +383,14 @@ static void advectCentered(Solver* s, const Grid* flags, const Grid* vel, Grid* 
   const float dt = s->dt;
   const bool fast = NC == 1 && fastPath(s, OS, OT);
   float* fwd = (NC == 1) ? s->getReal() : s->getVec();
-  if (fast) MF_LAUNCH_IJK(s, k_sl_f, cv3(vel), grid->d, fwd, dt);
+  if (fast) MF_LAUNCH_IJK_PDL(s, k_sl_f, cv3(vel), grid->d, fwd, dt);
   else MF_LAUNCH_IJK(s, (k_sl<NC, OS, OT>), cv3(vel), grid->d, fwd, dt, np);
   if (order == 1) {
     float* old = grid->d; grid->d = fwd; fwd = old;       // orig.swap(fwd)
   } else {
     float* nw = (NC == 1) ? s->getReal() : s->getVec();
-    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_centered_f<1>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
-    else if (fast) MF_LAUNCH_IJK(s, k_mc_centered_f<2>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
+    if (fast && clampMode == 1) MF_LAUNCH_IJK_PDL(s, k_mc_centered_f<1>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
+    else if (fast) MF_LAUNCH_IJK_PDL(s, k_mc_centered_f<2>, flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, mcPow2Scale(strength));
     else MF_LAUNCH_IJK(s, (k_mc_centered<NC, OS, OT>), flags->di(), cv3(vel), grid->d, fwd, nw, dt, strength, clampMode, np);
     float* old = grid->d; grid->d = nw;                   // orig.swap(newGrid)
     if (NC == 1) s->putReal(old); else s->putVec(old);
@@ -421,7 +421,7 @@ static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid,
   const bool fast = fastPath(s, OS, OT);
   // MF_ADVECT_TMA=1: the TMA-staged variant (advect_tma.cuh) for self-advection on a single GPU
   if (fast && self && tmaUsable(s) && tmaEnabled()) launchSlMacTma(s, vel, &fw, dt);
-  else if (fast) MF_LAUNCH_IJK(s, k_sl_mac_f, cv3(vel), cv3(grid), v3(&fw), dt);
+  else if (fast) MF_LAUNCH_IJK_PDL(s, k_sl_mac_f, cv3(vel), cv3(grid), v3(&fw), dt);
   else MF_LAUNCH_IJK(s, (k_sl_mac<OS, OT>), cv3(vel), cv3(grid), v3(&fw), dt);
   if (order == 1) {
     applyOutflowBC(s, flags, v3(&fw), cv3(grid), dt);
@@ -429,8 +429,8 @@ static void advectMAC(Solver* s, const Grid* flags, const Grid* vel, Grid* grid,
   } else {
     float* nw = s->getVec();
     Grid ng = *grid; ng.d = nw;
-    if (fast && clampMode == 1) MF_LAUNCH_IJK(s, k_mc_mac_f<1>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
-    else if (fast) MF_LAUNCH_IJK(s, k_mc_mac_f<2>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
+    if (fast && clampMode == 1) MF_LAUNCH_IJK_PDL(s, k_mc_mac_f<1>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
+    else if (fast) MF_LAUNCH_IJK_PDL(s, k_mc_mac_f<2>, flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, mcPow2Scale(strength));
     else MF_LAUNCH_IJK(s, (k_mc_mac<OS, OT>), flags->di(), cv3(vel), cv3(grid), cv3(&fw), v3(&ng), dt, strength, clampMode);
     applyOutflowBC(s, flags, v3(&ng), cv3(grid), dt);
     float* old = grid->d; grid->d = nw;

@@ -46,6 +46,7 @@ __device__ __forceinline__ float interpolF(const float* __restrict__ d, const Ge
 }
 
 #define IJK_FROM_BLOCK_F \
+  MF_PDL_PROLOGUE \
   const GeoF g = geoF(gg); \
   const int i = blockIdx.x * blockDim.x + threadIdx.x; \
   const int j = blockIdx.y * blockDim.y + threadIdx.y; \

@@ -218,6 +218,12 @@ inline dim3 ijkGridOf(dim3 b, const Geo& g) { return dim3(cdiv(g.nx, b.x), cdiv(
 #define MF_LAUNCH_IJK(s, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { const mf::Geo _g = mf::geo((s), _r); \
   if (_g.k1 > _g.k0) { MF_LAUNCH(s, kern, mf::ijkGridOf(_b, _g), _b, _g, __VA_ARGS__); } } (s)->rankSync(); } while (0)
 
+// the same with programmatic dependent launch: for kernels that begin with MF_PDL_PROLOGUE (MF_NO_STEP_PDL=1: plain launches)
+inline bool stepPdl() { static const bool on = getenv("MF_NO_STEP_PDL") == nullptr; return on; }
+#define MF_LAUNCH_STEP(s, kern, grid, block, ...) do { if (mf::stepPdl()) { MF_LAUNCH_PDL(s, kern, grid, block, __VA_ARGS__); } else { MF_LAUNCH(s, kern, grid, block, __VA_ARGS__); } } while (0)
+#define MF_LAUNCH_IJK_PDL(s, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { const mf::Geo _g = mf::geo((s), _r); \
+  if (_g.k1 > _g.k0) { MF_LAUNCH_STEP(s, kern, mf::ijkGridOf(_b, _g), _b, _g, __VA_ARGS__); } } (s)->rankSync(); } while (0)
+
 // reductions (reduce.cu)
 // Deterministic two-stage reductions: per-block partial in fixed order, last block sums partials in block order.
 double reduce_dot(Solver* s, const float* a, const float* b, long long n);     // sum of float(a*b) in double (GridDotProduct)

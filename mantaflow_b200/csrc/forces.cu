@@ -128,6 +128,7 @@ __device__ __forceinline__ float buoy(float v, float strength, float factorSum) 
 template <int W>
 __global__ void __launch_bounds__(256) k_add_buoyancy(Geo g, const int* __restrict__ flags, const float* __restrict__ factor, V3 vel,
                                                       float sx, float sy, float sz) {
+  MF_PDL_PROLOGUE
   MF_CELLS_W(g, W)
   if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
   const long long Y = g.nx, Z = g.Z;
@@ -255,6 +256,7 @@ __device__ __forceinline__ void wallBcsApply(const Geo& g, int i, int j, int k, 
 // exit below and the kernel was bound by the rules' instructions (380 per warp) instead of the flag stream.
 template <int W>
 __global__ void __launch_bounds__(256) k_set_wall_bcs(Geo g, const int* __restrict__ flags, V3 vel, CV3 obvel, int haveObvel, int split) {
+  MF_PDL_PROLOGUE
   MF_CELLS_W(g, W)
   const long long Y = g.nx, Z = g.Z;
   int f[W], fxm[W], fxp[W], fym[W], fyp[W], fzm[W], fzp[W];
@@ -511,7 +513,7 @@ int mf_add_buoyancy(const mf_grid* fp, const mf_grid* dp, mf_grid* vp, float gx,
   const float fx = ((-gx * dt) / gridScale) * coefficient;
   const float fy = ((-gy * dt) / gridScale) * coefficient;
   const float fz = ((-gz * dt) / gridScale) * coefficient;
-  MF_LAUNCH_IJK_W(s, k_add_buoyancy, flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
+  MF_LAUNCH_IJK_W_PDL(s, k_add_buoyancy, flags->di(), G(dp)->d, v3(G(vp)), fx, fy, fz);
   MF_LAUNCH_CHECK();
   MF_API_END
 }
@@ -562,7 +564,7 @@ int mf_set_wall_bcs(const mf_grid* fp, mf_grid* vp, const mf_grid* obvel, const 
       MF_RANKS(s, r) { const Geo g = geo(s, r);
         if (g.k1 > g.k0) { MF_LAUNCH(s, k_set_wall_bcs_edge<4>, dim3(1, cdiv(g.ny, 64), cdiv(g.k1 - g.k0, 2)), eb, g, flags->di(), v3(vel), ov, obvel ? 1 : 0); } }
     }
-    MF_LAUNCH_IJK_W(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0, split);
+    MF_LAUNCH_IJK_W_PDL(s, k_set_wall_bcs, flags->di(), v3(vel), ov, obvel ? 1 : 0, split);
   } else {
     mfAssert(s->nx >= 3 && s->ny >= 3, "setWallBcs: grid too small");
     float* tmp = s->getVec();

@@ -45,7 +45,7 @@ static void computeRhs(Solver* s, float* rhs, const Grid* vel, const Grid* flags
   a.surfTens = p->surfTens; a.gfClamp = p->gfClamp;
   a.writeBorder = freshTemp ? 1 : 0;
   const bool plain = !p->fractions && !p->obvel && !(p->phi && p->curv) && !p->perCellCorr;
-  if (plain && s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs_plain<4>, quadTileBlocks(s, g, 4), 256, g, a.flags, rhs, a.vel, a.writeBorder, redCtx(s, r), s->redOut); } }
+  if (plain && s->nx % 4 == 0) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH_STEP(s, k_make_rhs_plain<4>, quadTileBlocks(s, g, 4), 256, g, a.flags, rhs, a.vel, a.writeBorder, redCtx(s, r), s->redOut); } }
   else if (plain) { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs_plain<1>, quadTileBlocks(s, g, 1), 256, g, a.flags, rhs, a.vel, a.writeBorder, redCtx(s, r), s->redOut); } }
   else { MF_RANKS(s, r) { const Geo g = geo(s, r); MF_LAUNCH(s, k_make_rhs, tileBlocks(s, g), 256, g, a, redCtx(s, r), s->redOut); } }
   redFinish<2>(s, RedOps<2>{ { 0, 0 } }, FinStore<2>{ s->redOut });
@@ -329,7 +329,7 @@ static void solveSystem(Solver* s, float* rhs, const Grid* vel, Grid* pressure, 
 }
 
 static void correctVel(Solver* s, Grid* vel, const Grid* pressure, const Grid* flags, const mf_pressure_params* p) {
-  MF_LAUNCH_IJK_W(s, k_correct_velocity, flags->di(), v3(vel), pressure->d);
+  MF_LAUNCH_IJK_W_PDL(s, k_correct_velocity, flags->di(), v3(vel), pressure->d);
   if (p->phi) {
     MF_LAUNCH_IJK(s, k_correct_velocity_gf, flags->di(), v3(vel), pressure->d, G(p->phi)->d, p->gfClamp,
                   p->curv ? G(p->curv)->d : nullptr, p->surfTens);

@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(256) k_make_rhs(Geo g, RhsArgs a, RedCtx ctx, 
 template <int W>
 __global__ void __launch_bounds__(256) k_make_rhs_plain(Geo g, const int* __restrict__ flags, float* __restrict__ rhs, CV3 vel, int writeBorder,
                                                         RedCtx ctx, double* out) {
+  MF_PDL_PROLOGUE
   __shared__ double sh[32];
   double sum = 0.0, cnt = 0.0;
   MF_QTILE_LOOP_BEGIN(g, W)
@@ -371,6 +372,7 @@ __global__ void __launch_bounds__(256) k_apply_matrix(Geo g, const int* __restri
 // knCorrectVelocity (pressure.cpp:87-109), in place; W x-consecutive cells per thread (quad.cuh)
 template <int W>
 __global__ void __launch_bounds__(256) k_correct_velocity(Geo g, const int* __restrict__ flags, V3 vel, const float* __restrict__ p) {
+  MF_PDL_PROLOGUE
   MF_CELLS_W(g, W)
   if (j < 1 || j >= g.ny - 1 || (g.is3D && (k < 1 || k >= g.nz - 1))) return;     // bnd = 1 rows only (warp-uniform)
   const long long Y = g.nx, Z = g.Z;

@@ -96,4 +96,9 @@ inline dim3 quadGridOf(dim3 b, const Geo& g, int W) { return dim3(cdiv(cdiv(g.nx
   if (_g.k1 > _g.k0) { if ((s)->nx % 4 == 0) { MF_LAUNCH(s, kern<4>, mf::quadGridOf(_b, _g, 4), _b, _g, __VA_ARGS__); } \
                        else { MF_LAUNCH(s, kern<1>, mf::quadGridOf(_b, _g, 1), _b, _g, __VA_ARGS__); } } } (s)->rankSync(); } while (0)
 
+// the same with programmatic dependent launch: for kernels that begin with MF_PDL_PROLOGUE
+#define MF_LAUNCH_IJK_W_PDL(s, kern, ...) do { const dim3 _b = mf::ijkBlockOf(s); MF_RANKS(s, _r) { const mf::Geo _g = mf::geo((s), _r); \
+  if (_g.k1 > _g.k0) { if ((s)->nx % 4 == 0) { MF_LAUNCH_STEP(s, kern<4>, mf::quadGridOf(_b, _g, 4), _b, _g, __VA_ARGS__); } \
+                       else { MF_LAUNCH_STEP(s, kern<1>, mf::quadGridOf(_b, _g, 1), _b, _g, __VA_ARGS__); } } } (s)->rankSync(); } while (0)
+
 }  // namespace mf
