@@ -38,3 +38,23 @@ def test_reference_arm_under_a_two_process_launch():
     (d,) = _lines(p.stdout)
     assert d["n_gpus"] == 2 and d["config"]["grid"] == [32, 32, 32] and d["config"]["job_grid"] == [32, 32, 64]
     assert "bounded sample" in d["config"]["workload"] and "32x32x32" in d["config"]["workload"]
+
+
+def test_algo_bytes_follow_the_operator_format():
+    """roofline bookkeeping: a 27-point colour sweep moves 27 coefficients of the level's entry size + x, b, x-out per vertex of
+    its colour; level sizes follow the reference's coarsening rule (multigrid.cpp:256-276); a level whose operator and vectors fit
+    the L2 is labelled latency-bound, not given an HBM fraction"""
+    sys.path.insert(0, ROOT)
+    import bench
+    sizes = bench.mg_level_sizes((256, 256, 256))
+    assert [tuple(s) for s in sizes[:3]] == [(256, 256, 256), (129, 129, 129), (65, 65, 65)]
+    assert sizes[-1][0] * sizes[-1][1] * sizes[-1][2] <= 1000
+    nv1 = 129 ** 3
+    b4, bound4 = bench.algo_bytes("k_mg_smooth@L1", (256, 256, 256), 256 ** 3, {1: 4})
+    b2, bound2 = bench.algo_bytes("k_mg_smooth@L1", (256, 256, 256), 256 ** 3, {1: 2})
+    assert b4 == (27 * 4 + 12) / 8.0 * nv1 and bound4 == "hbm"
+    assert b2 == (27 * 2 + 12) / 8.0 * nv1 and bound2 in ("hbm", "latency")
+    b, bound = bench.algo_bytes("k_mg_smooth@L3", (256, 256, 256), 256 ** 3, {})
+    assert bound == "latency" and b == (27 * 4 + 12) / 8.0 * 33 ** 3
+    assert bench.algo_bytes("k_mc_mac_f", (256, 256, 256), 256 ** 3)[0] == 40.0 * 256 ** 3
+    assert bench.algo_bytes("k_not_a_kernel", (256, 256, 256), 256 ** 3) == (None, None)
