@@ -37,11 +37,25 @@ struct LvlD {
   const unsigned short* code;   // level 0 only: compact operator (or nullptr)
   unsigned bxMagic;    // blocked: ceil(2^32 / (PX-2)), see mgBlockThread
   // blocked levels: the operator in binary16 (else nullptr).  Planes are interleaved in pairs: entry e of the row stored at position
-  // p is the half Ah[2 * ((e >> 1) * ash + p) + (e & 1)], i.e. seven planes of 4-byte (half2) elements with plane stride ash -- the
+  // p is the half Ah[2 * (mgHPair(e) * ash + p) + mgHHalf(e)], i.e. seven planes of 4-byte (half2) elements with plane stride ash -- the
   // element size of every other array of the level, so that a z-slab partition of the level cuts the binary16 planes at the same
   // allocation granules as the vectors (2-byte planes put half of a rank's boundary granule on its neighbour: +0.6 ms per step at N = 8)
   const __half* Ah; long long ash;
 };
+
+// Pairing of the 14 stored entries of a 3-D row into the seven binary16 plane pairs.  Entry e >= 1 of a row is read by ONE other
+// vertex, the neighbour in stencil direction 13 + e, i.e. in the sweep of the colour that differs by the parity of that direction.
+// Entries whose directions have the same parity are read in the same sweep from overlapping sectors, so they share an element:
+// (2,4) [110], (5,7) and (11,13) [111], (6,12) [011], (8,10) [101]; the diagonal pairs with 1 [100], and 3 [010] with 9 [001]
+// (those three elements are half used per sweep): 60 B per vertex and sweep instead of 80 B with the pairing (2q, 2q + 1).
+__host__ __device__ constexpr int mgHPair(int e) {
+  return (e == 0 || e == 1) ? 0 : (e == 2 || e == 4) ? 1 : (e == 5 || e == 7) ? 2 : (e == 11 || e == 13) ? 3 : (e == 6 || e == 12) ? 4 : (e == 8 || e == 10) ? 5 : 6;
+}
+__host__ __device__ constexpr int mgHHalf(int e) { return (e == 1 || e == 4 || e == 7 || e == 13 || e == 12 || e == 10 || e == 9) ? 1 : 0; }
+__host__ __device__ constexpr int mgHEntry(int q, int h) {
+  return h == 0 ? (q == 0 ? 0 : q == 1 ? 2 : q == 2 ? 5 : q == 3 ? 11 : q == 4 ? 6 : q == 5 ? 8 : 3)
+                : (q == 0 ? 1 : q == 1 ? 4 : q == 2 ? 7 : q == 3 ? 13 : q == 4 ? 12 : q == 5 ? 10 : 9);
+}
 
 struct MgDims { int is3D; int dim; int SS; int SS0; int zmin; int zmax; };   // mStencilSize, mStencilSize0, mStencilMin/Max.z
 
@@ -298,39 +312,21 @@ __device__ __forceinline__ bool mgBlockThread(const LvlD& L, int c, int lz0, int
 }
 // b - sum A x over the stencil in the reference's order (multigrid.cpp:691-706, :755-770); ap / xp = the vertex' own entries of
 // operator plane 0 and of x.  The lower half of the stencil is read from the neighbours' rows (symmetric storage).
-template <bool IS3D, bool WITH_CENTER, bool HALF>
-__device__ __forceinline__ float mgStencilSub(const char* __restrict__ ap, const char* xp, const MgOff1& o, float sum) {
-  constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
-  // binary16: the vertex' own row (terms SS-1 .. NS-1 = stored entries 0 .. SS-1) lies in plane PAIRS at its own position: one
-  // 4-byte load per two entries (LvlD::Ah); the lower half of the stencil comes from 13 different neighbours' rows, entry by entry
-  __half2 own[(SS + 1) / 2];
-  if (HALF) {
-#pragma unroll
-    for (int q = 0; q < (SS + 1) / 2; q++) own[q] = *reinterpret_cast<const __half2*>(ap + o.ao[SS - 1 + 2 * q]);
-  }
-#pragma unroll
-  for (int s = 0; s < NS; s++) {
-    if (s == SS - 1 && !WITH_CENTER) continue;
-    float a;
-    if (HALF && s >= SS - 1) { const int e = s - (SS - 1); a = (e & 1) ? __high2float(own[e >> 1]) : __low2float(own[e >> 1]); }
-    else a = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
-    sum -= a * *reinterpret_cast<const float*>(xp + o.xo[s]);
-  }
-  return sum;
-}
-// The same in two steps: the row's coefficients (the operator is constant between hierarchy builds, so a kernel launched with
+// b - sum A x in two steps: the row's coefficients (the operator is constant between hierarchy builds, so a kernel launched with
 // programmatic dependent launch may load them BEFORE griddepcontrol.wait, while its predecessor drains), then the sum.
+// binary16: the vertex' own row (terms SS-1 .. NS-1 = stored entries 0 .. SS-1) lies in plane PAIRS at its own position: one
+// 4-byte load per two entries (LvlD::Ah); the lower half of the stencil comes from 13 different neighbours' rows, entry by entry.
 template <bool IS3D, bool HALF>
 __device__ __forceinline__ void mgLoadRow(const char* __restrict__ ap, const MgOff1& o, float (&a)[IS3D ? 27 : 9]) {
   constexpr int NS = IS3D ? 27 : 9, SS = IS3D ? 14 : 5;
   __half2 own[(SS + 1) / 2];
   if (HALF) {
 #pragma unroll
-    for (int q = 0; q < (SS + 1) / 2; q++) own[q] = *reinterpret_cast<const __half2*>(ap + o.ao[SS - 1 + 2 * q]);
+    for (int q = 0; q < (SS + 1) / 2; q++) own[q] = *reinterpret_cast<const __half2*>(ap + o.ao[SS - 1 + mgHEntry(q, 0)]);
   }
 #pragma unroll
   for (int s = 0; s < NS; s++) {
-    if (HALF && s >= SS - 1) { const int e = s - (SS - 1); a[s] = (e & 1) ? __high2float(own[e >> 1]) : __low2float(own[e >> 1]); }
+    if (HALF && s >= SS - 1) { const int e = s - (SS - 1); a[s] = mgHHalf(e) ? __high2float(own[mgHPair(e)]) : __low2float(own[mgHPair(e)]); }
     else a[s] = HALF ? __half2float(*reinterpret_cast<const __half*>(ap + o.ao[s])) : *reinterpret_cast<const float*>(ap + o.ao[s]);
   }
 }
@@ -698,7 +694,7 @@ __global__ void __launch_bounds__(256) k_mg_pack_half(LvlD L, MgDims D, __half* 
     const float a = L.A[e * L.as + p];
     const __half h = __float2half_rn(a);
     bad |= !(__half2float(h) == a);
-    Ah[2 * ((e >> 1) * L.ash + p) + (e & 1)] = h;
+    Ah[2 * (mgHPair(e) * L.ash + p) + mgHHalf(e)] = h;
   }
   rowBad[p] = bad ? 1.f : 0.f;
 }

@@ -347,9 +347,9 @@ static void buildOffsets(MgHierarchy* mg, int l) {
           const long long dp = (long long)((cz + dz + 2) / 2 - 1) * L.NC * PXY + (long long)(nc - c) * PXY
                              + (long long)((cy + dy + 2) / 2 - 1) * L.PX + ((cx + dx + 2) / 2 - 1);
           O.t[c].xo[s] = 4 * dp;
-          // stored entry e of the row at shift d: float planes 4 * (e * as + d); binary16 plane pairs 4 * ((e >> 1) * as + d) + 2 * (e & 1)
+          // stored entry e of the row at shift d: float planes 4 * (e * as + d); binary16 plane pairs 4 * (mgHPair(e) * as + d) + 2 * mgHHalf(e)
           const long long e = (s < SS) ? (SS - 1 - s) : (s - SS + 1), d = (s < SS) ? dp : 0;
-          O.t[c].ao[s] = half ? 4 * ((e >> 1) * as + d) + 2 * (e & 1) : 4 * (e * as + d);
+          O.t[c].ao[s] = half ? 4 * (mgHPair((int)e) * as + d) + 2 * mgHHalf((int)e) : 4 * (e * as + d);
         }
   }
 }
