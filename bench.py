@@ -47,7 +47,8 @@ ALGO_BYTES_PER_CELL = {
     "k_mc_mac": 40.0,          # vel(=orig) 12 + fwd 12 + flags 4 + dst 12
     "k_sl_f": 20.0, "k_mc_centered_f": 28.0, "k_sl_mac_f": 24.0, "k_mc_mac_f": 40.0,   # the 32-bit-index kernels (advect_fast.cuh)
     "k_set_wall_bcs": 4.0,     # streams the flags; velocities are only touched in the thin shell where a wall condition applies
-    "k_add_buoyancy": 32.0,    # flags 4 + density 4 + vel 12 r + 12 w
+    "k_add_buoyancy": 21.4,    # reference sweep: flags 4 + density 4 + vel 12 r + 12 w = 32; the kernel reads / stores a velocity component only
+                               # where the force has one: 359.6 MB per launch measured (ncu) = 21.4 B/cell -- the figure the fraction is taken on
     "k_wall_buoyancy": 32.0,
     "k_make_rhs": 20.0,        # flags 4 + vel 12 + rhs 4
     "k_make_rhs_plain": 20.0,
